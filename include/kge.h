@@ -1,0 +1,219 @@
+/* kge.h - C ABI of the B200 serving-engine hot path (libkge.so).
+ *
+ * The reference (alikhabazian/Kubernetes-gpu-cluster) has no FFI of its own: its Helm values
+ * start a container (`vllm serve <model> ...`, ref:values-01-minimal-example.yaml:4-7,
+ * ref:old_README.md:1089-1095) whose engine runs the LLM forward pass.  This header is the
+ * boundary between that engine's host side (scheduler / HTTP server, C++ or Python) and the
+ * sm_100a kernels.  Every entry point cites the step of the deployed engine it replaces
+ * ("vllm:" = vLLM 0.22.0 sources, the engine the values files pin by image tag).
+ *
+ * Conventions: plain pointers and sizes only; all tensor pointers are DEVICE pointers unless
+ * the name says host; bf16 tensors are passed as void*; `stream` is a cudaStream_t passed as
+ * void* (NULL = default stream); return 0 = ok, negative = error with text in
+ * kge_last_error() (thread-local).  No entry point falls back to the CPU: without a CUDA
+ * device every compute call fails with -2.
+ */
+#ifndef KGE_H_
+#define KGE_H_
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define KGE_ABI_VERSION 1
+
+const char* kge_last_error(void);
+int kge_abi_version(void);
+/* 0 = no usable CUDA device, else the SM count of the current device. */
+int kge_device_sm_count(void);
+
+/* ---------------------------------------------------------------- per-op entry points --- */
+
+/* Token (+ learned position) embedding gather.
+ * vllm:model_executor/models/llama.py:392-393,407; opt.py:61-70,276-281 (offset 2).
+ * out[t,:] = table[ids[t],:] (+ pos_table[positions[t]+pos_offset,:], one bf16 rounding). */
+int kge_embed(void* out, const int32_t* ids, const void* table, const void* pos_table,
+              const int32_t* positions, int pos_offset, int T, int d, void* stream);
+
+/* RMSNorm, vllm:ir/ops/layernorm.py:10-21.  y = bf16(bf16(x*rsqrt(mean(x^2)+eps)) * w). */
+int kge_rmsnorm(void* y, const void* x, const void* w, int T, int d, float eps, void* stream);
+
+/* Fused residual-add + RMSNorm, vllm:ir/ops/layernorm.py:40-58.
+ * s = fp32(x)+fp32(residual); residual <- bf16(s); y = norm(s) (un-rounded s). */
+int kge_add_rmsnorm(void* y, void* residual, const void* x, const void* w, int T, int d,
+                    float eps, void* stream);
+
+/* LayerNorm (OPT), vllm:model_executor/models/opt.py:148-150,166-168,250-253.
+ * If `add` is non-NULL: h = bf16(fp32(residual)+fp32(add)) is written back to `residual`
+ * first (opt.py:181,194) and the norm is taken of h; y may be NULL (add only). */
+int kge_layernorm(void* y, void* residual, const void* add, const void* w, const void* b, int T,
+                  int d, float eps, void* stream);
+
+/* y[T,f] = silu(x[:, :f]) * x[:, f:], vllm:model_executor/layers/activation.py:137-141. */
+int kge_silu_mul(void* y, const void* x, int T, int f, void* stream);
+
+/* Dense projection y[T,N] = act(x[T,K] * w[N,K]^T + bias[N]); bf16 in/out, fp32 accumulate,
+ * one rounding.  act: 0 none, 1 relu.  Replaces F.linear in QKV/O/MLP/LM-head
+ * (vllm:model_executor/models/llama.py:94-121,164-180; opt.py:92-106,151-165;
+ * layers/logits_processor.py:89-99).  tcgen05/TMEM/TMA kernel; K % 64 == 0, 16-byte aligned
+ * rows.  `workspace` (>= kge_gemm_workspace_bytes) is device scratch for split-K. */
+int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
+                  int act, void* workspace, int64_t workspace_bytes, void* stream);
+int64_t kge_gemm_workspace_bytes(int T, int N, int K);
+
+/* RoPE (neox pairing, Llama-3 scaled cache) on the q and k parts of a packed qkv buffer
+ * [T,(H+2KV)*hd], in place, then scatter of k and v rows into the paged cache.
+ * vllm:model_executor/layers/rotary_embedding/common.py:160-183 (each op rounds in bf16);
+ * vllm:v1/attention/backends/flash_attn.py:850-874 (reshape_and_cache).
+ * cos_sin [max_pos, hd] bf16 = cos(hd/2) | sin(hd/2) per row, or NULL for no rotation (OPT).
+ * Cache layout (this engine's, HBM-resident): [num_blocks, KV, block_size, hd] bf16 for K and
+ * for V; slot = block*block_size + offset; slot < 0 skips the row. */
+int kge_rope_kvwrite(void* qkv, const void* cos_sin, const int32_t* positions,
+                     const int64_t* slot_mapping, void* k_cache, void* v_cache, int T, int H,
+                     int KV, int hd, int block_size, void* stream);
+
+/* Build the cos|sin cache on the host exactly as
+ * vllm:model_executor/layers/rotary_embedding/base.py:69-93 + llama3_rope.py:33-54 and round
+ * to bf16.  out_host: [max_pos, hd] uint16 bf16 bit patterns.  factor == 0 => no scaling. */
+int kge_rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                        double low_freq_factor, double high_freq_factor, int orig_max_pos);
+
+/* Causal paged attention over a flattened batch (prefill chunks and decode rows mixed):
+ * vllm:v1/attention/backends/flash_attn.py:667; semantics vllm:v1/attention/backends/
+ * cpu_attn.py:292-398.  Request b owns query rows [qsl[b], qsl[b+1]) which are the LAST
+ * rows of its seq_lens[b]-long context; q is read from the packed qkv buffer (row stride
+ * q_stride elements); out [T, H*hd].  scale = hd^-0.5 applied in fp32; softmax in fp32.
+ * `workspace` >= kge_attn_workspace_bytes() of device scratch (split-KV partials). */
+int kge_paged_attn(void* out, const void* q, int q_stride, const void* k_cache,
+                   const void* v_cache, const int32_t* block_table, int max_blocks_per_seq,
+                   const int32_t* seq_lens, const int32_t* query_start_loc, int B, int T,
+                   int max_q_len, int max_seq_len, int H, int KV, int hd, int block_size,
+                   float scale, void* workspace, int64_t workspace_bytes, void* stream);
+int64_t kge_attn_workspace_bytes(int B, int H, int hd, int max_seq_len);
+
+/* Greedy sampling, vllm:v1/sample/sampler.py:91,235-236: argmax over fp32(bf16 logits),
+ * lowest index wins ties.  logits [B, ld] bf16 (ld >= V: padded vocab columns ignored). */
+int kge_argmax(int32_t* out_ids, const void* logits, int B, int V, int ld, void* stream);
+
+/* Temperature / top-k / top-p sampling, vllm:v1/sample/sampler.py:254-296 and
+ * vllm:v1/sample/ops/topk_topp_sampler.py:328-369,395-417: rows with temperature < 1e-5 are
+ * greedy; others draw argmax(softmax(mask(logits/T)) / q), q ~ Exp(1).  `exp_noise` [B,V]
+ * fp32 supplies q (NULL: Philox noise from seeds[b] and step).  top_k[b] <= 0 or >= V and
+ * top_p[b] >= 1 disable the filters.  `workspace` >= kge_sample_workspace_bytes(B,V). */
+int kge_sample(int32_t* out_ids, const void* logits, int B, int V, int ld,
+               const float* temperature, const int32_t* top_k, const float* top_p,
+               const float* exp_noise, const uint64_t* seeds, uint64_t step, void* workspace,
+               int64_t workspace_bytes, void* stream);
+int64_t kge_sample_workspace_bytes(int B, int V);
+
+/* -------------------------------------------------------------------- engine (model) --- */
+
+typedef struct kge_engine kge_engine;
+
+typedef struct {
+  int32_t max_num_seqs;           /* vllm --max-num-seqs                                  */
+  int32_t max_num_batched_tokens; /* vllm --max-num-batched-tokens (per-step token budget) */
+  int32_t max_model_len;          /* vllm --max-model-len                                 */
+  int32_t block_size;             /* KV block size in tokens (16)                         */
+  int32_t num_blocks;             /* 0: size from gpu_memory_utilization                  */
+  float gpu_memory_utilization;   /* vllm --gpu-memory-utilization                        */
+  int32_t tp_rank, tp_size;       /* vllm --tensor-parallel-size                          */
+  int32_t enable_chunked_prefill; /* vllm --enable-chunked-prefill                        */
+  int32_t device;                 /* CUDA device ordinal                                   */
+} kge_engine_config;
+
+/* One engine step's device-side metadata - what vLLM hands its attention backend
+ * (vllm:v1/attention/backends/cpu_attn.py:107-118).  HOST pointers; kge_step copies them. */
+typedef struct {
+  int32_t T, B;
+  const int32_t* token_ids;       /* [T]   */
+  const int32_t* positions;       /* [T]   */
+  const int32_t* query_start_loc; /* [B+1] */
+  const int32_t* seq_lens;        /* [B]   */
+  const int32_t* block_table;     /* [B, max_blocks] */
+  int32_t max_blocks;
+  const int64_t* slot_mapping;    /* [T]   */
+  const int32_t* logits_rows;     /* [R] rows of the flattened batch that need logits */
+  int32_t R;
+} kge_step_batch;
+
+/* Load an HF-layout directory (config.json + *.safetensors), the same thing the values
+ * files point the engine at (ref:values-01-minimal-example3.yaml:8,22-30), or, when
+ * `dummy_seed` >= 0 and the directory holds only config.json, random weights
+ * (--load-format dummy).  Allocates weights, activations and the paged KV pool. */
+int kge_engine_create(kge_engine** out, const char* model_dir, const kge_engine_config* cfg,
+                      int64_t dummy_seed);
+void kge_engine_destroy(kge_engine* e);
+int kge_engine_num_blocks(const kge_engine* e);
+int kge_engine_vocab(const kge_engine* e);
+int64_t kge_engine_weight_bytes(const kge_engine* e);
+int64_t kge_engine_launches(const kge_engine* e);
+
+/* One forward pass + greedy sampling of the R requested rows (the GPUModelRunner.execute_model
+ * + Sampler path, vllm:v1/worker/gpu_model_runner.py:3955, vllm:v1/sample/sampler.py:67).
+ * out_ids_host [R]; out_logits_host [R, vocab] fp32 or NULL.  Synchronous. */
+int kge_step(kge_engine* e, const kge_step_batch* batch, int32_t* out_ids_host,
+             float* out_logits_host);
+
+/* Tensor parallelism (one engine = one rank = one GPU): all ranks share a 128-byte NCCL
+ * unique id made by rank 0; after kge_engine_init_tp the forward pass sums the row-parallel
+ * projections with a bf16 ncclAllReduce (vllm:model_executor/layers/linear.py:1559;
+ * ref:values-01-minimal-example8.yaml:32-38 --disable-custom-all-reduce --tensor-parallel-size 2).
+ * Every rank must then call kge_step / kge_engine_step with identical batches. */
+int kge_nccl_unique_id(char* out128);
+int kge_engine_init_tp(kge_engine* e, const char* id128);
+
+/* ----------------------------------------------- scheduler + serving loop (host side) --- */
+
+typedef struct {
+  int32_t max_tokens;
+  int32_t min_tokens;
+  int32_t ignore_eos;
+  float temperature;     /* < 1e-5 => greedy (vllm:sampling_params.py:25) */
+  int32_t top_k;         /* <= 0 => off */
+  float top_p;           /* >= 1 => off */
+  uint64_t seed;
+  const int32_t* stop_token_ids;
+  int32_t num_stop_token_ids;
+} kge_sampling_params;
+
+typedef struct {
+  int64_t request_id;
+  int32_t token;         /* sampled token, or -1 if the step only advanced a prefill chunk */
+  int32_t finished;      /* 0 running, 1 "stop", 2 "length"                                 */
+  int32_t num_scheduled; /* tokens of this request run this step                            */
+} kge_step_output;
+
+/* Continuous batching: vllm:v1/core/sched/scheduler.py:329-830,1283 (RUNNING first under the
+ * token budget, tail preemption + recompute, WAITING admission), stop rules
+ * vllm:v1/core/sched/utils.py:94-130, block manager vllm:v1/core/kv_cache_manager.py:236-430. */
+int kge_add_request(kge_engine* e, int64_t request_id, const int32_t* prompt_ids, int32_t n,
+                    const kge_sampling_params* sp);
+int kge_abort_request(kge_engine* e, int64_t request_id);
+int kge_has_unfinished(const kge_engine* e);
+/* Schedule + forward + sample + update.  Writes up to cap outputs; returns the count (>= 0)
+ * or a negative error. */
+int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap);
+/* Counters for /metrics (vllm:v1/metrics/loggers.py:452-788). */
+int kge_engine_stats(const kge_engine* e, int32_t* num_running, int32_t* num_waiting,
+                     float* kv_usage, int64_t* num_preemptions);
+
+/* The scheduler alone (no device), for host-logic tests: same policy object the engine uses. */
+typedef struct kge_sched kge_sched;
+kge_sched* kge_sched_create(int32_t max_num_seqs, int32_t max_num_batched_tokens,
+                            int32_t max_model_len, int32_t block_size, int32_t num_blocks,
+                            int32_t enable_chunked_prefill, int32_t eos_token_id);
+void kge_sched_destroy(kge_sched* s);
+int kge_sched_add(kge_sched* s, int64_t request_id, const int32_t* prompt_ids, int32_t n,
+                  const kge_sampling_params* sp);
+/* Returns the number of scheduled requests; ids/num_tokens [cap]. */
+int kge_sched_schedule(kge_sched* s, int64_t* ids, int32_t* num_tokens, int32_t cap);
+/* Feed sampled tokens for requests that reached their last known token this step. */
+int kge_sched_update(kge_sched* s, const int64_t* ids, const int32_t* tokens, int32_t n,
+                     kge_step_output* outs, int32_t cap);
+int kge_sched_counts(const kge_sched* s, int32_t* running, int32_t* waiting, int32_t* free_blocks);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* KGE_H_ */

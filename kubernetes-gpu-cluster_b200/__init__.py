@@ -1,0 +1,265 @@
+"""kubernetes-gpu-cluster_b200: B200-native serving engine behind the container contract of the
+reference's Helm values (ref:values-01-minimal-example*.yaml -> `vllm serve <model> ...`).
+
+This package is a thin ctypes layer over libkge.so (CUDA kernels + C++ engine, include/kge.h).
+It mirrors the deployed engine's Python surface for the hot path - `LLM.generate` with
+`SamplingParams` (vllm:entrypoints/llm.py, vllm:sampling_params.py) - so parity tests read like
+tests of the engine the values files deploy.  There is NO CPU path: every compute call raises
+if libkge.so is missing or no CUDA device is present.
+
+The directory name is not a Python identifier; load it with kge_loader.load() (repo root).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from dataclasses import dataclass, field
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libkge.so")
+
+
+class KgeError(RuntimeError):
+    pass
+
+
+class EngineConfig(C.Structure):
+    _fields_ = [("max_num_seqs", C.c_int32), ("max_num_batched_tokens", C.c_int32),
+                ("max_model_len", C.c_int32), ("block_size", C.c_int32), ("num_blocks", C.c_int32),
+                ("gpu_memory_utilization", C.c_float), ("tp_rank", C.c_int32), ("tp_size", C.c_int32),
+                ("enable_chunked_prefill", C.c_int32), ("device", C.c_int32)]
+
+
+class StepBatch(C.Structure):
+    _fields_ = [("T", C.c_int32), ("B", C.c_int32), ("token_ids", C.c_void_p), ("positions", C.c_void_p),
+                ("query_start_loc", C.c_void_p), ("seq_lens", C.c_void_p), ("block_table", C.c_void_p),
+                ("max_blocks", C.c_int32), ("slot_mapping", C.c_void_p), ("logits_rows", C.c_void_p),
+                ("R", C.c_int32)]
+
+
+class CSamplingParams(C.Structure):
+    _fields_ = [("max_tokens", C.c_int32), ("min_tokens", C.c_int32), ("ignore_eos", C.c_int32),
+                ("temperature", C.c_float), ("top_k", C.c_int32), ("top_p", C.c_float), ("seed", C.c_uint64),
+                ("stop_token_ids", C.c_void_p), ("num_stop_token_ids", C.c_int32)]
+
+
+class StepOutput(C.Structure):
+    _fields_ = [("request_id", C.c_int64), ("token", C.c_int32), ("finished", C.c_int32),
+                ("num_scheduled", C.c_int32)]
+
+
+# name -> (restype, argtypes); every symbol include/kge.h declares
+_P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
+SIGNATURES = {
+    "kge_last_error": (C.c_char_p, []),
+    "kge_abi_version": (_I, []),
+    "kge_device_sm_count": (_I, []),
+    "kge_embed": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
+    "kge_rmsnorm": (_I, [_P, _P, _P, _I, _I, _F, _P]),
+    "kge_add_rmsnorm": (_I, [_P, _P, _P, _P, _I, _I, _F, _P]),
+    "kge_layernorm": (_I, [_P, _P, _P, _P, _P, _I, _I, _F, _P]),
+    "kge_silu_mul": (_I, [_P, _P, _I, _I, _P]),
+    "kge_gemm_bf16": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _L, _P]),
+    "kge_gemm_workspace_bytes": (_L, [_I, _I, _I]),
+    "kge_rope_kvwrite": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
+    "kge_rope_cache_host": (_I, [_P, _I, _I, C.c_double, C.c_double, C.c_double, C.c_double, _I]),
+    "kge_paged_attn": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _L, _P]),
+    "kge_attn_workspace_bytes": (_L, [_I, _I, _I, _I]),
+    "kge_argmax": (_I, [_P, _P, _I, _I, _I, _P]),
+    "kge_sample": (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, C.c_uint64, _P, _L, _P]),
+    "kge_sample_workspace_bytes": (_L, [_I, _I]),
+    "kge_engine_create": (_I, [C.POINTER(_P), C.c_char_p, C.POINTER(EngineConfig), _L]),
+    "kge_engine_destroy": (None, [_P]),
+    "kge_engine_num_blocks": (_I, [_P]),
+    "kge_engine_vocab": (_I, [_P]),
+    "kge_engine_weight_bytes": (_L, [_P]),
+    "kge_engine_launches": (_L, [_P]),
+    "kge_step": (_I, [_P, C.POINTER(StepBatch), _P, _P]),
+    "kge_nccl_unique_id": (_I, [_P]),
+    "kge_engine_init_tp": (_I, [_P, _P]),
+    "kge_add_request": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
+    "kge_abort_request": (_I, [_P, _L]),
+    "kge_has_unfinished": (_I, [_P]),
+    "kge_engine_step": (_I, [_P, C.POINTER(StepOutput), C.c_int32]),
+    "kge_engine_stats": (_I, [_P, _P, _P, _P, _P]),
+    "kge_sched_create": (_P, [C.c_int32] * 7),
+    "kge_sched_destroy": (None, [_P]),
+    "kge_sched_add": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
+    "kge_sched_schedule": (_I, [_P, _P, _P, C.c_int32]),
+    "kge_sched_update": (_I, [_P, _P, _P, C.c_int32, C.POINTER(StepOutput), C.c_int32]),
+    "kge_sched_counts": (_I, [_P, _P, _P, _P]),
+}
+
+_lib = None
+
+
+def lib() -> C.CDLL:
+    """Load libkge.so (built in-tree by __graft_entry__.build() / make).  Raises if missing."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise KgeError(f"{LIB_PATH} not built: run `python -c 'import __graft_entry__ as g; g.build()'`"
+                           " - there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = L
+    return _lib
+
+
+def check(rc: int, what: str = "") -> int:
+    if rc < 0:
+        raise KgeError(f"{what}: {lib().kge_last_error().decode()} (rc={rc})")
+    return rc
+
+
+def require_cuda() -> int:
+    n = lib().kge_device_sm_count()
+    if n <= 0:
+        raise KgeError("no CUDA device: this engine has no CPU path")
+    return n
+
+
+# ------------------------------------------------------------------------- public API
+
+
+@dataclass
+class SamplingParams:
+    """Subset of vllm:sampling_params.py used on the hot path (same names and defaults)."""
+    max_tokens: int = 16
+    min_tokens: int = 0
+    temperature: float = 1.0
+    top_k: int = 0
+    top_p: float = 1.0
+    seed: int | None = None
+    ignore_eos: bool = False
+    stop_token_ids: list = field(default_factory=list)
+
+    def to_c(self):
+        arr = (C.c_int32 * max(1, len(self.stop_token_ids)))(*self.stop_token_ids)
+        c = CSamplingParams(self.max_tokens, self.min_tokens, int(self.ignore_eos), self.temperature,
+                            self.top_k, self.top_p, self.seed or 0,
+                            C.cast(arr, C.c_void_p), len(self.stop_token_ids))
+        c._keep = arr
+        return c
+
+
+@dataclass
+class CompletionOutput:
+    token_ids: list
+    finish_reason: str | None = None
+
+
+@dataclass
+class RequestOutput:
+    request_id: int
+    prompt_token_ids: list
+    outputs: list
+
+
+class LLM:
+    """`vllm.LLM`-shaped front end over the C++ engine (vllm:entrypoints/llm.py):
+    LLM(model=<HF directory>, ...).generate(prompt_token_ids, sampling_params)."""
+
+    def __init__(self, model: str, *, max_model_len: int = 0, max_num_seqs: int = 0,
+                 max_num_batched_tokens: int = 0, gpu_memory_utilization: float = 0.9,
+                 block_size: int = 16, num_gpu_blocks_override: int = 0, tensor_parallel_size: int = 1,
+                 tp_rank: int = 0, enable_chunked_prefill: bool = True, load_format: str = "auto",
+                 seed: int = 0, device: int = 0):
+        require_cuda()
+        self.cfg = EngineConfig(max_num_seqs, max_num_batched_tokens, max_model_len, block_size,
+                                num_gpu_blocks_override, gpu_memory_utilization, tp_rank,
+                                tensor_parallel_size, int(enable_chunked_prefill), device)
+        h = C.c_void_p()
+        dummy = seed if load_format == "dummy" else -1
+        check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")
+        self._h = h
+        self._next_id = 0
+        self._outs = (StepOutput * 4096)()
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().kge_engine_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def num_gpu_blocks(self) -> int:
+        return lib().kge_engine_num_blocks(self._h)
+
+    @property
+    def vocab_size(self) -> int:
+        return lib().kge_engine_vocab(self._h)
+
+    @property
+    def weight_bytes(self) -> int:
+        return lib().kge_engine_weight_bytes(self._h)
+
+    @property
+    def kernel_launches(self) -> int:
+        return lib().kge_engine_launches(self._h)
+
+    def init_tp(self, unique_id: bytes):
+        check(lib().kge_engine_init_tp(self._h, unique_id), "kge_engine_init_tp")
+
+    def add_request(self, prompt_token_ids, sp: SamplingParams) -> int:
+        rid = self._next_id
+        self._next_id += 1
+        arr = (C.c_int32 * len(prompt_token_ids))(*prompt_token_ids)
+        c = sp.to_c()
+        check(lib().kge_add_request(self._h, rid, arr, len(prompt_token_ids), C.byref(c)), "kge_add_request")
+        return rid
+
+    def step(self):
+        """One engine step (schedule + forward + sample + update).  Returns a list of
+        (request_id, token or -1, finished 0|1|2, num_scheduled)."""
+        n = check(lib().kge_engine_step(self._h, self._outs, len(self._outs)), "kge_engine_step")
+        return [(o.request_id, o.token, o.finished, o.num_scheduled) for o in self._outs[:n]]
+
+    def has_unfinished(self) -> bool:
+        return bool(lib().kge_has_unfinished(self._h))
+
+    def stats(self):
+        r, w, p = C.c_int32(), C.c_int32(), C.c_int64()
+        u = C.c_float()
+        check(lib().kge_engine_stats(self._h, C.byref(r), C.byref(w), C.byref(u), C.byref(p)), "kge_engine_stats")
+        return {"num_running": r.value, "num_waiting": w.value, "kv_usage": u.value, "num_preemptions": p.value}
+
+    def generate(self, prompt_token_ids, sampling_params: SamplingParams | list | None = None,
+                 on_step=None):
+        """prompt_token_ids: list of token-id lists.  Returns RequestOutput per prompt, in order."""
+        sps = sampling_params or SamplingParams()
+        if not isinstance(sps, list):
+            sps = [sps] * len(prompt_token_ids)
+        ids = [self.add_request(p, sp) for p, sp in zip(prompt_token_ids, sps)]
+        toks = {i: [] for i in ids}
+        fin = {}
+        while self.has_unfinished():
+            outs = self.step()
+            if not outs:
+                raise KgeError("engine made no progress (KV pool too small for the waiting request?)")
+            for rid, tok, f, _ in outs:
+                if tok >= 0:
+                    toks[rid].append(tok)
+                if f:
+                    fin[rid] = "stop" if f == 1 else "length"
+            if on_step:
+                on_step(outs)
+        return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i))])
+                for i, p in zip(ids, prompt_token_ids)]
+
+    # raw step with caller-built metadata (tests / bench device-resident leg)
+    def raw_step(self, token_ids, positions, query_start_loc, seq_lens, block_table, max_blocks,
+                 slot_mapping, logits_rows, want_logits=False):
+        import numpy as np
+        a = lambda x, dt: np.ascontiguousarray(np.asarray(x, dtype=dt))
+        tid, pos, qsl = a(token_ids, np.int32), a(positions, np.int32), a(query_start_loc, np.int32)
+        sl, bt, sm, rows = a(seq_lens, np.int32), a(block_table, np.int32), a(slot_mapping, np.int64), a(logits_rows, np.int32)
+        b = StepBatch(len(tid), len(sl), tid.ctypes.data, pos.ctypes.data, qsl.ctypes.data, sl.ctypes.data,
+                      bt.ctypes.data, max_blocks, sm.ctypes.data, rows.ctypes.data, len(rows))
+        out = np.zeros(max(1, len(rows)), dtype=np.int32)
+        lg = np.zeros((len(rows), self.vocab_size), dtype=np.float32) if want_logits else None
+        check(lib().kge_step(self._h, C.byref(b), out.ctypes.data, lg.ctypes.data if want_logits else None), "kge_step")
+        return out[:len(rows)], lg

@@ -1,0 +1,81 @@
+// Error channel, version/device queries and the host-side RoPE cache builder of the C ABI.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <vector>
+
+#include "common.cuh"
+#include "kge.h"
+
+namespace kge {
+static thread_local char g_err[1024] = "";
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+}  // namespace kge
+
+extern "C" const char* kge_last_error(void) { return kge::g_err; }
+extern "C" int kge_abi_version(void) { return KGE_ABI_VERSION; }
+
+extern "C" int kge_device_sm_count(void) {
+  int n = 0, dev = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) { (void)cudaGetLastError(); return 0; }
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  int sms = 0;
+  if (cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess) return 0;
+  return sms;
+}
+
+static inline uint16_t f32_to_bf16_rne(float f) {
+  uint32_t u;
+  memcpy(&u, &f, 4);
+  if ((u & 0x7fffffffu) > 0x7f800000u) return (uint16_t)((u >> 16) | 0x40);  // NaN
+  u += 0x7fffu + ((u >> 16) & 1u);
+  return (uint16_t)(u >> 16);
+}
+
+// vllm:model_executor/layers/rotary_embedding/base.py:69-93 (fp32 inv_freq, fp32 outer product,
+// fp32 cos/sin, cast to the model dtype) and llama3_rope.py:33-54 (frequency rescale).
+extern "C" int kge_rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                                   double low_freq_factor, double high_freq_factor, int orig_max_pos) {
+  KGE_REQUIRE(out_host && max_pos > 0 && hd > 0 && hd % 2 == 0, "kge_rope_cache_host: bad arguments");
+  const int half = hd / 2;
+  std::vector<float> inv(half);
+  for (int i = 0; i < half; ++i) {
+    const float e = (float)(2 * i) / (float)hd;               // arange(0,rd,2,float)/rd
+    const float pw = powf((float)theta, e);                   // base ** e in fp32
+    float f = 1.0f / pw;
+    if (factor != 0.0) {
+      const float low_wl = (float)orig_max_pos / (float)low_freq_factor;
+      const float high_wl = (float)orig_max_pos / (float)high_freq_factor;
+      const float wl = (float)(2.0 * M_PI) / f;               // python float * fp32 tensor -> fp32
+      if (wl < high_wl) {
+        // keep
+      } else if (wl > low_wl) {
+        f = f / (float)factor;
+      } else {
+        float smooth = 0.f;
+        if (low_freq_factor != high_freq_factor)
+          smooth = ((float)orig_max_pos / wl - (float)low_freq_factor) /
+                   (float)(high_freq_factor - low_freq_factor);
+        f = (1.0f - smooth) * f / (float)factor + smooth * f;
+      }
+    }
+    inv[i] = f;
+  }
+  for (int p = 0; p < max_pos; ++p) {
+    for (int i = 0; i < half; ++i) {
+      const float fr = (float)p * inv[i];
+      // correctly rounded fp32 cos/sin of the fp32 angle
+      out_host[(size_t)p * hd + i] = f32_to_bf16_rne((float)cos((double)fr));
+      out_host[(size_t)p * hd + half + i] = f32_to_bf16_rne((float)sin((double)fr));
+    }
+  }
+  return 0;
+}

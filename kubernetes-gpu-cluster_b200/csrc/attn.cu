@@ -1,0 +1,481 @@
+// Causal paged attention over the engine's HND cache ([block][kv_head][slot][hd], bf16).
+//
+// Two kernels share the same tile machinery (cp.async-staged, XOR-swizzled K/V tiles of 64 keys,
+// fp32 online softmax, GQA packing: the M rows of a tile are (token, q-head-in-group) pairs so
+// each K/V tile fetched from HBM serves every q head of its kv head):
+//   attn_general_kernel  prefill chunks and mixed batches; warps split the M rows.
+//   attn_decode_kernel   pure decode steps; split-KV across CTAs, warps split the keys of a tile;
+//                        partial (m, l, O) go to workspace and attn_merge_kernel combines them.
+// HBM-bound at decode: algorithmic bytes = sum_b ctx_b * KV * hd * 2 (K) * 2 (V) * 2 B per layer.
+#include "common.cuh"
+#include "kge.h"
+
+namespace kge {
+
+constexpr int BN = 64;            // keys per tile
+constexpr float kLog2e = 1.4426950408889634f;
+
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return (uint32_t)__cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void cp_async16(uint32_t dst, const void* src, bool valid) {
+  const int sz = valid ? 16 : 0;   // src-size 0 => zero fill
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;"); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N)); }
+
+__device__ __forceinline__ void ldsm_x4(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t& r0, uint32_t& r1, uint32_t& r2, uint32_t& r3, uint32_t addr) {
+  asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+               : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+               : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+               : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+
+// byte offset of 16-byte chunk `c` of row `r` in a [rows][HD] bf16 tile, XOR swizzled
+template <int HD>
+__device__ __forceinline__ uint32_t swz(int r, int c) {
+  static_assert(HD % 64 == 0, "rows must span whole 128-byte lines for this swizzle");
+  return (uint32_t)(r * HD * 2 + ((c ^ (r & 7)) << 4));
+}
+
+// Stage one 64-key tile of K or V for (request, kv head) into shared memory.
+template <int HD, int NTHREADS>
+__device__ __forceinline__ void load_kv_tile(uint32_t sdst, const bf16* __restrict__ cache,
+                                             const int32_t* __restrict__ btab, int kvh, int KV,
+                                             int bs_shift, int key0, int kv_len, int tid) {
+  constexpr int CH = HD / 8;
+  for (int i = tid; i < BN * CH; i += NTHREADS) {
+    const int r = i / CH, c = i % CH;
+    const int key = key0 + r;
+    const bool ok = key < kv_len;
+    const bf16* src = cache;
+    if (ok) {
+      const int blk = btab[key >> bs_shift];
+      src = cache + ((((int64_t)blk * KV + kvh) << bs_shift) + (key & ((1 << bs_shift) - 1))) * HD + c * 8;
+    }
+    cp_async16(sdst + swz<HD>(r, c), src, ok);
+  }
+}
+
+// --------------------------------------------------------------------------- general
+// grid (q tiles, KV, B); 128 threads; warp w owns tile rows 16w..16w+15.
+template <int HD>
+__global__ void __launch_bounds__(128)
+attn_general_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
+                    const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
+                    const int32_t* __restrict__ block_table, int max_blocks,
+                    const int32_t* __restrict__ seq_lens, const int32_t* __restrict__ qsl,
+                    int H, int KV, int bs_shift, float scale_log2) {
+  constexpr int BM = 64, CH = HD / 8, NT = 128;
+  const int b = blockIdx.z, kvh = blockIdx.y;
+  const int G = H / KV;
+  const int TT = BM / G;                          // tokens per tile
+  const int q0 = qsl[b], q_len = qsl[b + 1] - q0;
+  const int tok0 = blockIdx.x * TT;
+  if (tok0 >= q_len) return;
+  const int seq_len = seq_lens[b];
+  const int ctx0 = seq_len - q_len;               // keys visible before this chunk's first token
+  const int ntok = min(TT, q_len - tok0);
+  const int kv_len = ctx0 + tok0 + ntok;          // causal upper bound for this tile
+  const int ntiles = (kv_len + BN - 1) / BN;
+  const int32_t* btab = block_table + (int64_t)b * max_blocks;
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t sQ = smem_u32(smem);
+  const uint32_t sK = sQ + BM * HD * 2;           // 2 stages
+  const uint32_t sV = sK + 2 * BN * HD * 2;       // 2 stages
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, tg = lane & 3;
+
+  // Q tile: row r -> token tok0 + r / G, head kvh*G + r % G
+  for (int i = tid; i < BM * CH; i += NT) {
+    const int r = i / CH, c = i % CH;
+    const int tk = r / G, hh = r % G;
+    const bool ok = tk < ntok;
+    const bf16* src = ok ? q + (int64_t)(q0 + tok0 + tk) * q_stride + (kvh * G + hh) * HD + c * 8 : q;
+    cp_async16(sQ + swz<HD>(r, c), src, ok);
+  }
+  load_kv_tile<HD, NT>(sK, k_cache, btab, kvh, KV, bs_shift, 0, kv_len, tid);
+  load_kv_tile<HD, NT>(sV, v_cache, btab, kvh, KV, bs_shift, 0, kv_len, tid);
+  cp_async_commit();
+
+  uint32_t qf[HD / 16][4];
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+  // causal limits of this thread's two rows (key index must be <= limit)
+  const int r0 = warp * 16 + g, r1 = r0 + 8;
+  const int lim0 = (r0 / G < ntok) ? ctx0 + tok0 + r0 / G : -1;
+  const int lim1 = (r1 / G < ntok) ? ctx0 + tok0 + r1 / G : -1;
+
+  for (int kt = 0; kt < ntiles; ++kt) {
+    const int st = kt & 1;
+    if (kt + 1 < ntiles) {
+      load_kv_tile<HD, NT>(sK + (st ^ 1) * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, (kt + 1) * BN, kv_len, tid);
+      load_kv_tile<HD, NT>(sV + (st ^ 1) * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, (kt + 1) * BN, kv_len, tid);
+      cp_async_commit();
+      cp_async_wait<1>();
+    } else {
+      cp_async_wait<0>();
+    }
+    __syncthreads();
+    if (kt == 0) {
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk)
+        ldsm_x4(qf[kk][0], qf[kk][1], qf[kk][2], qf[kk][3],
+                sQ + swz<HD>(warp * 16 + (lane & 15), kk * 2 + (lane >> 4)));
+    }
+    const uint32_t kb = sK + st * BN * HD * 2, vb = sV + st * BN * HD * 2;
+    float s[BN / 8][4];
+#pragma unroll
+    for (int j = 0; j < BN / 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+#pragma unroll
+      for (int jj = 0; jj < BN / 16; ++jj) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4(b0, b1, b2, b3, kb + swz<HD>(jj * 16 + (lane & 7) + ((lane >> 4) << 3), kk * 2 + ((lane >> 3) & 1)));
+        mma_bf16(s[2 * jj], qf[kk], b0, b1);
+        mma_bf16(s[2 * jj + 1], qf[kk], b2, b3);
+      }
+    }
+    // mask + online softmax (scores scaled into log2 domain)
+    const int key_base = kt * BN + 2 * tg;
+    float mx0 = m0, mx1 = m1;
+#pragma unroll
+    for (int j = 0; j < BN / 8; ++j) {
+      const int k0 = key_base + j * 8;
+      s[j][0] = (k0 <= lim0) ? s[j][0] * scale_log2 : -INFINITY;
+      s[j][1] = (k0 + 1 <= lim0) ? s[j][1] * scale_log2 : -INFINITY;
+      s[j][2] = (k0 <= lim1) ? s[j][2] * scale_log2 : -INFINITY;
+      s[j][3] = (k0 + 1 <= lim1) ? s[j][3] * scale_log2 : -INFINITY;
+      mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float base0 = (mx0 == -INFINITY) ? 0.f : mx0, base1 = (mx1 == -INFINITY) ? 0.f : mx1;
+    const float c0 = exp2f(m0 - base0), c1 = exp2f(m1 - base1);   // m=-inf -> 0
+    m0 = mx0; m1 = mx1;
+    float rs0 = 0.f, rs1 = 0.f;
+    uint32_t pf[BN / 16][4];
+#pragma unroll
+    for (int j = 0; j < BN / 8; ++j) {
+      const float p0 = exp2f(s[j][0] - base0), p1 = exp2f(s[j][1] - base0);
+      const float p2 = exp2f(s[j][2] - base1), p3 = exp2f(s[j][3] - base1);
+      rs0 += p0 + p1; rs1 += p2 + p3;
+      pf[j >> 1][(j & 1) * 2 + 0] = pack_bf2(p0, p1);
+      pf[j >> 1][(j & 1) * 2 + 1] = pack_bf2(p2, p3);
+    }
+    l0 = l0 * c0 + rs0; l1 = l1 * c1 + rs1;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+#pragma unroll
+    for (int kk = 0; kk < BN / 16; ++kk) {
+#pragma unroll
+      for (int nn = 0; nn < HD / 16; ++nn) {
+        uint32_t b0, b1, b2, b3;
+        ldsm_x4_t(b0, b1, b2, b3, vb + swz<HD>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), nn * 2 + (lane >> 4)));
+        mma_bf16(o[2 * nn], pf[kk], b0, b1);
+        mma_bf16(o[2 * nn + 1], pf[kk], b2, b3);
+      }
+    }
+    __syncthreads();   // tile consumed before the next prefetch overwrites the other stage
+  }
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+  const float inv0 = l0 > 0.f ? 1.f / l0 : 0.f, inv1 = l1 > 0.f ? 1.f / l1 : 0.f;
+  if (lim0 >= 0) {
+    bf16* dst = out + (int64_t)(q0 + tok0 + r0 / G) * H * HD + (kvh * G + r0 % G) * HD + 2 * tg;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i)
+      *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf2(o[i][0] * inv0, o[i][1] * inv0);
+  }
+  if (lim1 >= 0) {
+    bf16* dst = out + (int64_t)(q0 + tok0 + r1 / G) * H * HD + (kvh * G + r1 % G) * HD + 2 * tg;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i)
+      *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf2(o[i][2] * inv1, o[i][3] * inv1);
+  }
+}
+
+// --------------------------------------------------------------------------- decode
+// grid (splits, KV, B); 128 threads.  One query token per request; the G (<=16) q heads of the
+// kv head are the M rows.  Warp w handles keys 16w..16w+15 of every 64-key tile.
+// Partial results: part_o [B, H, splits, HD] fp32 (un-normalised), part_ml [B, H, splits, 2].
+template <int HD, int STAGES>
+__global__ void __launch_bounds__(128)
+attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __restrict__ part_ml,
+                   const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
+                   const bf16* __restrict__ v_cache, const int32_t* __restrict__ block_table,
+                   int max_blocks, const int32_t* __restrict__ seq_lens,
+                   const int32_t* __restrict__ qsl, int H, int KV, int bs_shift, float scale_log2) {
+  constexpr int CH = HD / 8, NT = 128;
+  const int b = blockIdx.z, kvh = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
+  const int G = H / KV;
+  const int kv_len = seq_lens[b];
+  const int ntiles_all = (kv_len + BN - 1) / BN;
+  const int tps = (ntiles_all + nsplit - 1) / nsplit;
+  const int t_begin = split * tps, t_end = min(ntiles_all, t_begin + tps);
+  const int32_t* btab = block_table + (int64_t)b * max_blocks;
+  const int qrow = qsl[b];
+
+  extern __shared__ __align__(128) uint8_t smem[];
+  const uint32_t sQ = smem_u32(smem);                 // 16 x HD
+  const uint32_t sK = sQ + 16 * HD * 2;
+  const uint32_t sV = sK + STAGES * BN * HD * 2;
+  float* sRed = reinterpret_cast<float*>(smem + 16 * HD * 2);  // [4][16][HD+2], aliases the K stages after the loop
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int g = lane >> 2, tg = lane & 3;
+
+  for (int i = tid; i < 16 * CH; i += NT) {
+    const int r = i / CH, c = i % CH;
+    const bool ok = r < G;
+    const bf16* src = ok ? q + (int64_t)qrow * q_stride + (kvh * G + r) * HD + c * 8 : q;
+    cp_async16(sQ + swz<HD>(r, c), src, ok);
+  }
+  // prologue: STAGES-1 tiles in flight
+#pragma unroll
+  for (int s = 0; s < STAGES - 1; ++s) {
+    if (t_begin + s < t_end) {
+      load_kv_tile<HD, NT>(sK + s * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, (t_begin + s) * BN, kv_len, tid);
+      load_kv_tile<HD, NT>(sV + s * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, (t_begin + s) * BN, kv_len, tid);
+    }
+    cp_async_commit();
+  }
+
+  uint32_t qf[HD / 16][4];
+  float o[HD / 8][4];
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
+  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+
+  for (int kt = t_begin; kt < t_end; ++kt) {
+    const int it = kt - t_begin, st = it % STAGES;
+    const int nxt = kt + STAGES - 1;
+    cp_async_wait<STAGES - 2>();
+    __syncthreads();             // tile `it` landed for all threads; stage (it-1)%STAGES is free
+    if (nxt < t_end) {
+      const int ns = (it + STAGES - 1) % STAGES;
+      load_kv_tile<HD, NT>(sK + ns * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, nxt * BN, kv_len, tid);
+      load_kv_tile<HD, NT>(sV + ns * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, nxt * BN, kv_len, tid);
+    }
+    cp_async_commit();
+    if (it == 0) {
+#pragma unroll
+      for (int kk = 0; kk < HD / 16; ++kk)
+        ldsm_x4(qf[kk][0], qf[kk][1], qf[kk][2], qf[kk][3], sQ + swz<HD>(lane & 15, kk * 2 + (lane >> 4)));
+    }
+    const uint32_t kb = sK + st * BN * HD * 2, vb = sV + st * BN * HD * 2;
+    float s[2][4] = {{0.f, 0.f, 0.f, 0.f}, {0.f, 0.f, 0.f, 0.f}};
+#pragma unroll
+    for (int kk = 0; kk < HD / 16; ++kk) {
+      uint32_t b0, b1, b2, b3;
+      ldsm_x4(b0, b1, b2, b3, kb + swz<HD>(warp * 16 + (lane & 7) + ((lane >> 4) << 3), kk * 2 + ((lane >> 3) & 1)));
+      mma_bf16(s[0], qf[kk], b0, b1);
+      mma_bf16(s[1], qf[kk], b2, b3);
+    }
+    const int key_base = kt * BN + warp * 16 + 2 * tg;
+    float mx0 = m0, mx1 = m1;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int k0 = key_base + j * 8;
+      s[j][0] = (k0 < kv_len) ? s[j][0] * scale_log2 : -INFINITY;
+      s[j][1] = (k0 + 1 < kv_len) ? s[j][1] * scale_log2 : -INFINITY;
+      s[j][2] = (k0 < kv_len) ? s[j][2] * scale_log2 : -INFINITY;
+      s[j][3] = (k0 + 1 < kv_len) ? s[j][3] * scale_log2 : -INFINITY;
+      mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
+      mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
+    }
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
+    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
+    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+    const float base0 = (mx0 == -INFINITY) ? 0.f : mx0, base1 = (mx1 == -INFINITY) ? 0.f : mx1;
+    const float c0 = exp2f(m0 - base0), c1 = exp2f(m1 - base1);
+    m0 = mx0; m1 = mx1;
+    uint32_t pf[4];
+    float rs0 = 0.f, rs1 = 0.f;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const float p0 = exp2f(s[j][0] - base0), p1 = exp2f(s[j][1] - base0);
+      const float p2 = exp2f(s[j][2] - base1), p3 = exp2f(s[j][3] - base1);
+      rs0 += p0 + p1; rs1 += p2 + p3;
+      pf[j * 2 + 0] = pack_bf2(p0, p1);
+      pf[j * 2 + 1] = pack_bf2(p2, p3);
+    }
+    l0 = l0 * c0 + rs0; l1 = l1 * c1 + rs1;
+#pragma unroll
+    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+#pragma unroll
+    for (int nn = 0; nn < HD / 16; ++nn) {
+      uint32_t b0, b1, b2, b3;
+      ldsm_x4_t(b0, b1, b2, b3, vb + swz<HD>(warp * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), nn * 2 + (lane >> 4)));
+      mma_bf16(o[2 * nn], pf, b0, b1);
+      mma_bf16(o[2 * nn + 1], pf, b2, b3);
+    }
+  }
+  cp_async_wait<0>();
+  __syncthreads();               // every warp is done with the K/V stages that sRed aliases
+  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+
+  // merge the four warps' (m, l, O) through shared memory: sRed[w][row][HD] + ml at [HD], [HD+1]
+  constexpr int RS = HD + 2;
+  float* mine = sRed + warp * 16 * RS;
+#pragma unroll
+  for (int i = 0; i < HD / 8; ++i) {
+    mine[g * RS + i * 8 + 2 * tg] = o[i][0];
+    mine[g * RS + i * 8 + 2 * tg + 1] = o[i][1];
+    mine[(g + 8) * RS + i * 8 + 2 * tg] = o[i][2];
+    mine[(g + 8) * RS + i * 8 + 2 * tg + 1] = o[i][3];
+  }
+  if (tg == 0) {
+    mine[g * RS + HD] = m0; mine[g * RS + HD + 1] = l0;
+    mine[(g + 8) * RS + HD] = m1; mine[(g + 8) * RS + HD + 1] = l1;
+  }
+  __syncthreads();
+  // thread -> (row, column slice); rows < G only
+  for (int i = tid; i < G * HD; i += NT) {
+    const int r = i / HD, c = i % HD;
+    float mm = -INFINITY;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) mm = fmaxf(mm, sRed[(w * 16 + r) * RS + HD]);
+    float acc = 0.f, ll = 0.f;
+    const float basem = (mm == -INFINITY) ? 0.f : mm;
+#pragma unroll
+    for (int w = 0; w < 4; ++w) {
+      const float sc = exp2f(sRed[(w * 16 + r) * RS + HD] - basem);
+      acc += sRed[(w * 16 + r) * RS + c] * sc;
+      ll += sRed[(w * 16 + r) * RS + HD + 1] * sc;
+    }
+    const int head = kvh * G + r;
+    if (nsplit == 1) {
+      out[(int64_t)qrow * H * HD + head * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+    } else {
+      const int64_t pi = ((int64_t)b * H + head) * nsplit + split;
+      part_o[pi * HD + c] = acc;
+      if (c == 0) { part_ml[pi * 2] = mm; part_ml[pi * 2 + 1] = ll; }
+    }
+  }
+}
+
+// grid (H, B); HD threads.
+__global__ void attn_merge_kernel(bf16* __restrict__ out, const float* __restrict__ part_o,
+                                  const float* __restrict__ part_ml, const int32_t* __restrict__ qsl,
+                                  int H, int HD, int nsplit) {
+  const int b = blockIdx.y, head = blockIdx.x, c = threadIdx.x;
+  const int64_t p0 = ((int64_t)b * H + head) * nsplit;
+  float mm = -INFINITY;
+  for (int s = 0; s < nsplit; ++s) mm = fmaxf(mm, part_ml[(p0 + s) * 2]);
+  const float basem = (mm == -INFINITY) ? 0.f : mm;
+  float acc = 0.f, ll = 0.f;
+  for (int s = 0; s < nsplit; ++s) {
+    const float sc = exp2f(part_ml[(p0 + s) * 2] - basem);
+    acc += part_o[(p0 + s) * HD + c] * sc;
+    ll += part_ml[(p0 + s) * 2 + 1] * sc;
+  }
+  out[(int64_t)qsl[b] * H * HD + head * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+}
+
+constexpr int kDecodeStages = 3;
+template <int HD> constexpr int general_smem() { return 64 * HD * 2 + 4 * BN * HD * 2; }
+template <int HD> constexpr int decode_smem() {
+  static_assert(4 * 16 * (HD + 2) * 4 <= kDecodeStages * BN * HD * 2, "sRed must fit in the K stages");
+  return 16 * HD * 2 + 2 * kDecodeStages * BN * HD * 2;
+}
+
+static int decode_splits(int B, int KV, int max_seq_len) {
+  const int target = 148 * 4;
+  int s = (target + B * KV - 1) / (B * KV);
+  const int max_s = (max_seq_len + 4 * BN - 1) / (4 * BN);   // >= 256 keys per split
+  if (s > max_s) s = max_s;
+  if (s > 32) s = 32;
+  if (s < 1) s = 1;
+  return s;
+}
+
+template <int HD>
+static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, const bf16* vc,
+                       const int32_t* bt, int max_blocks, const int32_t* sl, const int32_t* qsl, int B,
+                       int max_q_len, int max_seq_len, int H, int KV, int bs, float scale, void* ws,
+                       int64_t ws_bytes, cudaStream_t st) {
+  const float sl2 = scale * kLog2e;
+  int bs_shift = 0;
+  while ((1 << bs_shift) < bs) ++bs_shift;
+  const int G = H / KV;
+  if (max_q_len == 1 && G <= 16) {
+    const int ns = decode_splits(B, KV, max_seq_len);
+    float* po = nullptr; float* pml = nullptr;
+    if (ns > 1) {
+      const int64_t need = (int64_t)B * H * ns * (HD + 2) * 4;
+      KGE_REQUIRE(ws && ws_bytes >= need, "kge_paged_attn: workspace %lld < %lld bytes", (long long)ws_bytes, (long long)need);
+      po = (float*)ws;
+      pml = po + (int64_t)B * H * ns * HD;
+    }
+    auto kern = attn_decode_kernel<HD, kDecodeStages>;
+    KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
+    kern<<<dim3(ns, KV, B), 128, decode_smem<HD>(), st>>>(out, po, pml, q, q_stride, kc, vc, bt, max_blocks,
+                                                          sl, qsl, H, KV, bs_shift, sl2);
+    KGE_LAUNCH_OK();
+    if (ns > 1) {
+      attn_merge_kernel<<<dim3(H, B), HD, 0, st>>>(out, po, pml, qsl, H, HD, ns);
+      KGE_LAUNCH_OK();
+    }
+    return 0;
+  }
+  KGE_REQUIRE(G <= 64, "kge_paged_attn: GQA group %d > 64 unsupported", G);
+  const int TT = 64 / G;
+  auto kern = attn_general_kernel<HD>;
+  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, general_smem<HD>()));
+  kern<<<dim3((max_q_len + TT - 1) / TT, KV, B), 128, general_smem<HD>(), st>>>(
+      out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, H, KV, bs_shift, sl2);
+  KGE_LAUNCH_OK();
+  return 0;
+}
+
+}  // namespace kge
+
+using namespace kge;
+
+extern "C" int64_t kge_attn_workspace_bytes(int B, int H, int hd, int max_seq_len) {
+  (void)max_seq_len;
+  return (int64_t)B * H * 32 * (hd + 2) * 4;
+}
+
+extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void* k_cache,
+                              const void* v_cache, const int32_t* block_table, int max_blocks_per_seq,
+                              const int32_t* seq_lens, const int32_t* query_start_loc, int B, int T,
+                              int max_q_len, int max_seq_len, int H, int KV, int hd, int block_size,
+                              float scale, void* workspace, int64_t workspace_bytes, void* stream) {
+  KGE_REQUIRE(out && q && k_cache && v_cache && block_table && seq_lens && query_start_loc,
+              "kge_paged_attn: null pointer");
+  KGE_REQUIRE(H > 0 && KV > 0 && H % KV == 0, "kge_paged_attn: H=%d must be a multiple of KV=%d", H, KV);
+  KGE_REQUIRE(block_size > 0 && (block_size & (block_size - 1)) == 0, "kge_paged_attn: block_size=%d must be a power of two", block_size);
+  KGE_REQUIRE(q_stride % 8 == 0, "kge_paged_attn: q_stride must be a multiple of 8");
+  if (B <= 0 || T <= 0) return 0;
+  KGE_REQUIRE(max_q_len >= 1 && max_seq_len >= 1, "kge_paged_attn: max_q_len/max_seq_len must be >= 1");
+  cudaStream_t st = (cudaStream_t)stream;
+  if (hd == 64)
+    return launch_attn<64>((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache,
+                           block_table, max_blocks_per_seq, seq_lens, query_start_loc, B, max_q_len,
+                           max_seq_len, H, KV, block_size, scale, workspace, workspace_bytes, st);
+  if (hd == 128)
+    return launch_attn<128>((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache,
+                            block_table, max_blocks_per_seq, seq_lens, query_start_loc, B, max_q_len,
+                            max_seq_len, H, KV, block_size, scale, workspace, workspace_bytes, st);
+  kge::set_error("kge_paged_attn: head_dim=%d unsupported (64, 128)", hd);
+  return -1;
+}

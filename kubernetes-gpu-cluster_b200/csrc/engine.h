@@ -1,0 +1,79 @@
+// Engine object behind the kge_engine handle: device weights, activation arena, paged KV pool,
+// per-step metadata staging, scheduler.  One engine = one GPU (one TP rank).
+#pragma once
+#include <cuda_runtime.h>
+#include <nccl.h>
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "kge.h"
+#include "loader.h"
+#include "scheduler.h"
+
+namespace kge {
+
+struct Linear {
+  bf16* w = nullptr;     // [N, K] row-major
+  bf16* b = nullptr;     // [N] or null
+  int N = 0, K = 0;
+};
+
+struct LayerW {
+  Linear qkv, o, up, down;           // up = gate_up (llama, [2f,d]) or fc1 (opt)
+  bf16 *ln1_w = nullptr, *ln1_b = nullptr, *ln2_w = nullptr, *ln2_b = nullptr;
+};
+
+// Per-step metadata, laid out once in pinned host memory and mirrored on the device with the
+// same offsets so one cudaMemcpyAsync moves everything.
+struct StepMeta {
+  int32_t *ids, *pos, *qsl, *seq_lens, *rows, *btab, *top_k;
+  int64_t* slots;
+  float *temp, *top_p;
+  uint64_t* seeds;
+};
+
+}  // namespace kge
+
+struct kge_engine {
+  kge::ModelSpec spec;
+  kge_engine_config cfg;
+  int tp_rank = 0, tp_size = 1;
+  ncclComm_t comm = nullptr;
+  int H_loc = 0, KV_loc = 0, ffn_loc = 0;
+  cudaStream_t stream = nullptr;
+
+  std::vector<void*> allocs;                 // everything cudaMalloc'ed, freed in destroy
+  kge::bf16 *embed = nullptr, *pos_embed = nullptr, *lm_head = nullptr;
+  kge::bf16 *final_w = nullptr, *final_b = nullptr, *cos_sin = nullptr;
+  std::vector<kge::LayerW> layers;
+  std::vector<kge::bf16*> kc, vc;
+  int num_blocks = 0, max_blocks_per_seq = 0;
+  int64_t weight_bytes = 0, kv_bytes = 0;
+
+  kge::bf16 *h = nullptr, *res = nullptr, *xn = nullptr, *qkv = nullptr, *attn = nullptr;
+  kge::bf16 *gu = nullptr, *act = nullptr, *xsel = nullptr, *logits = nullptr;
+  float* logits_f32 = nullptr;
+  int32_t* d_out = nullptr;
+  int ld_logits = 0;
+  void *ws_gemm = nullptr, *ws_attn = nullptr;
+  int64_t ws_gemm_bytes = 0, ws_attn_bytes = 0;
+
+  uint8_t *meta_host = nullptr, *meta_dev = nullptr;
+  int64_t meta_bytes = 0;
+  int32_t* out_host = nullptr;               // pinned [max_num_seqs]
+
+  std::unique_ptr<kge::Scheduler> sched;
+  int64_t launches = 0;
+  uint64_t step_count = 0;
+  std::string err;
+};
+
+namespace kge {
+// engine_fwd.cu
+int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
+                   const StepMeta& dm, bool any_random);
+StepMeta carve_meta(uint8_t* base, int T, int B, int R, int max_blocks, int64_t* total);
+}  // namespace kge

@@ -1,0 +1,300 @@
+// One engine step on the device: embedding -> L x (norm, QKV, RoPE+KV write, paged attention,
+// O, norm, MLP) -> final norm -> logits of the requested rows -> sampling.  Plus the C entry
+// points kge_step (metadata given by the caller) and kge_engine_step (scheduler-driven).
+#include <string.h>
+
+#include <algorithm>
+
+#include "engine.h"
+
+using namespace kge;
+
+namespace kge {
+
+#define FWD(call)                          \
+  do {                                     \
+    int _rc = (call);                      \
+    if (_rc) return _rc;                   \
+    ++e->launches;                         \
+  } while (0)
+
+static int linear(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int T, int act) {
+  return kge_gemm_bf16(y, x, l.w, l.b, T, l.N, l.K, act, e->ws_gemm, e->ws_gemm_bytes, e->stream);
+}
+
+int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n);   // tp.cu
+
+int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
+                   const StepMeta& m, bool any_random) {
+  const ModelSpec& s = e->spec;
+  const int d = s.d, hd = s.hd, Hl = e->H_loc, KVl = e->KV_loc, bs = e->cfg.block_size;
+  cudaStream_t st = e->stream;
+  const float scale = 1.0f / sqrtf((float)hd);
+  const int qkv_n = e->layers[0].qkv.N;
+  if (s.is_opt()) {
+    FWD(kge_embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
+    for (int i = 0; i < s.L; ++i) {
+      const LayerW& L = e->layers[i];
+      // first LN of the layer; for i > 0 it also folds in the previous layer's fc2 output
+      FWD(kge_layernorm(e->xn, e->res, i == 0 ? nullptr : e->h, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
+      FWD(linear(e, e->qkv, e->xn, L.qkv, T, 0));
+      FWD(kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+      FWD(kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+                         max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+      FWD(linear(e, e->h, e->attn, L.o, T, 0));
+      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+      FWD(kge_layernorm(e->xn, e->res, e->h, L.ln2_w, L.ln2_b, T, d, 1e-5f, st));
+      FWD(linear(e, e->act, e->xn, L.up, T, 1));
+      FWD(linear(e, e->h, e->act, L.down, T, 0));
+      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+    }
+    FWD(kge_layernorm(e->xn, e->res, e->h, e->final_w, e->final_b, T, d, 1e-5f, st));
+  } else {
+    FWD(kge_embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
+    for (int i = 0; i < s.L; ++i) {
+      const LayerW& L = e->layers[i];
+      if (i == 0) FWD(kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
+      else FWD(kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
+      FWD(linear(e, e->qkv, e->xn, L.qkv, T, 0));
+      FWD(kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+      FWD(kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+                         max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+      FWD(linear(e, e->h, e->attn, L.o, T, 0));
+      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+      FWD(kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
+      FWD(linear(e, e->gu, e->xn, L.up, T, 0));
+      FWD(kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
+      FWD(linear(e, e->h, e->act, L.down, T, 0));
+      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+    }
+    FWD(kge_add_rmsnorm(e->xn, e->res, e->h, e->final_w, T, d, s.eps, st));
+  }
+  if (R > 0) {
+    // logits only for the last token of each sampled request (logits_processor.py:54-99)
+    FWD(kge_embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
+    Linear head;
+    head.w = e->lm_head; head.b = nullptr; head.N = s.vocab; head.K = d;
+    // y rows are written with stride N = vocab; keep ld == vocab so the row layout stays dense
+    FWD(linear(e, e->logits, e->xsel, head, R, 0));
+    if (any_random)
+      FWD(kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
+                     e->step_count, nullptr, 0, st));
+    else
+      FWD(kge_argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
+  }
+  return 0;
+}
+
+__global__ void bf16_to_f32_kernel(float* o, const bf16* x, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) o[i] = bf2f(x[i]);
+}
+
+// Copy the caller's host metadata into the pinned block, ship it, run, read the ids back.
+static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, const int32_t* top_k,
+                    const float* top_p, const uint64_t* seeds, int32_t* out_ids_host, float* out_logits_host) {
+  const int T = b->T, B = b->B, R = b->R;
+  KGE_REQUIRE(T > 0 && B > 0, "kge_step: empty batch");
+  KGE_REQUIRE(T <= e->cfg.max_num_batched_tokens, "kge_step: T=%d exceeds max_num_batched_tokens=%d", T, e->cfg.max_num_batched_tokens);
+  KGE_REQUIRE(B <= e->cfg.max_num_seqs && R <= e->cfg.max_num_seqs, "kge_step: B=%d / R=%d exceed max_num_seqs=%d", B, R, e->cfg.max_num_seqs);
+  KGE_REQUIRE(b->max_blocks > 0 && b->max_blocks <= e->max_blocks_per_seq, "kge_step: max_blocks=%d out of range", b->max_blocks);
+  KGE_CUDA_OK(cudaSetDevice(e->cfg.device));
+  int64_t bytes = 0;
+  StepMeta hm = carve_meta(e->meta_host, T, B, R, b->max_blocks, &bytes);
+  StepMeta dm = carve_meta(e->meta_dev, T, B, R, b->max_blocks, nullptr);
+  memcpy(hm.ids, b->token_ids, (size_t)T * 4);
+  memcpy(hm.pos, b->positions, (size_t)T * 4);
+  memcpy(hm.qsl, b->query_start_loc, (size_t)(B + 1) * 4);
+  memcpy(hm.seq_lens, b->seq_lens, (size_t)B * 4);
+  memcpy(hm.btab, b->block_table, (size_t)B * b->max_blocks * 4);
+  memcpy(hm.slots, b->slot_mapping, (size_t)T * 8);
+  if (R > 0) memcpy(hm.rows, b->logits_rows, (size_t)R * 4);
+  bool any_random = false;
+  for (int i = 0; i < R; ++i) {
+    hm.temp[i] = temp ? temp[i] : 0.f;
+    hm.top_k[i] = top_k ? top_k[i] : 0;
+    hm.top_p[i] = top_p ? top_p[i] : 1.f;
+    hm.seeds[i] = seeds ? seeds[i] : 0;
+    any_random |= hm.temp[i] >= 1e-5f;
+  }
+  int max_q = 1, max_seq = 1;
+  for (int i = 0; i < B; ++i) {
+    const int ql = b->query_start_loc[i + 1] - b->query_start_loc[i];
+    KGE_REQUIRE(ql >= 1 && ql <= b->seq_lens[i], "kge_step: request %d has q_len=%d seq_len=%d", i, ql, b->seq_lens[i]);
+    KGE_REQUIRE(b->seq_lens[i] <= b->max_blocks * e->cfg.block_size, "kge_step: request %d seq_len=%d exceeds its block table", i, b->seq_lens[i]);
+    max_q = std::max(max_q, ql);
+    max_seq = std::max(max_seq, b->seq_lens[i]);
+  }
+  KGE_REQUIRE(b->query_start_loc[B] == T, "kge_step: query_start_loc[B]=%d != T=%d", b->query_start_loc[B], T);
+  KGE_CUDA_OK(cudaMemcpyAsync(e->meta_dev, e->meta_host, (size_t)bytes, cudaMemcpyHostToDevice, e->stream));
+  if (int rc = engine_forward(e, T, B, R, b->max_blocks, max_q, max_seq, dm, any_random)) return rc;
+  ++e->step_count;
+  if (R > 0) {
+    KGE_CUDA_OK(cudaMemcpyAsync(e->out_host, e->d_out, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (out_logits_host) {
+      // debug/parity path: logits as fp32 through a scratch carved from the (idle) gate_up buffer
+      float* tmp = reinterpret_cast<float*>(e->gu);
+      const int64_t n = (int64_t)R * e->spec.vocab;
+      KGE_REQUIRE(n * 4 <= (int64_t)e->cfg.max_num_batched_tokens * e->layers[0].up.N * 2,
+                  "kge_step: logits read-back needs R*vocab*4 <= gate_up buffer");
+      bf16_to_f32_kernel<<<148 * 4, 256, 0, e->stream>>>(tmp, e->logits, n);
+      KGE_CUDA_OK(cudaMemcpyAsync(out_logits_host, tmp, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
+    }
+  }
+  KGE_CUDA_OK(cudaStreamSynchronize(e->stream));
+  if (R > 0 && out_ids_host) memcpy(out_ids_host, e->out_host, (size_t)R * 4);
+  return 0;
+}
+
+}  // namespace kge
+
+extern "C" int kge_step(kge_engine* e, const kge_step_batch* batch, int32_t* out_ids_host, float* out_logits_host) {
+  KGE_REQUIRE(e && batch, "kge_step: null argument");
+  return run_step(e, batch, nullptr, nullptr, nullptr, nullptr, out_ids_host, out_logits_host);
+}
+
+static SamplingParams to_sp(const kge_sampling_params* p) {
+  SamplingParams sp;
+  if (!p) return sp;
+  sp.max_tokens = p->max_tokens;
+  sp.min_tokens = p->min_tokens;
+  sp.ignore_eos = p->ignore_eos != 0;
+  sp.temperature = p->temperature;
+  sp.top_k = p->top_k;
+  sp.top_p = p->top_p;
+  sp.seed = p->seed;
+  if (p->stop_token_ids && p->num_stop_token_ids > 0)
+    sp.stop_token_ids.assign(p->stop_token_ids, p->stop_token_ids + p->num_stop_token_ids);
+  return sp;
+}
+
+extern "C" int kge_add_request(kge_engine* e, int64_t request_id, const int32_t* prompt_ids, int32_t n,
+                               const kge_sampling_params* sp) {
+  KGE_REQUIRE(e && prompt_ids, "kge_add_request: null argument");
+  for (int i = 0; i < n; ++i)
+    KGE_REQUIRE(prompt_ids[i] >= 0 && prompt_ids[i] < e->spec.vocab, "kge_add_request: token id %d out of vocabulary", prompt_ids[i]);
+  const char* why = nullptr;
+  if (!e->sched->add(request_id, prompt_ids, n, to_sp(sp), &why)) {
+    kge::set_error("kge_add_request: %s", why ? why : "rejected");
+    return -1;
+  }
+  return 0;
+}
+
+extern "C" int kge_abort_request(kge_engine* e, int64_t request_id) {
+  KGE_REQUIRE(e, "kge_abort_request: null engine");
+  return e->sched->abort(request_id) ? 0 : -1;
+}
+
+extern "C" int kge_has_unfinished(const kge_engine* e) { return e && e->sched->has_unfinished() ? 1 : 0; }
+
+extern "C" int kge_engine_stats(const kge_engine* e, int32_t* num_running, int32_t* num_waiting, float* kv_usage,
+                                int64_t* num_preemptions) {
+  KGE_REQUIRE(e, "kge_engine_stats: null engine");
+  if (num_running) *num_running = e->sched->num_running();
+  if (num_waiting) *num_waiting = e->sched->num_waiting();
+  if (kv_usage) *kv_usage = 1.f - (float)e->sched->free_blocks() / (float)std::max(1, e->sched->usable_blocks());
+  if (num_preemptions) *num_preemptions = e->sched->num_preemptions();
+  return 0;
+}
+
+extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap) {
+  KGE_REQUIRE(e && outs, "kge_engine_step: null argument");
+  const std::vector<Scheduled>& sc = e->sched->schedule();
+  if (sc.empty()) return 0;
+  const int bs = e->cfg.block_size;
+  const int B = (int)sc.size();
+  KGE_REQUIRE(B <= cap, "kge_engine_step: output capacity %d < %d scheduled requests", cap, B);
+  std::vector<int32_t> ids, pos, qsl(1, 0), seq_lens, rows, top_k;
+  std::vector<int64_t> slots;
+  std::vector<float> temp, top_p;
+  std::vector<uint64_t> seeds;
+  int max_blocks = 1;
+  for (auto& s : sc) max_blocks = std::max(max_blocks, (int)s.req->blocks.size());
+  std::vector<int32_t> btab((size_t)B * max_blocks, 0);
+  for (int i = 0; i < B; ++i) {
+    Request* r = sc[i].req;
+    const int n = sc[i].num_tokens, start = r->num_computed - n;
+    for (int t = start; t < start + n; ++t) {
+      ids.push_back(r->token_at(t));
+      pos.push_back(t);
+      slots.push_back((int64_t)r->blocks[t / bs] * bs + t % bs);
+    }
+    qsl.push_back((int)ids.size());
+    seq_lens.push_back(start + n);
+    std::copy(r->blocks.begin(), r->blocks.end(), btab.begin() + (size_t)i * max_blocks);
+    if (Scheduler::needs_sample(sc[i])) {
+      rows.push_back((int)ids.size() - 1);
+      temp.push_back(r->sp.temperature);
+      top_k.push_back(r->sp.top_k);
+      top_p.push_back(r->sp.top_p);
+      seeds.push_back(r->sp.seed ? r->sp.seed : (uint64_t)r->id * 0x9E3779B97F4A7C15ull + 1);
+    }
+  }
+  kge_step_batch b;
+  b.T = (int)ids.size(); b.B = B;
+  b.token_ids = ids.data(); b.positions = pos.data(); b.query_start_loc = qsl.data();
+  b.seq_lens = seq_lens.data(); b.block_table = btab.data(); b.max_blocks = max_blocks;
+  b.slot_mapping = slots.data(); b.logits_rows = rows.data(); b.R = (int)rows.size();
+  std::vector<int32_t> sampled(rows.size());
+  if (int rc = run_step(e, &b, temp.data(), top_k.data(), top_p.data(), seeds.data(), sampled.data(), nullptr)) return rc;
+  std::vector<StepResult> res;
+  e->sched->update(sampled, &res);
+  for (size_t i = 0; i < res.size(); ++i) {
+    outs[i].request_id = res[i].request_id;
+    outs[i].token = res[i].token;
+    outs[i].finished = res[i].finished;
+    outs[i].num_scheduled = res[i].num_scheduled;
+  }
+  return (int)res.size();
+}
+
+// ------------------------------------------------------------- scheduler alone (host tests)
+struct kge_sched { std::unique_ptr<Scheduler> s; };
+
+extern "C" kge_sched* kge_sched_create(int32_t max_num_seqs, int32_t max_num_batched_tokens, int32_t max_model_len,
+                                       int32_t block_size, int32_t num_blocks, int32_t enable_chunked_prefill,
+                                       int32_t eos_token_id) {
+  SchedConfig c;
+  c.max_num_seqs = max_num_seqs; c.max_num_batched_tokens = max_num_batched_tokens;
+  c.max_model_len = max_model_len; c.block_size = block_size; c.num_blocks = num_blocks;
+  c.enable_chunked_prefill = enable_chunked_prefill != 0; c.eos_token_id = eos_token_id;
+  kge_sched* k = new kge_sched();
+  k->s.reset(new Scheduler(c));
+  return k;
+}
+extern "C" void kge_sched_destroy(kge_sched* s) { delete s; }
+extern "C" int kge_sched_add(kge_sched* s, int64_t request_id, const int32_t* prompt_ids, int32_t n,
+                             const kge_sampling_params* sp) {
+  KGE_REQUIRE(s && prompt_ids, "kge_sched_add: null argument");
+  const char* why = nullptr;
+  if (!s->s->add(request_id, prompt_ids, n, to_sp(sp), &why)) { kge::set_error("kge_sched_add: %s", why ? why : "rejected"); return -1; }
+  return 0;
+}
+extern "C" int kge_sched_schedule(kge_sched* s, int64_t* ids, int32_t* num_tokens, int32_t cap) {
+  KGE_REQUIRE(s && ids && num_tokens, "kge_sched_schedule: null argument");
+  const auto& sc = s->s->schedule();
+  KGE_REQUIRE((int)sc.size() <= cap, "kge_sched_schedule: capacity %d < %d", cap, (int)sc.size());
+  for (size_t i = 0; i < sc.size(); ++i) { ids[i] = sc[i].req->id; num_tokens[i] = sc[i].num_tokens; }
+  return (int)sc.size();
+}
+extern "C" int kge_sched_update(kge_sched* s, const int64_t* ids, const int32_t* tokens, int32_t n,
+                                kge_step_output* outs, int32_t cap) {
+  KGE_REQUIRE(s, "kge_sched_update: null argument");
+  (void)ids;
+  std::vector<int32_t> sampled(tokens, tokens + n);
+  std::vector<StepResult> res;
+  s->s->update(sampled, &res);
+  KGE_REQUIRE((int)res.size() <= cap, "kge_sched_update: capacity %d < %d", cap, (int)res.size());
+  for (size_t i = 0; i < res.size(); ++i) {
+    outs[i].request_id = res[i].request_id; outs[i].token = res[i].token;
+    outs[i].finished = res[i].finished; outs[i].num_scheduled = res[i].num_scheduled;
+  }
+  return (int)res.size();
+}
+extern "C" int kge_sched_counts(const kge_sched* s, int32_t* running, int32_t* waiting, int32_t* free_blocks) {
+  KGE_REQUIRE(s, "kge_sched_counts: null argument");
+  if (running) *running = s->s->num_running();
+  if (waiting) *waiting = s->s->num_waiting();
+  if (free_blocks) *free_blocks = s->s->free_blocks();
+  return 0;
+}

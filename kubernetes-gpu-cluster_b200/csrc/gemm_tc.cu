@@ -1,0 +1,374 @@
+// Dense projection  y[T,N] = act(x[T,K] * w[N,K]^T + bias)  on the 5th-gen tensor cores.
+//
+// Weight-stationary orientation ("swap-AB"): the 128-row MMA M dimension runs over WEIGHT rows
+// (N is always large: 768..128256) and the MMA N dimension (16..256) over TOKENS, so a decode
+// step with T = 16..256 tokens wastes no tensor-core rows and streams every weight byte exactly
+// once, while prefill uses 128x256 tiles.  D[weight row, token] lives in TMEM (fp32); the
+// epilogue reads it back with tcgen05.ld, adds bias (one scalar per TMEM lane), applies the
+// activation, rounds once to bf16 and stores y transposed.
+//
+// Persistent, warp-specialised: warp 0 = TMA producer (cp.async.bulk.tensor, 128B swizzle),
+// warp 1 = tcgen05.mma issuer (one elected lane), warp 2 = TMEM allocator, warps 4-7 = epilogue.
+// smem ring of STAGES {W tile 128x64, X tile TOKNx64}; two TMEM accumulator stages so the
+// epilogue of tile i overlaps the main loop of tile i+1.
+// Split-K (decode, when N/128 tiles cannot fill 148 SMs): fp32 partial tiles go to workspace
+// (they stay L2-resident), a per-tile counter elects the last CTA, which sums the partials in
+// split order (deterministic), finishes the epilogue and re-arms the counter.
+//
+// Roofline: decode T<=256 -> HBM, algorithmic bytes = N*K*2 (weights) + T*(K+N)*2;
+//           prefill        -> tensor, 2*T*N*K flop.
+#include <cuda.h>
+
+#include "common.cuh"
+#include "kge.h"
+
+namespace kge {
+
+constexpr int BLK_M = 128;   // weight rows per tile (UMMA M)
+constexpr int BLK_K = 64;    // 64 bf16 = 128 B = one swizzle row
+constexpr int UMMA_K = 16;
+constexpr int kGemmThreads = 256;
+constexpr uint32_t kSpinLimit = 1u << 30;
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok, spins = 0;
+  do {
+    asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    if (!ok && ++spins > kSpinLimit) __trap();   // a lost arrival becomes an error, not a hang
+  } while (!ok);
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n}"
+               ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+               : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+                 "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+               : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+
+// K-major, 128B-swizzled operand tile (rows of 128 B, 8-row atoms 1024 B apart).
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  uint64_t d = (uint64_t)((saddr & 0x3FFFFu) >> 4);
+  d |= (uint64_t)1 << 16;                    // leading byte offset (unused for swizzled K-major)
+  d |= (uint64_t)(1024 >> 4) << 32;          // stride byte offset between 8-row atoms
+  d |= (uint64_t)1 << 46;                    // descriptor version (Blackwell)
+  d |= (uint64_t)2 << 61;                    // SWIZZLE_128B
+  return d;
+}
+
+struct GemmParams {
+  bf16* y;
+  const bf16* bias;
+  float* partial;        // [splits][m_tiles][n_tiles][TOKN][128] fp32
+  int* counters;         // [m_tiles * n_tiles], zero between launches
+  int T, N, K, act;
+  int m_tiles, n_tiles, splits, kb_total, kb_per_split;
+};
+
+template <int TOKN, int STAGES>
+__global__ void __launch_bounds__(kGemmThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
+               const GemmParams p) {
+  constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = TOKN * BLK_K * 2;
+  constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
+  constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TOKN >> 3) << 17) | ((uint32_t)(BLK_M >> 4) << 24);
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
+  // bars: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  int* flag_slot = reinterpret_cast<int*>(tmem_slot + 1);
+  const uint32_t smem_base = smem_addr(smem);
+  const uint32_t bar_base = smem_addr(bars);
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  auto tfull_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + s); };
+  auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  const int total = p.m_tiles * p.n_tiles * p.splits;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int n_tile = w % p.n_tiles, m_tile = (w / p.n_tiles) % p.m_tiles, split = w / (p.n_tiles * p.m_tiles);
+        const int kb0 = split * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          const uint32_t a_dst = smem_base + stage * STAGE_BYTES, b_dst = a_dst + A_BYTES;
+          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+          tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * BLK_M);
+          tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      int stage = 0; uint32_t phase = 0;
+      int acc = 0; uint32_t acc_phase = 0;
+      for (int w = blockIdx.x; w < total; w += gridDim.x) {
+        const int split = w / (p.n_tiles * p.m_tiles);
+        const int kb0 = split * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+        mbar_wait(tempty_bar(acc), acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * TOKN;
+        for (int kb = kb0; kb < kb1; ++kb) {
+          mbar_wait(full_bar(stage), phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_base + stage * STAGE_BYTES, b_addr = a_addr + A_BYTES;
+          const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(b_addr);
+#pragma unroll
+          for (int k = 0; k < BLK_K / UMMA_K; ++k) {
+            // +32 B per 16-element k step inside the 128 B swizzle row (start address field is >>4)
+            tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+          }
+          tc_commit(empty_bar(stage));          // frees the smem slot when these MMAs retire
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        }
+        tc_commit(tfull_bar(acc));              // accumulator complete
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+      }
+    }
+  } else if (warp >= 4) {
+    const int q = warp - 4;                      // TMEM lane quarter == warp % 4
+    const int et = threadIdx.x - 128;            // 0..127 == weight row within the tile
+    int acc = 0; uint32_t acc_phase = 0;
+    for (int w = blockIdx.x; w < total; w += gridDim.x) {
+      const int n_tile = w % p.n_tiles, m_tile = (w / p.n_tiles) % p.m_tiles, split = w / (p.n_tiles * p.m_tiles);
+      const int tile_id = m_tile * p.n_tiles + n_tile;
+      const int n = m_tile * BLK_M + et;         // weight row == output column
+      const int t0 = n_tile * TOKN;
+      mbar_wait(tfull_bar(acc), acc_phase);
+      tc_fence_after();
+      const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
+      const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
+      if (p.splits == 1) {
+#pragma unroll 1
+        for (int c = 0; c < TOKN; c += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + c, r);
+          if (n < p.N) {
+#pragma unroll
+            for (int j = 0; j < 16; ++j) {
+              const int t = t0 + c + j;
+              if (t < p.T) {
+                float v = __uint_as_float(r[j]) + bv;
+                if (p.act == 1) v = fmaxf(v, 0.f);
+                p.y[(int64_t)t * p.N + n] = f2bf(v);
+              }
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
+      } else {
+        float* mine = p.partial + ((int64_t)split * p.m_tiles * p.n_tiles + tile_id) * (TOKN * BLK_M);
+#pragma unroll 1
+        for (int c = 0; c < TOKN; c += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + c, r);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) mine[(c + j) * BLK_M + et] = __uint_as_float(r[j]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        __threadfence();
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) *flag_slot = atomicAdd(&p.counters[tile_id], 1);
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        const bool last = (*flag_slot == p.splits - 1);
+        asm volatile("bar.sync 1, 128;" ::: "memory");   // flag_slot read by all before it is reused
+        if (last) {
+          __threadfence();
+          const float* base = p.partial + (int64_t)tile_id * (TOKN * BLK_M);
+          const int64_t sstride = (int64_t)p.m_tiles * p.n_tiles * (TOKN * BLK_M);
+          if (n < p.N) {
+            for (int j = 0; j < TOKN; ++j) {
+              const int t = t0 + j;
+              if (t >= p.T) break;
+              float v = 0.f;
+              for (int s = 0; s < p.splits; ++s) v += __ldcg(base + s * sstride + j * BLK_M + et);
+              v += bv;
+              if (p.act == 1) v = fmaxf(v, 0.f);
+              p.y[(int64_t)t * p.N + n] = f2bf(v);
+            }
+          }
+          if (et == 0) p.counters[tile_id] = 0;   // re-arm for the next launch
+        }
+      }
+      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
+// ------------------------------------------------------------------------------ host
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn) return fn;
+  void* ptr = nullptr;
+  cudaDriverEntryPointQueryResult qres;
+  if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+      qres != cudaDriverEntryPointSuccess)
+    return nullptr;
+  fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  return fn;
+}
+
+// 2-D row-major bf16 [rows, cols] with a {64 x box_rows} box and 128B swizzle.
+static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
+  EncodeTiledFn enc = get_encode_fn();
+  KGE_REQUIRE(enc, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
+  cuuint32_t box[2] = {(cuuint32_t)BLK_K, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  KGE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld", (int)r, (long long)rows, (long long)cols);
+  return 0;
+}
+
+// Split-K only happens with < 120 output tiles, so the tile counters always fit the first
+// kCounterBytes of the workspace whatever the shape; the caller zeroes them ONCE (the kernel
+// re-arms them), and shapes that share one workspace never overlay counters with partials.
+constexpr int64_t kCounterBytes = 1024;
+
+struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; };
+
+static GemmPlan plan_gemm(int T, int N, int K) {
+  GemmPlan g;
+  g.tokn = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
+  g.m_tiles = (N + BLK_M - 1) / BLK_M;
+  g.n_tiles = (T + g.tokn - 1) / g.tokn;
+  g.kb_total = (K + BLK_K - 1) / BLK_K;
+  const int tiles = g.m_tiles * g.n_tiles;
+  int splits = 1;
+  if (tiles < 120) {
+    splits = 148 / tiles;                       // fill one wave of 148 SMs, never more
+    const int max_by_k = g.kb_total / 8 > 0 ? g.kb_total / 8 : 1;   // >= 8 k-blocks (512 of K) per split
+    if (splits > max_by_k) splits = max_by_k;
+    if (splits > 16) splits = 16;
+    if (splits < 1) splits = 1;
+  }
+  g.kb_per_split = (g.kb_total + splits - 1) / splits;
+  g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;   // drop empty splits
+  return g;
+}
+
+template <int TOKN>
+static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
+  constexpr int STAGES = (200 * 1024 / stage_bytes) > 8 ? 8 : (200 * 1024 / stage_bytes);
+  constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
+  auto kern = gemm_tc_kernel<TOKN, STAGES>;
+  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int total = p.m_tiles * p.n_tiles * p.splits;
+  int sms = 148;
+  const int grid = total < sms ? total : sms;
+  kern<<<grid, kGemmThreads, smem, st>>>(tw, tx, p);
+  KGE_LAUNCH_OK();
+  return 0;
+}
+
+}  // namespace kge
+
+using namespace kge;
+
+extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
+  if (T <= 0 || N <= 0 || K <= 0) return 0;
+  const GemmPlan g = plan_gemm(T, N, K);
+  if (g.splits == 1) return kCounterBytes;
+  return kCounterBytes + (int64_t)g.splits * g.m_tiles * g.n_tiles * g.tokn * BLK_M * 4;
+}
+
+extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
+                             int act, void* workspace, int64_t workspace_bytes, void* stream) {
+  KGE_REQUIRE(y && x && w, "kge_gemm_bf16: null pointer");
+  KGE_REQUIRE(T >= 0 && N > 0 && K > 0 && K % 8 == 0, "kge_gemm_bf16: K=%d must be a positive multiple of 8", K);
+  KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kge_gemm_bf16: x and w must be 16-byte aligned");
+  KGE_REQUIRE(act == 0 || act == 1, "kge_gemm_bf16: act=%d unsupported", act);
+  if (T == 0) return 0;
+  const GemmPlan g = plan_gemm(T, N, K);
+  GemmParams p;
+  p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
+  p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
+  p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
+  p.partial = nullptr; p.counters = nullptr;
+  if (g.splits > 1) {
+    const int64_t need = kge_gemm_workspace_bytes(T, N, K);
+    KGE_REQUIRE(workspace && workspace_bytes >= need, "kge_gemm_bf16: workspace %lld < %lld bytes (T=%d N=%d K=%d)",
+                (long long)workspace_bytes, (long long)need, T, N, K);
+    p.counters = (int*)workspace;
+    p.partial = (float*)((uint8_t*)workspace + kCounterBytes);
+  }
+  CUtensorMap tw, tx;
+  if (int rc = make_tmap(&tw, w, N, K, BLK_M)) return rc;
+  if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  switch (g.tokn) {
+    case 16: return launch_gemm<16>(tw, tx, p, st);
+    case 32: return launch_gemm<32>(tw, tx, p, st);
+    case 64: return launch_gemm<64>(tw, tx, p, st);
+    case 128: return launch_gemm<128>(tw, tx, p, st);
+    default: return launch_gemm<256>(tw, tx, p, st);
+  }
+}

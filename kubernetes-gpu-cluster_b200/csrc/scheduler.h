@@ -1,0 +1,100 @@
+// Continuous-batching scheduler and paged-KV block manager (host side, no CUDA).
+// Policy follows vllm:v1/core/sched/scheduler.py:329-830 (FCFS: RUNNING first under the token
+// budget, tail preemption with recompute when blocks run out, WAITING admission up to
+// max_num_seqs), :1283 update_from_output, stop rules vllm:v1/core/sched/utils.py:94-130 and the
+// block accounting of vllm:v1/core/kv_cache_manager.py:236-430 (block 0 is the null block).
+#pragma once
+#include <stdint.h>
+
+#include <deque>
+#include <memory>
+#include <unordered_map>
+#include <vector>
+
+namespace kge {
+
+struct SamplingParams {
+  int32_t max_tokens = 16;
+  int32_t min_tokens = 0;
+  bool ignore_eos = false;
+  float temperature = 1.0f;
+  int32_t top_k = 0;
+  float top_p = 1.0f;
+  uint64_t seed = 0;
+  std::vector<int32_t> stop_token_ids;
+};
+
+enum class ReqStatus { Waiting, Running, Preempted, FinishedStop, FinishedLength, Aborted };
+
+struct Request {
+  int64_t id = 0;
+  std::vector<int32_t> prompt;
+  std::vector<int32_t> output;
+  SamplingParams sp;
+  int32_t num_computed = 0;
+  std::vector<int32_t> blocks;
+  ReqStatus status = ReqStatus::Waiting;
+  int32_t num_preemptions = 0;
+  int32_t num_tokens() const { return (int32_t)(prompt.size() + output.size()); }
+  int32_t token_at(int32_t i) const {
+    return i < (int32_t)prompt.size() ? prompt[i] : output[i - prompt.size()];
+  }
+};
+
+struct SchedConfig {
+  int32_t max_num_seqs = 1024;
+  int32_t max_num_batched_tokens = 8192;
+  int32_t max_model_len = 4096;
+  int32_t block_size = 16;
+  int32_t num_blocks = 0;              // including null block 0
+  bool enable_chunked_prefill = true;
+  int32_t eos_token_id = -1;
+};
+
+struct Scheduled {
+  Request* req;
+  int32_t num_tokens;                  // tokens run this step, starting at req->num_computed - num_tokens
+};
+
+struct StepResult {
+  int64_t request_id;
+  int32_t token;                       // -1: prefill chunk only
+  int32_t finished;                    // 0 running, 1 stop, 2 length
+  int32_t num_scheduled;
+};
+
+class Scheduler {
+ public:
+  explicit Scheduler(const SchedConfig& c);
+  // Returns false (with reason) when the request can never run.
+  bool add(int64_t id, const int32_t* prompt, int32_t n, const SamplingParams& sp, const char** why);
+  bool abort(int64_t id);
+  // One scheduling pass; advances num_computed of every scheduled request.
+  const std::vector<Scheduled>& schedule();
+  // `tokens[i]` is the sampled token for the i-th scheduled request that reached its last known
+  // token this step (needs_sample order).  Appends one StepResult per scheduled request.
+  void update(const std::vector<int32_t>& sampled, std::vector<StepResult>* out);
+  static bool needs_sample(const Scheduled& s) { return s.req->num_computed == s.req->num_tokens(); }
+  bool has_unfinished() const { return !running_.empty() || !waiting_.empty(); }
+  int32_t num_running() const { return (int32_t)running_.size(); }
+  int32_t num_waiting() const { return (int32_t)waiting_.size(); }
+  int32_t free_blocks() const { return (int32_t)free_.size(); }
+  int32_t usable_blocks() const { return cfg_.num_blocks - 1; }
+  int64_t num_preemptions() const { return preemptions_; }
+  const SchedConfig& config() const { return cfg_; }
+  Request* find(int64_t id);
+
+ private:
+  bool alloc(Request* r, int32_t n_new);
+  void release(Request* r);
+  void finish(Request* r, ReqStatus st);
+  SchedConfig cfg_;
+  std::vector<int32_t> free_;          // stack of free block ids
+  std::deque<Request*> waiting_;
+  std::vector<Request*> running_;
+  std::unordered_map<int64_t, std::unique_ptr<Request>> reqs_;
+  std::vector<Scheduled> sched_;
+  int64_t preemptions_ = 0;
+};
+
+}  // namespace kge

@@ -93,7 +93,7 @@ CONFIGS: dict[str, ModelConfig] = {
                                  500000.0, _llama3_scaling(8.0), 128000, 128001,
                                  "meta-llama/Llama-3.1-70B"),
     # Small shapes of the same two architectures, sized so the oracle finishes in seconds.
-    "tiny-opt": ModelConfig("opt", 1000, 128, 2, 4, 4, 32, 512, 256, 1e-5, True,
+    "tiny-opt": ModelConfig("opt", 1000, 256, 2, 4, 4, 64, 512, 256, 1e-5, True,
                             bos=2, eos=2, name="tiny-opt"),
     "tiny-llama": ModelConfig("llama", 1024, 256, 2, 4, 2, 64, 512, 16384, 1e-5, False,
                               500000.0, _llama3_scaling(8.0), 1, 2, "tiny-llama"),

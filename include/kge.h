@@ -155,6 +155,34 @@ int64_t kge_engine_launches(const kge_engine* e);
 int kge_step(kge_engine* e, const kge_step_batch* batch, int32_t* out_ids_host,
              float* out_logits_host);
 
+/* Per-kernel timing for the roofline report: when enabled, every launch of the forward pass is
+ * bracketed by CUDA events on the engine's stream and accumulated per category together with its
+ * ALGORITHMIC work (bytes that must cross HBM once / flops), DESIGN.md "kernels".  Categories:
+ * 0 gemm (T<=256: weight streaming), 1 gemm (T>256: tensor bound), 2 decode attention,
+ * 3 general (prefill / mixed) attention, 4 norms, 5 rope+kv write, 6 activation, 7 embed/gather,
+ * 8 sampling, 9 all-reduce.  Timing adds event overhead: never enable it for a headline number. */
+#define KGE_NUM_KERNEL_CATS 10
+typedef struct {
+  int64_t launches;
+  double ms;          /* summed device time of the launches            */
+  double bytes;       /* summed algorithmic HBM bytes                  */
+  double flops;       /* summed algorithmic flops                      */
+} kge_kernel_stats;
+int kge_engine_set_timing(kge_engine* e, int enable);
+int kge_engine_get_timing(kge_engine* e, kge_kernel_stats* out /* [KGE_NUM_KERNEL_CATS] */);
+/* Host<->device traffic of the serving loop so far: per-step metadata in, sampled ids out. */
+int kge_engine_io_bytes(const kge_engine* e, int64_t* h2d, int64_t* d2h);
+
+/* Device-resident replay of one fixed-shape job (the bench's `value` leg): B requests of
+ * prompt_len tokens each are prefilled whole, `prefill_batch` requests per step, then decoded
+ * out_len-1 more steps greedily; all step metadata is uploaded BEFORE the timed region, sampled ids
+ * feed the next step on the device, and nothing is synchronised until the end.  prompts_host
+ * [B, prompt_len]; out_tokens_host [B, out_len]; *ms = device time of the whole job (CUDA events on
+ * the engine's stream); *decode_ms = the decode part.  Uses KV blocks 1..; the scheduler must be idle. */
+int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_host, int32_t B, int32_t prompt_len,
+                            int32_t out_len, int32_t prefill_batch, int32_t* out_tokens_host, float* ms,
+                            float* decode_ms);
+
 /* Tensor parallelism (one engine = one rank = one GPU): all ranks share a 128-byte NCCL
  * unique id made by rank 0; after kge_engine_init_tp the forward pass sums the row-parallel
  * projections with a bf16 ncclAllReduce (vllm:model_executor/layers/linear.py:1559;

@@ -48,6 +48,14 @@ class StepOutput(C.Structure):
                 ("num_scheduled", C.c_int32)]
 
 
+class KernelStats(C.Structure):
+    _fields_ = [("launches", C.c_int64), ("ms", C.c_double), ("bytes", C.c_double), ("flops", C.c_double)]
+
+
+NUM_KERNEL_CATS = 10
+KERNEL_CATS = ["gemm_decode", "gemm_prefill", "attn_decode", "attn_general", "norm", "rope_kvwrite",
+               "activation", "embed_gather", "sampling", "all_reduce"]
+
 # name -> (restype, argtypes); every symbol include/kge.h declares
 _P, _I, _L, _F = C.c_void_p, C.c_int, C.c_int64, C.c_float
 SIGNATURES = {
@@ -75,6 +83,10 @@ SIGNATURES = {
     "kge_engine_weight_bytes": (_L, [_P]),
     "kge_engine_launches": (_L, [_P]),
     "kge_step": (_I, [_P, C.POINTER(StepBatch), _P, _P]),
+    "kge_engine_set_timing": (_I, [_P, _I]),
+    "kge_engine_get_timing": (_I, [_P, _P]),
+    "kge_engine_io_bytes": (_I, [_P, _P, _P]),
+    "kge_engine_run_resident": (_I, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "kge_nccl_unique_id": (_I, [_P]),
     "kge_engine_init_tp": (_I, [_P, _P]),
     "kge_add_request": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
@@ -200,6 +212,33 @@ class LLM:
     @property
     def kernel_launches(self) -> int:
         return lib().kge_engine_launches(self._h)
+
+    def set_timing(self, enable: bool):
+        check(lib().kge_engine_set_timing(self._h, int(enable)), "kge_engine_set_timing")
+
+    def kernel_stats(self) -> dict:
+        """Per-category device time and algorithmic work since set_timing(True)."""
+        arr = (KernelStats * NUM_KERNEL_CATS)()
+        check(lib().kge_engine_get_timing(self._h, arr), "kge_engine_get_timing")
+        return {KERNEL_CATS[i]: dict(launches=arr[i].launches, ms=arr[i].ms, bytes=arr[i].bytes, flops=arr[i].flops)
+                for i in range(NUM_KERNEL_CATS) if arr[i].launches}
+
+    def io_bytes(self):
+        a, b = C.c_int64(), C.c_int64()
+        check(lib().kge_engine_io_bytes(self._h, C.byref(a), C.byref(b)), "kge_engine_io_bytes")
+        return a.value, b.value
+
+    def run_resident(self, prompts, out_len: int, prefill_batch: int):
+        """Device-resident replay of a fixed-shape greedy job (see include/kge.h).
+        Returns (tokens [B][out_len], total_ms, decode_ms)."""
+        import numpy as np
+        pr = np.ascontiguousarray(np.asarray(prompts, dtype=np.int32))
+        B, P = pr.shape
+        out = np.zeros((B, out_len), dtype=np.int32)
+        ms, dms = C.c_float(), C.c_float()
+        check(lib().kge_engine_run_resident(self._h, pr.ctypes.data, B, P, out_len, prefill_batch, out.ctypes.data,
+                                            C.byref(ms), C.byref(dms)), "kge_engine_run_resident")
+        return out.tolist(), ms.value, dms.value
 
     def init_tp(self, unique_id: bytes):
         check(lib().kge_engine_init_tp(self._h, unique_id), "kge_engine_init_tp")

@@ -67,6 +67,13 @@ struct kge_engine {
 
   std::unique_ptr<kge::Scheduler> sched;
   int64_t launches = 0;
+  int64_t h2d_bytes = 0, d2h_bytes = 0;      // metadata in / sampled ids out, summed over steps
+  // optional per-launch CUDA-event timing (kge_engine_set_timing): category totals
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_pool;
+  std::vector<int> ev_cat;                   // category of each recorded (start, stop) pair
+  std::vector<double> ev_work_bytes, ev_work_flops;
+  kge_kernel_stats stats[KGE_NUM_KERNEL_CATS] = {};
   uint64_t step_count = 0;
   std::string err;
 };
@@ -74,6 +81,7 @@ struct kge_engine {
 namespace kge {
 // engine_fwd.cu
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
-                   const StepMeta& dm, bool any_random);
+                   const StepMeta& dm, bool any_random, double sum_seq, double attn_flops);
+void collect_timing(kge_engine* e);
 StepMeta carve_meta(uint8_t* base, int T, int B, int R, int max_blocks, int64_t* total);
 }  // namespace kge

@@ -11,76 +11,116 @@ using namespace kge;
 
 namespace kge {
 
-#define FWD(call)                          \
+static void timer_begin(kge_engine* e, int cat, double bytes, double flops) {
+  if (!e->timing) return;
+  const size_t idx = e->ev_cat.size() * 2;
+  while (e->ev_pool.size() < idx + 2) {
+    cudaEvent_t ev;
+    cudaEventCreate(&ev);
+    e->ev_pool.push_back(ev);
+  }
+  e->ev_cat.push_back(cat);
+  e->ev_work_bytes.push_back(bytes);
+  e->ev_work_flops.push_back(flops);
+  cudaEventRecord(e->ev_pool[idx], e->stream);
+}
+static void timer_end(kge_engine* e) {
+  if (!e->timing) return;
+  cudaEventRecord(e->ev_pool[e->ev_cat.size() * 2 - 1], e->stream);
+}
+// after the stream has been synchronised
+void collect_timing(kge_engine* e) {
+  for (size_t i = 0; i < e->ev_cat.size(); ++i) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime(&ms, e->ev_pool[2 * i], e->ev_pool[2 * i + 1]) != cudaSuccess) continue;
+    kge_kernel_stats& st = e->stats[e->ev_cat[i]];
+    st.launches += 1; st.ms += ms; st.bytes += e->ev_work_bytes[i]; st.flops += e->ev_work_flops[i];
+  }
+  e->ev_cat.clear(); e->ev_work_bytes.clear(); e->ev_work_flops.clear();
+}
+
+#define FWD(cat, bytes, flops, call)       \
   do {                                     \
+    timer_begin(e, cat, bytes, flops);     \
     int _rc = (call);                      \
     if (_rc) return _rc;                   \
+    timer_end(e);                          \
     ++e->launches;                         \
   } while (0)
 
-static int linear(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int T, int act) {
+enum { C_GEMM_S = 0, C_GEMM_L = 1, C_ATT_DEC = 2, C_ATT_GEN = 3, C_NORM = 4, C_ROPE = 5, C_ACT = 6, C_EMBED = 7, C_SAMPLE = 8, C_AR = 9 };
+
+static int linear_rc(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int T, int act) {
   return kge_gemm_bf16(y, x, l.w, l.b, T, l.N, l.K, act, e->ws_gemm, e->ws_gemm_bytes, e->stream);
 }
+#define LINEAR(y, x, l, T, act)                                                                   \
+  FWD((T) <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)(l).N * (l).K + (double)(T) * ((l).K + (l).N)), \
+      2.0 * (T) * (double)(l).N * (l).K, linear_rc(e, y, x, l, T, act))
 
 int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n);   // tp.cu
 
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
-                   const StepMeta& m, bool any_random) {
+                   const StepMeta& m, bool any_random, double sum_seq, double attn_flops) {
   const ModelSpec& s = e->spec;
   const int d = s.d, hd = s.hd, Hl = e->H_loc, KVl = e->KV_loc, bs = e->cfg.block_size;
   cudaStream_t st = e->stream;
   const float scale = 1.0f / sqrtf((float)hd);
   const int qkv_n = e->layers[0].qkv.N;
+  const double Td2 = (double)T * d * 2;
+  const int c_att = max_q_len == 1 ? C_ATT_DEC : C_ATT_GEN;
+  const double att_bytes = sum_seq * KVl * hd * 4.0 + (double)T * Hl * hd * 4.0;
+  const double att_fl = attn_flops * Hl * hd;
+  const double rope_bytes = (double)T * (Hl + 2 * KVl) * hd * 2 * 2;
+  const double ar_bytes = Td2;
   if (s.is_opt()) {
-    FWD(kge_embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
+    FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
       // first LN of the layer; for i > 0 it also folds in the previous layer's fc2 output
-      FWD(kge_layernorm(e->xn, e->res, i == 0 ? nullptr : e->h, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
-      FWD(linear(e, e->qkv, e->xn, L.qkv, T, 0));
-      FWD(kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
-      FWD(kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+      FWD(C_NORM, (i ? 4 : 2) * Td2, 0, kge_layernorm(e->xn, e->res, i == 0 ? nullptr : e->h, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
+      LINEAR(e->qkv, e->xn, L.qkv, T, 0);
+      FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
                          max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
-      FWD(linear(e, e->h, e->attn, L.o, T, 0));
-      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
-      FWD(kge_layernorm(e->xn, e->res, e->h, L.ln2_w, L.ln2_b, T, d, 1e-5f, st));
-      FWD(linear(e, e->act, e->xn, L.up, T, 1));
-      FWD(linear(e, e->h, e->act, L.down, T, 0));
-      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+      LINEAR(e->h, e->attn, L.o, T, 0);
+      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
+      FWD(C_NORM, 4 * Td2, 0, kge_layernorm(e->xn, e->res, e->h, L.ln2_w, L.ln2_b, T, d, 1e-5f, st));
+      LINEAR(e->act, e->xn, L.up, T, 1);
+      LINEAR(e->h, e->act, L.down, T, 0);
+      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
     }
-    FWD(kge_layernorm(e->xn, e->res, e->h, e->final_w, e->final_b, T, d, 1e-5f, st));
+    FWD(C_NORM, 4 * Td2, 0, kge_layernorm(e->xn, e->res, e->h, e->final_w, e->final_b, T, d, 1e-5f, st));
   } else {
-    FWD(kge_embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
+    FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
-      if (i == 0) FWD(kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
-      else FWD(kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
-      FWD(linear(e, e->qkv, e->xn, L.qkv, T, 0));
-      FWD(kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
-      FWD(kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+      if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
+      else FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
+      LINEAR(e->qkv, e->xn, L.qkv, T, 0);
+      FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
                          max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
-      FWD(linear(e, e->h, e->attn, L.o, T, 0));
-      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
-      FWD(kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
-      FWD(linear(e, e->gu, e->xn, L.up, T, 0));
-      FWD(kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
-      FWD(linear(e, e->h, e->act, L.down, T, 0));
-      if (e->tp_size > 1) FWD(tp_all_reduce(e, e->h, (int64_t)T * d));
+      LINEAR(e->h, e->attn, L.o, T, 0);
+      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
+      FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
+      LINEAR(e->gu, e->xn, L.up, T, 0);
+      FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
+      LINEAR(e->h, e->act, L.down, T, 0);
+      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
     }
-    FWD(kge_add_rmsnorm(e->xn, e->res, e->h, e->final_w, T, d, s.eps, st));
+    FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, e->final_w, T, d, s.eps, st));
   }
   if (R > 0) {
     // logits only for the last token of each sampled request (logits_processor.py:54-99)
-    FWD(kge_embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
+    FWD(C_EMBED, 2.0 * R * d * 2, 0, kge_embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
     Linear head;
     head.w = e->lm_head; head.b = nullptr; head.N = s.vocab; head.K = d;
-    // y rows are written with stride N = vocab; keep ld == vocab so the row layout stays dense
-    FWD(linear(e, e->logits, e->xsel, head, R, 0));
+    LINEAR(e->logits, e->xsel, head, R, 0);
     if (any_random)
-      FWD(kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
+      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
                      e->step_count, nullptr, 0, st));
     else
-      FWD(kge_argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
+      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
   }
   return 0;
 }
@@ -117,8 +157,11 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
     any_random |= hm.temp[i] >= 1e-5f;
   }
   int max_q = 1, max_seq = 1;
+  double sum_seq = 0, attn_flops = 0;
   for (int i = 0; i < B; ++i) {
     const int ql = b->query_start_loc[i + 1] - b->query_start_loc[i];
+    sum_seq += b->seq_lens[i];
+    attn_flops += 4.0 * ql * ((double)(b->seq_lens[i] - ql) + 0.5 * (ql + 1));
     KGE_REQUIRE(ql >= 1 && ql <= b->seq_lens[i], "kge_step: request %d has q_len=%d seq_len=%d", i, ql, b->seq_lens[i]);
     KGE_REQUIRE(b->seq_lens[i] <= b->max_blocks * e->cfg.block_size, "kge_step: request %d seq_len=%d exceeds its block table", i, b->seq_lens[i]);
     max_q = std::max(max_q, ql);
@@ -126,7 +169,9 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
   }
   KGE_REQUIRE(b->query_start_loc[B] == T, "kge_step: query_start_loc[B]=%d != T=%d", b->query_start_loc[B], T);
   KGE_CUDA_OK(cudaMemcpyAsync(e->meta_dev, e->meta_host, (size_t)bytes, cudaMemcpyHostToDevice, e->stream));
-  if (int rc = engine_forward(e, T, B, R, b->max_blocks, max_q, max_seq, dm, any_random)) return rc;
+  e->h2d_bytes += bytes;
+  e->d2h_bytes += (int64_t)R * 4;
+  if (int rc = engine_forward(e, T, B, R, b->max_blocks, max_q, max_seq, dm, any_random, sum_seq, attn_flops)) return rc;
   ++e->step_count;
   if (R > 0) {
     KGE_CUDA_OK(cudaMemcpyAsync(e->out_host, e->d_out, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));
@@ -141,6 +186,7 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
     }
   }
   KGE_CUDA_OK(cudaStreamSynchronize(e->stream));
+  if (e->timing) collect_timing(e);
   if (R > 0 && out_ids_host) memcpy(out_ids_host, e->out_host, (size_t)R * 4);
   return 0;
 }

@@ -185,6 +185,70 @@ def make_weights(cfg: ModelConfig, seed: int = 0, dtype=torch.bfloat16,
     return w
 
 
+def make_timing_weights(cfg: ModelConfig, dtype=torch.bfloat16) -> dict[str, torch.Tensor]:
+    """Weights for TIMING the oracle at full model size without holding the full model: one layer's
+    tensors are generated (cheap uniform init, std 0.02) and every layer aliases them, so the
+    arithmetic and the bytes streamed per layer are those of the real shape while host memory stays
+    at one layer + embeddings.  Values are meaningless; never use for parity."""
+    one = ModelConfig(**{**cfg.__dict__, "num_layers": 1})
+    g = torch.Generator().manual_seed(0)
+    a = 0.02 * 3 ** 0.5
+    w1 = {}
+    for k, v in make_shapes(one).items():
+        w1[k] = torch.empty(v, dtype=dtype).uniform_(-a, a, generator=g) if "norm" not in k else torch.ones(v, dtype=dtype)
+    w = {}
+    for k, v in w1.items():
+        if ".layers.0." in k:
+            for i in range(cfg.num_layers):
+                w[k.replace(".layers.0.", f".layers.{i}.")] = v
+        else:
+            w[k] = v
+    return w
+
+
+def make_shapes(cfg: ModelConfig) -> dict[str, tuple]:
+    """Tensor name -> shape of the HF checkpoint for cfg (same names as make_weights)."""
+    d, f, L = cfg.hidden_size, cfg.ffn, cfg.num_layers
+    s: dict[str, tuple] = {}
+    if cfg.model_type == "opt":
+        p = "model.decoder."
+        s[p + "embed_tokens.weight"] = (cfg.vocab_size, d)
+        s[p + "embed_positions.weight"] = (cfg.max_position + 2, d)
+        for i in range(L):
+            q = f"{p}layers.{i}."
+            for nm in ("q_proj", "k_proj", "v_proj", "out_proj"):
+                s[q + f"self_attn.{nm}.weight"] = (d, d)
+                s[q + f"self_attn.{nm}.bias"] = (d,)
+            s[q + "self_attn_layer_norm.weight"] = (d,)
+            s[q + "self_attn_layer_norm.bias"] = (d,)
+            s[q + "fc1.weight"] = (f, d)
+            s[q + "fc1.bias"] = (f,)
+            s[q + "fc2.weight"] = (d, f)
+            s[q + "fc2.bias"] = (d,)
+            s[q + "final_layer_norm.weight"] = (d,)
+            s[q + "final_layer_norm.bias"] = (d,)
+        s[p + "final_layer_norm.weight"] = (d,)
+        s[p + "final_layer_norm.bias"] = (d,)
+    else:
+        H, KV, hd = cfg.num_heads, cfg.num_kv_heads, cfg.head_dim
+        s["model.embed_tokens.weight"] = (cfg.vocab_size, d)
+        for i in range(L):
+            q = f"model.layers.{i}."
+            s[q + "self_attn.q_proj.weight"] = (H * hd, d)
+            s[q + "self_attn.k_proj.weight"] = (KV * hd, d)
+            s[q + "self_attn.v_proj.weight"] = (KV * hd, d)
+            s[q + "self_attn.o_proj.weight"] = (d, H * hd)
+            s[q + "mlp.gate_proj.weight"] = (f, d)
+            s[q + "mlp.up_proj.weight"] = (f, d)
+            s[q + "mlp.down_proj.weight"] = (d, f)
+            s[q + "input_layernorm.weight"] = (d,)
+            s[q + "post_attention_layernorm.weight"] = (d,)
+        s["model.norm.weight"] = (d,)
+        if not cfg.tied:
+            s["lm_head.weight"] = (cfg.vocab_size, d)
+    return s
+
+
 def save_model_dir(path: str, cfg: ModelConfig, weights: dict[str, torch.Tensor]) -> None:
     """Write an HF-layout directory: config.json + model.safetensors (the layout the
     reference mounts at /models/<name>, ref:values-01-minimal-example3.yaml:8,22-30)."""
@@ -320,21 +384,25 @@ class OracleModel:
         c = cfg
         self.scale = c.head_dim ** -0.5
         L = c.num_layers
+        _memo: dict = {}
+
+        def cat(names):
+            # layers may alias one storage (make_timing_weights): fuse each distinct set once
+            key = tuple(self.w[n].data_ptr() for n in names)
+            if key not in _memo:
+                _memo[key] = torch.cat([self.w[n] for n in names], 0)
+            return _memo[key]
         if c.model_type == "llama":
             self.cos_sin = rope_cos_sin_cache(c, max_pos or min(c.max_position, 8192), dtype)
             # fused row orders as in QKVParallelLinear / MergedColumnParallelLinear
-            self.qkv = [torch.cat([self.w[f"model.layers.{i}.self_attn.{n}_proj.weight"]
-                                   for n in "qkv"], 0) for i in range(L)]
-            self.gate_up = [torch.cat([self.w[f"model.layers.{i}.mlp.gate_proj.weight"],
-                                       self.w[f"model.layers.{i}.mlp.up_proj.weight"]], 0)
+            self.qkv = [cat([f"model.layers.{i}.self_attn.{n}_proj.weight" for n in "qkv"]) for i in range(L)]
+            self.gate_up = [cat([f"model.layers.{i}.mlp.gate_proj.weight", f"model.layers.{i}.mlp.up_proj.weight"])
                             for i in range(L)]
             self.lm_head = self.w["model.embed_tokens.weight"] if c.tied else self.w["lm_head.weight"]
         else:
             p = "model.decoder.layers."
-            self.qkv = [torch.cat([self.w[f"{p}{i}.self_attn.{n}_proj.weight"] for n in "qkv"], 0)
-                        for i in range(L)]
-            self.qkv_b = [torch.cat([self.w[f"{p}{i}.self_attn.{n}_proj.bias"] for n in "qkv"], 0)
-                          for i in range(L)]
+            self.qkv = [cat([f"{p}{i}.self_attn.{n}_proj.weight" for n in "qkv"]) for i in range(L)]
+            self.qkv_b = [cat([f"{p}{i}.self_attn.{n}_proj.bias" for n in "qkv"]) for i in range(L)]
             self.lm_head = self.w["model.decoder.embed_tokens.weight"]
 
     # -- kv

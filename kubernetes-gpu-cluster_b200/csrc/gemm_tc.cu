@@ -11,9 +11,11 @@
 // warp 1 = tcgen05.mma issuer (one elected lane), warp 2 = TMEM allocator, warps 4-7 = epilogue.
 // smem ring of STAGES {W tile 128x64, X tile TOKNx64}; two TMEM accumulator stages so the
 // epilogue of tile i overlaps the main loop of tile i+1.
-// Split-K (decode, when N/128 tiles cannot fill 148 SMs): fp32 partial tiles go to workspace
-// (they stay L2-resident), a per-tile counter elects the last CTA, which sums the partials in
-// split order (deterministic), finishes the epilogue and re-arms the counter.
+// Split-K (decode, when N/128 tiles cannot fill 148 SMs): the S CTAs of a thread-block CLUSTER
+// share one output tile and each take 1/S of K.  Their fp32 partial accumulators are exchanged
+// through distributed shared memory (st.shared::cluster): CTA r receives column slice r of every
+// peer, sums the S partials in rank order (deterministic), adds bias, rounds once and stores.
+// No global scratch, no atomics, no serial tail; the cluster guarantees co-scheduling.
 //
 // Roofline: decode T<=256 -> HBM, algorithmic bytes = N*K*2 (weights) + T*(K+N)*2;
 //           prefill        -> tensor, 2*T*N*K flop.
@@ -83,13 +85,27 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
 struct GemmParams {
   bf16* y;
   const bf16* bias;
-  float* partial;        // [splits][m_tiles][n_tiles][TOKN][128] fp32
-  int* counters;         // [m_tiles * n_tiles], zero between launches
   int T, N, K, act;
   int m_tiles, n_tiles, splits, kb_total, kb_per_split;
 };
 
-template <int TOKN, int STAGES>
+__device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ uint32_t cluster_nctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
+__device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
+__device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
+__device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
+  uint32_t r;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(local), "r"(rank));
+  return r;
+}
+__device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
+  asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+
+// exchange buffer of the split variant: [src rank][local column][128 rows] fp32
+__host__ __device__ constexpr int xbuf_bytes(int tokn) { return (tokn + 8) * BLK_M * 4; }
+
+template <int TOKN, int STAGES, bool SPLIT>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
@@ -103,7 +119,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
   // bars: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-  int* flag_slot = reinterpret_cast<int*>(tmem_slot + 1);
+  uint32_t* colmap = tmem_slot + 2;                      // [TOKN] remote address of each column's slot (SPLIT)
+  float* xbuf = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 2048);   // SPLIT only
   const uint32_t smem_base = smem_addr(smem);
   const uint32_t bar_base = smem_addr(bars);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -130,14 +147,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
 
-  const int total = p.m_tiles * p.n_tiles * p.splits;
+  // work decomposition: persistent round-robin over tiles, or (SPLIT) one tile per cluster with
+  // the cluster rank selecting the K range
+  const int S = SPLIT ? (int)cluster_nctarank() : 1;
+  const int crank = SPLIT ? (int)cluster_ctarank() : 0;
+  const int total = p.m_tiles * p.n_tiles;
+  const int w_first = SPLIT ? (int)blockIdx.x / S : (int)blockIdx.x;
+  const int w_step = SPLIT ? (1 << 30) : (int)gridDim.x;
+  const int kb0 = crank * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+  const int cols_per = (TOKN + S - 1) / S;               // columns finished by each cluster rank
+  if (SPLIT) cluster_arrive();                           // phase A: every CTA of the cluster has started
 
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x) {
-        const int n_tile = w % p.n_tiles, m_tile = (w / p.n_tiles) % p.m_tiles, split = w / (p.n_tiles * p.m_tiles);
-        const int kb0 = split * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+      for (int w = w_first; w < total; w += w_step) {
+        const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t a_dst = smem_base + stage * STAGE_BYTES, b_dst = a_dst + A_BYTES;
@@ -152,9 +177,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int w = blockIdx.x; w < total; w += gridDim.x) {
-        const int split = w / (p.n_tiles * p.m_tiles);
-        const int kb0 = split * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+      for (int w = w_first; w < total; w += w_step) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * TOKN;
@@ -179,16 +202,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     const int q = warp - 4;                      // TMEM lane quarter == warp % 4
     const int et = threadIdx.x - 128;            // 0..127 == weight row within the tile
     int acc = 0; uint32_t acc_phase = 0;
-    for (int w = blockIdx.x; w < total; w += gridDim.x) {
-      const int n_tile = w % p.n_tiles, m_tile = (w / p.n_tiles) % p.m_tiles, split = w / (p.n_tiles * p.m_tiles);
-      const int tile_id = m_tile * p.n_tiles + n_tile;
+    if (SPLIT) {
+      // remote slot of column c: owner rank c / cols_per, my slice of its exchange buffer
+      for (int c = et; c < TOKN; c += 128) {
+        const int owner = c / cols_per, lc = c - owner * cols_per;
+        colmap[c] = mapa_u32(smem_addr(xbuf) + (uint32_t)((crank * cols_per + lc) * BLK_M * 4), (uint32_t)owner);
+      }
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+    }
+    for (int w = w_first; w < total; w += w_step) {
+      const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
       const int n = m_tile * BLK_M + et;         // weight row == output column
       const int t0 = n_tile * TOKN;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
       const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
-      if (p.splits == 1) {
+      if (!SPLIT) {
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
           uint32_t r[16];
@@ -209,43 +239,37 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(acc));
       } else {
-        float* mine = p.partial + ((int64_t)split * p.m_tiles * p.n_tiles + tile_id) * (TOKN * BLK_M);
+        cluster_wait();                          // phase A done: peers' shared memory is live
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
           uint32_t r[16];
           tmem_ld16(taddr + c, r);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) mine[(c + j) * BLK_M + et] = __uint_as_float(r[j]);
+          for (int j = 0; j < 16; ++j) st_cluster_f32(colmap[c + j] + (uint32_t)(et * 4), __uint_as_float(r[j]));
         }
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(acc));
-        __threadfence();
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        if (et == 0) *flag_slot = atomicAdd(&p.counters[tile_id], 1);
-        asm volatile("bar.sync 1, 128;" ::: "memory");
-        const bool last = (*flag_slot == p.splits - 1);
-        asm volatile("bar.sync 1, 128;" ::: "memory");   // flag_slot read by all before it is reused
-        if (last) {
-          __threadfence();
-          const float* base = p.partial + (int64_t)tile_id * (TOKN * BLK_M);
-          const int64_t sstride = (int64_t)p.m_tiles * p.n_tiles * (TOKN * BLK_M);
-          if (n < p.N) {
-            for (int j = 0; j < TOKN; ++j) {
-              const int t = t0 + j;
-              if (t >= p.T) break;
-              float v = 0.f;
-              for (int s = 0; s < p.splits; ++s) v += __ldcg(base + s * sstride + j * BLK_M + et);
-              v += bv;
-              if (p.act == 1) v = fmaxf(v, 0.f);
-              p.y[(int64_t)t * p.N + n] = f2bf(v);
-            }
+        cluster_arrive();                        // phase B: my partials are in the owners' buffers
+        cluster_wait();
+        const int c_begin = crank * cols_per, c_end = min(TOKN, c_begin + cols_per);
+        if (n < p.N) {
+          for (int c = c_begin; c < c_end; ++c) {
+            const int t = t0 + c;
+            if (t >= p.T) break;
+            float v = 0.f;
+            for (int s2 = 0; s2 < S; ++s2) v += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et];
+            v += bv;
+            if (p.act == 1) v = fmaxf(v, 0.f);
+            p.y[(int64_t)t * p.N + n] = f2bf(v);
           }
-          if (et == 0) p.counters[tile_id] = 0;   // re-arm for the next launch
         }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+  }
+  if (SPLIT && warp < 4) {                       // non-epilogue warps take part in both cluster phases
+    cluster_wait();
+    cluster_arrive();
+    cluster_wait();
   }
   tc_fence_before();
   __syncthreads();
@@ -287,10 +311,67 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
   return 0;
 }
 
-// Split-K only happens with < 120 output tiles, so the tile counters always fit the first
-// kCounterBytes of the workspace whatever the shape; the caller zeroes them ONCE (the kernel
-// re-arms them), and shapes that share one workspace never overlay counters with partials.
-constexpr int64_t kCounterBytes = 1024;
+template <int TOKN, bool SPLIT>
+static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
+  constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : 0);     // barriers + column map (+ exchange buffer)
+  constexpr int budget = 224 * 1024 - 1024 - extra;
+  constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
+  static_assert(STAGES >= 3, "pipeline too shallow");
+  constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT>;
+  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  const int tiles = p.m_tiles * p.n_tiles;
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kGemmThreads);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  if (SPLIT) {
+    cfg.gridDim = dim3(tiles * p.splits);
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = p.splits; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+  } else {
+    cfg.gridDim = dim3(tiles < 148 ? tiles : 148);
+  }
+  KGE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
+  return 0;
+}
+
+template <int TOKN>
+static int query_max_clusters(int S) {
+  constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
+  constexpr int extra = 2048 + xbuf_bytes(TOKN);
+  constexpr int budget = 224 * 1024 - 1024 - extra;
+  constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
+  constexpr int smem = STAGES * stage_bytes + 1024 + extra;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, true>;
+  if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3(S * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeClusterDimension;
+  attr[0].val.clusterDim.x = S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { (void)cudaGetLastError(); return 0; }
+  return n;
+}
+
+// How many clusters of size S of the split kernel can be co-resident (GPC packing decides: 148 SMs
+// hold e.g. 34 clusters of 4 but fewer than 148/3 clusters of 3).  Cached per (token tile, S).
+static int max_clusters(int tokn, int S) {
+  static int cache[4][9];
+  static bool have[4][9];
+  const int ti = tokn == 16 ? 0 : tokn == 32 ? 1 : tokn == 64 ? 2 : 3;
+  if (!have[ti][S]) {
+    cache[ti][S] = ti == 0 ? query_max_clusters<16>(S) : ti == 1 ? query_max_clusters<32>(S)
+                 : ti == 2 ? query_max_clusters<64>(S) : query_max_clusters<128>(S);
+    have[ti][S] = true;
+  }
+  return cache[ti][S];
+}
 
 struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; };
 
@@ -302,31 +383,17 @@ static GemmPlan plan_gemm(int T, int N, int K) {
   g.kb_total = (K + BLK_K - 1) / BLK_K;
   const int tiles = g.m_tiles * g.n_tiles;
   int splits = 1;
-  if (tiles < 120) {
-    splits = 148 / tiles;                       // fill one wave of 148 SMs, never more
-    const int max_by_k = g.kb_total / 8 > 0 ? g.kb_total / 8 : 1;   // >= 8 k-blocks (512 of K) per split
-    if (splits > max_by_k) splits = max_by_k;
-    if (splits > 16) splits = 16;
-    if (splits < 1) splits = 1;
+  if (tiles <= 74 && g.tokn <= 128) {
+    int smax = 148 / tiles;                     // never more CTAs than SMs
+    const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
+    if (smax > max_by_k) smax = max_by_k;
+    if (smax > 8) smax = 8;                     // portable cluster size
+    for (int s = smax; s >= 2; --s)             // largest S whose clusters all fit in ONE wave
+      if (tiles <= max_clusters(g.tokn, s)) { splits = s; break; }
   }
   g.kb_per_split = (g.kb_total + splits - 1) / splits;
   g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;   // drop empty splits
   return g;
-}
-
-template <int TOKN>
-static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
-  constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
-  constexpr int STAGES = (200 * 1024 / stage_bytes) > 8 ? 8 : (200 * 1024 / stage_bytes);
-  constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + 256 /*barriers*/;
-  auto kern = gemm_tc_kernel<TOKN, STAGES>;
-  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-  const int total = p.m_tiles * p.n_tiles * p.splits;
-  int sms = 148;
-  const int grid = total < sms ? total : sms;
-  kern<<<grid, kGemmThreads, smem, st>>>(tw, tx, p);
-  KGE_LAUNCH_OK();
-  return 0;
 }
 
 }  // namespace kge
@@ -334,14 +401,13 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
 using namespace kge;
 
 extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
-  if (T <= 0 || N <= 0 || K <= 0) return 0;
-  const GemmPlan g = plan_gemm(T, N, K);
-  if (g.splits == 1) return kCounterBytes;
-  return kCounterBytes + (int64_t)g.splits * g.m_tiles * g.n_tiles * g.tokn * BLK_M * 4;
+  (void)T; (void)N; (void)K;
+  return 0;   // split-K partials are exchanged through distributed shared memory
 }
 
 extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                              int act, void* workspace, int64_t workspace_bytes, void* stream) {
+  (void)workspace; (void)workspace_bytes;
   KGE_REQUIRE(y && x && w, "kge_gemm_bf16: null pointer");
   KGE_REQUIRE(T >= 0 && N > 0 && K > 0 && K % 8 == 0, "kge_gemm_bf16: K=%d must be a positive multiple of 8", K);
   KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kge_gemm_bf16: x and w must be 16-byte aligned");
@@ -352,23 +418,23 @@ extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* 
   p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
-  p.partial = nullptr; p.counters = nullptr;
-  if (g.splits > 1) {
-    const int64_t need = kge_gemm_workspace_bytes(T, N, K);
-    KGE_REQUIRE(workspace && workspace_bytes >= need, "kge_gemm_bf16: workspace %lld < %lld bytes (T=%d N=%d K=%d)",
-                (long long)workspace_bytes, (long long)need, T, N, K);
-    p.counters = (int*)workspace;
-    p.partial = (float*)((uint8_t*)workspace + kCounterBytes);
-  }
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w, N, K, BLK_M)) return rc;
   if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
+  if (g.splits > 1) {
+    switch (g.tokn) {
+      case 16: return launch_gemm<16, true>(tw, tx, p, st);
+      case 32: return launch_gemm<32, true>(tw, tx, p, st);
+      case 64: return launch_gemm<64, true>(tw, tx, p, st);
+      default: return launch_gemm<128, true>(tw, tx, p, st);
+    }
+  }
   switch (g.tokn) {
-    case 16: return launch_gemm<16>(tw, tx, p, st);
-    case 32: return launch_gemm<32>(tw, tx, p, st);
-    case 64: return launch_gemm<64>(tw, tx, p, st);
-    case 128: return launch_gemm<128>(tw, tx, p, st);
-    default: return launch_gemm<256>(tw, tx, p, st);
+    case 16: return launch_gemm<16, false>(tw, tx, p, st);
+    case 32: return launch_gemm<32, false>(tw, tx, p, st);
+    case 64: return launch_gemm<64, false>(tw, tx, p, st);
+    case 128: return launch_gemm<128, false>(tw, tx, p, st);
+    default: return launch_gemm<256, false>(tw, tx, p, st);
   }
 }

@@ -97,12 +97,28 @@ def test_real_width_models_logits_and_ids(kge, model_dirs, name):
     for b in range(2):
         t2 = ref[b].topk(2).values
         assert out[b] == ref_ids[b][0] or (t2[0] - t2[1]).item() <= MARGIN, (b, out[b], ref_ids[b][0])
+    # teacher-forced decode: feed the ORACLE's tokens so a near-tie cannot derail the comparison, and
+    # check every decode step's logits (decode attention + split-K GEMMs at real width)
+    for s in range(1, 8):
+        ids = [ref_ids[0][s - 1], ref_ids[1][s - 1]]
+        t = 40 + s - 1
+        out, lg = llm.raw_step(ids, [t, t], [0, 1, 2], [t + 1, t + 1], bt, 3,
+                               [bt[b][t // bs] * bs + t % bs for b in range(2)], [0, 1], want_logits=True)
+        ref, got = ref_lg[s], torch.from_numpy(lg)
+        err = (got - ref).abs()
+        assert (err <= 3e-2 * scale + 1.6e-2 * ref.abs()).all(), f"decode step {s}: max-abs {err.max().item():.4g}"
+        for b in range(2):
+            t2 = ref[b].topk(2).values
+            assert out[b] == ref_ids[b][s] or (t2[0] - t2[1]).item() <= MARGIN, (s, b)
     llm.close()
     llm = kge.LLM(d, max_model_len=128, max_num_seqs=4, max_num_batched_tokens=128, num_gpu_blocks_override=32)
     outs = llm.generate(prompts, kge.SamplingParams(max_tokens=8, temperature=0.0, ignore_eos=True))
     llm.close()
+    # free-running: with a 50k-128k vocabulary and random weights the oracle's own bf16 top-2 gap is
+    # below MARGIN on a large share of steps, so each request may leave the oracle's path at such a
+    # step (compare_greedy asserts that every divergence IS such a near-tie)
     equal, near = compare_greedy([o.outputs[0].token_ids for o in outs], ref_ids, ref_lg)
-    assert near <= 1 and equal >= 8, (equal, near)
+    assert near <= 2, (equal, near)
 
 
 def test_chunked_prefill_and_preemption_do_not_change_tokens(kge, model_dirs):

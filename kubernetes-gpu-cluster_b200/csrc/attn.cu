@@ -47,24 +47,46 @@ __device__ __forceinline__ uint32_t swz(int r, int c) {
   return (uint32_t)(r * HD * 2 + ((c ^ (r & 7)) << 4));
 }
 
-// Stage one 64-key tile of K or V for (request, kv head) into shared memory.
+// Stage one 64-key tile of K AND V for (request, kv head) into shared memory.
+// Thread t owns chunk column c = t % CH of rows t / CH + j * (NTHREADS / CH); the swizzled
+// destination offsets are tile-invariant (dst[], computed once per kernel) and the source element
+// offset of a row (one block-table lookup, broadcast across the lanes that share the row) is
+// computed once and used for both K and V.
 template <int HD, int NTHREADS>
-__device__ __forceinline__ void load_kv_tile(uint32_t sdst, const bf16* __restrict__ cache,
-                                             const int32_t* __restrict__ btab, int kvh, int KV,
-                                             int bs_shift, int key0, int kv_len, int tid) {
-  constexpr int CH = HD / 8;
-  for (int i = tid; i < BN * CH; i += NTHREADS) {
-    const int r = i / CH, c = i % CH;
-    const int key = key0 + r;
-    const bool ok = key < kv_len;
-    const bf16* src = cache;
-    if (ok) {
-      const int blk = btab[key >> bs_shift];
-      src = cache + ((((int64_t)blk * KV + kvh) << bs_shift) + (key & ((1 << bs_shift) - 1))) * HD + c * 8;
-    }
-    cp_async16(sdst + swz<HD>(r, c), src, ok);
+struct KvLoader {
+  static constexpr int CH = HD / 8;
+  static constexpr int RP = NTHREADS / CH;       // rows per pass
+  static constexpr int NP = BN / RP;             // passes per tile
+  uint32_t dst[NP];
+  int row0, c8;
+  const int32_t* btab;
+  int64_t head_off;                              // kvh * block_size * HD
+  int64_t blk_stride;                            // KV * block_size * HD
+  int bs_shift, bs_mask;
+
+  __device__ __forceinline__ void init(const int32_t* bt, int kvh, int KV, int shift, int tid) {
+    btab = bt; bs_shift = shift; bs_mask = (1 << shift) - 1;
+    row0 = tid / CH;
+    const int c = tid % CH;
+    c8 = c * 8;
+    head_off = ((int64_t)kvh << shift) * HD;
+    blk_stride = ((int64_t)KV << shift) * HD;
+#pragma unroll
+    for (int j = 0; j < NP; ++j) dst[j] = swz<HD>(row0 + j * RP, c);
   }
-}
+  __device__ __forceinline__ void load(uint32_t sK, uint32_t sV, const bf16* __restrict__ kc,
+                                       const bf16* __restrict__ vc, int key0, int kv_len) const {
+#pragma unroll
+    for (int j = 0; j < NP; ++j) {
+      const int key = key0 + row0 + j * RP;
+      const bool ok = key < kv_len;
+      int64_t off = 0;
+      if (ok) off = (int64_t)btab[key >> bs_shift] * blk_stride + head_off + (key & bs_mask) * HD + c8;
+      cp_async16(sK + dst[j], kc + off, ok);
+      cp_async16(sV + dst[j], vc + off, ok);
+    }
+  }
+};
 
 // --------------------------------------------------------------------------- general
 // grid (q tiles, KV, B); 128 threads; warp w owns tile rows 16w..16w+15.
@@ -104,8 +126,9 @@ attn_general_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_st
     const bf16* src = ok ? q + (int64_t)(q0 + tok0 + tk) * q_stride + (kvh * G + hh) * HD + c * 8 : q;
     cp_async16(sQ + swz<HD>(r, c), src, ok);
   }
-  load_kv_tile<HD, NT>(sK, k_cache, btab, kvh, KV, bs_shift, 0, kv_len, tid);
-  load_kv_tile<HD, NT>(sV, v_cache, btab, kvh, KV, bs_shift, 0, kv_len, tid);
+  KvLoader<HD, NT> ld;
+  ld.init(btab, kvh, KV, bs_shift, tid);
+  ld.load(sK, sV, k_cache, v_cache, 0, kv_len);
   cp_async_commit();
 
   uint32_t qf[HD / 16][4];
@@ -121,8 +144,7 @@ attn_general_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_st
   for (int kt = 0; kt < ntiles; ++kt) {
     const int st = kt & 1;
     if (kt + 1 < ntiles) {
-      load_kv_tile<HD, NT>(sK + (st ^ 1) * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, (kt + 1) * BN, kv_len, tid);
-      load_kv_tile<HD, NT>(sV + (st ^ 1) * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, (kt + 1) * BN, kv_len, tid);
+      ld.load(sK + (st ^ 1) * BN * HD * 2, sV + (st ^ 1) * BN * HD * 2, k_cache, v_cache, (kt + 1) * BN, kv_len);
       cp_async_commit();
       cp_async_wait<1>();
     } else {
@@ -246,13 +268,13 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
     const bf16* src = ok ? q + (int64_t)qrow * q_stride + (kvh * G + r) * HD + c * 8 : q;
     cp_async16(sQ + swz<HD>(r, c), src, ok);
   }
+  KvLoader<HD, NT> ld;
+  ld.init(btab, kvh, KV, bs_shift, tid);
   // prologue: STAGES-1 tiles in flight
 #pragma unroll
   for (int s = 0; s < STAGES - 1; ++s) {
-    if (t_begin + s < t_end) {
-      load_kv_tile<HD, NT>(sK + s * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, (t_begin + s) * BN, kv_len, tid);
-      load_kv_tile<HD, NT>(sV + s * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, (t_begin + s) * BN, kv_len, tid);
-    }
+    if (t_begin + s < t_end)
+      ld.load(sK + s * BN * HD * 2, sV + s * BN * HD * 2, k_cache, v_cache, (t_begin + s) * BN, kv_len);
     cp_async_commit();
   }
 
@@ -269,8 +291,7 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
     __syncthreads();             // tile `it` landed for all threads; stage (it-1)%STAGES is free
     if (nxt < t_end) {
       const int ns = (it + STAGES - 1) % STAGES;
-      load_kv_tile<HD, NT>(sK + ns * BN * HD * 2, k_cache, btab, kvh, KV, bs_shift, nxt * BN, kv_len, tid);
-      load_kv_tile<HD, NT>(sV + ns * BN * HD * 2, v_cache, btab, kvh, KV, bs_shift, nxt * BN, kv_len, tid);
+      ld.load(sK + ns * BN * HD * 2, sV + ns * BN * HD * 2, k_cache, v_cache, nxt * BN, kv_len);
     }
     cp_async_commit();
     if (it == 0) {

@@ -91,6 +91,34 @@ int kge_paged_attn(void* out, const void* q, int q_stride, const void* k_cache,
                    float scale, void* workspace, int64_t workspace_bytes, void* stream);
 int64_t kge_attn_workspace_bytes(int B, int H, int hd, int max_seq_len);
 
+/* Decode attention (one query token per request) for hosts that cannot allocate device memory.
+ * No counterpart in the reference or in the engine it deploys: this entry point exists only here.
+ *
+ * Use it when your process has no way to hand kge_paged_attn a workspace: the engine's KV pool is
+ * sized from --gpu-memory-utilization and may have left nothing for a later cudaMalloc, and a
+ * serving loop that must keep every stream moving cannot afford the device-wide stall cudaMalloc
+ * causes.  You still pass the inputs and the output; the split-KV partial results go to an array
+ * compiled into libkge.so, kge_paged_attn_decode_noalloc_max_bytes() (8 MiB) of device memory that
+ * every GPU using the library holds until the process exits.  The call itself performs no
+ * cudaMalloc / cudaFree and calls nothing that allocates.
+ *
+ * Limits and rules:
+ *  - a batch whose partials do not fit (B * H * splits * (hd + 2) * 4 bytes, splits as chosen by
+ *    kge_paged_attn for the same B / KV / max_seq_len) is rejected with -1 and a message saying so;
+ *  - the FIRST call on each device looks up the array's device address (with that device current).
+ *    Make that first call during start-up, before any stream capture begins;
+ *  - all calls on a device share the one array, which keeps whatever the last call left in it.
+ *    Nothing in it needs clearing (each launch overwrites every slot it later reads), but two
+ *    calls that run on the GPU at the same time - different streams, different threads - corrupt
+ *    each other's partials: serialise them;
+ *  - same arguments and results as kge_paged_attn with max_q_len == 1 (H / KV <= 16, hd 64 or 128). */
+int kge_paged_attn_decode_noalloc(void* out, const void* q, int q_stride, const void* k_cache,
+                                  const void* v_cache, const int32_t* block_table,
+                                  int max_blocks_per_seq, const int32_t* seq_lens,
+                                  const int32_t* query_start_loc, int B, int max_seq_len, int H, int KV,
+                                  int hd, int block_size, float scale, void* stream);
+int64_t kge_paged_attn_decode_noalloc_max_bytes(void);
+
 /* Greedy sampling, vllm:v1/sample/sampler.py:91,235-236: argmax over fp32(bf16 logits),
  * lowest index wins ties.  logits [B, ld] bf16 (ld >= V: padded vocab columns ignored). */
 int kge_argmax(int32_t* out_ids, const void* logits, int B, int V, int ld, void* stream);

@@ -73,6 +73,8 @@ SIGNATURES = {
     "kge_rope_cache_host": (_I, [_P, _I, _I, C.c_double, C.c_double, C.c_double, C.c_double, _I]),
     "kge_paged_attn": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _L, _P]),
     "kge_attn_workspace_bytes": (_L, [_I, _I, _I, _I]),
+    "kge_paged_attn_decode_noalloc": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _F, _P]),
+    "kge_paged_attn_decode_noalloc_max_bytes": (_L, []),
     "kge_argmax": (_I, [_P, _P, _I, _I, _I, _P]),
     "kge_sample": (_I, [_P, _P, _I, _I, _I, _P, _P, _P, _P, _P, C.c_uint64, _P, _L, _P]),
     "kge_sample_workspace_bytes": (_L, [_I, _I]),

@@ -500,3 +500,86 @@ extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void
   kge::set_error("kge_paged_attn: head_dim=%d unsupported (64, 128)", hd);
   return -1;
 }
+
+// ---------------------------------------------------------------------------------------------
+// Decode attention for callers that must not allocate.
+//
+// Who this is for: a host that has handed the whole device to the engine up front - the KV pool is
+// sized from gpu_memory_utilization, so a later cudaMalloc can simply fail - or one that drives
+// decode steps from a latency-critical thread where cudaMalloc's implicit device-wide
+// synchronisation would stall every stream.  Such a caller can still pass inputs and outputs it
+// already owns, but has nowhere to get the split-KV scratch from.  Here that scratch lives in the
+// library image itself: a file-scope device array that every GPU which loads libkge.so carries
+// (kNoAllocScratchBytes of its memory, from load until the process exits).
+//
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol, not a device address - passing
+// it to a kernel would fault (or, where the GPU can reach host memory, quietly scribble somewhere
+// wrong).  The device address is looked up once per device with cudaGetSymbolAddress, with that
+// device current, and is what the kernels receive.
+constexpr int64_t kNoAllocScratchBytes = 8ll << 20;     // 8 MiB per device
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace kge {
+constexpr int kMaxDevices = 64;
+static void* g_noalloc_ptr[kMaxDevices];                // device address of the array, per device
+static bool g_noalloc_ready[kMaxDevices];
+
+// One-time set-up for the CURRENT device.  Not thread-safe against a concurrent first call on the
+// same device; later calls only read.
+static int noalloc_scratch(void** out) {
+  int dev = -1;
+  KGE_CUDA_OK(cudaGetDevice(&dev));
+  KGE_REQUIRE(dev >= 0 && dev < kMaxDevices, "kge_paged_attn_decode_noalloc: device ordinal %d unsupported", dev);
+  if (!g_noalloc_ready[dev]) {
+    void* ptr = nullptr;
+    cudaError_t err = cudaGetSymbolAddress(&ptr, g_noalloc_scratch);
+    if (err != cudaSuccess || ptr == nullptr) {
+      kge::set_error("kge_paged_attn_decode_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                     cudaGetErrorString(err));
+      return -2;
+    }
+    g_noalloc_ptr[dev] = ptr;
+    g_noalloc_ready[dev] = true;
+  }
+  *out = g_noalloc_ptr[dev];
+  return 0;
+}
+}  // namespace kge
+
+extern "C" int64_t kge_paged_attn_decode_noalloc_max_bytes(void) { return kNoAllocScratchBytes; }
+
+extern "C" int kge_paged_attn_decode_noalloc(void* out, const void* q, int q_stride, const void* k_cache,
+                                             const void* v_cache, const int32_t* block_table,
+                                             int max_blocks_per_seq, const int32_t* seq_lens,
+                                             const int32_t* query_start_loc, int B, int max_seq_len, int H,
+                                             int KV, int hd, int block_size, float scale, void* stream) {
+  KGE_REQUIRE(out && q && k_cache && v_cache && block_table && seq_lens && query_start_loc,
+              "kge_paged_attn_decode_noalloc: null pointer");
+  KGE_REQUIRE(H > 0 && KV > 0 && H % KV == 0 && H / KV <= 16,
+              "kge_paged_attn_decode_noalloc: H=%d KV=%d (group must be <= 16)", H, KV);
+  KGE_REQUIRE(hd == 64 || hd == 128, "kge_paged_attn_decode_noalloc: head_dim=%d unsupported (64, 128)", hd);
+  KGE_REQUIRE(block_size > 0 && (block_size & (block_size - 1)) == 0,
+              "kge_paged_attn_decode_noalloc: block_size=%d must be a power of two", block_size);
+  KGE_REQUIRE(q_stride % 8 == 0, "kge_paged_attn_decode_noalloc: q_stride must be a multiple of 8");
+  if (B <= 0) return 0;
+  KGE_REQUIRE(max_seq_len >= 1, "kge_paged_attn_decode_noalloc: max_seq_len must be >= 1");
+  // same split choice as kge_paged_attn; the partials of all splits must fit the fixed array
+  const int ns = decode_splits(B, KV, max_seq_len);
+  const int64_t need = ns > 1 ? (int64_t)B * H * ns * (hd + 2) * 4 : 0;
+  KGE_REQUIRE(need <= kNoAllocScratchBytes,
+              "kge_paged_attn_decode_noalloc: this batch needs %lld bytes of split-KV scratch but the built-in array "
+              "holds %lld (B=%d H=%d splits=%d head_dim=%d); use kge_paged_attn with a caller workspace",
+              (long long)need, (long long)kNoAllocScratchBytes, B, H, ns, hd);
+  void* ws = nullptr;
+  if (int rc = noalloc_scratch(&ws)) return rc;
+  cudaStream_t st = (cudaStream_t)stream;
+  // every (request, head, split) slot of the scratch is written by this launch before the merge
+  // kernel reads it, so nothing has to be cleared between calls
+  if (hd == 64)
+    return launch_attn<64>((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, block_table,
+                           max_blocks_per_seq, seq_lens, query_start_loc, B, 1, max_seq_len, H, KV, block_size, scale,
+                           ws, kNoAllocScratchBytes, st);
+  return launch_attn<128>((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, block_table,
+                          max_blocks_per_seq, seq_lens, query_start_loc, B, 1, max_seq_len, H, KV, block_size, scale,
+                          ws, kNoAllocScratchBytes, st);
+}

@@ -30,8 +30,10 @@ WORKLOADS = {
     "c3": ("llama-3.1-8b", 64, 2048, 256, 4),
     "c2": ("llama-3.2-1b", 32, 128, 128, 32),
     "c1": ("opt-125m", 1, 128, 128, 1),
+    # tensor parallel over all --gpus ranks (BASELINE config 4): one model, NCCL all-reduce, strong scaling
+    "c4": ("llama-3.1-70b", 64, 2048, 256, 4),
 }
-CPU_SAMPLE = {"c3": (4, 128, 8), "c2": (8, 128, 16), "c1": (1, 128, 128)}   # (requests, in, out)
+CPU_SAMPLE = {"c3": (4, 128, 8), "c2": (8, 128, 16), "c1": (1, 128, 128), "c4": (1, 64, 2)}   # (requests, in, out)
 
 
 def model_cfg(name):
@@ -49,6 +51,9 @@ def model_cfg(name):
                     num_key_value_heads=8, head_dim=64, tie_word_embeddings=True, rope_scaling=l3(32.0))
     if name == "llama-3.1-8b":
         return dict(base, hidden_size=4096, num_hidden_layers=32, intermediate_size=14336, num_attention_heads=32,
+                    num_key_value_heads=8, head_dim=128, tie_word_embeddings=False, rope_scaling=l3(8.0))
+    if name == "llama-3.1-70b":
+        return dict(base, hidden_size=8192, num_hidden_layers=80, intermediate_size=28672, num_attention_heads=64,
                     num_key_value_heads=8, head_dim=128, tie_word_embeddings=False, rope_scaling=l3(8.0))
     raise ValueError(name)
 
@@ -173,14 +178,24 @@ def run_ours(args):
     name, B, pin, pout, pbatch = WORKLOADS[args.workload]
     hf = model_cfg(name)
     vocab = hf["vocab_size"]
-    prompts = make_prompts(vocab, B, pin, seed=rank)
+    tp = world if args.workload == "c4" else 1      # c4: ONE model sharded over all ranks; else replicas
+    replicas = 1 if tp > 1 else world
+    prompts = make_prompts(vocab, B, pin, seed=0 if tp > 1 else rank)
     bs = 16
     nblk = B * ((pin + pout + bs - 1) // bs) + 2
     with tempfile.TemporaryDirectory() as d:
         json.dump(hf, open(os.path.join(d, "config.json"), "w"))
         llm = kge.LLM(d, max_model_len=pin + pout + 16, max_num_seqs=max(B, 8),
                       max_num_batched_tokens=max(pbatch * pin, 256), num_gpu_blocks_override=nblk,
-                      load_format="dummy", seed=1234, device=local)
+                      load_format="dummy", seed=1234, device=local, tensor_parallel_size=tp, tp_rank=rank if tp > 1 else 0)
+    if tp > 1:
+        import ctypes as C
+        buf = C.create_string_buffer(128)
+        if rank == 0:
+            kge.check(kge.lib().kge_nccl_unique_id(buf), "kge_nccl_unique_id")
+        t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        llm.init_tp(bytes(t.cpu().numpy().tobytes()))
     sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True)
 
     def barrier():
@@ -214,7 +229,7 @@ def run_ours(args):
     clk = clocks.summary()
     ms_step = max_over_ranks(ms_total / args.steps)
     dec_ms_step = max_over_ranks(dec_total / args.steps)
-    value = world * B * pout / (ms_step * 1e-3)
+    value = replicas * B * pout / (ms_step * 1e-3)
 
     # ---- e2e: public API with host buffers, scheduler-driven, per-step H2D/D2H inside the timing
     for _ in range(min(args.warmup, 1)):
@@ -227,7 +242,7 @@ def run_ours(args):
     barrier()
     e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
     io1 = llm.io_bytes()
-    e2e = world * B * pout / e2e_s
+    e2e = replicas * B * pout / e2e_s
     toks_e2e = [o.outputs[0].token_ids for o in outs]
     same = sum(a == b for x, y in zip(toks_e2e, toks_res) for a, b in zip(x, y))
 
@@ -258,11 +273,12 @@ def run_ours(args):
     line = {
         "metric": "output tokens/sec at fixed concurrency", "value": value, "unit": "output tokens/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_step,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16",
+        "higher_is_better": True, "scaling": "strong" if tp > 1 else "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic token-id prompts U[1000,V-1000), hash-random weights (--load-format dummy)",
         "config": {"workload": f"{args.workload}: {name}, {B} concurrent requests, {pin}-in/{pout}-out, greedy, "
                                f"paged KV block 16, {pbatch} prompts per prefill step",
-                   "parallelism": f"dp{world} (independent replicas, no collective)",
+                   "parallelism": (f"tp{tp} (NCCL bf16 all-reduce after o_proj and down_proj)" if tp > 1
+                                   else f"dp{world} (independent replicas, no collective)"),
                    "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)"},
         "decode_ms_per_step": dec_ms_step, "decode_ms_per_token_step": dec_ms_step / max(1, pout - 1),
         "e2e": {"value": e2e, "unit": "output tokens/s", "h2d_bytes_per_step": (io1[0] - io0[0]) // args.steps,

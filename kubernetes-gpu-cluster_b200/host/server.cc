@@ -1,0 +1,663 @@
+// kge-serve: the container entrypoint the reference's values files expect (`vllm serve MODEL ...`,
+// installed as bin/vllm -> kge-serve), serving the OpenAI-compatible surface of the engine it
+// replaces: POST /v1/completions, POST /v1/chat/completions, GET /v1/models, GET /health,
+// GET /metrics (vllm:entrypoints/openai/completion/api_router.py:34-66, .../models/api_router.py:20,
+// vllm:entrypoints/serve/instrumentator/health.py:22-35, metrics.py:30-44).
+//
+// One engine thread owns the kge_engine handles (one per tensor-parallel rank) and is the only
+// caller of kge_add_request / kge_engine_step; HTTP connections are served by their own threads and
+// never touch the GPU, so kubelet's /health probes are answered while a step is running.
+#include <arpa/inet.h>
+#include <netinet/in.h>
+#include <netinet/tcp.h>
+#include <signal.h>
+#include <sys/socket.h>
+#include <sys/stat.h>
+#include <unistd.h>
+
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
+#include <map>
+#include <memory>
+#include <mutex>
+#include <string>
+#include <thread>
+#include <vector>
+
+#include "args.h"
+#include "json.h"
+#include "kge.h"
+
+using namespace kge;
+
+namespace {
+
+struct ReqState {
+  std::mutex mu;
+  std::condition_variable cv;
+  std::vector<int32_t> tokens;
+  int finished = 0;            // 0 running, 1 stop, 2 length, 3 error/aborted
+  std::string error;
+  int prompt_len = 0;
+};
+
+struct Submit {
+  int64_t id;
+  std::vector<int32_t> prompt;
+  kge_sampling_params sp;
+  std::vector<int32_t> stop_ids;
+  std::shared_ptr<ReqState> st;
+};
+
+struct Server {
+  ServeArgs args;
+  std::vector<kge_engine*> engines;       // one per TP rank
+  int vocab = 0;
+  std::mutex mu;
+  std::condition_variable cv;
+  std::deque<Submit> submits;
+  std::deque<int64_t> aborts;
+  std::map<int64_t, std::shared_ptr<ReqState>> live;   // engine thread only
+  std::atomic<bool> stop{false}, healthy{true};
+  std::atomic<int64_t> next_id{1};
+  std::atomic<int64_t> prompt_tokens{0}, generation_tokens{0}, success_stop{0}, success_length{0}, num_steps{0};
+  std::atomic<int> running{0}, waiting{0};
+  std::atomic<int64_t> preemptions{0};
+  std::atomic<float> kv_usage{0.f};
+  time_t created = time(nullptr);
+};
+
+Server* g_srv = nullptr;
+
+// ---------------------------------------------------------------------------------- engine thread
+int step_all(Server& s, kge_step_output* outs, int cap) {
+  if (s.engines.size() == 1) return kge_engine_step(s.engines[0], outs, cap);
+  // tensor parallel: every rank runs the identical step; ranks > 0 in helper threads so the NCCL
+  // all-reduces inside the step can meet
+  std::vector<std::thread> th;
+  std::vector<int> rcs(s.engines.size(), 0);
+  std::vector<std::vector<kge_step_output>> tmp(s.engines.size());
+  for (size_t r = 1; r < s.engines.size(); ++r) {
+    tmp[r].resize(cap);
+    th.emplace_back([&, r] { rcs[r] = kge_engine_step(s.engines[r], tmp[r].data(), cap); });
+  }
+  const int n = kge_engine_step(s.engines[0], outs, cap);
+  for (auto& t : th) t.join();
+  for (size_t r = 1; r < s.engines.size(); ++r)
+    if (rcs[r] < 0 || rcs[r] != n) return -3;
+  return n;
+}
+
+void engine_loop(Server* sp) {
+  Server& s = *sp;
+  std::vector<kge_step_output> outs(8192);
+  while (!s.stop) {
+    std::deque<Submit> subs;
+    std::deque<int64_t> abs_;
+    {
+      std::unique_lock<std::mutex> lk(s.mu);
+      if (s.submits.empty() && s.aborts.empty() && !kge_has_unfinished(s.engines[0]))
+        s.cv.wait_for(lk, std::chrono::milliseconds(50));
+      subs.swap(s.submits);
+      abs_.swap(s.aborts);
+    }
+    for (auto& sub : subs) {
+      sub.sp.stop_token_ids = sub.stop_ids.empty() ? nullptr : sub.stop_ids.data();
+      sub.sp.num_stop_token_ids = (int)sub.stop_ids.size();
+      int rc = 0;
+      for (auto* e : s.engines) {
+        rc = kge_add_request(e, sub.id, sub.prompt.data(), (int)sub.prompt.size(), &sub.sp);
+        if (rc) break;
+      }
+      if (rc) {
+        std::lock_guard<std::mutex> lk(sub.st->mu);
+        sub.st->error = kge_last_error();
+        sub.st->finished = 3;
+        sub.st->cv.notify_all();
+      } else {
+        s.live[sub.id] = sub.st;
+        s.prompt_tokens += (int64_t)sub.prompt.size();
+      }
+    }
+    for (int64_t id : abs_) {
+      for (auto* e : s.engines) kge_abort_request(e, id);
+      s.live.erase(id);
+    }
+    if (!kge_has_unfinished(s.engines[0])) continue;
+    const int n = step_all(s, outs.data(), (int)outs.size());
+    if (n < 0) {
+      fprintf(stderr, "engine step failed: %s\n", kge_last_error());
+      s.healthy = false;
+      for (auto& kv : s.live) {
+        std::lock_guard<std::mutex> lk(kv.second->mu);
+        kv.second->error = std::string("engine step failed: ") + kge_last_error();
+        kv.second->finished = 3;
+        kv.second->cv.notify_all();
+      }
+      s.live.clear();
+      s.stop = true;
+      break;
+    }
+    ++s.num_steps;
+    for (int i = 0; i < n; ++i) {
+      auto it = s.live.find(outs[i].request_id);
+      if (it == s.live.end()) continue;
+      auto st = it->second;
+      {
+        std::lock_guard<std::mutex> lk(st->mu);
+        if (outs[i].token >= 0) { st->tokens.push_back(outs[i].token); ++s.generation_tokens; }
+        if (outs[i].finished) st->finished = outs[i].finished;
+      }
+      st->cv.notify_all();
+      if (outs[i].finished) {
+        (outs[i].finished == 1 ? s.success_stop : s.success_length)++;
+        s.live.erase(it);
+      }
+    }
+    int32_t r = 0, w = 0;
+    float u = 0;
+    int64_t p = 0;
+    kge_engine_stats(s.engines[0], &r, &w, &u, &p);
+    s.running = r; s.waiting = w; s.kv_usage = u; s.preemptions = p;
+  }
+}
+
+// ---------------------------------------------------------------------------------- HTTP helpers
+struct HttpReq {
+  std::string method, path, body;
+  bool keep_alive = true;
+};
+
+bool send_all(int fd, const char* p, size_t n) {
+  while (n) {
+    ssize_t w = ::send(fd, p, n, MSG_NOSIGNAL);
+    if (w <= 0) return false;
+    p += w; n -= (size_t)w;
+  }
+  return true;
+}
+bool send_str(int fd, const std::string& s) { return send_all(fd, s.data(), s.size()); }
+
+// returns 1 ok, 0 clean EOF, -1 error
+int read_request(int fd, std::string& buf, HttpReq* r) {
+  size_t hend;
+  while ((hend = buf.find("\r\n\r\n")) == std::string::npos) {
+    if (buf.size() > (1 << 20)) return -1;
+    char tmp[8192];
+    ssize_t n = ::recv(fd, tmp, sizeof tmp, 0);
+    if (n == 0) return buf.empty() ? 0 : -1;
+    if (n < 0) return -1;
+    buf.append(tmp, (size_t)n);
+  }
+  std::string head = buf.substr(0, hend);
+  size_t le = head.find("\r\n");
+  std::string line = head.substr(0, le);
+  size_t s1 = line.find(' '), s2 = line.rfind(' ');
+  if (s1 == std::string::npos || s2 == s1) return -1;
+  r->method = line.substr(0, s1);
+  r->path = line.substr(s1 + 1, s2 - s1 - 1);
+  size_t q = r->path.find('?');
+  if (q != std::string::npos) r->path.resize(q);
+  r->keep_alive = line.find("HTTP/1.1") != std::string::npos;
+  size_t clen = 0;
+  size_t pos = le == std::string::npos ? head.size() : le + 2;
+  while (pos < head.size()) {
+    size_t e = head.find("\r\n", pos);
+    if (e == std::string::npos) e = head.size();
+    std::string h = head.substr(pos, e - pos);
+    pos = e + 2;
+    size_t c = h.find(':');
+    if (c == std::string::npos) continue;
+    std::string k = h.substr(0, c), v = h.substr(c + 1);
+    for (auto& ch : k) ch = (char)tolower(ch);
+    while (!v.empty() && v[0] == ' ') v.erase(0, 1);
+    if (k == "content-length") clen = (size_t)strtoull(v.c_str(), nullptr, 10);
+    if (k == "connection") {
+      for (auto& ch : v) ch = (char)tolower(ch);
+      if (v.find("close") != std::string::npos) r->keep_alive = false;
+      if (v.find("keep-alive") != std::string::npos) r->keep_alive = true;
+    }
+  }
+  if (clen > (64u << 20)) return -1;
+  buf.erase(0, hend + 4);
+  while (buf.size() < clen) {
+    char tmp[65536];
+    ssize_t n = ::recv(fd, tmp, sizeof tmp, 0);
+    if (n <= 0) return -1;
+    buf.append(tmp, (size_t)n);
+  }
+  r->body = buf.substr(0, clen);
+  buf.erase(0, clen);
+  return 1;
+}
+
+const char* status_text(int code) {
+  switch (code) {
+    case 200: return "OK";
+    case 400: return "Bad Request";
+    case 404: return "Not Found";
+    case 405: return "Method Not Allowed";
+    case 500: return "Internal Server Error";
+    case 503: return "Service Unavailable";
+  }
+  return "OK";
+}
+
+bool respond(int fd, int code, const std::string& ctype, const std::string& body, bool keep) {
+  std::string h = "HTTP/1.1 " + std::to_string(code) + " " + status_text(code) + "\r\n";
+  if (!ctype.empty()) h += "Content-Type: " + ctype + "\r\n";
+  h += "Content-Length: " + std::to_string(body.size()) + "\r\n";
+  h += keep ? "Connection: keep-alive\r\n\r\n" : "Connection: close\r\n\r\n";
+  return send_str(fd, h + body);
+}
+
+// {"error":{"message","type","param","code"}} with HTTP status = code (vllm:entrypoints/openai/engine/protocol.py:59-67)
+bool respond_error(int fd, int code, const std::string& msg, const std::string& type, bool keep) {
+  std::string b = "{\"error\":{\"message\":\"" + json_escape(msg) + "\",\"type\":\"" + type + "\",\"param\":null,\"code\":" +
+                  std::to_string(code) + "}}";
+  return respond(fd, code, "application/json", b, keep);
+}
+
+bool send_chunk(int fd, const std::string& data) {
+  char hdr[32];
+  snprintf(hdr, sizeof hdr, "%zx\r\n", data.size());
+  return send_str(fd, std::string(hdr) + data + "\r\n");
+}
+
+std::string ids_json(const std::vector<int32_t>& v, size_t from = 0) {
+  std::string s = "[";
+  for (size_t i = from; i < v.size(); ++i) { if (i > from) s += ","; s += std::to_string(v[i]); }
+  return s + "]";
+}
+
+// ---------------------------------------------------------------------------------- completions
+struct ParsedReq {
+  std::vector<std::vector<int32_t>> prompts;
+  kge_sampling_params sp{};
+  std::vector<int32_t> stop_ids;
+  bool stream = false, include_usage = false, echo = false;
+  int n = 1;
+  std::string model;
+};
+
+// prompt: [int] | [[int]]; strings need a tokenizer, which this build does not carry yet
+std::string parse_prompt(const Json* p, int vocab, std::vector<std::vector<int32_t>>* out) {
+  if (!p) return "prompt is required";
+  if (p->is_str()) return "string prompts need a tokenizer, which this engine build does not include yet: send token ids (prompt: [int] or [[int]])";
+  if (!p->is_arr() || p->arr.empty()) return "prompt must be a non-empty array of token ids";
+  auto one = [&](const Json& a, std::vector<int32_t>* v) -> std::string {
+    for (auto& t : a.arr) {
+      if (!t.is_num()) return "prompt arrays must hold integers";
+      const int64_t id = (int64_t)t.num;
+      if (id < 0 || id >= vocab) return "token id " + std::to_string(id) + " is out of vocabulary";
+      v->push_back((int32_t)id);
+    }
+    if (v->empty()) return "prompt is empty";
+    return "";
+  };
+  if (p->arr[0].is_num()) {
+    out->emplace_back();
+    return one(*p, &out->back());
+  }
+  if (p->arr[0].is_str()) return "string prompts need a tokenizer, which this engine build does not include yet: send token ids";
+  for (auto& a : p->arr) {
+    if (!a.is_arr()) return "prompt must be [int] or [[int]]";
+    out->emplace_back();
+    std::string e = one(a, &out->back());
+    if (!e.empty()) return e;
+  }
+  return "";
+}
+
+std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
+  r->sp.max_tokens = (int)j.int_or(chat ? "max_completion_tokens" : "max_tokens", j.int_or("max_tokens", 16));
+  r->sp.min_tokens = (int)j.int_or("min_tokens", 0);
+  r->sp.ignore_eos = j.bool_or("ignore_eos", false) ? 1 : 0;
+  r->sp.temperature = (float)j.num_or("temperature", 1.0);     // omitted => 1.0 (vllm:sampling_params.py:205)
+  r->sp.top_p = (float)j.num_or("top_p", 1.0);
+  r->sp.top_k = (int)j.int_or("top_k", 0);
+  if (r->sp.top_k < 0) r->sp.top_k = 0;
+  r->sp.seed = (uint64_t)j.int_or("seed", 0);
+  r->n = (int)j.int_or("n", 1);
+  r->stream = j.bool_or("stream", false);
+  r->echo = j.bool_or("echo", false);
+  r->model = j.str_or("model", "");
+  if (const Json* so = j.get("stream_options")) r->include_usage = so->bool_or("include_usage", false);
+  if (const Json* st = j.get("stop_token_ids"))
+    if (st->is_arr()) for (auto& t : st->arr) if (t.is_num()) r->stop_ids.push_back((int32_t)t.num);
+  if (const Json* st = j.get("stop"))
+    if (!st->is_null() && !(st->is_arr() && st->arr.empty())) return "stop strings need a tokenizer; use stop_token_ids";
+  if (const Json* lp = j.get("logprobs"))
+    if (!lp->is_null() && !(lp->type == Json::Bool && !lp->b)) return "logprobs are not supported";
+  if (r->sp.max_tokens < 1) return "max_tokens must be at least 1";
+  if (r->sp.temperature < 0) return "temperature must be non-negative";
+  if (r->sp.top_p <= 0 || r->sp.top_p > 1) return "top_p must be in (0, 1]";
+  if (r->n < 1 || r->n > 64) return "n must be in [1, 64]";
+  if (r->echo) return "echo is not supported";
+  return "";
+}
+
+void push_abort(Server& s, int64_t id) {
+  std::lock_guard<std::mutex> lk(s.mu);
+  s.aborts.push_back(id);
+  s.cv.notify_all();
+}
+
+bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
+  Json j;
+  std::string perr;
+  if (!json_parse(hr.body, &j, &perr) || !j.is_obj()) return respond_error(fd, 400, "invalid JSON body: " + perr, "BadRequestError", hr.keep_alive);
+  ParsedReq pr;
+  std::string err = parse_sampling(j, &pr, chat);
+  if (err.empty()) {
+    if (chat) {
+      // chat needs the model's chat template + tokenizer; token ids may be passed in `prompt_token_ids`
+      err = parse_prompt(j.get("prompt_token_ids"), s.vocab, &pr.prompts);
+      if (!err.empty()) err = "chat completions need a tokenizer and chat template, which this engine build does not include yet; "
+                              "pass prompt_token_ids: [int] (" + err + ")";
+    } else {
+      err = parse_prompt(j.get("prompt"), s.vocab, &pr.prompts);
+    }
+  }
+  if (!err.empty()) return respond_error(fd, 400, err, "BadRequestError", hr.keep_alive);
+  if (!pr.model.empty() && pr.model != s.args.served_model_name)
+    return respond_error(fd, 404, "The model `" + pr.model + "` does not exist.", "NotFoundError", hr.keep_alive);
+
+  struct Sub { int64_t id; std::shared_ptr<ReqState> st; size_t sent = 0; bool done = false; };
+  std::vector<Sub> subs;
+  int prompt_tokens = 0;
+  {
+    std::lock_guard<std::mutex> lk(s.mu);
+    for (auto& p : pr.prompts)
+      for (int k = 0; k < pr.n; ++k) {
+        Submit sb;
+        sb.id = s.next_id++;
+        sb.prompt = p;
+        sb.sp = pr.sp;
+        if (pr.n > 1 && sb.sp.seed) sb.sp.seed += (uint64_t)k;
+        sb.stop_ids = pr.stop_ids;
+        sb.st = std::make_shared<ReqState>();
+        sb.st->prompt_len = (int)p.size();
+        subs.push_back({sb.id, sb.st});
+        prompt_tokens += (int)p.size();
+        s.submits.push_back(std::move(sb));
+      }
+    s.cv.notify_all();
+  }
+  const std::string rid = std::string(chat ? "chatcmpl-" : "cmpl-") + std::to_string(subs[0].id);
+  const std::string model = json_escape(s.args.served_model_name);
+  const long created = (long)time(nullptr);
+  auto reason = [](int f) { return f == 1 ? "\"stop\"" : f == 2 ? "\"length\"" : "null"; };
+
+  if (!pr.stream) {
+    std::string choices;
+    int completion = 0;
+    for (size_t i = 0; i < subs.size(); ++i) {
+      auto& st = *subs[i].st;
+      std::unique_lock<std::mutex> lk(st.mu);
+      st.cv.wait(lk, [&] { return st.finished != 0; });
+      if (st.finished == 3) {
+        for (auto& o : subs) push_abort(s, o.id);
+        return respond_error(fd, 400, st.error, "BadRequestError", hr.keep_alive);
+      }
+      completion += (int)st.tokens.size();
+      if (i) choices += ",";
+      if (chat)
+        choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"\"},\"token_ids\":" +
+                   ids_json(st.tokens) + ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
+      else
+        choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"\",\"token_ids\":" + ids_json(st.tokens) +
+                   ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
+    }
+    std::string body = "{\"id\":\"" + rid + "\",\"object\":\"" + (chat ? "chat.completion" : "text_completion") + "\",\"created\":" +
+                       std::to_string(created) + ",\"model\":\"" + model + "\",\"choices\":[" + choices + "],\"usage\":{\"prompt_tokens\":" +
+                       std::to_string(prompt_tokens) + ",\"total_tokens\":" + std::to_string(prompt_tokens + completion) +
+                       ",\"completion_tokens\":" + std::to_string(completion) + "}}";
+    return respond(fd, 200, "application/json", body, hr.keep_alive);
+  }
+
+  // SSE: data: {chunk}\n\n ... data: [DONE]\n\n (vllm:entrypoints/openai/completion/serving.py:436,463)
+  std::string h = "HTTP/1.1 200 OK\r\nContent-Type: text/event-stream; charset=utf-8\r\nCache-Control: no-cache\r\n"
+                  "Transfer-Encoding: chunked\r\n";
+  h += hr.keep_alive ? "Connection: keep-alive\r\n\r\n" : "Connection: close\r\n\r\n";
+  bool ok = send_str(fd, h);
+  const char* obj = chat ? "chat.completion.chunk" : "text_completion";
+  int completion = 0;
+  size_t remaining = subs.size();
+  while (ok && remaining) {
+    for (size_t i = 0; i < subs.size() && ok; ++i) {
+      Sub& sb = subs[i];
+      if (sb.done) continue;
+      std::vector<int32_t> fresh;
+      int fin = 0;
+      std::string e;
+      {
+        std::unique_lock<std::mutex> lk(sb.st->mu);
+        sb.st->cv.wait_for(lk, std::chrono::milliseconds(subs.size() > 1 ? 2 : 1000),
+                           [&] { return sb.st->tokens.size() > sb.sent || sb.st->finished != 0; });
+        fresh.assign(sb.st->tokens.begin() + sb.sent, sb.st->tokens.end());
+        fin = sb.st->finished;
+        e = sb.st->error;
+      }
+      if (fin == 3) {
+        ok = send_chunk(fd, "data: {\"error\":{\"message\":\"" + json_escape(e) + "\",\"type\":\"BadRequestError\",\"param\":null,\"code\":400}}\n\n");
+        sb.done = true; --remaining;
+        continue;
+      }
+      for (size_t k = 0; k < fresh.size() && ok; ++k) {
+        const bool last = fin && k + 1 == fresh.size();
+        std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
+                        "\",\"choices\":[{\"index\":" + std::to_string(i);
+        if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"\"}";
+        else c += ",\"text\":\"\"";
+        c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (last ? reason(fin) : "null") +
+             ",\"stop_reason\":null}]}";
+        ok = send_chunk(fd, "data: " + c + "\n\n");
+        ++completion;
+      }
+      sb.sent += fresh.size();
+      if (fin) { sb.done = true; --remaining; }
+    }
+  }
+  if (!ok) {                                     // client went away: free the KV blocks
+    for (auto& o : subs) if (!o.done) push_abort(s, o.id);
+    return false;
+  }
+  if (pr.include_usage)
+    ok = send_chunk(fd, "data: {\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
+                            "\",\"choices\":[],\"usage\":{\"prompt_tokens\":" + std::to_string(prompt_tokens) + ",\"total_tokens\":" +
+                            std::to_string(prompt_tokens + completion) + ",\"completion_tokens\":" + std::to_string(completion) + "}}\n\n");
+  ok = ok && send_chunk(fd, "data: [DONE]\n\n") && send_str(fd, "0\r\n\r\n");
+  return ok;
+}
+
+std::string metrics_text(Server& s) {
+  const std::string m = "model_name=\"" + s.args.served_model_name + "\"";
+  std::string o;
+  auto gauge = [&](const char* name, const char* help, double v) {
+    o += std::string("# HELP ") + name + " " + help + "\n# TYPE " + name + " gauge\n" + name + "{" + m + "} " + std::to_string(v) + "\n";
+  };
+  auto counter = [&](const char* name, const char* help, const std::string& labels, double v, bool head) {
+    if (head) o += std::string("# HELP ") + name + " " + help + "\n# TYPE " + name + " counter\n";
+    o += std::string(name) + "{" + m + labels + "} " + std::to_string(v) + "\n";
+  };
+  gauge("vllm:num_requests_running", "Number of requests in model execution batches.", s.running);
+  gauge("vllm:num_requests_waiting", "Number of requests waiting to be processed.", s.waiting);
+  gauge("vllm:kv_cache_usage_perc", "KV-cache usage. 1 means 100 percent usage.", s.kv_usage);
+  gauge("vllm:gpu_cache_usage_perc", "GPU KV-cache usage (v0.8 name). 1 means 100 percent usage.", s.kv_usage);
+  counter("vllm:num_preemptions_total", "Cumulative number of preemption from the engine.", "", (double)s.preemptions, true);
+  counter("vllm:prompt_tokens_total", "Number of prefill tokens processed.", "", (double)s.prompt_tokens, true);
+  counter("vllm:generation_tokens_total", "Number of generation tokens processed.", "", (double)s.generation_tokens, true);
+  counter("vllm:request_success_total", "Count of successfully processed requests.", ",finished_reason=\"stop\"", (double)s.success_stop, true);
+  counter("vllm:request_success_total", "", ",finished_reason=\"length\"", (double)s.success_length, false);
+  counter("kge:engine_steps_total", "Engine steps executed.", "", (double)s.num_steps, true);
+  return o;
+}
+
+void serve_conn(Server* sp, int fd) {
+  Server& s = *sp;
+  int one = 1;
+  setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
+  std::string buf;
+  while (!s.stop) {
+    HttpReq r;
+    const int rc = read_request(fd, buf, &r);
+    if (rc <= 0) break;
+    bool ok = true;
+    if (r.path == "/health" || r.path == "/ping") {
+      ok = respond(fd, s.healthy ? 200 : 503, "", "", r.keep_alive);
+    } else if (r.path == "/v1/models" && r.method == "GET") {
+      const std::string m = json_escape(s.args.served_model_name);
+      ok = respond(fd, 200, "application/json",
+                   "{\"object\":\"list\",\"data\":[{\"id\":\"" + m + "\",\"object\":\"model\",\"created\":" + std::to_string((long)s.created) +
+                       ",\"owned_by\":\"vllm\",\"root\":\"" + json_escape(s.args.model) + "\",\"parent\":null,\"max_model_len\":" +
+                       std::to_string(s.args.max_model_len) + "}]}",
+                   r.keep_alive);
+    } else if (r.path == "/metrics" && r.method == "GET") {
+      ok = respond(fd, 200, "text/plain; version=0.0.4; charset=utf-8", metrics_text(s), r.keep_alive);
+    } else if (r.path == "/version") {
+      ok = respond(fd, 200, "application/json", "{\"version\":\"kge-b200-0.1\"}", r.keep_alive);
+    } else if (r.path == "/v1/completions" || r.path == "/v1/chat/completions") {
+      if (r.method != "POST") ok = respond_error(fd, 405, "Method Not Allowed", "MethodNotAllowed", r.keep_alive);
+      else if (!s.healthy) ok = respond_error(fd, 503, "engine is not healthy", "ServiceUnavailable", r.keep_alive);
+      else ok = handle_generate(s, fd, r, r.path != "/v1/completions");
+    } else {
+      ok = respond_error(fd, 404, "Not Found", "NotFoundError", r.keep_alive);
+    }
+    if (!ok || !r.keep_alive) break;
+  }
+  ::close(fd);
+}
+
+void on_signal(int) { if (g_srv) g_srv->stop = true; }
+
+bool is_dir(const std::string& p) {
+  struct stat st;
+  return stat(p.c_str(), &st) == 0 && S_ISDIR(st.st_mode);
+}
+
+// HF id -> local snapshot directory (no network in the pod's engine: the chart mounts or pre-pulls it)
+std::string resolve_model(const std::string& model) {
+  if (is_dir(model)) return model;
+  const char* hf = getenv("HF_HOME");
+  std::string base = hf ? std::string(hf) : std::string(getenv("HOME") ? getenv("HOME") : "/root") + "/.cache/huggingface";
+  std::string name = model;
+  for (auto& c : name) if (c == '/') c = '-';
+  std::string repl = model;
+  size_t p;
+  while ((p = repl.find('/')) != std::string::npos) repl.replace(p, 1, "--");
+  std::string snap = base + "/hub/models--" + repl + "/snapshots";
+  if (is_dir(snap)) {
+    // first snapshot
+    std::string cmd = "ls -1 '" + snap + "' 2>/dev/null | head -1";
+    if (FILE* f = popen(cmd.c_str(), "r")) {
+      char line[512] = {0};
+      if (fgets(line, sizeof line, f)) {
+        std::string l = line;
+        while (!l.empty() && (l.back() == '\n' || l.back() == '\r')) l.pop_back();
+        pclose(f);
+        if (!l.empty()) return snap + "/" + l;
+      } else pclose(f);
+    }
+  }
+  return "";
+}
+
+}  // namespace
+
+int main(int argc, char** argv) {
+  Server s;
+  std::string err = parse_serve_args(argc, argv, &s.args);
+  if (!err.empty()) {
+    fprintf(stderr, "usage: vllm serve MODEL [--host H] [--port P] [--max-model-len N] [--tensor-parallel-size N] ...\nerror: %s\n", err.c_str());
+    return 2;
+  }
+  const ServeArgs& a = s.args;
+  if (a.dry_run) {
+    printf("{\"model\":\"%s\",\"served_model_name\":\"%s\",\"host\":\"%s\",\"port\":%d,\"max_model_len\":%d,\"dtype\":\"%s\","
+           "\"tensor_parallel_size\":%d,\"pipeline_parallel_size\":%d,\"gpu_memory_utilization\":%.4f,\"max_num_seqs\":%d,"
+           "\"max_num_batched_tokens\":%d,\"block_size\":%d,\"enable_chunked_prefill\":%s,\"enable_prefix_caching\":%s,"
+           "\"enforce_eager\":%s,\"disable_custom_all_reduce\":%s,\"trust_remote_code\":%s,\"load_format\":\"%s\",\"seed\":%lld}\n",
+           json_escape(a.model).c_str(), json_escape(a.served_model_name).c_str(), a.host.c_str(), a.port, a.max_model_len, a.dtype.c_str(),
+           a.tensor_parallel_size, a.pipeline_parallel_size, a.gpu_memory_utilization, a.max_num_seqs, a.max_num_batched_tokens,
+           a.block_size, a.enable_chunked_prefill ? "true" : "false", a.enable_prefix_caching ? "true" : "false",
+           a.enforce_eager ? "true" : "false", a.disable_custom_all_reduce ? "true" : "false", a.trust_remote_code ? "true" : "false",
+           a.load_format.c_str(), (long long)a.seed);
+    return 0;
+  }
+  if (a.enable_prefix_caching) fprintf(stderr, "WARNING: --enable-prefix-caching accepted but prefix caching is not implemented; every prompt is computed\n");
+  if (a.dtype == "float16" || a.dtype == "half" || a.dtype == "float32")
+    fprintf(stderr, "WARNING: --dtype %s: this engine computes in bfloat16 (fp32 accumulation); checkpoints are converted at load\n", a.dtype.c_str());
+  const int sms = kge_device_sm_count();
+  if (sms <= 0) { fprintf(stderr, "error: no CUDA device visible (this engine has no CPU backend)\n"); return 1; }
+  const std::string dir = resolve_model(a.model);
+  if (dir.empty()) { fprintf(stderr, "error: model '%s' is neither a directory nor a cached HF snapshot under $HF_HOME\n", a.model.c_str()); return 1; }
+
+  // engines: one per tensor-parallel rank on devices 0..tp-1 (the pod sees exactly requestGPU devices)
+  s.engines.resize(a.tensor_parallel_size, nullptr);
+  std::vector<int> rcs(a.tensor_parallel_size, 0);
+  std::vector<std::string> errs(a.tensor_parallel_size);
+  auto create = [&](int r) {
+    kge_engine_config c{};
+    c.max_num_seqs = a.max_num_seqs; c.max_num_batched_tokens = a.max_num_batched_tokens;
+    c.max_model_len = a.max_model_len; c.block_size = a.block_size; c.num_blocks = a.num_gpu_blocks_override;
+    c.gpu_memory_utilization = (float)a.gpu_memory_utilization; c.tp_rank = r; c.tp_size = a.tensor_parallel_size;
+    c.enable_chunked_prefill = a.enable_chunked_prefill; c.device = r;
+    rcs[r] = kge_engine_create(&s.engines[r], dir.c_str(), &c, a.load_format == "dummy" ? a.seed : -1);
+    if (rcs[r]) errs[r] = kge_last_error();
+  };
+  {
+    std::vector<std::thread> th;
+    for (int r = 0; r < a.tensor_parallel_size; ++r) th.emplace_back(create, r);
+    for (auto& t : th) t.join();
+  }
+  for (int r = 0; r < a.tensor_parallel_size; ++r)
+    if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
+  if (a.tensor_parallel_size > 1) {
+    char id[128];
+    if (kge_nccl_unique_id(id)) { fprintf(stderr, "error: %s\n", kge_last_error()); return 1; }
+    std::vector<std::thread> th;
+    for (int r = 0; r < a.tensor_parallel_size; ++r)
+      th.emplace_back([&, r] { rcs[r] = kge_engine_init_tp(s.engines[r], id); if (rcs[r]) errs[r] = kge_last_error(); });
+    for (auto& t : th) t.join();
+    for (int r = 0; r < a.tensor_parallel_size; ++r)
+      if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
+  }
+  s.vocab = kge_engine_vocab(s.engines[0]);
+  if (s.args.max_model_len <= 0) s.args.max_model_len = 8192;
+  fprintf(stderr, "INFO: model %s loaded: %.2f GB weights/rank, %d KV blocks, tp=%d\n", dir.c_str(),
+          kge_engine_weight_bytes(s.engines[0]) / 1e9, kge_engine_num_blocks(s.engines[0]), a.tensor_parallel_size);
+
+  g_srv = &s;
+  signal(SIGINT, on_signal);
+  signal(SIGTERM, on_signal);
+  signal(SIGPIPE, SIG_IGN);
+  int lfd = socket(AF_INET, SOCK_STREAM, 0);
+  int one = 1;
+  setsockopt(lfd, SOL_SOCKET, SO_REUSEADDR, &one, sizeof one);
+  sockaddr_in addr{};
+  addr.sin_family = AF_INET;
+  addr.sin_port = htons((uint16_t)a.port);
+  if (inet_pton(AF_INET, a.host.c_str(), &addr.sin_addr) != 1) addr.sin_addr.s_addr = INADDR_ANY;
+  if (bind(lfd, (sockaddr*)&addr, sizeof addr) || listen(lfd, 1024)) { perror("bind/listen"); return 1; }
+  std::thread eng(engine_loop, &s);
+  fprintf(stderr, "INFO: Uvicorn-compatible server running on http://%s:%d (Press CTRL+C to quit)\n", a.host.c_str(), a.port);
+  while (!s.stop) {
+    fd_set rf;
+    FD_ZERO(&rf);
+    FD_SET(lfd, &rf);
+    timeval tv{0, 200000};
+    if (select(lfd + 1, &rf, nullptr, nullptr, &tv) <= 0) continue;
+    int fd = accept(lfd, nullptr, nullptr);
+    if (fd < 0) continue;
+    std::thread(serve_conn, &s, fd).detach();
+  }
+  s.stop = true;
+  { std::lock_guard<std::mutex> lk(s.mu); s.cv.notify_all(); }
+  eng.join();
+  ::close(lfd);
+  for (auto* e : s.engines) kge_engine_destroy(e);
+  return s.healthy ? 0 : 1;
+}

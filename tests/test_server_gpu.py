@@ -1,0 +1,140 @@
+"""The drop-in server end to end on a GPU: `vllm serve <dir>` (kge-serve), OpenAI-compatible HTTP,
+token-id prompts (no tokenizer offline), greedy ids equal to the in-process engine's."""
+import json
+import os
+import socket
+import subprocess
+import time
+import urllib.error
+import urllib.request
+
+import pytest
+
+from oracle import model as om
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+BIN = os.path.join(ROOT, "kubernetes-gpu-cluster_b200", "bin", "vllm")
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def http(port, path, body=None, timeout=60):
+    req = urllib.request.Request(f"http://127.0.0.1:{port}{path}", data=None if body is None else json.dumps(body).encode(),
+                                 headers={"Content-Type": "application/json"})
+    try:
+        with urllib.request.urlopen(req, timeout=timeout) as r:
+            return r.status, r.read().decode()
+    except urllib.error.HTTPError as e:
+        return e.code, e.read().decode()
+
+
+@pytest.fixture(scope="module")
+def server(tmp_path_factory):
+    assert os.path.exists(BIN), "build the server: make -C kubernetes-gpu-cluster_b200"
+    cfg = om.CONFIGS["tiny-llama"]
+    w = om.make_weights(cfg, seed=0)
+    d = str(tmp_path_factory.mktemp("srv-model"))
+    om.save_model_dir(d, cfg, w)
+    port = free_port()
+    proc = subprocess.Popen([BIN, "serve", d, "--host", "127.0.0.1", "--port", str(port), "--max-model-len", "256",
+                             "--max-num-seqs", "8", "--max-num-batched-tokens", "128", "--num-gpu-blocks-override", "128",
+                             "--served-model-name", "tiny", "--enforce-eager", "--trust-remote-code"],
+                            stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    t0 = time.time()
+    while True:
+        try:
+            if http(port, "/health", timeout=2)[0] == 200:
+                break
+        except Exception:
+            pass
+        assert proc.poll() is None, proc.stderr.read()[-2000:]
+        assert time.time() - t0 < 120, "server did not come up"
+        time.sleep(0.2)
+    yield port, cfg, w, d
+    proc.terminate()
+    try:
+        proc.wait(timeout=20)
+    except subprocess.TimeoutExpired:
+        proc.kill()
+
+
+def test_models_health_metrics(server):
+    port = server[0]
+    st, body = http(port, "/v1/models")
+    m = json.loads(body)
+    assert st == 200 and m["object"] == "list" and m["data"][0]["id"] == "tiny" and m["data"][0]["owned_by"] == "vllm"
+    assert m["data"][0]["max_model_len"] == 256
+    assert http(port, "/health") == (200, "")
+    st, txt = http(port, "/metrics")
+    assert st == 200 and "vllm:num_requests_running" in txt and "vllm:kv_cache_usage_perc" in txt
+    assert http(port, "/nope")[0] == 404
+
+
+def test_completions_match_in_process_engine(server, kge):
+    port, cfg, w, d = server
+    prompts = om.make_prompts(cfg, 3, 20, seed=11)
+    llm = kge.LLM(d, max_model_len=256, max_num_seqs=8, max_num_batched_tokens=128, num_gpu_blocks_override=128)
+    ref = [o.outputs[0].token_ids for o in llm.generate(prompts, kge.SamplingParams(max_tokens=10, temperature=0.0, ignore_eos=True))]
+    llm.close()
+    st, body = http(port, "/v1/completions", {"model": "tiny", "prompt": prompts, "max_tokens": 10, "temperature": 0,
+                                               "ignore_eos": True})
+    assert st == 200, body
+    r = json.loads(body)
+    assert r["object"] == "text_completion" and r["id"].startswith("cmpl-") and r["model"] == "tiny"
+    assert [c["index"] for c in r["choices"]] == [0, 1, 2]
+    assert [c["token_ids"] for c in r["choices"]] == ref
+    assert all(c["finish_reason"] == "length" for c in r["choices"])
+    assert r["usage"] == {"prompt_tokens": 60, "total_tokens": 90, "completion_tokens": 30}
+    # single [int] prompt + stop_token_ids
+    st, body = http(port, "/v1/completions", {"prompt": prompts[0], "max_tokens": 10, "temperature": 0, "ignore_eos": True,
+                                               "stop_token_ids": [ref[0][3]]})
+    c = json.loads(body)["choices"][0]
+    first = ref[0].index(ref[0][3])
+    assert c["finish_reason"] == "stop" and c["token_ids"] == ref[0][:first + 1]
+
+
+def test_streaming_sse(server, kge):
+    port, cfg, w, d = server
+    prompt = om.make_prompts(cfg, 1, 12, seed=5)[0]
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions",
+                                 data=json.dumps({"prompt": prompt, "max_tokens": 6, "temperature": 0, "ignore_eos": True,
+                                                  "stream": True, "stream_options": {"include_usage": True}}).encode(),
+                                 headers={"Content-Type": "application/json"})
+    with urllib.request.urlopen(req, timeout=60) as r:
+        assert r.headers["Content-Type"].startswith("text/event-stream")
+        raw = r.read().decode()
+    events = [e for e in raw.split("\n\n") if e.strip()]
+    assert all(e.startswith("data: ") for e in events) and events[-1] == "data: [DONE]"
+    chunks = [json.loads(e[6:]) for e in events[:-1]]
+    toks = [t for c in chunks if c["choices"] for t in c["choices"][0]["token_ids"]]
+    assert len(toks) == 6
+    assert chunks[-2]["choices"][0]["finish_reason"] == "length"
+    assert chunks[-1]["choices"] == [] and chunks[-1]["usage"]["completion_tokens"] == 6
+    st, body = http(port, "/v1/completions", {"prompt": prompt, "max_tokens": 6, "temperature": 0, "ignore_eos": True})
+    assert json.loads(body)["choices"][0]["token_ids"] == toks
+
+
+def test_errors_use_the_openai_error_shape(server):
+    port = server[0]
+    st, body = http(port, "/v1/completions", {"prompt": "hello", "max_tokens": 4})
+    e = json.loads(body)["error"]
+    assert st == 400 and e["code"] == 400 and "tokenizer" in e["message"] and e["type"] == "BadRequestError"
+    st, body = http(port, "/v1/completions", {"model": "other", "prompt": [5, 6], "max_tokens": 4})
+    assert st == 404 and "does not exist" in json.loads(body)["error"]["message"]
+    st, body = http(port, "/v1/completions", {"prompt": [5, 10 ** 7]})
+    assert st == 400 and "out of vocabulary" in body
+    st, body = http(port, "/v1/completions", {"prompt": list(range(3, 300)), "max_tokens": 4})
+    assert st == 400 and "max_model_len" in body
+    st, body = http(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "hi"}]})
+    assert st == 400 and "chat template" in body
+    st, body = http(port, "/v1/chat/completions", {"prompt_token_ids": [5, 6, 7], "max_tokens": 3, "temperature": 0})
+    r = json.loads(body)
+    assert st == 200 and r["object"] == "chat.completion" and r["choices"][0]["message"]["role"] == "assistant"
+    assert len(r["choices"][0]["token_ids"]) >= 1

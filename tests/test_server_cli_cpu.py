@@ -63,3 +63,27 @@ def test_bad_command_lines():
     assert dry("serve", "m", "--gpu-memory-utilization", "1.5")[0] == 2
     rc, out = dry("m", "--served-model-name", "alias", "--load-format", "dummy", "--seed", "7", "--max-num-seqs", "64")
     assert rc == 0 and out["served_model_name"] == "alias" and out["load_format"] == "dummy" and out["seed"] == 7
+
+
+def test_deploy_values_keep_gpu_count_and_tp_consistent():
+    """deploy/values-kge-*.yaml: same schema as the reference's values files (one modelSpec each),
+    requestGPU == --tensor-parallel-size, and the flags they pass parse."""
+    import glob
+
+    import yaml
+    files = sorted(glob.glob(os.path.join(ROOT, "deploy", "values-kge-*.yaml")))
+    assert len(files) >= 3
+    for f in files:
+        spec = yaml.safe_load(open(f))["servingEngineSpec"]
+        assert len(spec["modelSpec"]) == 1
+        m = spec["modelSpec"][0]
+        vc = m.get("vllmConfig", {})
+        argv = ["serve", m["modelURL"], "--host", "0.0.0.0", "--port", "8000"]
+        if "maxModelLen" in vc:
+            argv += ["--max-model-len", str(vc["maxModelLen"])]
+        if "gpuMemoryUtilization" in vc:
+            argv += ["--gpu-memory-utilization", str(vc["gpuMemoryUtilization"])]
+        argv += [str(a) for a in vc.get("extraArgs", [])]
+        rc, out = dry(*argv)
+        assert rc == 0, (f, out)
+        assert out["tensor_parallel_size"] == m["requestGPU"], f

@@ -104,6 +104,27 @@ class ClockSampler(threading.Thread):
                 "samples": len(sm)}
 
 
+def max_over_ranks(x, world, device="cuda"):
+    """Timing of a multi-rank run = the slowest rank's (all_reduce MAX); identity at world 1."""
+    if world == 1:
+        return x
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor([x], dtype=torch.float64, device=device)
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    return t.item()
+
+
+def job_throughput(replicas, B, pout, seconds):
+    """Whole-job output tokens/s: every replica decodes B*pout tokens in the (max-over-ranks) time."""
+    return replicas * B * pout / seconds
+
+
+def rank_prompts(vocab, B, pin, rank, tp):
+    """Replicas serve different requests (seed = rank); the ranks of one TP group serve the same ones."""
+    return make_prompts(vocab, B, pin, seed=0 if tp > 1 else rank)
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -180,7 +201,7 @@ def run_ours(args):
     vocab = hf["vocab_size"]
     tp = world if args.workload == "c4" else 1      # c4: ONE model sharded over all ranks; else replicas
     replicas = 1 if tp > 1 else world
-    prompts = make_prompts(vocab, B, pin, seed=0 if tp > 1 else rank)
+    prompts = rank_prompts(vocab, B, pin, rank, tp)
     bs = 16
     nblk = B * ((pin + pout + bs - 1) // bs) + 2
     with tempfile.TemporaryDirectory() as d:
@@ -203,12 +224,8 @@ def run_ours(args):
         if world > 1:
             dist.barrier()
 
-    def max_over_ranks(x):
-        if world == 1:
-            return x
-        t = torch.tensor([x], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        return t.item()
+    def mx(x):
+        return max_over_ranks(x, world)
 
     # ---- value: device-resident replay
     for _ in range(args.warmup):
@@ -227,9 +244,9 @@ def run_ours(args):
     wall_resident = time.perf_counter() - t_wall0
     launches = llm.kernel_launches - l0
     clk = clocks.summary()
-    ms_step = max_over_ranks(ms_total / args.steps)
-    dec_ms_step = max_over_ranks(dec_total / args.steps)
-    value = replicas * B * pout / (ms_step * 1e-3)
+    ms_step = mx(ms_total / args.steps)
+    dec_ms_step = mx(dec_total / args.steps)
+    value = job_throughput(replicas, B, pout, ms_step * 1e-3)
 
     # ---- e2e: public API with host buffers, scheduler-driven, per-step H2D/D2H inside the timing
     for _ in range(min(args.warmup, 1)):
@@ -240,9 +257,9 @@ def run_ours(args):
     for _ in range(args.steps):
         outs = llm.generate(prompts, sp)
     barrier()
-    e2e_s = max_over_ranks((time.perf_counter() - t0) / args.steps)
+    e2e_s = mx((time.perf_counter() - t0) / args.steps)
     io1 = llm.io_bytes()
-    e2e = replicas * B * pout / e2e_s
+    e2e = job_throughput(replicas, B, pout, e2e_s)
     toks_e2e = [o.outputs[0].token_ids for o in outs]
     same = sum(a == b for x, y in zip(toks_e2e, toks_res) for a, b in zip(x, y))
 

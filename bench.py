@@ -173,7 +173,7 @@ def run_reference(args):
     v = sum(vals) / len(vals)
     name, B, pin, pout, _ = WORKLOADS[args.workload]
     info["value"] = v
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": "output tokens/sec at fixed concurrency", "value": v, "unit": "output tokens/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup_ref, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
@@ -181,7 +181,7 @@ def run_reference(args):
                                f"(CPU arm runs the bounded sample named in cpu_baseline.sample)"},
         "cpu_baseline": info,
         "e2e": {"value": v, "unit": "output tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-    }))
+    })
 
 
 def run_ours(args):
@@ -308,10 +308,27 @@ def run_ours(args):
     if rank == 0:
         if world == 1 and not args.no_cpu:
             _, line["cpu_baseline"] = cpu_reference(args.workload)
-        print(json.dumps(line))
+        emit(line)
     llm.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+_REAL_STDOUT = None
+
+
+def protect_stdout():
+    """stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner,
+    torchrun notices) is sent to stderr instead; emit() writes to the saved descriptor."""
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
+
+
+def emit(line: dict):
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
 
 
 def main():
@@ -324,6 +341,7 @@ def main():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
     args.warmup_ref = min(args.warmup, 1)
+    protect_stdout()
     if args.impl == "reference":
         run_reference(args)
     else:

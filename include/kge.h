@@ -61,6 +61,14 @@ int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T
                   int act, void* workspace, int64_t workspace_bytes, void* stream);
 int64_t kge_gemm_workspace_bytes(int T, int N, int K);
 
+/* Fused SwiGLU front half: y[T,f] = silu(x * w[:f]^T) * (x * w[f:]^T) with w = [gate | up] stacked
+ * [2f, K] (vllm:model_executor/models/llama.py:94-110 gate_up_proj + activation.py:137-141), same
+ * cast points as the two separate ops (both GEMM outputs and the SiLU rounded to bf16 before the
+ * product).  One kernel: each 128-row MMA tile holds 64 gate rows and their 64 up rows, so the
+ * [T,2f] intermediate never goes to HBM.  f % 64 == 0. */
+int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
+                            void* stream);
+
 /* RoPE (neox pairing, Llama-3 scaled cache) on the q and k parts of a packed qkv buffer
  * [T,(H+2KV)*hd], in place, then scatter of k and v rows into the paged cache.
  * vllm:model_executor/layers/rotary_embedding/common.py:160-183 (each op rounds in bf16);

@@ -69,6 +69,7 @@ SIGNATURES = {
     "kge_silu_mul": (_I, [_P, _P, _I, _I, _P]),
     "kge_gemm_bf16": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _L, _P]),
     "kge_gemm_workspace_bytes": (_L, [_I, _I, _I]),
+    "kge_gemm_silu_gate_bf16": (_I, [_P, _P, _P, _I, _I, _I, _P]),
     "kge_rope_kvwrite": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "kge_rope_cache_host": (_I, [_P, _I, _I, C.c_double, C.c_double, C.c_double, C.c_double, _I]),
     "kge_paged_attn": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _L, _P]),

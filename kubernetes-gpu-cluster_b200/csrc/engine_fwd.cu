@@ -103,8 +103,14 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       LINEAR(e->h, e->attn, L.o, T, 0);
       if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
       FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
-      LINEAR(e->gu, e->xn, L.up, T, 0);
-      FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
+      if (e->ffn_loc % 64 == 0) {
+        // gate_up GEMM with the SiLU*mul in its epilogue: [T,2f] never reaches HBM
+        FWD(T <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)L.up.N * L.up.K + (double)T * (L.up.K + e->ffn_loc)),
+            2.0 * T * (double)L.up.N * L.up.K, kge_gemm_silu_gate_bf16(e->act, e->xn, L.up.w, T, e->ffn_loc, L.up.K, st));
+      } else {
+        LINEAR(e->gu, e->xn, L.up, T, 0);
+        FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
+      }
       LINEAR(e->h, e->act, L.down, T, 0);
       if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
     }

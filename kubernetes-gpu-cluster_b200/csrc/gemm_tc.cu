@@ -105,7 +105,16 @@ __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
 // exchange buffer of the split variant: [src rank][local column][128 rows] fp32
 __host__ __device__ constexpr int xbuf_bytes(int tokn) { return (tokn + 8) * BLK_M * 4; }
 
-template <int TOKN, int STAGES, bool SPLIT>
+// GATED: the 128 MMA rows of a tile are 64 gate rows (TMEM lanes 0-63) and the matching 64 up rows
+// (lanes 64-127) of a stacked [2f, K] weight; the epilogue emits silu(gate) * up for the 64
+// outputs with vLLM's cast points (vllm:model_executor/layers/activation.py:137-141).
+__device__ __forceinline__ float silu_gate_bf16(float g_acc, float u_acc) {
+  const float g = rbf(g_acc), u = rbf(u_acc);            // the gate_up GEMM output is bf16
+  const float sg = rbf(__fdividef(g, 1.0f + __expf(-g))); // F.silu rounds to bf16 (fast exp/div: <= 2 ulp in fp32)
+  return sg * u;                                          // caller rounds the product once
+}
+
+template <int TOKN, int STAGES, bool SPLIT, bool GATED>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
@@ -120,7 +129,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   // bars: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
   uint32_t* colmap = tmem_slot + 2;                      // [TOKN] remote address of each column's slot (SPLIT)
-  float* xbuf = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 2048);   // SPLIT only
+  float* xbuf = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 2048);   // SPLIT: exchange buffer;
+                                                                                // GATED && !SPLIT: up->gate hand-off [2][16][64]
+  constexpr int ROWS_OUT = GATED ? 64 : BLK_M;           // output columns produced per tile
   const uint32_t smem_base = smem_addr(smem);
   const uint32_t bar_base = smem_addr(bars);
   auto full_bar = [&](int s) { return bar_base + 8u * s; };
@@ -167,7 +178,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
           mbar_wait(empty_bar(stage), phase ^ 1);
           const uint32_t a_dst = smem_base + stage * STAGE_BYTES, b_dst = a_dst + A_BYTES;
           mbar_expect_tx(full_bar(stage), STAGE_BYTES);
-          tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * BLK_M);
+          if (GATED) {
+            tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * 64);                     // gate rows
+            tma_load_2d(a_dst + 64 * BLK_K * 2, &tmap_w, full_bar(stage), kb * BLK_K, p.N + m_tile * 64);  // up rows
+          } else {
+            tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * BLK_M);
+          }
           tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -212,13 +228,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     }
     for (int w = w_first; w < total; w += w_step) {
       const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
-      const int n = m_tile * BLK_M + et;         // weight row == output column
+      const int n = m_tile * ROWS_OUT + (GATED ? (et & 63) : et);   // output column of this thread's row
       const int t0 = n_tile * TOKN;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
       const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
-      if (!SPLIT) {
+      if (!SPLIT && !GATED) {
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
           uint32_t r[16];
@@ -238,6 +254,40 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(tempty_bar(acc));
+      } else if (!SPLIT) {
+        // Gate rows live in warps q=0,1 and their up rows in warps q=2,3 (TMEM lane quarters), so each
+        // pair swaps half of every 16-column chunk through shared memory: the gate warp finishes
+        // columns 0-7, the up warp columns 8-15.  Double-buffered, one 64-thread named barrier per chunk.
+        const int pair = q & 1, r64 = et & 63;
+        const int bar_id = 2 + pair;
+        const bool is_up = q >= 2;
+#pragma unroll 1
+        for (int c = 0; c < TOKN; c += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + c, r);
+          float* hb = xbuf + ((c >> 4) & 1) * (2 * 8 * 64);     // [0]: up cols 0-7, [1]: gate cols 8-15
+          if (is_up) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hb[j * 64 + r64] = __uint_as_float(r[j]);
+          } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) hb[(8 + j) * 64 + r64] = __uint_as_float(r[8 + j]);
+          }
+          asm volatile("bar.sync %0, 64;" ::"r"(bar_id) : "memory");
+          if (n < p.N) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+              const int col = is_up ? 8 + j : j;
+              const int t = t0 + c + col;
+              const float gacc = is_up ? hb[(8 + j) * 64 + r64] : __uint_as_float(r[j]);
+              const float uacc = is_up ? __uint_as_float(r[8 + j]) : hb[j * 64 + r64];
+              if (t < p.T) p.y[(int64_t)t * p.N + n] = f2bf(silu_gate_bf16(gacc, uacc));
+            }
+          }
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));
       } else {
         cluster_wait();                          // phase A done: peers' shared memory is live
 #pragma unroll 1
@@ -251,14 +301,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         cluster_arrive();                        // phase B: my partials are in the owners' buffers
         cluster_wait();
         const int c_begin = crank * cols_per, c_end = min(TOKN, c_begin + cols_per);
-        if (n < p.N) {
+        if (n < p.N && (!GATED || et < 64)) {
           for (int c = c_begin; c < c_end; ++c) {
             const int t = t0 + c;
             if (t >= p.T) break;
-            float v = 0.f;
-            for (int s2 = 0; s2 < S; ++s2) v += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et];
-            v += bv;
-            if (p.act == 1) v = fmaxf(v, 0.f);
+            float v = 0.f, u = 0.f;
+            for (int s2 = 0; s2 < S; ++s2) {
+              v += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et];
+              if (GATED) u += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et + 64];
+            }
+            if (GATED) {
+              v = silu_gate_bf16(v, u);
+            } else {
+              v += bv;
+              if (p.act == 1) v = fmaxf(v, 0.f);
+            }
             p.y[(int64_t)t * p.N + n] = f2bf(v);
           }
         }
@@ -311,15 +368,16 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
   return 0;
 }
 
-template <int TOKN, bool SPLIT>
+template <int TOKN, bool SPLIT, bool GATED>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
-  constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : 0);     // barriers + column map (+ exchange buffer)
+  // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
+  constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
   constexpr int budget = 224 * 1024 - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -346,7 +404,7 @@ static int query_max_clusters(int S) {
   constexpr int budget = 224 * 1024 - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   constexpr int smem = STAGES * stage_bytes + 1024 + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, true>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, true, false>;   // the gated variant has the same footprint
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(S * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem;
@@ -375,10 +433,10 @@ static int max_clusters(int tokn, int S) {
 
 struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; };
 
-static GemmPlan plan_gemm(int T, int N, int K) {
+static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
   GemmPlan g;
   g.tokn = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
-  g.m_tiles = (N + BLK_M - 1) / BLK_M;
+  g.m_tiles = (N + rows_out - 1) / rows_out;
   g.n_tiles = (T + g.tokn - 1) / g.tokn;
   g.kb_total = (K + BLK_K - 1) / BLK_K;
   const int tiles = g.m_tiles * g.n_tiles;
@@ -394,6 +452,25 @@ static GemmPlan plan_gemm(int T, int N, int K) {
   g.kb_per_split = (g.kb_total + splits - 1) / splits;
   g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;   // drop empty splits
   return g;
+}
+
+template <bool GATED>
+static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  if (g.splits > 1) {
+    switch (g.tokn) {
+      case 16: return launch_gemm<16, true, GATED>(tw, tx, p, st);
+      case 32: return launch_gemm<32, true, GATED>(tw, tx, p, st);
+      case 64: return launch_gemm<64, true, GATED>(tw, tx, p, st);
+      default: return launch_gemm<128, true, GATED>(tw, tx, p, st);
+    }
+  }
+  switch (g.tokn) {
+    case 16: return launch_gemm<16, false, GATED>(tw, tx, p, st);
+    case 32: return launch_gemm<32, false, GATED>(tw, tx, p, st);
+    case 64: return launch_gemm<64, false, GATED>(tw, tx, p, st);
+    case 128: return launch_gemm<128, false, GATED>(tw, tx, p, st);
+    default: return launch_gemm<256, false, GATED>(tw, tx, p, st);
+  }
 }
 
 }  // namespace kge
@@ -422,19 +499,23 @@ extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* 
   if (int rc = make_tmap(&tw, w, N, K, BLK_M)) return rc;
   if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
-  if (g.splits > 1) {
-    switch (g.tokn) {
-      case 16: return launch_gemm<16, true>(tw, tx, p, st);
-      case 32: return launch_gemm<32, true>(tw, tx, p, st);
-      case 64: return launch_gemm<64, true>(tw, tx, p, st);
-      default: return launch_gemm<128, true>(tw, tx, p, st);
-    }
-  }
-  switch (g.tokn) {
-    case 16: return launch_gemm<16, false>(tw, tx, p, st);
-    case 32: return launch_gemm<32, false>(tw, tx, p, st);
-    case 64: return launch_gemm<64, false>(tw, tx, p, st);
-    case 128: return launch_gemm<128, false>(tw, tx, p, st);
-    default: return launch_gemm<256, false>(tw, tx, p, st);
-  }
+  return dispatch_gemm<false>(g, tw, tx, p, st);
+}
+
+extern "C" int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
+                                       void* stream) {
+  KGE_REQUIRE(y && x && w_gate_up, "kge_gemm_silu_gate_bf16: null pointer");
+  KGE_REQUIRE(T >= 0 && f > 0 && K > 0 && K % 8 == 0, "kge_gemm_silu_gate_bf16: K=%d must be a positive multiple of 8", K);
+  KGE_REQUIRE(f % 64 == 0, "kge_gemm_silu_gate_bf16: f=%d must be a multiple of 64", f);
+  KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_gate_up & 15) == 0, "kge_gemm_silu_gate_bf16: x and w must be 16-byte aligned");
+  if (T == 0) return 0;
+  const GemmPlan g = plan_gemm(T, f, K, 64);
+  GemmParams p;
+  p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
+  p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
+  p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
+  CUtensorMap tw, tx;
+  if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, 64)) return rc;     // 64-row boxes: gate half, up half
+  if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
+  return dispatch_gemm<true>(g, tw, tx, p, (cudaStream_t)stream);
 }

@@ -269,6 +269,32 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
         assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 3e-3
 
 
+@pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048),
+                                   (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024)])
+def test_gemm_silu_gate_fused(kge, L, T, f, K):
+    """Fused gate_up GEMM + SiLU*mul against the oracle's two ops (F.linear then silu_and_mul), incl.
+    cluster split-K shapes (f/64 tiles <= 74) and 256-token tiles."""
+    g = torch.Generator().manual_seed(T + f + K)
+    x = torch.randn(T, K, generator=g).to(BF)
+    w = (torch.randn(2 * f, K, generator=g) * (2.0 / K ** 0.5)).to(BF)
+    xd, wd = dev(x), dev(w)
+    y = torch.full((T, f), float("nan"), dtype=BF, device="cuda")
+    for _ in range(2):
+        y.fill_(float("nan"))
+        check_ok(kge, L.kge_gemm_silu_gate_bf16(p(y), p(xd), p(wd), T, f, K, None), "gemm_silu_gate")
+        sync()
+        gu = torch.nn.functional.linear(x.float(), w.float()).to(BF)       # bf16 GEMM output, fp32 accumulate
+        ref = om.silu_and_mul(gu).float()
+        got = y.cpu().float()
+        assert torch.isfinite(got).all()
+        scale = ref.abs().max().item()
+        err = (got - ref).abs()
+        tol = 2e-3 * scale + 2.5e-2 * ref.abs()      # two bf16-rounded GEMM outputs feed a product
+        assert (err <= tol).all(), f"max err {err.max().item():.4g} (scale {scale:.3g})"
+        assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 4e-3
+    assert L.kge_gemm_silu_gate_bf16(p(y), p(xd), p(wd), T, f + 8, K, None) == -1      # f % 64
+
+
 def test_gemm_rejects_bad_arguments(kge, L):
     x = torch.zeros(4, 64, dtype=BF, device="cuda")
     assert L.kge_gemm_bf16(p(x), p(x), p(x), None, 4, 4, 60, 0, None, 0, None) == -1       # K % 8

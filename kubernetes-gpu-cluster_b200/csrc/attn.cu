@@ -7,6 +7,8 @@
 //   attn_decode_kernel   pure decode steps; split-KV across CTAs, warps split the keys of a tile;
 //                        partial (m, l, O) go to workspace and attn_merge_kernel combines them.
 // HBM-bound at decode: algorithmic bytes = sum_b ctx_b * KV * hd * 2 (K) * 2 (V) * 2 B per layer.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "kge.h"
 
@@ -467,6 +469,10 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
   return 0;
 }
 
+int paged_attn_prefill_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc, const bf16* vc, const int32_t* bt,
+                          int max_blocks, const int32_t* sl, const int32_t* qsl, int B, int max_q_len, int H, int KV,
+                          int hd, int bs, float scale, cudaStream_t st);   // attn_tc.cu
+
 }  // namespace kge
 
 using namespace kge;
@@ -489,6 +495,11 @@ extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void
   if (B <= 0 || T <= 0) return 0;
   KGE_REQUIRE(max_q_len >= 1 && max_seq_len >= 1, "kge_paged_attn: max_q_len/max_seq_len must be >= 1");
   cudaStream_t st = (cudaStream_t)stream;
+  KGE_REQUIRE(hd == 64 || hd == 128, "kge_paged_attn: head_dim=%d unsupported (64, 128)", hd);
+  static const bool legacy = getenv("KGE_ATTN_LEGACY") != nullptr;     // A/B switch during bring-up
+  if (!(max_q_len == 1 && H / KV <= 16) && !legacy)
+    return paged_attn_prefill_tc((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, block_table,
+                                 max_blocks_per_seq, seq_lens, query_start_loc, B, max_q_len, H, KV, hd, block_size, scale, st);
   if (hd == 64)
     return launch_attn<64>((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache,
                            block_table, max_blocks_per_seq, seq_lens, query_start_loc, B, max_q_len,

@@ -84,9 +84,33 @@ def bench_attn(cases):
                           "GB/s": round(bytes_ / ms / 1e6, 1)}), flush=True)
 
 
+def bench_prefill(cases):
+    for (B, qlen, H, KV, hd) in cases:
+        bs = 16
+        nb_seq = (qlen + bs - 1) // bs
+        nblk = B * nb_seq + 1
+        kc = torch.randn(nblk, KV, bs, hd, device="cuda", dtype=BF)
+        vc = torch.randn(nblk, KV, bs, hd, device="cuda", dtype=BF)
+        bt = (torch.arange(B * nb_seq, dtype=torch.int32).view(B, nb_seq) + 1).cuda()
+        sl = torch.full((B,), qlen, dtype=torch.int32, device="cuda")
+        qsl = (torch.arange(B + 1, dtype=torch.int32) * qlen).cuda()
+        qw = (H + 2 * KV) * hd
+        q = torch.randn(B * qlen, qw, device="cuda", dtype=BF)
+        out = torch.empty(B * qlen, H * hd, device="cuda", dtype=BF)
+
+        def run(i):
+            kge.check(L.kge_paged_attn(out.data_ptr(), q.data_ptr(), qw, kc.data_ptr(), vc.data_ptr(), bt.data_ptr(), nb_seq,
+                                       sl.data_ptr(), qsl.data_ptr(), B, B * qlen, qlen, qlen, H, KV, hd, bs, hd ** -0.5,
+                                       None, 0, None), "attn")
+        ms = time_ms(run, 10)
+        flops = 4.0 * H * hd * B * qlen * (qlen + 1) / 2
+        print(json.dumps({"prefill B": B, "q_len": qlen, "H": H, "KV": KV, "hd": hd, "ms": round(ms, 4),
+                          "TFLOP/s": round(flops / ms / 1e9, 1)}), flush=True)
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["gemm", "attn"])
+    ap.add_argument("what", choices=["gemm", "attn", "prefill"])
     ap.add_argument("--cublas", action="store_true")
     ap.add_argument("--only", type=int, default=-1)
     a = ap.parse_args()
@@ -98,5 +122,7 @@ if __name__ == "__main__":
         if a.only >= 0:
             shapes = [shapes[a.only]]
         bench_gemm(shapes, a.cublas)
+    elif a.what == "prefill":
+        bench_prefill([(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128), (32, 128, 32, 8, 64), (4, 2048, 12, 12, 64)])
     else:
         bench_attn([(64, 2176, 32, 8, 128), (64, 1024, 32, 8, 128), (32, 192, 32, 8, 64), (8, 8192, 32, 8, 128)])

@@ -20,7 +20,7 @@ namespace kge {
 namespace atc {
 
 constexpr int BM = 128, BNK = 128;             // query rows, keys per tile
-constexpr uint32_t kSpin = 1u << 30;
+constexpr uint32_t kSpin = 1u << 26;   // ~seconds: a lost arrival traps instead of hanging the GPU
 constexpr float kLog2e = 1.4426950408889634f;
 
 __device__ __forceinline__ uint32_t s_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -82,6 +82,25 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr) {
          ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
 
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+      "{%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15,%16,%17,%18,%19,%20,%21,%22,%23,%24,%25,%26,%27,%28,%29,%30,%31,%32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+  asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+
+// Pipeline (per 128-key tile j): the MMA thread issues S_{j+1} = Q K_{j+1}^T into the other S buffer
+// as soon as K_{j+1} has landed, so the tensor core works on it while the softmax warps turn S_j
+// into P_j; PV_j accumulates straight into the O columns of TMEM.  O is only rescaled when a row's
+// maximum grows by more than 2^8 since its reference maximum was fixed ("lazy rescale": P stays
+// <= 256, well inside bf16/fp32 range), so most tiles never touch O from the softmax side.
+constexpr float kRescaleThreshold = 8.0f;
+
 template <int HD>
 __global__ void __launch_bounds__(160, 1)
 attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
@@ -91,7 +110,8 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   constexpr int CH = HD / 8;                       // 16-byte chunks per row
   constexpr uint32_t TILE_BYTES = 128 * HD * 2;    // Q, K or V tile
   constexpr uint32_t P_BYTES = 128 * BNK * 2;
-  constexpr uint32_t TMEM_COLS = 256;              // S [0,128) + O_t [128,128+HD)
+  constexpr uint32_t TMEM_COLS = 512;              // S0 [0,128), S1 [128,256), O [256,256+HD)
+  constexpr uint32_t O_COL = 256;
   // S: M=128, N=128, both K-major.  PV: M=128, N=HD, A K-major, B MN-major (bit 16).
   constexpr uint32_t IDESC_S = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BNK >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
   constexpr uint32_t IDESC_O = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(HD >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -100,7 +120,8 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   const int G = H / KV;
   const int TT = BM / G;
   const int q0 = qsl[b], q_len = qsl[b + 1] - q0;
-  const int tok0 = blockIdx.x * TT;
+  // heaviest (latest) query tiles first: their CTAs walk the longest causal prefix
+  const int tok0 = ((int)gridDim.x - 1 - (int)blockIdx.x) * TT;
   if (tok0 >= q_len) return;
   const int seq_len = seq_lens[b];
   const int ctx0 = seq_len - q_len;
@@ -116,15 +137,21 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   const uint32_t sV = sK + 2 * TILE_BYTES;         // 2 stages
   const uint32_t sP = sV + 2 * TILE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * TILE_BYTES + P_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 8);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
   const uint32_t bar0 = s_addr(bars);
-  const uint32_t kv_full0 = bar0, kv_full1 = bar0 + 8, s_full = bar0 + 16, p_full = bar0 + 24, o_full = bar0 + 32;
+  // k_full[2], v_full[2], s_full[2], p_full, o_full
+  auto k_full = [&](int s) { return bar0 + 8u * s; };
+  auto v_full = [&](int s) { return bar0 + 16u + 8u * s; };
+  auto s_full = [&](int s) { return bar0 + 32u + 8u * s; };
+  const uint32_t p_full = bar0 + 48, o_full = bar0 + 56;
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (warp == 4) {
     if (lane == 0) {
-      mbar_init(kv_full0, 128); mbar_init(kv_full1, 128);
-      mbar_init(s_full, 1); mbar_init(p_full, 128); mbar_init(o_full, 1);
+      mbar_init(k_full(0), 128); mbar_init(k_full(1), 128);
+      mbar_init(v_full(0), 128); mbar_init(v_full(1), 128);
+      mbar_init(s_full(0), 1); mbar_init(s_full(1), 1);
+      mbar_init(p_full, 128); mbar_init(o_full, 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncwarp();
@@ -139,24 +166,32 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   if (warp == 4) {
     // ------------------------------------------------------------------ MMA issuer
     if (lane == 0) {
-      for (int j = 0; j < ntiles; ++j) {
+      auto issue_s = [&](int j) {
         const int st = j & 1;
-        mbar_wait(st ? kv_full1 : kv_full0, (uint32_t)((j >> 1) & 1));
+        mbar_wait(k_full(st), (uint32_t)((j >> 1) & 1));
         tc_after();
-        const uint32_t kt = sK + st * TILE_BYTES, vt = sV + st * TILE_BYTES;
+        const uint32_t kt = sK + st * TILE_BYTES;
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) {
           const uint32_t off = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);
-          tc_mma(tmem, desc_kmajor(sQ + off), desc_kmajor(kt + off), IDESC_S, k > 0 ? 1u : 0u);
+          tc_mma(tmem + st * 128, desc_kmajor(sQ + off), desc_kmajor(kt + off), IDESC_S, k > 0 ? 1u : 0u);
         }
-        tc_commit(s_full);
+        tc_commit(s_full(st));
+      };
+      issue_s(0);
+      for (int j = 0; j < ntiles; ++j) {
+        // S_{j+1} may overwrite S buffer (j+1)&1 = the buffer of S_{j-1}: the softmax warps finished
+        // reading it before they arrived on p_full(j-1), which this thread has already waited for
+        if (j + 1 < ntiles) issue_s(j + 1);
         mbar_wait(p_full, (uint32_t)(j & 1));
+        mbar_wait(v_full(j & 1), (uint32_t)((j >> 1) & 1));
         tc_after();
+        const uint32_t vt = sV + (j & 1) * TILE_BYTES;
 #pragma unroll
         for (int k = 0; k < BNK / 16; ++k) {
           const uint32_t aoff = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);   // P: keys are the K dimension
           const uint32_t boff = (uint32_t)(k * 16 * 128);                             // V: 16 keys = 16 rows of 128 B
-          tc_mma(tmem + 128, desc_kmajor(sP + aoff), desc_mnmajor(vt + boff), IDESC_O, k > 0 ? 1u : 0u);
+          tc_mma(tmem + O_COL, desc_kmajor(sP + aoff), desc_mnmajor(vt + boff), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(o_full);
       }
@@ -167,27 +202,29 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
     const int tk = r / G, hh = r % G;
     const bool row_ok = tk < ntok;
     const int lim = row_ok ? ctx0 + tok0 + tk : -1;          // last visible key of this row
-    // loader geometry: thread t owns chunk column t % CH of rows t / CH + i * (128 / CH)
     constexpr int RP = 128 / CH, NP = 128 / RP;
     const int lrow0 = tid / CH, lc = tid % CH;
     const int64_t head_off = ((int64_t)kvh << bs_shift) * HD;
     const int64_t blk_stride = ((int64_t)KV << bs_shift) * HD;
     const int bs_mask = (1 << bs_shift) - 1;
-    auto load_kv = [&](int j) {
-      const uint32_t kt = sK + (j & 1) * TILE_BYTES, vt = sV + (j & 1) * TILE_BYTES;
+    // cp.async groups are committed in a fixed rhythm (K two tiles ahead, V one tile ahead), so
+    // "at most 2 groups pending" always means the tile about to be published has landed
+    auto load_tile = [&](int t, bool is_k) {
+      if (t < ntiles) {
+        const uint32_t dt = (is_k ? sK : sV) + (t & 1) * TILE_BYTES;
+        const bf16* cache = is_k ? k_cache : v_cache;
 #pragma unroll
-      for (int i = 0; i < NP; ++i) {
-        const int row = lrow0 + i * RP;
-        const int key = j * BNK + row;
-        const bool ok = key < kv_len;
-        int64_t off = 0;
-        if (ok) off = (int64_t)btab[key >> bs_shift] * blk_stride + head_off + (key & bs_mask) * HD + lc * 8;
-        const uint32_t d = tile_off(row, lc);
-        cp16(kt + d, k_cache + off, ok);
-        cp16(vt + d, v_cache + off, ok);
+        for (int i = 0; i < NP; ++i) {
+          const int row = lrow0 + i * RP;
+          const int key = t * BNK + row;
+          const bool ok = key < kv_len;
+          int64_t off = 0;
+          if (ok) off = (int64_t)btab[key >> bs_shift] * blk_stride + head_off + (key & bs_mask) * HD + lc * 8;
+          cp16(dt + tile_off(row, lc), cache + off, ok);
+        }
       }
+      cp_commit();
     };
-    // Q tile
 #pragma unroll
     for (int i = 0; i < NP; ++i) {
       const int row = lrow0 + i * RP;
@@ -196,83 +233,101 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
       const bf16* src = ok ? q + (int64_t)(q0 + tok0 + t2) * q_stride + (kvh * G + h2) * HD + lc * 8 : q;
       cp16(sQ + tile_off(row, lc), src, ok);
     }
-    load_kv(0);
-    cp_commit();
+    // commit order K0 | K1 | V0 | K2 | V1 | K3 | V2 ...: whenever a tile is published, exactly two
+    // younger groups may still be in flight
+    load_tile(0, true);        // group 0: Q + K0 (what S_0 needs)
+    load_tile(1, true);        // group 1: K1
+    load_tile(0, false);       // group 2: V0
+    cp_wait<2>();              // group 0 landed
+    fence_async_smem();
+    mbar_arrive(k_full(0));
 
-    float o[HD];
-#pragma unroll
-    for (int i = 0; i < HD; ++i) o[i] = 0.f;
-    float m = -INFINITY, l = 0.f;
+    float m_ref = -INFINITY, l = 0.f;
     const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);
 
     for (int j = 0; j < ntiles; ++j) {
-      if (j + 1 < ntiles) { load_kv(j + 1); cp_commit(); cp_wait<1>(); }
-      else cp_wait<0>();
-      fence_async_smem();                 // my cp.async bytes -> visible to the tensor-core proxy
-      tc_before();                        // my TMEM reads of the previous tile are ordered before the next MMA
-      mbar_arrive((j & 1) ? kv_full1 : kv_full0);
-
-      mbar_wait(s_full, (uint32_t)(j & 1));
+      mbar_wait(s_full(j & 1), (uint32_t)((j >> 1) & 1));
       tc_after();
+      // S_j is complete, so K stage j&1 is free: fetch K_{j+2}; then publish K_{j+1} (two groups back)
+      load_tile(j + 2, true);
+      if (j + 1 < ntiles) { cp_wait<2>(); fence_async_smem(); mbar_arrive(k_full((j + 1) & 1)); }
       const int kbase = j * BNK;
-      // pass 1: row maximum of the masked, scaled scores
-      float mx = m;
-#pragma unroll 1
-      for (int c = 0; c < BNK; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(t_row + c, v);
+      uint32_t sv[128];
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (kbase + c + i <= lim) mx = fmaxf(mx, __uint_as_float(v[i]) * scale_log2);
+      for (int c = 0; c < BNK; c += 32) tmem_ld32(t_row + (j & 1) * 128 + c, *reinterpret_cast<uint32_t(*)[32]>(&sv[c]));
+      float mx = -INFINITY;
+#pragma unroll
+      for (int i = 0; i < BNK; ++i) {
+        const float x = (kbase + i <= lim) ? __uint_as_float(sv[i]) * scale_log2 : -INFINITY;
+        sv[i] = __float_as_uint(x);
+        mx = fmaxf(mx, x);
       }
-      const float base = (mx == -INFINITY) ? 0.f : mx;
-      const float alpha = exp2f(m - base);
-      m = mx;
-      // pass 2: P = exp2(s - max) as bf16 into the A-operand tile, row sum
-      float rs = 0.f;
+      // PV_{j-1} must be done before O is rescaled, sP is overwritten or V stage (j+1)&1 is refilled
+      if (j > 0) { mbar_wait(o_full, (uint32_t)((j - 1) & 1)); tc_after(); }
+      load_tile(j + 1, false);
+      const bool grow = mx > m_ref + kRescaleThreshold;        // includes the first finite maximum
+      if (__any_sync(0xffffffffu, grow)) {
+        float alpha = 1.f;
+        if (grow) {
+          alpha = (m_ref == -INFINITY) ? 0.f : exp2f(m_ref - mx);
+          m_ref = mx;
+          l *= alpha;
+        }
+        if (j > 0) {
 #pragma unroll 1
-      for (int c = 0; c < BNK; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(t_row + c, v);
+          for (int c = 0; c < HD; c += 32) {
+            uint32_t v[32];
+            tmem_ld32(t_row + O_COL + c, v);
 #pragma unroll
-        for (int g8 = 0; g8 < 4; ++g8) {
-          uint32_t pk[4];
-#pragma unroll
-          for (int i = 0; i < 4; ++i) {
-            const int c0 = c + g8 * 8 + i * 2;
-            const float p0 = (kbase + c0 <= lim) ? exp2f(__uint_as_float(v[g8 * 8 + i * 2]) * scale_log2 - base) : 0.f;
-            const float p1 = (kbase + c0 + 1 <= lim) ? exp2f(__uint_as_float(v[g8 * 8 + i * 2 + 1]) * scale_log2 - base) : 0.f;
-            rs += p0 + p1;
-            pk[i] = pack_bf2(p0, p1);
+            for (int i = 0; i < 32; ++i) v[i] = __float_as_uint(__uint_as_float(v[i]) * alpha);
+            tmem_st32(t_row + O_COL + c, v);
           }
-          const uint32_t dst = sP + tile_off(r, (c >> 3) + g8);
-          asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
         }
       }
-      l = l * alpha + rs;
-      fence_async_smem();                 // P bytes -> tensor-core proxy
-      tc_before();
-      mbar_arrive(p_full);
-
-      mbar_wait(o_full, (uint32_t)(j & 1));
-      tc_after();
+      const float base = (m_ref == -INFINITY) ? 0.f : m_ref;
+      float rs = 0.f;
 #pragma unroll
+      for (int c8 = 0; c8 < BNK / 8; ++c8) {
+        uint32_t pk[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+          const float p0 = exp2f(__uint_as_float(sv[c8 * 8 + i * 2]) - base);        // masked entries are -inf -> 0
+          const float p1 = exp2f(__uint_as_float(sv[c8 * 8 + i * 2 + 1]) - base);
+          rs += p0 + p1;
+          pk[i] = pack_bf2(p0, p1);
+        }
+        const uint32_t dst = sP + tile_off(r, c8);
+        asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
+      }
+      l += rs;
+      cp_wait<2>();                       // V_j (committed one tile ago) has landed
+      fence_async_smem();                 // P and V_j bytes -> tensor-core proxy
+      tc_before();                        // my TMEM reads/writes are ordered before the MMAs that follow
+      mbar_arrive(v_full(j & 1));
+      mbar_arrive(p_full);
+    }
+    cp_wait<0>();
+    mbar_wait(o_full, (uint32_t)((ntiles - 1) & 1));
+    tc_after();
+    {
+      // tcgen05.ld is warp-collective (.sync.aligned): every lane loads, only rows with a token store
+      const float inv = l > 0.f ? 1.f / l : 0.f;
+      bf16* dst = out + (int64_t)(q0 + tok0 + (row_ok ? tk : 0)) * H * HD + (kvh * G + hh) * HD;
+#pragma unroll 1
       for (int c = 0; c < HD; c += 32) {
         uint32_t v[32];
-        tmem_ld32(t_row + 128 + c, v);
+        tmem_ld32(t_row + O_COL + c, v);
+        if (row_ok) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i) o[c + i] = o[c + i] * alpha + __uint_as_float(v[i]);
-      }
-    }
-    if (row_ok) {
-      const float inv = l > 0.f ? 1.f / l : 0.f;
-      bf16* dst = out + (int64_t)(q0 + tok0 + tk) * H * HD + (kvh * G + hh) * HD;
-#pragma unroll
-      for (int c = 0; c < HD; c += 8) {
-        uint4 w;
-        w.x = pack_bf2(o[c] * inv, o[c + 1] * inv); w.y = pack_bf2(o[c + 2] * inv, o[c + 3] * inv);
-        w.z = pack_bf2(o[c + 4] * inv, o[c + 5] * inv); w.w = pack_bf2(o[c + 6] * inv, o[c + 7] * inv);
-        *reinterpret_cast<uint4*>(dst + c) = w;
+          for (int i = 0; i < 32; i += 8) {
+            uint4 w;
+            w.x = pack_bf2(__uint_as_float(v[i]) * inv, __uint_as_float(v[i + 1]) * inv);
+            w.y = pack_bf2(__uint_as_float(v[i + 2]) * inv, __uint_as_float(v[i + 3]) * inv);
+            w.z = pack_bf2(__uint_as_float(v[i + 4]) * inv, __uint_as_float(v[i + 5]) * inv);
+            w.w = pack_bf2(__uint_as_float(v[i + 6]) * inv, __uint_as_float(v[i + 7]) * inv);
+            *reinterpret_cast<uint4*>(dst + c + i) = w;
+          }
+        }
       }
     }
   }

@@ -1,8 +1,8 @@
 // Prefill / mixed-batch paged attention on the 5th-gen tensor cores.
 //
 // One CTA = 128 query rows ((token, q-head-in-group) pairs of one kv head of one request) x the
-// causal prefix of that request, walked in 128-key tiles:
-//   S  = Q K^T      tcgen05.mma, A = Q tile, B = K tile (both K-major, 128B swizzle), D in TMEM [0,128)
+// causal prefix of that request, walked in 64-key tiles (two CTAs per SM):
+//   S  = Q K^T      tcgen05.mma, A = Q tile, B = K tile (both K-major, 128B swizzle), D in TMEM (2 buffers)
 //   P  = softmax    4 warps, ONE THREAD PER ROW: tcgen05.ld its S row, scale + causal mask + running
 //                   max/sum in fp32 (no shuffles), bf16 P written straight into the swizzled A-operand
 //                   layout in shared memory
@@ -19,7 +19,7 @@ namespace kge {
 
 namespace atc {
 
-constexpr int BM = 128, BNK = 128;             // query rows, keys per tile
+constexpr int BM = 128, BNK = 64;              // query rows, keys per tile (64: two CTAs fit one SM)
 constexpr uint32_t kSpin = 1u << 26;   // ~seconds: a lost arrival traps instead of hanging the GPU
 constexpr float kLog2e = 1.4426950408889634f;
 
@@ -68,17 +68,18 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
 
 // shared-memory operand tiles: [64-element column half][rows][128 B], 16-byte chunks XOR-swizzled by
 // row % 8 (SWIZZLE_128B); `rows` = 128 for every tile here
+template <int ROWS>
 __device__ __forceinline__ uint32_t tile_off(int row, int chunk /* 16-byte chunk of the full row */) {
-  return (uint32_t)((chunk >> 3) * (128 * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
+  return (uint32_t)((chunk >> 3) * (ROWS * 128) + row * 128 + (((chunk & 7) ^ (row & 7)) << 4));
 }
 // K-major operand (A, or B = K tile): rows of 128 B, 8-row atoms 1024 B apart
 __device__ __forceinline__ uint64_t desc_kmajor(uint32_t saddr) {
   return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(1024 >> 4) << 32) | ((uint64_t)1 << 46) |
          ((uint64_t)2 << 61);
 }
-// MN-major B operand (V tile [key][hd]): 64-wide hd halves 16 KB apart (LBO), 8-key atoms 1024 B apart (SBO)
+// MN-major B operand (V tile [key][hd]): 64-wide hd halves BNK*128 B apart (LBO), 8-key atoms 1024 B apart (SBO)
 __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t saddr) {
-  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((128 * 128) >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+  return (uint64_t)((saddr & 0x3FFFFu) >> 4) | ((uint64_t)((BNK * 128) >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
          ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
 }
 
@@ -102,16 +103,17 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
 constexpr float kRescaleThreshold = 8.0f;
 
 template <int HD>
-__global__ void __launch_bounds__(160, 1)
+__global__ void __launch_bounds__(160, 2)
 attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
                const bf16* __restrict__ v_cache, const int32_t* __restrict__ block_table, int max_blocks,
                const int32_t* __restrict__ seq_lens, const int32_t* __restrict__ qsl, int H, int KV, int bs_shift,
                float scale_log2) {
   constexpr int CH = HD / 8;                       // 16-byte chunks per row
-  constexpr uint32_t TILE_BYTES = 128 * HD * 2;    // Q, K or V tile
+  constexpr uint32_t Q_BYTES = 128 * HD * 2;
+  constexpr uint32_t TILE_BYTES = BNK * HD * 2;    // K or V tile
   constexpr uint32_t P_BYTES = 128 * BNK * 2;
-  constexpr uint32_t TMEM_COLS = 512;              // S0 [0,128), S1 [128,256), O [256,256+HD)
-  constexpr uint32_t O_COL = 256;
+  constexpr uint32_t TMEM_COLS = 256;              // S0 [0,64), S1 [64,128), O [128,128+HD)
+  constexpr uint32_t O_COL = 128;
   // S: M=128, N=128, both K-major.  PV: M=128, N=HD, A K-major, B MN-major (bit 16).
   constexpr uint32_t IDESC_S = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BNK >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
   constexpr uint32_t IDESC_O = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(HD >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
@@ -131,12 +133,13 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   const int32_t* btab = block_table + (int64_t)b * max_blocks;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem = smem_raw;                        // no static shared memory: the dynamic window starts 1024-aligned
+  if ((s_addr(smem) & 1023u) != 0) __trap();
   const uint32_t sQ = s_addr(smem);
-  const uint32_t sK = sQ + TILE_BYTES;             // 2 stages
+  const uint32_t sK = sQ + Q_BYTES;                // 2 stages
   const uint32_t sV = sK + 2 * TILE_BYTES;         // 2 stages
   const uint32_t sP = sV + 2 * TILE_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 5 * TILE_BYTES + P_BYTES);
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Q_BYTES + 4 * TILE_BYTES + P_BYTES);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
   const uint32_t bar0 = s_addr(bars);
   // k_full[2], v_full[2], s_full[2], p_full, o_full
@@ -173,8 +176,9 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         const uint32_t kt = sK + st * TILE_BYTES;
 #pragma unroll
         for (int k = 0; k < HD / 16; ++k) {
-          const uint32_t off = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);
-          tc_mma(tmem + st * 128, desc_kmajor(sQ + off), desc_kmajor(kt + off), IDESC_S, k > 0 ? 1u : 0u);
+          const uint32_t qoff = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);
+          const uint32_t koff = (uint32_t)((k >> 2) * (BNK * 128) + (k & 3) * 32);
+          tc_mma(tmem + st * BNK, desc_kmajor(sQ + qoff), desc_kmajor(kt + koff), IDESC_S, k > 0 ? 1u : 0u);
         }
         tc_commit(s_full(st));
       };
@@ -189,7 +193,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         const uint32_t vt = sV + (j & 1) * TILE_BYTES;
 #pragma unroll
         for (int k = 0; k < BNK / 16; ++k) {
-          const uint32_t aoff = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);   // P: keys are the K dimension
+          const uint32_t aoff = (uint32_t)((k >> 2) * (128 * 128) + (k & 3) * 32);   // P: keys are the K dimension (one 64-key half)
           const uint32_t boff = (uint32_t)(k * 16 * 128);                             // V: 16 keys = 16 rows of 128 B
           tc_mma(tmem + O_COL, desc_kmajor(sP + aoff), desc_mnmajor(vt + boff), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
         }
@@ -202,7 +206,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
     const int tk = r / G, hh = r % G;
     const bool row_ok = tk < ntok;
     const int lim = row_ok ? ctx0 + tok0 + tk : -1;          // last visible key of this row
-    constexpr int RP = 128 / CH, NP = 128 / RP;
+    constexpr int RP = 128 / CH, NP = BNK / RP, NPQ = 128 / RP;
     const int lrow0 = tid / CH, lc = tid % CH;
     const int64_t head_off = ((int64_t)kvh << bs_shift) * HD;
     const int64_t blk_stride = ((int64_t)KV << bs_shift) * HD;
@@ -220,18 +224,18 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
           const bool ok = key < kv_len;
           int64_t off = 0;
           if (ok) off = (int64_t)btab[key >> bs_shift] * blk_stride + head_off + (key & bs_mask) * HD + lc * 8;
-          cp16(dt + tile_off(row, lc), cache + off, ok);
+          cp16(dt + tile_off<BNK>(row, lc), cache + off, ok);
         }
       }
       cp_commit();
     };
 #pragma unroll
-    for (int i = 0; i < NP; ++i) {
+    for (int i = 0; i < NPQ; ++i) {
       const int row = lrow0 + i * RP;
       const int t2 = row / G, h2 = row % G;
       const bool ok = t2 < ntok;
       const bf16* src = ok ? q + (int64_t)(q0 + tok0 + t2) * q_stride + (kvh * G + h2) * HD + lc * 8 : q;
-      cp16(sQ + tile_off(row, lc), src, ok);
+      cp16(sQ + tile_off<128>(row, lc), src, ok);
     }
     // commit order K0 | K1 | V0 | K2 | V1 | K3 | V2 ...: whenever a tile is published, exactly two
     // younger groups may still be in flight
@@ -252,9 +256,9 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
       load_tile(j + 2, true);
       if (j + 1 < ntiles) { cp_wait<2>(); fence_async_smem(); mbar_arrive(k_full((j + 1) & 1)); }
       const int kbase = j * BNK;
-      uint32_t sv[128];
+      uint32_t sv[BNK];
 #pragma unroll
-      for (int c = 0; c < BNK; c += 32) tmem_ld32(t_row + (j & 1) * 128 + c, *reinterpret_cast<uint32_t(*)[32]>(&sv[c]));
+      for (int c = 0; c < BNK; c += 32) tmem_ld32(t_row + (j & 1) * BNK + c, *reinterpret_cast<uint32_t(*)[32]>(&sv[c]));
       float mx = -INFINITY;
 #pragma unroll
       for (int i = 0; i < BNK; ++i) {
@@ -296,7 +300,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
           rs += p0 + p1;
           pk[i] = pack_bf2(p0, p1);
         }
-        const uint32_t dst = sP + tile_off(r, c8);
+        const uint32_t dst = sP + tile_off<128>(r, c8);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
       }
       l += rs;
@@ -339,7 +343,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   }
 }
 
-template <int HD> constexpr int tc_smem() { return 5 * 128 * HD * 2 + 128 * BNK * 2 + 256 + 1024; }
+template <int HD> constexpr int tc_smem() { return 128 * HD * 2 + 4 * BNK * HD * 2 + 128 * BNK * 2 + 256; }
 
 }  // namespace atc
 

@@ -1,11 +1,11 @@
 // Causal paged attention over the engine's HND cache ([block][kv_head][slot][hd], bf16).
 //
-// Two kernels share the same tile machinery (cp.async-staged, XOR-swizzled K/V tiles of 64 keys,
-// fp32 online softmax, GQA packing: the M rows of a tile are (token, q-head-in-group) pairs so
-// each K/V tile fetched from HBM serves every q head of its kv head):
-//   attn_general_kernel  prefill chunks and mixed batches; warps split the M rows.
-//   attn_decode_kernel   pure decode steps; split-KV across CTAs, warps split the keys of a tile;
-//                        partial (m, l, O) go to workspace and attn_merge_kernel combines them.
+// Decode steps (one query token per request) run here; batches with longer query chunks go to the
+// tcgen05 kernel in attn_tc.cu.  cp.async-staged, XOR-swizzled K/V tiles of 64 keys, fp32 online
+// softmax, GQA packing (the M rows of a tile are the q heads of one kv head, so each K/V tile
+// fetched from HBM serves all of them):
+//   attn_decode_kernel   split-KV across CTAs, warps split the keys of a tile; partial (m, l, O)
+//                        go to workspace and attn_merge_kernel combines them.
 // HBM-bound at decode: algorithmic bytes = sum_b ctx_b * KV * hd * 2 (K) * 2 (V) * 2 B per layer.
 #include <stdlib.h>
 
@@ -90,151 +90,6 @@ struct KvLoader {
   }
 };
 
-// --------------------------------------------------------------------------- general
-// grid (q tiles, KV, B); 128 threads; warp w owns tile rows 16w..16w+15.
-template <int HD>
-__global__ void __launch_bounds__(128)
-attn_general_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
-                    const bf16* __restrict__ k_cache, const bf16* __restrict__ v_cache,
-                    const int32_t* __restrict__ block_table, int max_blocks,
-                    const int32_t* __restrict__ seq_lens, const int32_t* __restrict__ qsl,
-                    int H, int KV, int bs_shift, float scale_log2) {
-  constexpr int BM = 64, CH = HD / 8, NT = 128;
-  const int b = blockIdx.z, kvh = blockIdx.y;
-  const int G = H / KV;
-  const int TT = BM / G;                          // tokens per tile
-  const int q0 = qsl[b], q_len = qsl[b + 1] - q0;
-  const int tok0 = blockIdx.x * TT;
-  if (tok0 >= q_len) return;
-  const int seq_len = seq_lens[b];
-  const int ctx0 = seq_len - q_len;               // keys visible before this chunk's first token
-  const int ntok = min(TT, q_len - tok0);
-  const int kv_len = ctx0 + tok0 + ntok;          // causal upper bound for this tile
-  const int ntiles = (kv_len + BN - 1) / BN;
-  const int32_t* btab = block_table + (int64_t)b * max_blocks;
-
-  extern __shared__ __align__(128) uint8_t smem[];
-  const uint32_t sQ = smem_u32(smem);
-  const uint32_t sK = sQ + BM * HD * 2;           // 2 stages
-  const uint32_t sV = sK + 2 * BN * HD * 2;       // 2 stages
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int g = lane >> 2, tg = lane & 3;
-
-  // Q tile: row r -> token tok0 + r / G, head kvh*G + r % G
-  for (int i = tid; i < BM * CH; i += NT) {
-    const int r = i / CH, c = i % CH;
-    const int tk = r / G, hh = r % G;
-    const bool ok = tk < ntok;
-    const bf16* src = ok ? q + (int64_t)(q0 + tok0 + tk) * q_stride + (kvh * G + hh) * HD + c * 8 : q;
-    cp_async16(sQ + swz<HD>(r, c), src, ok);
-  }
-  KvLoader<HD, NT> ld;
-  ld.init(btab, kvh, KV, bs_shift, tid);
-  ld.load(sK, sV, k_cache, v_cache, 0, kv_len);
-  cp_async_commit();
-
-  uint32_t qf[HD / 16][4];
-  float o[HD / 8][4];
-#pragma unroll
-  for (int i = 0; i < HD / 8; ++i) { o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f; }
-  float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-  // causal limits of this thread's two rows (key index must be <= limit)
-  const int r0 = warp * 16 + g, r1 = r0 + 8;
-  const int lim0 = (r0 / G < ntok) ? ctx0 + tok0 + r0 / G : -1;
-  const int lim1 = (r1 / G < ntok) ? ctx0 + tok0 + r1 / G : -1;
-
-  for (int kt = 0; kt < ntiles; ++kt) {
-    const int st = kt & 1;
-    if (kt + 1 < ntiles) {
-      ld.load(sK + (st ^ 1) * BN * HD * 2, sV + (st ^ 1) * BN * HD * 2, k_cache, v_cache, (kt + 1) * BN, kv_len);
-      cp_async_commit();
-      cp_async_wait<1>();
-    } else {
-      cp_async_wait<0>();
-    }
-    __syncthreads();
-    if (kt == 0) {
-#pragma unroll
-      for (int kk = 0; kk < HD / 16; ++kk)
-        ldsm_x4(qf[kk][0], qf[kk][1], qf[kk][2], qf[kk][3],
-                sQ + swz<HD>(warp * 16 + (lane & 15), kk * 2 + (lane >> 4)));
-    }
-    const uint32_t kb = sK + st * BN * HD * 2, vb = sV + st * BN * HD * 2;
-    float s[BN / 8][4];
-#pragma unroll
-    for (int j = 0; j < BN / 8; ++j) { s[j][0] = s[j][1] = s[j][2] = s[j][3] = 0.f; }
-#pragma unroll
-    for (int kk = 0; kk < HD / 16; ++kk) {
-#pragma unroll
-      for (int jj = 0; jj < BN / 16; ++jj) {
-        uint32_t b0, b1, b2, b3;
-        ldsm_x4(b0, b1, b2, b3, kb + swz<HD>(jj * 16 + (lane & 7) + ((lane >> 4) << 3), kk * 2 + ((lane >> 3) & 1)));
-        mma_bf16(s[2 * jj], qf[kk], b0, b1);
-        mma_bf16(s[2 * jj + 1], qf[kk], b2, b3);
-      }
-    }
-    // mask + online softmax (scores scaled into log2 domain)
-    const int key_base = kt * BN + 2 * tg;
-    float mx0 = m0, mx1 = m1;
-#pragma unroll
-    for (int j = 0; j < BN / 8; ++j) {
-      const int k0 = key_base + j * 8;
-      s[j][0] = (k0 <= lim0) ? s[j][0] * scale_log2 : -INFINITY;
-      s[j][1] = (k0 + 1 <= lim0) ? s[j][1] * scale_log2 : -INFINITY;
-      s[j][2] = (k0 <= lim1) ? s[j][2] * scale_log2 : -INFINITY;
-      s[j][3] = (k0 + 1 <= lim1) ? s[j][3] * scale_log2 : -INFINITY;
-      mx0 = fmaxf(mx0, fmaxf(s[j][0], s[j][1]));
-      mx1 = fmaxf(mx1, fmaxf(s[j][2], s[j][3]));
-    }
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1));
-    mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1));
-    mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-    const float base0 = (mx0 == -INFINITY) ? 0.f : mx0, base1 = (mx1 == -INFINITY) ? 0.f : mx1;
-    const float c0 = exp2f(m0 - base0), c1 = exp2f(m1 - base1);   // m=-inf -> 0
-    m0 = mx0; m1 = mx1;
-    float rs0 = 0.f, rs1 = 0.f;
-    uint32_t pf[BN / 16][4];
-#pragma unroll
-    for (int j = 0; j < BN / 8; ++j) {
-      const float p0 = exp2f(s[j][0] - base0), p1 = exp2f(s[j][1] - base0);
-      const float p2 = exp2f(s[j][2] - base1), p3 = exp2f(s[j][3] - base1);
-      rs0 += p0 + p1; rs1 += p2 + p3;
-      pf[j >> 1][(j & 1) * 2 + 0] = pack_bf2(p0, p1);
-      pf[j >> 1][(j & 1) * 2 + 1] = pack_bf2(p2, p3);
-    }
-    l0 = l0 * c0 + rs0; l1 = l1 * c1 + rs1;
-#pragma unroll
-    for (int i = 0; i < HD / 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
-#pragma unroll
-    for (int kk = 0; kk < BN / 16; ++kk) {
-#pragma unroll
-      for (int nn = 0; nn < HD / 16; ++nn) {
-        uint32_t b0, b1, b2, b3;
-        ldsm_x4_t(b0, b1, b2, b3, vb + swz<HD>(kk * 16 + (lane & 7) + (((lane >> 3) & 1) << 3), nn * 2 + (lane >> 4)));
-        mma_bf16(o[2 * nn], pf[kk], b0, b1);
-        mma_bf16(o[2 * nn + 1], pf[kk], b2, b3);
-      }
-    }
-    __syncthreads();   // tile consumed before the next prefetch overwrites the other stage
-  }
-  l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-  l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-  const float inv0 = l0 > 0.f ? 1.f / l0 : 0.f, inv1 = l1 > 0.f ? 1.f / l1 : 0.f;
-  if (lim0 >= 0) {
-    bf16* dst = out + (int64_t)(q0 + tok0 + r0 / G) * H * HD + (kvh * G + r0 % G) * HD + 2 * tg;
-#pragma unroll
-    for (int i = 0; i < HD / 8; ++i)
-      *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf2(o[i][0] * inv0, o[i][1] * inv0);
-  }
-  if (lim1 >= 0) {
-    bf16* dst = out + (int64_t)(q0 + tok0 + r1 / G) * H * HD + (kvh * G + r1 % G) * HD + 2 * tg;
-#pragma unroll
-    for (int i = 0; i < HD / 8; ++i)
-      *reinterpret_cast<uint32_t*>(dst + i * 8) = pack_bf2(o[i][2] * inv1, o[i][3] * inv1);
-  }
-}
-
 // --------------------------------------------------------------------------- decode
 // grid (splits, KV, B); 128 threads.  One query token per request; the G (<=16) q heads of the
 // kv head are the M rows.  Warp w handles keys 16w..16w+15 of every 64-key tile.
@@ -247,6 +102,8 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
                    int max_blocks, const int32_t* __restrict__ seq_lens,
                    const int32_t* __restrict__ qsl, int H, int KV, int bs_shift, float scale_log2) {
   constexpr int CH = HD / 8, NT = 128;
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.z, kvh = blockIdx.y, split = blockIdx.x, nsplit = gridDim.x;
   const int G = H / KV;
   const int kv_len = seq_lens[b];
@@ -399,6 +256,8 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
 __global__ void attn_merge_kernel(bf16* __restrict__ out, const float* __restrict__ part_o,
                                   const float* __restrict__ part_ml, const int32_t* __restrict__ qsl,
                                   int H, int HD, int nsplit) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.y, head = blockIdx.x, c = threadIdx.x;
   const int64_t p0 = ((int64_t)b * H + head) * nsplit;
   float mm = -INFINITY;
@@ -414,7 +273,6 @@ __global__ void attn_merge_kernel(bf16* __restrict__ out, const float* __restric
 }
 
 constexpr int kDecodeStages = 3;
-template <int HD> constexpr int general_smem() { return 64 * HD * 2 + 4 * BN * HD * 2; }
 template <int HD> constexpr int decode_smem() {
   static_assert(4 * 16 * (HD + 2) * 4 <= kDecodeStages * BN * HD * 2, "sRed must fit in the K stages");
   return 16 * HD * 2 + 2 * kDecodeStages * BN * HD * 2;
@@ -450,23 +308,14 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
     }
     auto kern = attn_decode_kernel<HD, kDecodeStages>;
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
-    kern<<<dim3(ns, KV, B), 128, decode_smem<HD>(), st>>>(out, po, pml, q, q_stride, kc, vc, bt, max_blocks,
-                                                          sl, qsl, H, KV, bs_shift, sl2);
-    KGE_LAUNCH_OK();
-    if (ns > 1) {
-      attn_merge_kernel<<<dim3(H, B), HD, 0, st>>>(out, po, pml, qsl, H, HD, ns);
-      KGE_LAUNCH_OK();
-    }
+    KGE_CUDA_OK(launch_pdl(kern, dim3(ns, KV, B), dim3(128), decode_smem<HD>(), st, out, po, pml, q, q_stride, kc, vc, bt,
+                           max_blocks, sl, qsl, H, KV, bs_shift, sl2));
+    if (ns > 1)
+      KGE_CUDA_OK(launch_pdl(attn_merge_kernel, dim3(H, B), dim3(HD), 0, st, out, (const float*)po, (const float*)pml, qsl, H, HD, ns));
     return 0;
   }
-  KGE_REQUIRE(G <= 64, "kge_paged_attn: GQA group %d > 64 unsupported", G);
-  const int TT = 64 / G;
-  auto kern = attn_general_kernel<HD>;
-  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, general_smem<HD>()));
-  kern<<<dim3((max_q_len + TT - 1) / TT, KV, B), 128, general_smem<HD>(), st>>>(
-      out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, H, KV, bs_shift, sl2);
-  KGE_LAUNCH_OK();
-  return 0;
+  kge::set_error("kge_paged_attn: internal: batch with query chunks reached the decode launcher");
+  return -1;
 }
 
 int paged_attn_prefill_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc, const bf16* vc, const int32_t* bt,
@@ -496,8 +345,7 @@ extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void
   KGE_REQUIRE(max_q_len >= 1 && max_seq_len >= 1, "kge_paged_attn: max_q_len/max_seq_len must be >= 1");
   cudaStream_t st = (cudaStream_t)stream;
   KGE_REQUIRE(hd == 64 || hd == 128, "kge_paged_attn: head_dim=%d unsupported (64, 128)", hd);
-  static const bool legacy = getenv("KGE_ATTN_LEGACY") != nullptr;     // A/B switch during bring-up
-  if (!(max_q_len == 1 && H / KV <= 16) && !legacy)
+  if (!(max_q_len == 1 && H / KV <= 16))
     return paged_attn_prefill_tc((bf16*)out, (const bf16*)q, q_stride, (const bf16*)k_cache, (const bf16*)v_cache, block_table,
                                  max_blocks_per_seq, seq_lens, query_start_loc, B, max_q_len, H, KV, hd, block_size, scale, st);
   if (hd == 64)

@@ -165,6 +165,10 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   __syncthreads();
   tc_after();
   const uint32_t tmem = *tmem_slot;
+  // TMEM is held: only now may the next kernel's CTAs arrive on this SM (they would otherwise
+  // compete for TMEM columns with a kernel they have to wait for)
+  pdl_launch_dependents();
+  pdl_wait();
 
   if (warp == 4) {
     // ------------------------------------------------------------------ MMA issuer
@@ -357,9 +361,8 @@ static int launch_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc, con
   const int TT = atc::BM / G;
   auto kern = atc::attn_tc_kernel<HD>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::tc_smem<HD>()));
-  kern<<<dim3((max_q_len + TT - 1) / TT, KV, B), 160, atc::tc_smem<HD>(), st>>>(out, q, q_stride, kc, vc, bt, max_blocks, sl,
-                                                                              qsl, H, KV, bs_shift, scale * atc::kLog2e);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(kern, dim3((max_q_len + TT - 1) / TT, KV, B), dim3(160), atc::tc_smem<HD>(), st, out, q, q_stride, kc,
+                         vc, bt, max_blocks, sl, qsl, H, KV, bs_shift, scale * atc::kLog2e));
   return 0;
 }
 

@@ -20,6 +20,8 @@ static inline int row_threads(int d) {
 __global__ void embed_kernel(bf16* __restrict__ out, const int32_t* __restrict__ ids,
                              const bf16* __restrict__ table, const bf16* __restrict__ pos_table,
                              const int32_t* __restrict__ positions, int pos_offset, int d) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   const int64_t row = ids[t];
   const uint4* src = reinterpret_cast<const uint4*>(table + row * d);
@@ -47,6 +49,8 @@ __global__ void __launch_bounds__(512)
 norm_kernel(bf16* __restrict__ y, bf16* __restrict__ residual, const bf16* __restrict__ x,
             const bf16* __restrict__ w, const bf16* __restrict__ b, int d, float eps) {
   __shared__ float red[33];
+  pdl_launch_dependents();
+  pdl_wait();
   const int64_t base = (int64_t)blockIdx.x * d;
   const int nvec = d / 8;
   float v[kMaxVecPerThread][8];
@@ -131,6 +135,8 @@ __device__ __forceinline__ float silu_bf(float g) {
   return rbf(g / (1.0f + expf(-g)));
 }
 __global__ void silu_mul_kernel(bf16* __restrict__ y, const bf16* __restrict__ x, int f, int64_t nvec) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int fv = f / 8;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < nvec;
        i += (int64_t)gridDim.x * blockDim.x) {
@@ -155,6 +161,8 @@ __global__ void rope_kvwrite_kernel(bf16* __restrict__ qkv, const bf16* __restri
                                     const int64_t* __restrict__ slot_mapping,
                                     bf16* __restrict__ k_cache, bf16* __restrict__ v_cache,
                                     int H, int KV, int hd, int block_size) {
+  pdl_launch_dependents();
+  pdl_wait();
   const int t = blockIdx.x;
   const int half = hd / 2, hv = half / 8;          // vectors per half head
   bf16* row = qkv + (int64_t)t * (H + 2 * KV) * hd;
@@ -211,6 +219,8 @@ __global__ void __launch_bounds__(1024)
 argmax_kernel(int32_t* __restrict__ out, const bf16* __restrict__ logits, int V, int ld) {
   __shared__ float sval[32];
   __shared__ int sidx[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const bf16* row = logits + (int64_t)blockIdx.x * ld;
   float best = -INFINITY;
   int bi = 0x7fffffff;
@@ -265,9 +275,8 @@ extern "C" int kge_embed(void* out, const int32_t* ids, const void* table, const
   KGE_REQUIRE(!pos_table || positions, "kge_embed: pos_table given without positions");
   if (T == 0) return 0;
   int th = d / 8 < 256 ? ((d / 8 + 31) / 32) * 32 : 256;
-  embed_kernel<<<T, th, 0, (cudaStream_t)stream>>>((bf16*)out, ids, (const bf16*)table,
-                                                   (const bf16*)pos_table, positions, pos_offset, d);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(embed_kernel, dim3(T), dim3(th), 0, (cudaStream_t)stream, (bf16*)out, ids, (const bf16*)table,
+                         (const bf16*)pos_table, positions, pos_offset, d));
   return 0;
 }
 
@@ -281,13 +290,9 @@ static int norm_common(int mode, void* y, void* residual, const void* x, const v
   const int th = row_threads(d);
   KGE_REQUIRE((d / 8 + th - 1) / th <= kMaxVecPerThread, "kge norm: d=%d too large", d);
   cudaStream_t s = (cudaStream_t)stream;
-  switch (mode) {
-    case 0: norm_kernel<0><<<T, th, 0, s>>>((bf16*)y, nullptr, (const bf16*)x, (const bf16*)w, nullptr, d, eps); break;
-    case 1: norm_kernel<1><<<T, th, 0, s>>>((bf16*)y, (bf16*)residual, (const bf16*)x, (const bf16*)w, nullptr, d, eps); break;
-    case 2: norm_kernel<2><<<T, th, 0, s>>>((bf16*)y, (bf16*)residual, nullptr, (const bf16*)w, (const bf16*)b, d, eps); break;
-    default: norm_kernel<3><<<T, th, 0, s>>>((bf16*)y, (bf16*)residual, (const bf16*)x, (const bf16*)w, (const bf16*)b, d, eps); break;
-  }
-  KGE_LAUNCH_OK();
+  auto kern = mode == 0 ? norm_kernel<0> : mode == 1 ? norm_kernel<1> : mode == 2 ? norm_kernel<2> : norm_kernel<3>;
+  KGE_CUDA_OK(launch_pdl(kern, dim3(T), dim3(th), 0, s, (bf16*)y, (bf16*)residual, (const bf16*)x, (const bf16*)w,
+                         (const bf16*)b, d, eps));
   return 0;
 }
 
@@ -314,8 +319,7 @@ extern "C" int kge_silu_mul(void* y, const void* x, int T, int f, void* stream) 
   const int64_t nvec = (int64_t)T * (f / 8);
   int64_t blocks = (nvec + 255) / 256;
   if (blocks > 148 * 16) blocks = 148 * 16;
-  silu_mul_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>((bf16*)y, (const bf16*)x, f, nvec);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(silu_mul_kernel, dim3((int)blocks), dim3(256), 0, (cudaStream_t)stream, (bf16*)y, (const bf16*)x, f, nvec));
   return 0;
 }
 
@@ -331,10 +335,8 @@ extern "C" int kge_rope_kvwrite(void* qkv, const void* cos_sin, const int32_t* p
   const int items = (H + KV) * (hd / 16) + KV * (hd / 8);
   int th = ((items + 31) / 32) * 32;
   if (th > 256) th = 256;
-  rope_kvwrite_kernel<<<T, th, 0, (cudaStream_t)stream>>>((bf16*)qkv, (const bf16*)cos_sin, positions,
-                                                          slot_mapping, (bf16*)k_cache, (bf16*)v_cache,
-                                                          H, KV, hd, block_size);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(rope_kvwrite_kernel, dim3(T), dim3(th), 0, (cudaStream_t)stream, (bf16*)qkv, (const bf16*)cos_sin,
+                         positions, slot_mapping, (bf16*)k_cache, (bf16*)v_cache, H, KV, hd, block_size));
   return 0;
 }
 
@@ -342,7 +344,6 @@ extern "C" int kge_argmax(int32_t* out_ids, const void* logits, int B, int V, in
   KGE_REQUIRE(out_ids && logits && V > 0 && ld >= V, "kge_argmax: bad arguments");
   KGE_REQUIRE(aligned16(logits) && ld % 8 == 0, "kge_argmax: logits rows must be 16-byte aligned");
   if (B <= 0) return 0;
-  argmax_kernel<<<B, 1024, 0, (cudaStream_t)stream>>>(out_ids, (const bf16*)logits, V, ld);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(argmax_kernel, dim3(B), dim3(1024), 0, (cudaStream_t)stream, out_ids, (const bf16*)logits, V, ld));
   return 0;
 }

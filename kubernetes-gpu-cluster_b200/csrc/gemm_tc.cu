@@ -157,6 +157,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  // TMEM is held: the next kernel may start arriving now (see attn_tc.cu for why not earlier)
+  pdl_launch_dependents();
+  if (warp != 0) pdl_wait();          // warp 0 (TMA producer) prefetches weights first, then waits
 
   // work decomposition: persistent round-robin over tiles, or (SPLIT) one tile per cluster with
   // the cluster rank selecting the K range
@@ -172,19 +175,39 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   if (warp == 0) {
     if (lane == 0) {
       int stage = 0; uint32_t phase = 0;
+      auto load_a = [&](int st, int kb, int m_tile) {
+        const uint32_t a_dst = smem_base + st * STAGE_BYTES;
+        if (GATED) {
+          tma_load_2d(a_dst, &tmap_w, full_bar(st), kb * BLK_K, m_tile * 64);                          // gate rows
+          tma_load_2d(a_dst + 64 * BLK_K * 2, &tmap_w, full_bar(st), kb * BLK_K, p.N + m_tile * 64);   // up rows
+        } else {
+          tma_load_2d(a_dst, &tmap_w, full_bar(st), kb * BLK_K, m_tile * BLK_M);
+        }
+      };
+      // Weights do not depend on the previous kernel: stream the first stages of W while it is
+      // still running, then wait for its output (the activations) and add the X tiles.
+      int pre = 0;
+      if (w_first < total) {
+        const int m_tile = w_first / p.n_tiles;
+        pre = min(STAGES, kb1 - kb0);
+        for (int i = 0; i < pre; ++i) {
+          mbar_expect_tx(full_bar(i), STAGE_BYTES);
+          load_a(i, kb0 + i, m_tile);
+        }
+      }
+      pdl_wait();
       for (int w = w_first; w < total; w += w_step) {
         const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
         for (int kb = kb0; kb < kb1; ++kb) {
-          mbar_wait(empty_bar(stage), phase ^ 1);
-          const uint32_t a_dst = smem_base + stage * STAGE_BYTES, b_dst = a_dst + A_BYTES;
-          mbar_expect_tx(full_bar(stage), STAGE_BYTES);
-          if (GATED) {
-            tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * 64);                     // gate rows
-            tma_load_2d(a_dst + 64 * BLK_K * 2, &tmap_w, full_bar(stage), kb * BLK_K, p.N + m_tile * 64);  // up rows
+          const uint32_t b_dst = smem_base + stage * STAGE_BYTES + A_BYTES;
+          if (w == w_first && kb - kb0 < pre) {
+            tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
           } else {
-            tma_load_2d(a_dst, &tmap_w, full_bar(stage), kb * BLK_K, m_tile * BLK_M);
+            mbar_wait(empty_bar(stage), phase ^ 1);
+            mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+            load_a(stage, kb, m_tile);
+            tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
           }
-          tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
@@ -384,12 +407,15 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   cfg.blockDim = dim3(kGemmThreads);
   cfg.dynamicSmemBytes = smem;
   cfg.stream = st;
-  cudaLaunchAttribute attr[1];
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = attr; cfg.numAttrs = 1;
   if (SPLIT) {
     cfg.gridDim = dim3(tiles * p.splits);
-    attr[0].id = cudaLaunchAttributeClusterDimension;
-    attr[0].val.clusterDim.x = p.splits; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
   } else {
     cfg.gridDim = dim3(tiles < 148 ? tiles : 148);
   }

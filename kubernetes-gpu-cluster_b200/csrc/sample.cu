@@ -56,6 +56,8 @@ sample_kernel(int32_t* __restrict__ out, const bf16* __restrict__ logits, int V,
   __shared__ uint32_t s_prefix;
   __shared__ float s_below;
   __shared__ int sidx[32];
+  pdl_launch_dependents();
+  pdl_wait();
   const int b = blockIdx.x, tid = threadIdx.x;
   const bf16* row = logits + (int64_t)b * ld;
   const float temp = temperature ? temperature[b] : 0.f;
@@ -189,8 +191,7 @@ extern "C" int kge_sample(int32_t* out_ids, const void* logits, int B, int V, in
   (void)workspace; (void)workspace_bytes;
   KGE_REQUIRE(out_ids && logits && V > 0 && ld >= V, "kge_sample: bad arguments");
   if (B <= 0) return 0;
-  sample_kernel<<<B, kSampleThreads, 0, (cudaStream_t)stream>>>(out_ids, (const bf16*)logits, V, ld, temperature,
-                                                                top_k, top_p, exp_noise, seeds, step);
-  KGE_LAUNCH_OK();
+  KGE_CUDA_OK(launch_pdl(sample_kernel, dim3(B), dim3(kSampleThreads), 0, (cudaStream_t)stream, out_ids, (const bf16*)logits, V,
+                         ld, temperature, top_k, top_p, exp_noise, seeds, step));
   return 0;
 }

@@ -278,7 +278,10 @@ template <int HD> constexpr int decode_smem() {
   return 16 * HD * 2 + 2 * kDecodeStages * BN * HD * 2;
 }
 
-static int decode_splits(int B, int KV, int max_seq_len) {
+int attn_decode_splits(int B, int KV, int max_seq_len);
+static int decode_splits(int B, int KV, int max_seq_len) { return attn_decode_splits(B, KV, max_seq_len); }
+// Split-KV factor of a decode launch; also part of the key of the engine's captured decode graphs.
+int attn_decode_splits(int B, int KV, int max_seq_len) {
   const int target = 148 * 4;
   int s = (target + B * KV - 1) / (B * KV);
   const int max_s = (max_seq_len + 4 * BN - 1) / (4 * BN);   // >= 256 keys per split

@@ -348,6 +348,7 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
 extern "C" void kge_engine_destroy(kge_engine* e) {
   if (!e) return;
   if (e->stream) cudaStreamSynchronize(e->stream);
+  for (auto& g : e->graphs) cudaGraphExecDestroy(g.exec);
   for (void* p : e->allocs) cudaFree(p);
   if (e->meta_host) cudaFreeHost(e->meta_host);
   if (e->out_host) cudaFreeHost(e->out_host);

@@ -65,6 +65,12 @@ struct kge_engine {
   int64_t meta_bytes = 0;
   int32_t* out_host = nullptr;               // pinned [max_num_seqs]
 
+  // CUDA graphs of pure decode steps, keyed by what is baked into the launches
+  struct DecodeGraph { int B, ns, stride; bool rnd; cudaGraphExec_t exec; int64_t launches; };
+  std::vector<DecodeGraph> graphs;
+  std::vector<std::pair<int64_t, int>> graph_seen;   // key hash -> eager runs so far
+  bool use_graphs = true;
+
   std::unique_ptr<kge::Scheduler> sched;
   int64_t launches = 0;
   int64_t h2d_bytes = 0, d2h_bytes = 0;      // metadata in / sampled ids out, summed over steps
@@ -83,5 +89,10 @@ namespace kge {
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
                    const StepMeta& dm, bool any_random, double sum_seq, double attn_flops);
 void collect_timing(kge_engine* e);
+int attn_decode_splits(int B, int KV, int max_seq_len);   // attn.cu
+// A pure decode step (one token per request, metadata at the fixed-stride layout `dm` in meta_dev):
+// eager the first time a (B, splits, stride, sampling) key is seen, captured into a CUDA graph the
+// second time, replayed afterwards.
+int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const StepMeta& dm, bool any_random, double sum_seq);
 StepMeta carve_meta(uint8_t* base, int T, int B, int R, int max_blocks, int64_t* total);
 }  // namespace kge

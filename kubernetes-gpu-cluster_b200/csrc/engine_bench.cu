@@ -98,7 +98,8 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   const int n_prefill_steps = (int)steps.size();
   for (int s = 1; s < out_len; ++s) {
     const int ctx = prompt_len + s;             // keys visible to the token decoded this step
-    const int mb = (ctx + bs - 1) / bs;
+    const int mb_used = (ctx + bs - 1) / bs;
+    const int mb = std::min(e->max_blocks_per_seq, (mb_used + 31) / 32 * 32);   // bucketed stride (graph key)
     StepMeta m = add_step(B, B, B, mb);
     ResidentStep& st = steps.back();
     st.max_q = 1; st.max_seq = ctx; st.ids_from_prev = true; st.out_row0 = out_rows;
@@ -109,7 +110,7 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
       m.qsl[b] = b;
       m.seq_lens[b] = ctx;
       m.rows[b] = b;
-      for (int j = 0; j < mb; ++j) m.btab[b * mb + j] = block_of(b, j);
+      for (int j = 0; j < mb_used; ++j) m.btab[b * mb + j] = block_of(b, j);
       st.sum_seq += ctx;
       st.attn_flops += 4.0 * ctx;
     }
@@ -132,10 +133,20 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   for (size_t si = 0; si < steps.size() && rc == 0; ++si) {
     const ResidentStep& st = steps[si];
     if ((int)si == n_prefill_steps) cudaEventRecord(ev1, e->stream);
-    const int mb = st.ids_from_prev ? (st.max_seq + bs - 1) / bs : (prompt_len + bs - 1) / bs;
-    StepMeta dm = carve_meta(d_arena + st.off, st.T, st.B, st.R, mb, nullptr);
-    if (st.ids_from_prev) dm.ids = ((int)si == n_prefill_steps) ? d_first : e->d_out;
-    rc = engine_forward(e, st.T, st.B, st.R, mb, st.max_q, st.max_seq, dm, false, st.sum_seq, st.attn_flops);
+    if (st.ids_from_prev) {
+      // decode: the step's metadata block is copied (device to device) to the engine's fixed slot so the
+      // captured graph of this (B, splits, stride) can be replayed; the ids are the previous step's samples
+      const int mb = std::min(e->max_blocks_per_seq, ((st.max_seq + bs - 1) / bs + 31) / 32 * 32);
+      int64_t bytes = 0;
+      StepMeta dm = carve_meta(e->meta_dev, st.T, st.B, st.R, mb, &bytes);
+      cudaMemcpyAsync(e->meta_dev, d_arena + st.off, (size_t)bytes, cudaMemcpyDeviceToDevice, e->stream);
+      cudaMemcpyAsync(dm.ids, ((int)si == n_prefill_steps) ? d_first : e->d_out, (size_t)st.B * 4, cudaMemcpyDeviceToDevice, e->stream);
+      rc = engine_decode_step(e, st.B, mb, st.max_seq, dm, false, st.sum_seq);
+    } else {
+      const int mb = (prompt_len + bs - 1) / bs;
+      StepMeta dm = carve_meta(d_arena + st.off, st.T, st.B, st.R, mb, nullptr);
+      rc = engine_forward(e, st.T, st.B, st.R, mb, st.max_q, st.max_seq, dm, false, st.sum_seq, st.attn_flops);
+    }
     if (rc) break;
     cudaMemcpyAsync(d_log + st.out_row0, e->d_out, (size_t)st.R * 4, cudaMemcpyDeviceToDevice, e->stream);
     if (!st.ids_from_prev)

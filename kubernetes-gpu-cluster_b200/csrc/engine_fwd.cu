@@ -131,6 +131,39 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
   return 0;
 }
 
+int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const StepMeta& dm, bool any_random, double sum_seq) {
+  const double attn_flops = 4.0 * sum_seq;
+  const int ns = attn_decode_splits(B, e->KV_loc, max_seq_len);
+  if (!e->use_graphs || e->timing || any_random)      // the Philox step counter is a launch argument: no replay
+    return engine_forward(e, B, B, B, stride, 1, max_seq_len, dm, any_random, sum_seq, attn_flops);
+  for (auto& g : e->graphs)
+    if (g.B == B && g.ns == ns && g.stride == stride && g.rnd == any_random) {
+      KGE_CUDA_OK(cudaGraphLaunch(g.exec, e->stream));
+      e->launches += g.launches;
+      return 0;
+    }
+  const int64_t key = ((int64_t)B << 40) ^ ((int64_t)ns << 32) ^ ((int64_t)stride << 1) ^ (any_random ? 1 : 0);
+  int* seen = nullptr;
+  for (auto& kv : e->graph_seen) if (kv.first == key) seen = &kv.second;
+  if (!seen) { e->graph_seen.push_back({key, 0}); seen = &e->graph_seen.back().second; }
+  if ((*seen)++ == 0)     // first sight: run eagerly so every lazy initialisation happens outside a capture
+    return engine_forward(e, B, B, B, stride, 1, max_seq_len, dm, any_random, sum_seq, attn_flops);
+  const int64_t l0 = e->launches;
+  KGE_CUDA_OK(cudaStreamBeginCapture(e->stream, cudaStreamCaptureModeThreadLocal));
+  const int rc = engine_forward(e, B, B, B, stride, 1, max_seq_len, dm, any_random, sum_seq, attn_flops);
+  cudaGraph_t graph = nullptr;
+  cudaError_t ce = cudaStreamEndCapture(e->stream, &graph);
+  if (rc) { if (graph) cudaGraphDestroy(graph); return rc; }
+  KGE_REQUIRE(ce == cudaSuccess && graph, "decode graph capture failed: %s", cudaGetErrorString(ce));
+  kge_engine::DecodeGraph g{B, ns, stride, any_random, nullptr, e->launches - l0};
+  ce = cudaGraphInstantiate(&g.exec, graph, 0);
+  cudaGraphDestroy(graph);
+  KGE_REQUIRE(ce == cudaSuccess, "cudaGraphInstantiate failed: %s", cudaGetErrorString(ce));
+  e->graphs.push_back(g);
+  KGE_CUDA_OK(cudaGraphLaunch(g.exec, e->stream));
+  return 0;
+}
+
 __global__ void bf16_to_f32_kernel(float* o, const bf16* x, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) o[i] = bf2f(x[i]);
 }
@@ -144,14 +177,26 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
   KGE_REQUIRE(B <= e->cfg.max_num_seqs && R <= e->cfg.max_num_seqs, "kge_step: B=%d / R=%d exceed max_num_seqs=%d", B, R, e->cfg.max_num_seqs);
   KGE_REQUIRE(b->max_blocks > 0 && b->max_blocks <= e->max_blocks_per_seq, "kge_step: max_blocks=%d out of range", b->max_blocks);
   KGE_CUDA_OK(cudaSetDevice(e->cfg.device));
+  // pure decode step with every row sampled: block-table rows at a bucketed stride so the captured
+  // graph of this (B, splits, stride) can be replayed while contexts grow
+  bool decode_only = (T == B && R == B && !out_logits_host);
+  for (int i = 0; decode_only && i < B; ++i) decode_only = (b->logits_rows[i] == i);
+  const int stride = decode_only ? std::min(e->max_blocks_per_seq, (b->max_blocks + 31) / 32 * 32) : b->max_blocks;
   int64_t bytes = 0;
-  StepMeta hm = carve_meta(e->meta_host, T, B, R, b->max_blocks, &bytes);
-  StepMeta dm = carve_meta(e->meta_dev, T, B, R, b->max_blocks, nullptr);
+  StepMeta hm = carve_meta(e->meta_host, T, B, R, stride, &bytes);
+  StepMeta dm = carve_meta(e->meta_dev, T, B, R, stride, nullptr);
   memcpy(hm.ids, b->token_ids, (size_t)T * 4);
   memcpy(hm.pos, b->positions, (size_t)T * 4);
   memcpy(hm.qsl, b->query_start_loc, (size_t)(B + 1) * 4);
   memcpy(hm.seq_lens, b->seq_lens, (size_t)B * 4);
-  memcpy(hm.btab, b->block_table, (size_t)B * b->max_blocks * 4);
+  if (stride == b->max_blocks) {
+    memcpy(hm.btab, b->block_table, (size_t)B * b->max_blocks * 4);
+  } else {
+    for (int i = 0; i < B; ++i) {
+      memcpy(hm.btab + (size_t)i * stride, b->block_table + (size_t)i * b->max_blocks, (size_t)b->max_blocks * 4);
+      memset(hm.btab + (size_t)i * stride + b->max_blocks, 0, (size_t)(stride - b->max_blocks) * 4);
+    }
+  }
   memcpy(hm.slots, b->slot_mapping, (size_t)T * 8);
   if (R > 0) memcpy(hm.rows, b->logits_rows, (size_t)R * 4);
   bool any_random = false;
@@ -177,7 +222,11 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
   KGE_CUDA_OK(cudaMemcpyAsync(e->meta_dev, e->meta_host, (size_t)bytes, cudaMemcpyHostToDevice, e->stream));
   e->h2d_bytes += bytes;
   e->d2h_bytes += (int64_t)R * 4;
-  if (int rc = engine_forward(e, T, B, R, b->max_blocks, max_q, max_seq, dm, any_random, sum_seq, attn_flops)) return rc;
+  if (decode_only && max_q == 1) {
+    if (int rc = engine_decode_step(e, B, stride, max_seq, dm, any_random, sum_seq)) return rc;
+  } else {
+    if (int rc = engine_forward(e, T, B, R, stride, max_q, max_seq, dm, any_random, sum_seq, attn_flops)) return rc;
+  }
   ++e->step_count;
   if (R > 0) {
     KGE_CUDA_OK(cudaMemcpyAsync(e->out_host, e->d_out, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));

@@ -114,7 +114,20 @@ __device__ __forceinline__ float silu_gate_bf16(float g_acc, float u_acc) {
   return sg * u;                                          // caller rounds the product once
 }
 
-template <int TOKN, int STAGES, bool SPLIT, bool GATED>
+__device__ __forceinline__ void tma_load_2d_mcast(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint16_t mask) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
+               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tc_commit_mcast(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+}
+
+// MCAST (prefill, TOKN = 256): the two CTAs of a cluster work on two adjacent weight-row tiles of the
+// SAME token tile in lockstep; each loads half of the X tile and TMA-multicasts it into both CTAs'
+// shared memory, so the X tile crosses L2 -> SM once per pair (32 KB instead of 48 KB per CTA and
+// k-block).  A stage is free only when BOTH CTAs' MMAs on it have retired (empty barrier count 2,
+// tcgen05.commit multicast to both).
+template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool MCAST>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
@@ -145,7 +158,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), MCAST ? 2 : 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -157,6 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (MCAST) { cluster_arrive(); cluster_wait(); }      // peer barriers are initialised before any remote signal
   // TMEM is held: the next kernel may start arriving now (see attn_tc.cu for why not earlier)
   pdl_launch_dependents();
   if (warp != 0) pdl_wait();          // warp 0 (TMA producer) prefetches weights first, then waits
@@ -165,9 +179,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   // the cluster rank selecting the K range
   const int S = SPLIT ? (int)cluster_nctarank() : 1;
   const int crank = SPLIT ? (int)cluster_ctarank() : 0;
-  const int total = p.m_tiles * p.n_tiles;
-  const int w_first = SPLIT ? (int)blockIdx.x / S : (int)blockIdx.x;
-  const int w_step = SPLIT ? (1 << 30) : (int)gridDim.x;
+  const int mrank = MCAST ? (int)cluster_ctarank() : 0;          // which tile of the weight-row pair
+  const int total = (MCAST ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
+  const int w_first = SPLIT ? (int)blockIdx.x / S : MCAST ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int w_step = SPLIT ? (1 << 30) : MCAST ? (int)gridDim.x / 2 : (int)gridDim.x;
+  auto m_tile_of = [&](int w) { return MCAST ? 2 * (w / p.n_tiles) + mrank : w / p.n_tiles; };
   const int kb0 = crank * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
   const int cols_per = (TOKN + S - 1) / S;               // columns finished by each cluster rank
   if (SPLIT) cluster_arrive();                           // phase A: every CTA of the cluster has started
@@ -187,8 +203,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       // Weights do not depend on the previous kernel: stream the first stages of W while it is
       // still running, then wait for its output (the activations) and add the X tiles.
       int pre = 0;
+      auto load_b = [&](int st, int kb, int n_tile) {
+        const uint32_t b_dst = smem_base + st * STAGE_BYTES + A_BYTES;
+        if (MCAST) tma_load_2d_mcast(b_dst + mrank * (128 * BLK_K * 2), &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN + mrank * 128, (uint16_t)3);
+        else tma_load_2d(b_dst, &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN);
+      };
       if (w_first < total) {
-        const int m_tile = w_first / p.n_tiles;
+        const int m_tile = m_tile_of(w_first);
         pre = min(STAGES, kb1 - kb0);
         for (int i = 0; i < pre; ++i) {
           mbar_expect_tx(full_bar(i), STAGE_BYTES);
@@ -197,16 +218,15 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       }
       pdl_wait();
       for (int w = w_first; w < total; w += w_step) {
-        const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
+        const int n_tile = w % p.n_tiles, m_tile = m_tile_of(w);
         for (int kb = kb0; kb < kb1; ++kb) {
-          const uint32_t b_dst = smem_base + stage * STAGE_BYTES + A_BYTES;
           if (w == w_first && kb - kb0 < pre) {
-            tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
+            load_b(stage, kb, n_tile);
           } else {
             mbar_wait(empty_bar(stage), phase ^ 1);
             mbar_expect_tx(full_bar(stage), STAGE_BYTES);
             load_a(stage, kb, m_tile);
-            tma_load_2d(b_dst, &tmap_x, full_bar(stage), kb * BLK_K, n_tile * TOKN);
+            load_b(stage, kb, n_tile);
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -230,7 +250,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
             // +32 B per 16-element k step inside the 128 B swizzle row (start address field is >>4)
             tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          tc_commit(empty_bar(stage));          // frees the smem slot when these MMAs retire
+          if (MCAST) tc_commit_mcast(empty_bar(stage), (uint16_t)3);   // both CTAs' producers wait for both MMAs
+          else tc_commit(empty_bar(stage));     // frees the smem slot when these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
         tc_commit(tfull_bar(acc));              // accumulator complete
@@ -250,7 +271,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
     for (int w = w_first; w < total; w += w_step) {
-      const int n_tile = w % p.n_tiles, m_tile = w / p.n_tiles;
+      const int n_tile = w % p.n_tiles, m_tile = m_tile_of(w);
       const int n = m_tile * ROWS_OUT + (GATED ? (et & 63) : et);   // output column of this thread's row
       const int t0 = n_tile * TOKN;
       mbar_wait(tfull_bar(acc), acc_phase);
@@ -353,6 +374,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (MCAST) { cluster_arrive(); cluster_wait(); }      // the peer may still signal my barriers until it is done too
   if (warp == 2) {
     tc_fence_after();
     asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -391,7 +413,7 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
   return 0;
 }
 
-template <int TOKN, bool SPLIT, bool GATED>
+template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
@@ -400,7 +422,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, MCAST>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -416,6 +438,12 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
+  } else if (MCAST) {
+    const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
+    cfg.gridDim = dim3(2 * (pairs < 74 ? pairs : 74));
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
   } else {
     cfg.gridDim = dim3(tiles < 148 ? tiles : 148);
   }
@@ -430,7 +458,7 @@ static int query_max_clusters(int S) {
   constexpr int budget = 224 * 1024 - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   constexpr int smem = STAGES * stage_bytes + 1024 + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, true, false>;   // the gated variant has the same footprint
+  auto kern = gemm_tc_kernel<TOKN, STAGES, true, false, false>;   // the gated variant has the same footprint
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(S * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem;
@@ -480,6 +508,9 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
   return g;
 }
 
+// prefill-sized problems share the X tile between the two CTAs of a cluster (TMA multicast)
+static bool gemm_uses_mcast(const GemmPlan& g) { return g.tokn == 256 && g.splits == 1 && g.m_tiles >= 2; }
+
 template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   if (g.splits > 1) {
@@ -495,7 +526,9 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
     case 32: return launch_gemm<32, false, GATED>(tw, tx, p, st);
     case 64: return launch_gemm<64, false, GATED>(tw, tx, p, st);
     case 128: return launch_gemm<128, false, GATED>(tw, tx, p, st);
-    default: return launch_gemm<256, false, GATED>(tw, tx, p, st);
+    default:
+      if (gemm_uses_mcast(g)) return launch_gemm<256, false, GATED, true>(tw, tx, p, st);
+      return launch_gemm<256, false, GATED>(tw, tx, p, st);
   }
 }
 
@@ -523,7 +556,7 @@ extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* 
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w, N, K, BLK_M)) return rc;
-  if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
+  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_mcast(g) ? 128 : g.tokn)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   return dispatch_gemm<false>(g, tw, tx, p, st);
 }
@@ -542,6 +575,6 @@ extern "C" int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gat
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, 64)) return rc;     // 64-row boxes: gate half, up half
-  if (int rc = make_tmap(&tx, x, T, K, g.tokn)) return rc;
+  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_mcast(g) ? 128 : g.tokn)) return rc;
   return dispatch_gemm<true>(g, tw, tx, p, (cudaStream_t)stream);
 }

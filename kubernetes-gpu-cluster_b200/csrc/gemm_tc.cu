@@ -20,6 +20,7 @@
 // Roofline: decode T<=256 -> HBM, algorithmic bytes = N*K*2 (weights) + T*(K+N)*2;
 //           prefill        -> tensor, 2*T*N*K flop.
 #include <cuda.h>
+#include <stdlib.h>
 
 #include "common.cuh"
 #include "kge.h"
@@ -30,7 +31,7 @@ constexpr int BLK_M = 128;   // weight rows per tile (UMMA M)
 constexpr int BLK_K = 64;    // 64 bf16 = 128 B = one swizzle row
 constexpr int UMMA_K = 16;
 constexpr int kGemmThreads = 256;
-constexpr uint32_t kSpinLimit = 1u << 30;
+constexpr uint32_t kSpinLimit = 1u << 24;   // seconds at most: a lost arrival traps instead of hanging the GPU
 
 __device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
@@ -122,19 +123,43 @@ __device__ __forceinline__ void tc_commit_mcast(uint32_t bar, uint16_t mask) {
   asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
 }
 
+__device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
+}
+__device__ __forceinline__ void tc_commit_cg2(uint32_t bar, uint16_t mask) {
+  asm volatile("tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
+}
+__device__ __forceinline__ void tc_mma_bf16_cg2(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t acc) {
+  asm volatile("{\n.reg .pred p;\nsetp.ne.b32 p, %4, 0;\ntcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n}"
+               ::"r"(d_tmem), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(acc) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
+  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(bar_cluster) : "memory");
+}
+
+// PAIR (prefill, TOKN = 256): cta_group::2.  The two CTAs of a cluster form one 256 x 256 MMA tile:
+// each holds its own 128 weight rows (A) and HALF of the token tile (B, 128 tokens) in shared memory
+// (32 KB per stage instead of 48 KB: less L2->SM traffic and less shared-memory bandwidth), the
+// leader CTA issues tcgen05.mma.cta_group::2 for both, accumulators land in each CTA's own TMEM.
+// All TMA loads of a stage complete on the LEADER's full barrier; tcgen05.commit multicasts the
+// "stage free" and "accumulator ready" arrivals to both CTAs; both epilogues release the accumulator
+// on the leader's tmem_empty barrier.
 // MCAST (prefill, TOKN = 256): the two CTAs of a cluster work on two adjacent weight-row tiles of the
 // SAME token tile in lockstep; each loads half of the X tile and TMA-multicasts it into both CTAs'
 // shared memory, so the X tile crosses L2 -> SM once per pair (32 KB instead of 48 KB per CTA and
 // k-block).  A stage is free only when BOTH CTAs' MMAs on it have retired (empty barrier count 2,
 // tcgen05.commit multicast to both).
-template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool MCAST>
+template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool MCAST, bool PAIR = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
-  constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = TOKN * BLK_K * 2;
+  static_assert(!(MCAST && PAIR) && !(PAIR && SPLIT), "one cluster scheme at a time");
+  constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = (PAIR ? 128 : TOKN) * BLK_K * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
-  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TOKN >> 3) << 17) | ((uint32_t)(BLK_M >> 4) << 24);
+  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TOKN >> 3) << 17) |
+                             ((uint32_t)((PAIR ? 2 * BLK_M : BLK_M) >> 4) << 24);
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -159,18 +184,23 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
   if (warp == 1 && lane == 0) {
     for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), MCAST ? 2 : 1); }
-    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), 4); }
+    for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), PAIR ? 8 : 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   if (warp == 2) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    if (PAIR) {
+      asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;" ::: "memory");
+    } else {
+      asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
+      asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
   }
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (MCAST) { cluster_arrive(); cluster_wait(); }      // peer barriers are initialised before any remote signal
+  if (MCAST || PAIR) { cluster_arrive(); cluster_wait(); }   // peer barriers are initialised before any remote signal
   // TMEM is held: the next kernel may start arriving now (see attn_tc.cu for why not earlier)
   pdl_launch_dependents();
   if (warp != 0) pdl_wait();          // warp 0 (TMA producer) prefetches weights first, then waits
@@ -179,11 +209,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   // the cluster rank selecting the K range
   const int S = SPLIT ? (int)cluster_nctarank() : 1;
   const int crank = SPLIT ? (int)cluster_ctarank() : 0;
-  const int mrank = MCAST ? (int)cluster_ctarank() : 0;          // which tile of the weight-row pair
-  const int total = (MCAST ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
-  const int w_first = SPLIT ? (int)blockIdx.x / S : MCAST ? (int)blockIdx.x / 2 : (int)blockIdx.x;
-  const int w_step = SPLIT ? (1 << 30) : MCAST ? (int)gridDim.x / 2 : (int)gridDim.x;
-  auto m_tile_of = [&](int w) { return MCAST ? 2 * (w / p.n_tiles) + mrank : w / p.n_tiles; };
+  constexpr bool TWO = MCAST || PAIR;
+  const int mrank = TWO ? (int)cluster_ctarank() : 0;            // which tile of the weight-row pair
+  const int total = (TWO ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
+  const int w_first = SPLIT ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int w_step = SPLIT ? (1 << 30) : TWO ? (int)gridDim.x / 2 : (int)gridDim.x;
+  auto m_tile_of = [&](int w) { return TWO ? 2 * (w / p.n_tiles) + mrank : w / p.n_tiles; };
+  // PAIR: every TMA of a stage completes on the leader's (rank 0) full barrier
+  auto lead_full = [&](int s) { return PAIR ? mapa_u32(full_bar(s), 0u) : full_bar(s); };
   const int kb0 = crank * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
   const int cols_per = (TOKN + S - 1) / S;               // columns finished by each cluster rank
   if (SPLIT) cluster_arrive();                           // phase A: every CTA of the cluster has started
@@ -193,12 +226,24 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       int stage = 0; uint32_t phase = 0;
       auto load_a = [&](int st, int kb, int m_tile) {
         const uint32_t a_dst = smem_base + st * STAGE_BYTES;
-        if (GATED) {
+        if (PAIR) {
+          if (GATED) {
+            tma_load_2d_cg2(a_dst, &tmap_w, lead_full(st), kb * BLK_K, m_tile * 64);
+            tma_load_2d_cg2(a_dst + 64 * BLK_K * 2, &tmap_w, lead_full(st), kb * BLK_K, p.N + m_tile * 64);
+          } else {
+            tma_load_2d_cg2(a_dst, &tmap_w, lead_full(st), kb * BLK_K, m_tile * BLK_M);
+          }
+        } else if (GATED) {
           tma_load_2d(a_dst, &tmap_w, full_bar(st), kb * BLK_K, m_tile * 64);                          // gate rows
           tma_load_2d(a_dst + 64 * BLK_K * 2, &tmap_w, full_bar(st), kb * BLK_K, p.N + m_tile * 64);   // up rows
         } else {
           tma_load_2d(a_dst, &tmap_w, full_bar(st), kb * BLK_K, m_tile * BLK_M);
         }
+      };
+      // the barrier that counts a stage's bytes: own (48 KB) or, PAIR, the leader's for both CTAs (2 x 32 KB)
+      auto expect = [&](int st) {
+        if (!PAIR) mbar_expect_tx(full_bar(st), STAGE_BYTES);
+        else if (mrank == 0) mbar_expect_tx(full_bar(st), 2 * STAGE_BYTES);
       };
       // Weights do not depend on the previous kernel: stream the first stages of W while it is
       // still running, then wait for its output (the activations) and add the X tiles.
@@ -206,13 +251,14 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       auto load_b = [&](int st, int kb, int n_tile) {
         const uint32_t b_dst = smem_base + st * STAGE_BYTES + A_BYTES;
         if (MCAST) tma_load_2d_mcast(b_dst + mrank * (128 * BLK_K * 2), &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN + mrank * 128, (uint16_t)3);
+        else if (PAIR) tma_load_2d_cg2(b_dst, &tmap_x, lead_full(st), kb * BLK_K, n_tile * TOKN + mrank * 128);
         else tma_load_2d(b_dst, &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN);
       };
       if (w_first < total) {
         const int m_tile = m_tile_of(w_first);
         pre = min(STAGES, kb1 - kb0);
         for (int i = 0; i < pre; ++i) {
-          mbar_expect_tx(full_bar(i), STAGE_BYTES);
+          expect(i);
           load_a(i, kb0 + i, m_tile);
         }
       }
@@ -224,7 +270,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
             load_b(stage, kb, n_tile);
           } else {
             mbar_wait(empty_bar(stage), phase ^ 1);
-            mbar_expect_tx(full_bar(stage), STAGE_BYTES);
+            expect(stage);
             load_a(stage, kb, m_tile);
             load_b(stage, kb, n_tile);
           }
@@ -233,7 +279,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       }
     }
   } else if (warp == 1) {
-    if (lane == 0) {
+    if (lane == 0 && (!PAIR || mrank == 0)) {          // PAIR: the leader issues for both CTAs
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
       for (int w = w_first; w < total; w += w_step) {
@@ -248,13 +294,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
 #pragma unroll
           for (int k = 0; k < BLK_K / UMMA_K; ++k) {
             // +32 B per 16-element k step inside the 128 B swizzle row (start address field is >>4)
-            tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            if (PAIR) tc_mma_bf16_cg2(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+            else tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
           if (MCAST) tc_commit_mcast(empty_bar(stage), (uint16_t)3);   // both CTAs' producers wait for both MMAs
+          else if (PAIR) tc_commit_cg2(empty_bar(stage), (uint16_t)3); // frees the stage in both CTAs
           else tc_commit(empty_bar(stage));     // frees the smem slot when these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        tc_commit(tfull_bar(acc));              // accumulator complete
+        if (PAIR) tc_commit_cg2(tfull_bar(acc), (uint16_t)3);   // both CTAs' epilogues
+        else tc_commit(tfull_bar(acc));         // accumulator complete
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
     }
@@ -297,7 +346,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        if (lane == 0) { if (PAIR) mbar_arrive_cluster(mapa_u32(tempty_bar(acc), 0u)); else mbar_arrive(tempty_bar(acc)); }
       } else if (!SPLIT) {
         // Gate rows live in warps q=0,1 and their up rows in warps q=2,3 (TMEM lane quarters), so each
         // pair swaps half of every 16-column chunk through shared memory: the gate warp finishes
@@ -331,7 +380,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         }
         tc_fence_before();
         __syncwarp();
-        if (lane == 0) mbar_arrive(tempty_bar(acc));
+        if (lane == 0) { if (PAIR) mbar_arrive_cluster(mapa_u32(tempty_bar(acc), 0u)); else mbar_arrive(tempty_bar(acc)); }
       } else {
         cluster_wait();                          // phase A done: peers' shared memory is live
 #pragma unroll 1
@@ -374,10 +423,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (MCAST) { cluster_arrive(); cluster_wait(); }      // the peer may still signal my barriers until it is done too
+  if (MCAST || PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
   if (warp == 2) {
     tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+    else asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
   }
 }
 
@@ -413,16 +463,16 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
   return 0;
 }
 
-template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false>
+template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false, bool PAIR = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
-  constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
+  constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
   constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
   constexpr int budget = 224 * 1024 - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, MCAST>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, MCAST, PAIR>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -438,7 +488,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
-  } else if (MCAST) {
+  } else if (MCAST || PAIR) {
     const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
     cfg.gridDim = dim3(2 * (pairs < 74 ? pairs : 74));
     attr[1].id = cudaLaunchAttributeClusterDimension;
@@ -508,8 +558,8 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
   return g;
 }
 
-// prefill-sized problems share the X tile between the two CTAs of a cluster (TMA multicast)
-static bool gemm_uses_mcast(const GemmPlan& g) { return g.tokn == 256 && g.splits == 1 && g.m_tiles >= 2; }
+// prefill-sized problems run as CTA pairs (cta_group::2, 256 x 256 MMA tiles)
+static bool gemm_uses_pair(const GemmPlan& g) { return g.tokn == 256 && g.splits == 1 && g.m_tiles >= 2; }
 
 template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
@@ -527,7 +577,7 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
     case 64: return launch_gemm<64, false, GATED>(tw, tx, p, st);
     case 128: return launch_gemm<128, false, GATED>(tw, tx, p, st);
     default:
-      if (gemm_uses_mcast(g)) return launch_gemm<256, false, GATED, true>(tw, tx, p, st);
+      if (gemm_uses_pair(g)) return launch_gemm<256, false, GATED, false, true>(tw, tx, p, st);
       return launch_gemm<256, false, GATED>(tw, tx, p, st);
   }
 }
@@ -556,7 +606,7 @@ extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* 
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w, N, K, BLK_M)) return rc;
-  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_mcast(g) ? 128 : g.tokn)) return rc;
+  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_pair(g) ? 128 : g.tokn)) return rc;
   cudaStream_t st = (cudaStream_t)stream;
   return dispatch_gemm<false>(g, tw, tx, p, st);
 }
@@ -575,6 +625,6 @@ extern "C" int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gat
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, 64)) return rc;     // 64-row boxes: gate half, up half
-  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_mcast(g) ? 128 : g.tokn)) return rc;
+  if (int rc = make_tmap(&tx, x, T, K, gemm_uses_pair(g) ? 128 : g.tokn)) return rc;
   return dispatch_gemm<true>(g, tw, tx, p, (cudaStream_t)stream);
 }

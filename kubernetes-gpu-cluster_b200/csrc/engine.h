@@ -71,6 +71,11 @@ struct kge_engine {
   std::vector<std::pair<int64_t, int>> graph_seen;   // key hash -> eager runs so far
   bool use_graphs = true;
 
+  // mixed steps: the scheduler lists running (decode) requests first; the forward pass sends that
+  // prefix to the decode attention kernel and the rest to the prefill kernel
+  int step_num_decode = 0, step_dec_max_seq = 1;
+  double step_dec_sum_seq = 0;
+
   std::unique_ptr<kge::Scheduler> sched;
   int64_t launches = 0;
   int64_t h2d_bytes = 0, d2h_bytes = 0;      // metadata in / sampled ids out, summed over steps

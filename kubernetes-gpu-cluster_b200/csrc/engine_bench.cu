@@ -56,6 +56,7 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   KGE_CUDA_OK(cudaSetDevice(e->cfg.device));
   const bool was_timing = e->timing;
   e->timing = false;
+  e->step_num_decode = 0;                 // resident steps are pure prefill or pure decode
 
   // ---- build every step's metadata on the host (untimed)
   std::vector<ResidentStep> steps;

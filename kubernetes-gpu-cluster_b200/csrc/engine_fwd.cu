@@ -70,6 +70,25 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
   const int c_att = max_q_len == 1 ? C_ATT_DEC : C_ATT_GEN;
   const double att_bytes = sum_seq * KVl * hd * 4.0 + (double)T * Hl * hd * 4.0;
   const double att_fl = attn_flops * Hl * hd;
+  const int D = (max_q_len > 1 && e->step_num_decode > 0 && e->step_num_decode < B) ? e->step_num_decode : 0;
+  const double dec_bytes = e->step_dec_sum_seq * KVl * hd * 4.0 + (double)D * Hl * hd * 4.0;
+  // attention of layer i: one launch, or (mixed step) decode kernel for the leading D one-token requests
+  // + prefill kernel for the others; query_start_loc entries are absolute rows, so sub-batches only
+  // offset the per-request arrays
+  auto attend = [&](int i) -> int {
+    if (D == 0) {
+      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+                         max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+      return 0;
+    }
+    FWD(C_ATT_DEC, dec_bytes, 4.0 * e->step_dec_sum_seq * Hl * hd,
+        kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, D, D, 1,
+                       e->step_dec_max_seq, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+    FWD(C_ATT_GEN, att_bytes - dec_bytes, att_fl - 4.0 * e->step_dec_sum_seq * Hl * hd,
+        kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab + (int64_t)D * max_blocks, max_blocks, m.seq_lens + D,
+                       m.qsl + D, B - D, T - D, max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+    return 0;
+  };
   const double rope_bytes = (double)T * (Hl + 2 * KVl) * hd * 2 * 2;
   const double ar_bytes = Td2;
   if (s.is_opt()) {
@@ -80,8 +99,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       FWD(C_NORM, (i ? 4 : 2) * Td2, 0, kge_layernorm(e->xn, e->res, i == 0 ? nullptr : e->h, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
       FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
-      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
-                         max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+      if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
       if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
       FWD(C_NORM, 4 * Td2, 0, kge_layernorm(e->xn, e->res, e->h, L.ln2_w, L.ln2_b, T, d, 1e-5f, st));
@@ -98,8 +116,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       else FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
       FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
-      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
-                         max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
+      if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
       if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
       FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
@@ -209,8 +226,17 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
   }
   int max_q = 1, max_seq = 1;
   double sum_seq = 0, attn_flops = 0;
+  e->step_num_decode = 0; e->step_dec_max_seq = 1; e->step_dec_sum_seq = 0;
+  bool prefix = true;
   for (int i = 0; i < B; ++i) {
     const int ql = b->query_start_loc[i + 1] - b->query_start_loc[i];
+    if (prefix && ql == 1) {
+      ++e->step_num_decode;
+      e->step_dec_max_seq = std::max(e->step_dec_max_seq, b->seq_lens[i]);
+      e->step_dec_sum_seq += b->seq_lens[i];
+    } else {
+      prefix = false;
+    }
     sum_seq += b->seq_lens[i];
     attn_flops += 4.0 * ql * ((double)(b->seq_lens[i] - ql) + 0.5 * (ql + 1));
     KGE_REQUIRE(ql >= 1 && ql <= b->seq_lens[i], "kge_step: request %d has q_len=%d seq_len=%d", i, ql, b->seq_lens[i]);

@@ -43,6 +43,12 @@ int kge_rmsnorm(void* y, const void* x, const void* w, int T, int d, float eps, 
 int kge_add_rmsnorm(void* y, void* residual, const void* x, const void* w, int T, int d,
                     float eps, void* stream);
 
+/* Per-head RMSNorm of the q and k parts of a packed qkv buffer [T,(H+2KV)*hd], in place, before RoPE:
+ * Qwen3's q_norm / k_norm (vllm:model_executor/models/qwen3.py:142-160), weights [hd] each, same
+ * arithmetic as kge_rmsnorm over head_dim. */
+int kge_head_rmsnorm(void* qkv, const void* q_weight, const void* k_weight, int T, int H, int KV, int hd,
+                     float eps, void* stream);
+
 /* LayerNorm (OPT), vllm:model_executor/models/opt.py:148-150,166-168,250-253.
  * If `add` is non-NULL: h = bf16(fp32(residual)+fp32(add)) is written back to `residual`
  * first (opt.py:181,194) and the norm is taken of h; y may be NULL (add only). */

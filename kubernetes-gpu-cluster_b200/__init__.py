@@ -65,6 +65,7 @@ SIGNATURES = {
     "kge_embed": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _P]),
     "kge_rmsnorm": (_I, [_P, _P, _P, _I, _I, _F, _P]),
     "kge_add_rmsnorm": (_I, [_P, _P, _P, _P, _I, _I, _F, _P]),
+    "kge_head_rmsnorm": (_I, [_P, _P, _P, _I, _I, _I, _I, _F, _P]),
     "kge_layernorm": (_I, [_P, _P, _P, _P, _P, _I, _I, _F, _P]),
     "kge_silu_mul": (_I, [_P, _P, _I, _I, _P]),
     "kge_gemm_bf16": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _L, _P]),

@@ -213,6 +213,30 @@ __global__ void rope_kvwrite_kernel(bf16* __restrict__ qkv, const bf16* __restri
   }
 }
 
+// ------------------------------------------------------------------------ per-head RMSNorm (Qwen3)
+// One warp per (token, q or k head): rms_norm over head_dim with vLLM's cast points, in place.
+__global__ void head_rmsnorm_kernel(bf16* __restrict__ qkv, const bf16* __restrict__ qw, const bf16* __restrict__ kw,
+                                    int T, int H, int KV, int hd, float eps) {
+  pdl_launch_dependents();
+  pdl_wait();
+  const int lane = threadIdx.x & 31;
+  const int64_t item = (int64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (item >= (int64_t)T * (H + KV)) return;
+  const int t = (int)(item / (H + KV)), head = (int)(item % (H + KV));
+  bf16* row = qkv + (int64_t)t * (H + 2 * KV) * hd + head * hd;
+  const bf16* w = head < H ? qw : kw;
+  const int per = hd / 32;                          // 2 (hd 64) or 4 (hd 128) elements per lane
+  float v[4], ss = 0.f;
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (i < per) { v[i] = bf2f(row[lane * per + i]); ss += v[i] * v[i]; }
+  ss = warp_sum(ss);
+  const float rstd = 1.0f / sqrtf(ss / (float)hd + eps);
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (i < per) row[lane * per + i] = f2bf(rbf(v[i] * rstd) * bf2f(w[lane * per + i]));
+}
+
 // ------------------------------------------------------------------------ greedy argmax
 // One CTA per row; 128-bit loads; ties resolve to the lowest index (torch.argmax semantics).
 __global__ void __launch_bounds__(1024)
@@ -337,6 +361,17 @@ extern "C" int kge_rope_kvwrite(void* qkv, const void* cos_sin, const int32_t* p
   if (th > 256) th = 256;
   KGE_CUDA_OK(launch_pdl(rope_kvwrite_kernel, dim3(T), dim3(th), 0, (cudaStream_t)stream, (bf16*)qkv, (const bf16*)cos_sin,
                          positions, slot_mapping, (bf16*)k_cache, (bf16*)v_cache, H, KV, hd, block_size));
+  return 0;
+}
+
+extern "C" int kge_head_rmsnorm(void* qkv, const void* q_weight, const void* k_weight, int T, int H, int KV, int hd,
+                                float eps, void* stream) {
+  KGE_REQUIRE(qkv && q_weight && k_weight, "kge_head_rmsnorm: null pointer");
+  KGE_REQUIRE(hd == 64 || hd == 128, "kge_head_rmsnorm: head_dim=%d unsupported (64, 128)", hd);
+  if (T <= 0) return 0;
+  const int64_t items = (int64_t)T * (H + KV);
+  KGE_CUDA_OK(launch_pdl(head_rmsnorm_kernel, dim3((unsigned)((items + 7) / 8)), dim3(256), 0, (cudaStream_t)stream, (bf16*)qkv,
+                         (const bf16*)q_weight, (const bf16*)k_weight, T, H, KV, hd, eps));
   return 0;
 }
 

@@ -94,7 +94,11 @@ static bool build_llama(Builder& b) {
         !(L.up.w = b.dalloc((int64_t)2 * fl * d)) || !(L.down.w = b.dalloc((int64_t)d * fl)) ||
         !(L.ln1_w = b.dalloc(d)) || !(L.ln2_w = b.dalloc(d)))
       return false;
+    if (s.qkv_bias && !(L.qkv.b = b.dalloc(L.qkv.N))) return false;
+    if (s.qk_norm && (!(L.q_norm = b.dalloc(hd)) || !(L.k_norm = b.dalloc(hd)))) return false;
     if (b.dummy()) {
+      if (s.qkv_bias) b.cst(L.qkv.b, L.qkv.N, 0.f);
+      if (s.qk_norm) { b.cst(L.q_norm, hd, 1.f); b.cst(L.k_norm, hd, 1.f); }
       b.rnd(L.qkv.w, (int64_t)L.qkv.N * d, kDummyScale);
       b.rnd(L.o.w, (int64_t)d * nq, kDummyScale);
       b.rnd(L.up.w, (int64_t)2 * fl * d, kDummyScale);
@@ -107,6 +111,15 @@ static bool build_llama(Builder& b) {
     if (!b.put(L.qkv.w, 0, p + "self_attn.q_proj.weight", (int64_t)rk * nq, (int64_t)(rk + 1) * nq, 0, -1)) return false;
     if (!b.put(L.qkv.w, (int64_t)nq * d, p + "self_attn.k_proj.weight", (int64_t)kv0 * hd, (int64_t)(kv0 + KVl) * hd, 0, -1)) return false;
     if (!b.put(L.qkv.w, (int64_t)(nq + nkv) * d, p + "self_attn.v_proj.weight", (int64_t)kv0 * hd, (int64_t)(kv0 + KVl) * hd, 0, -1)) return false;
+    if (s.qkv_bias) {
+      if (!b.put(L.qkv.b, 0, p + "self_attn.q_proj.bias", (int64_t)rk * nq, (int64_t)(rk + 1) * nq, 0, -1)) return false;
+      if (!b.put(L.qkv.b, nq, p + "self_attn.k_proj.bias", (int64_t)kv0 * hd, (int64_t)(kv0 + KVl) * hd, 0, -1)) return false;
+      if (!b.put(L.qkv.b, nq + nkv, p + "self_attn.v_proj.bias", (int64_t)kv0 * hd, (int64_t)(kv0 + KVl) * hd, 0, -1)) return false;
+    }
+    if (s.qk_norm) {
+      if (!b.put(L.q_norm, 0, p + "self_attn.q_norm.weight", 0, -1, 0, -1)) return false;
+      if (!b.put(L.k_norm, 0, p + "self_attn.k_norm.weight", 0, -1, 0, -1)) return false;
+    }
     if (!b.put(L.o.w, 0, p + "self_attn.o_proj.weight", 0, -1, (int64_t)rk * nq, (int64_t)(rk + 1) * nq)) return false;
     if (!b.put(L.up.w, 0, p + "mlp.gate_proj.weight", (int64_t)rk * fl, (int64_t)(rk + 1) * fl, 0, -1)) return false;
     if (!b.put(L.up.w, (int64_t)fl * d, p + "mlp.up_proj.weight", (int64_t)rk * fl, (int64_t)(rk + 1) * fl, 0, -1)) return false;

@@ -24,6 +24,7 @@ struct Linear {
 struct LayerW {
   Linear qkv, o, up, down;           // up = gate_up (llama, [2f,d]) or fc1 (opt)
   bf16 *ln1_w = nullptr, *ln1_b = nullptr, *ln2_w = nullptr, *ln2_b = nullptr;
+  bf16 *q_norm = nullptr, *k_norm = nullptr;   // qwen3: [hd] each
 };
 
 // Per-step metadata, laid out once in pinned host memory and mirrored on the device with the

@@ -115,6 +115,8 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
       else FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
+      if (s.qk_norm)
+        FWD(C_NORM, (double)T * (Hl + KVl) * hd * 4, 0, kge_head_rmsnorm(e->qkv, L.q_norm, L.k_norm, T, Hl, KVl, hd, s.eps, st));
       FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
       if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);

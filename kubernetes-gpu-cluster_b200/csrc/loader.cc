@@ -48,12 +48,19 @@ static bool parse_config(const Json& j, ModelSpec* s, std::string* err) {
     if (!j.bool_or("do_layer_norm_before", true)) { *err = "OPT with do_layer_norm_before=false (opt-350m) is not supported"; return false; }
     if (j.int_or("word_embed_proj_dim", s->d) != s->d) { *err = "OPT with word_embed_proj_dim != hidden_size is not supported"; return false; }
     if (j.str_or("activation_function", "relu") != "relu") { *err = "OPT activation_function must be relu"; return false; }
-  } else if (s->model_type == "llama") {
+  } else if (s->model_type == "llama" || s->model_type == "qwen2" || s->model_type == "qwen3") {
+    // Qwen2.5 / Qwen3 (the models the reference's values files deploy, ref:values-01-minimal-example2.yaml:8,
+    // ...example8.yaml:8) share Llama's graph: vllm:model_executor/models/qwen2.py:160-175, qwen3.py:142-160
+    const bool qwen = s->model_type != "llama";
+    s->qkv_bias = s->model_type == "qwen2";
+    s->qk_norm = s->model_type == "qwen3";
     s->KV = (int)j.int_or("num_key_value_heads", s->H);
     s->ffn = (int)j.int_or("intermediate_size", 0);
     s->tied = j.bool_or("tie_word_embeddings", false);
-    s->eps = (float)j.num_or("rms_norm_eps", 1e-5);
-    s->rope_theta = j.num_or("rope_theta", 10000.0);
+    s->eps = (float)j.num_or("rms_norm_eps", qwen ? 1e-6 : 1e-5);
+    s->rope_theta = j.num_or("rope_theta", qwen ? 1000000.0 : 10000.0);
+    if (const Json* rp = j.get("rope_parameters"))
+      if (rp->is_obj()) s->rope_theta = rp->num_or("rope_theta", s->rope_theta);
     if (const Json* rs = j.get("rope_scaling")) {
       if (rs->is_obj()) {
         std::string t = rs->str_or("rope_type", rs->str_or("type", ""));
@@ -68,9 +75,11 @@ static bool parse_config(const Json& j, ModelSpec* s, std::string* err) {
         }
       }
     }
-    if (j.bool_or("attention_bias", false) || j.bool_or("mlp_bias", false)) { *err = "llama with attention_bias/mlp_bias is not supported"; return false; }
+    if (!qwen && (j.bool_or("attention_bias", false) || j.bool_or("mlp_bias", false))) { *err = "llama with attention_bias/mlp_bias is not supported"; return false; }
+    if (s->model_type == "qwen3" && j.bool_or("attention_bias", false)) { *err = "qwen3 with attention_bias is not supported"; return false; }
+    if (j.bool_or("use_sliding_window", false)) { *err = "sliding-window attention is not supported"; return false; }
   } else {
-    *err = "unsupported model_type '" + s->model_type + "' (opt, llama)";
+    *err = "unsupported model_type '" + s->model_type + "' (opt, llama, qwen2, qwen3)";
     return false;
   }
   if (s->H <= 0 || s->d <= 0 || s->L <= 0 || s->vocab <= 0 || s->ffn <= 0) { *err = "config.json misses a required size"; return false; }

@@ -10,7 +10,9 @@
 namespace kge {
 
 struct ModelSpec {
-  std::string model_type;       // "opt" | "llama"
+  std::string model_type;       // "opt" | "llama" | "qwen2" | "qwen3"
+  bool qkv_bias = false;        // qwen2: q/k/v projections carry a bias
+  bool qk_norm = false;         // qwen3: RMSNorm over head_dim on q and k, per head, before RoPE
   int vocab = 0, d = 0, L = 0, H = 0, KV = 0, hd = 0, ffn = 0, max_pos = 0;
   float eps = 1e-5f;
   bool tied = false;

@@ -3,6 +3,8 @@
 TEST INFRASTRUCTURE (see oracle/__init__.py).  Restates, op by op and cast by cast:
   - OPT      vllm:model_executor/models/opt.py:61-70,120-124,170-197,268-295,384-385
   - Llama    vllm:model_executor/models/llama.py:94-121,223-233,316-333,395-434
+  - Qwen2    vllm:model_executor/models/qwen2.py:160-175 (Llama graph + q/k/v bias)
+  - Qwen3    vllm:model_executor/models/qwen3.py:142-160 (Llama graph + per-head RMSNorm of q and k before RoPE)
   - RMSNorm  vllm:ir/ops/layernorm.py:10-21,40-58
   - SiLU*mul vllm:model_executor/layers/activation.py:137-141
   - RoPE     vllm:model_executor/layers/rotary_embedding/base.py:69-93,140-184
@@ -42,6 +44,8 @@ class ModelConfig:
     bos: int = 0
     eos: int = 0
     name: str = ""
+    qkv_bias: bool = False      # qwen2
+    qk_norm: bool = False       # qwen3
 
     def to_hf(self) -> dict:
         """HF-layout config.json (the same file the product's loader reads)."""
@@ -58,8 +62,9 @@ class ModelConfig:
                 "bos_token_id": self.bos, "eos_token_id": self.eos, "pad_token_id": 1,
                 "torch_dtype": "bfloat16",
             }
+        arch = {"llama": "LlamaForCausalLM", "qwen2": "Qwen2ForCausalLM", "qwen3": "Qwen3ForCausalLM"}[self.model_type]
         d = {
-            "model_type": "llama", "architectures": ["LlamaForCausalLM"],
+            "model_type": self.model_type, "architectures": [arch],
             "vocab_size": self.vocab_size, "hidden_size": self.hidden_size,
             "num_hidden_layers": self.num_layers, "intermediate_size": self.ffn,
             "num_attention_heads": self.num_heads, "num_key_value_heads": self.num_kv_heads,
@@ -69,6 +74,8 @@ class ModelConfig:
             "bos_token_id": self.bos, "eos_token_id": self.eos,
             "torch_dtype": "bfloat16", "attention_bias": False, "mlp_bias": False,
         }
+        if self.model_type != "llama":
+            d.pop("attention_bias"); d.pop("mlp_bias")
         if self.rope_scaling:
             d["rope_scaling"] = dict(self.rope_scaling)
         return d
@@ -99,6 +106,11 @@ CONFIGS: dict[str, ModelConfig] = {
                               500000.0, _llama3_scaling(8.0), 1, 2, "tiny-llama"),
     "tiny-llama-hd128": ModelConfig("llama", 2048, 512, 3, 4, 1, 128, 1024, 16384, 1e-5, True,
                                     500000.0, _llama3_scaling(32.0), 1, 2, "tiny-llama-hd128"),
+    # the model families the reference's values files deploy (Qwen2.5 / Qwen3), tiny shapes
+    "tiny-qwen2": ModelConfig("qwen2", 1024, 256, 2, 4, 2, 64, 512, 4096, 1e-6, True, 1000000.0, None, 1, 2,
+                              "tiny-qwen2", qkv_bias=True),
+    "tiny-qwen3": ModelConfig("qwen3", 1024, 256, 2, 2, 1, 128, 512, 4096, 1e-6, True, 1000000.0, None, 1, 2,
+                              "tiny-qwen3", qk_norm=True),
     "small-opt": ModelConfig("opt", 50272, 768, 2, 12, 12, 64, 3072, 2048, 1e-5, True,
                              bos=2, eos=2, name="small-opt (opt-125m shape, 2 layers)"),
     "small-llama": ModelConfig("llama", 128256, 2048, 2, 32, 8, 64, 8192, 131072, 1e-5, True,
@@ -115,14 +127,15 @@ def config_from_hf(d: dict) -> ModelConfig:
                            d["hidden_size"] // d["num_attention_heads"], d["ffn_dim"],
                            d["max_position_embeddings"], 1e-5, True,
                            bos=d.get("bos_token_id", 2), eos=d.get("eos_token_id", 2))
-    if mt == "llama":
+    if mt in ("llama", "qwen2", "qwen3"):
         hd = d.get("head_dim") or d["hidden_size"] // d["num_attention_heads"]
-        return ModelConfig("llama", d["vocab_size"], d["hidden_size"], d["num_hidden_layers"],
+        return ModelConfig(mt, d["vocab_size"], d["hidden_size"], d["num_hidden_layers"],
                            d["num_attention_heads"], d.get("num_key_value_heads", d["num_attention_heads"]),
                            hd, d["intermediate_size"], d["max_position_embeddings"],
                            d.get("rms_norm_eps", 1e-5), d.get("tie_word_embeddings", False),
-                           d.get("rope_theta", 10000.0), d.get("rope_scaling"),
-                           d.get("bos_token_id", 1), d.get("eos_token_id", 2))
+                           d.get("rope_theta", 10000.0 if mt == "llama" else 1000000.0), d.get("rope_scaling"),
+                           d.get("bos_token_id", 1), d.get("eos_token_id", 2),
+                           qkv_bias=(mt == "qwen2"), qk_norm=(mt == "qwen3"))
     raise ValueError(f"unsupported model_type {mt}")
 
 
@@ -174,6 +187,13 @@ def make_weights(cfg: ModelConfig, seed: int = 0, dtype=torch.bfloat16,
             w[q + "self_attn.k_proj.weight"] = mat(KV * hd, d)
             w[q + "self_attn.v_proj.weight"] = mat(KV * hd, d)
             w[q + "self_attn.o_proj.weight"] = mat(d, H * hd)
+            if cfg.qkv_bias:
+                w[q + "self_attn.q_proj.bias"] = mat(H * hd)
+                w[q + "self_attn.k_proj.bias"] = mat(KV * hd)
+                w[q + "self_attn.v_proj.bias"] = mat(KV * hd)
+            if cfg.qk_norm:
+                w[q + "self_attn.q_norm.weight"] = norm_w(hd)
+                w[q + "self_attn.k_norm.weight"] = norm_w(hd)
             w[q + "mlp.gate_proj.weight"] = mat(f, d)
             w[q + "mlp.up_proj.weight"] = mat(f, d)
             w[q + "mlp.down_proj.weight"] = mat(d, f)
@@ -238,6 +258,13 @@ def make_shapes(cfg: ModelConfig) -> dict[str, tuple]:
             s[q + "self_attn.k_proj.weight"] = (KV * hd, d)
             s[q + "self_attn.v_proj.weight"] = (KV * hd, d)
             s[q + "self_attn.o_proj.weight"] = (d, H * hd)
+            if cfg.qkv_bias:
+                s[q + "self_attn.q_proj.bias"] = (H * hd,)
+                s[q + "self_attn.k_proj.bias"] = (KV * hd,)
+                s[q + "self_attn.v_proj.bias"] = (KV * hd,)
+            if cfg.qk_norm:
+                s[q + "self_attn.q_norm.weight"] = (hd,)
+                s[q + "self_attn.k_norm.weight"] = (hd,)
             s[q + "mlp.gate_proj.weight"] = (f, d)
             s[q + "mlp.up_proj.weight"] = (f, d)
             s[q + "mlp.down_proj.weight"] = (d, f)
@@ -392,12 +419,14 @@ class OracleModel:
             if key not in _memo:
                 _memo[key] = torch.cat([self.w[n] for n in names], 0)
             return _memo[key]
-        if c.model_type == "llama":
+        if c.model_type != "opt":
             self.cos_sin = rope_cos_sin_cache(c, max_pos or min(c.max_position, 8192), dtype)
             # fused row orders as in QKVParallelLinear / MergedColumnParallelLinear
             self.qkv = [cat([f"model.layers.{i}.self_attn.{n}_proj.weight" for n in "qkv"]) for i in range(L)]
             self.gate_up = [cat([f"model.layers.{i}.mlp.gate_proj.weight", f"model.layers.{i}.mlp.up_proj.weight"])
                             for i in range(L)]
+            self.qkv_b = ([cat([f"model.layers.{i}.self_attn.{n}_proj.bias" for n in "qkv"]) for i in range(L)]
+                          if c.qkv_bias else [None] * L)
             self.lm_head = self.w["model.embed_tokens.weight"] if c.tied else self.w["lm_head.weight"]
         else:
             p = "model.decoder.layers."
@@ -438,7 +467,7 @@ class OracleModel:
         pos = torch.cat([torch.arange(kv.length, kv.length + qsl[b + 1] - qsl[b])
                          for b, kv in enumerate(kvs)])
         H, KV, hd = c.num_heads, c.num_kv_heads, c.head_dim
-        if c.model_type == "llama":
+        if c.model_type != "opt":
             h = F.embedding(ids, w["model.embed_tokens.weight"])
             res = None
             cs = self.cos_sin.index_select(0, pos)
@@ -450,11 +479,15 @@ class OracleModel:
                     h = rms_norm(h, w[pre + "input_layernorm.weight"], c.eps)
                 else:
                     h, res = fused_add_rms_norm(h, res, w[pre + "input_layernorm.weight"], c.eps)
-                qkv = F.linear(h, self.qkv[i])
+                qkv = F.linear(h, self.qkv[i], self.qkv_b[i])
                 q, k, v = qkv.split([H * hd, KV * hd, KV * hd], dim=-1)
                 T = q.shape[0]
-                q = apply_rope_neox(q.reshape(T, H, hd), cos, sin).reshape(T, H * hd)
-                k = apply_rope_neox(k.reshape(T, KV, hd), cos, sin).reshape(T, KV * hd)
+                q, k = q.reshape(T, H, hd), k.reshape(T, KV, hd)
+                if c.qk_norm:   # qwen3.py:150-158: RMSNorm over head_dim, per head, before RoPE
+                    q = rms_norm(q, w[pre + "self_attn.q_norm.weight"], c.eps)
+                    k = rms_norm(k, w[pre + "self_attn.k_norm.weight"], c.eps)
+                q = apply_rope_neox(q, cos, sin).reshape(T, H * hd)
+                k = apply_rope_neox(k, cos, sin).reshape(T, KV * hd)
                 a = self._attend(i, q, k, v, kvs, qsl)
                 h = F.linear(a, w[pre + "self_attn.o_proj.weight"])
                 h, res = fused_add_rms_norm(h, res, w[pre + "post_attention_layernorm.weight"], c.eps)

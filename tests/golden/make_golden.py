@@ -84,15 +84,20 @@ def ops_vllm():
 
 
 def hf_models():
-    from transformers import LlamaConfig, LlamaForCausalLM, OPTConfig, OPTForCausalLM
+    from transformers import (LlamaConfig, LlamaForCausalLM, OPTConfig, OPTForCausalLM, Qwen2Config, Qwen2ForCausalLM,
+                              Qwen3Config, Qwen3ForCausalLM)
     out = {}
-    for name in ("tiny-opt", "tiny-llama", "tiny-llama-hd128"):
+    for name in ("tiny-opt", "tiny-llama", "tiny-llama-hd128", "tiny-qwen2", "tiny-qwen3"):
         c = om.CONFIGS[name]
         w = om.make_weights(c, seed=0, dtype=torch.float32)
         hf = c.to_hf()
         hf.pop("torch_dtype")
         if c.model_type == "opt":
             m = OPTForCausalLM(OPTConfig(**hf))
+        elif c.model_type == "qwen2":
+            m = Qwen2ForCausalLM(Qwen2Config(**hf))
+        elif c.model_type == "qwen3":
+            m = Qwen3ForCausalLM(Qwen3Config(**hf))
         else:
             m = LlamaForCausalLM(LlamaConfig(**hf))
         sd = dict(w)

@@ -52,7 +52,7 @@ def compare_greedy(got, ref_ids, ref_logits):
     return equal, near_tie
 
 
-@pytest.mark.parametrize("name", ["tiny-opt", "tiny-llama", "tiny-llama-hd128"])
+@pytest.mark.parametrize("name", ["tiny-opt", "tiny-llama", "tiny-llama-hd128", "tiny-qwen2", "tiny-qwen3"])
 def test_greedy_generation_matches_oracle(kge, model_dirs, name):
     cfg, w, d = model_dirs(name)
     prompts = [om.make_prompts(cfg, 1, n, seed=n)[0] for n in (5, 16, 17, 33, 64, 100)]

@@ -115,6 +115,25 @@ def test_layernorm_modes(kge, L, T, d):
     assert_near_exact(y, om.layer_norm(h, w, b))
 
 
+@pytest.mark.parametrize("hd", [64, 128])
+def test_head_rmsnorm_qwen3(kge, L, hd):
+    g = torch.Generator().manual_seed(hd)
+    T, H, KV = 9, 4, 2
+    qkv = torch.randn(T, (H + 2 * KV) * hd, generator=g).to(BF)
+    qw = (1 + 0.1 * torch.randn(hd, generator=g)).to(BF)
+    kw = (1 + 0.1 * torch.randn(hd, generator=g)).to(BF)
+    qd, qwd, kwd = dev(qkv), dev(qw), dev(kw)
+    check_ok(kge, L.kge_head_rmsnorm(p(qd), p(qwd), p(kwd), T, H, KV, hd, 1e-6, None), "head_rmsnorm")
+    sync()
+    q, k, v = qkv.split([H * hd, KV * hd, KV * hd], dim=-1)
+    eq = om.rms_norm(q.reshape(T, H, hd), qw, 1e-6).reshape(T, -1)
+    ek = om.rms_norm(k.reshape(T, KV, hd), kw, 1e-6).reshape(T, -1)
+    got = qd.cpu()
+    assert_near_exact(got[:, :H * hd], eq)
+    assert_near_exact(got[:, H * hd:(H + KV) * hd], ek)
+    assert torch.equal(got[:, (H + KV) * hd:], v)
+
+
 def test_silu_mul(kge, L, golden_dir):
     z = np.load(os.path.join(golden_dir, "ops_vllm.npz"))
     x = torch.from_numpy(z["silu_x"].copy()).view(BF)

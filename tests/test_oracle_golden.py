@@ -62,7 +62,7 @@ def test_top_k_top_p_mask(ops):
     assert torch.equal(got, torch.from_numpy(ops["tkp_masked"]))
 
 
-@pytest.mark.parametrize("name", ["tiny-opt", "tiny-llama", "tiny-llama-hd128"])
+@pytest.mark.parametrize("name", ["tiny-opt", "tiny-llama", "tiny-llama-hd128", "tiny-qwen2", "tiny-qwen3"])
 def test_model_vs_hf_fp32(hf, name):
     """fp32 oracle == HF fp32 to float tolerance: pins graph structure, weight naming,
     fused-row order, OPT position offset and llama3 RoPE scaling."""

@@ -189,6 +189,11 @@ def run_reference(args):
     })
 
 
+def log(msg):
+    sys.stderr.write(f"[bench {time.strftime('%H:%M:%S')} rank {os.environ.get('RANK', '0')}] {msg}\n")
+    sys.stderr.flush()
+
+
 def run_ours(args):
     import torch
     import torch.distributed as dist
@@ -223,6 +228,7 @@ def run_ours(args):
         dist.broadcast(t, 0)
         llm.init_tp(bytes(t.cpu().numpy().tobytes()))
     sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True)
+    log(f"engine ready: {llm.weight_bytes / 1e9:.1f} GB weights, {llm.num_gpu_blocks} KV blocks, tp={tp}")
 
     def barrier():
         torch.cuda.synchronize()
@@ -233,8 +239,9 @@ def run_ours(args):
         return max_over_ranks(x, world)
 
     # ---- value: device-resident replay
-    for _ in range(args.warmup):
-        toks_res, _, _ = llm.run_resident(prompts, pout, pbatch)
+    for i in range(args.warmup):
+        toks_res, ms_w, _ = llm.run_resident(prompts, pout, pbatch)
+        log(f"resident warm-up {i}: {ms_w:.0f} ms")
     barrier()
     clocks = ClockSampler(local)
     clocks.start()
@@ -265,6 +272,7 @@ def run_ours(args):
     e2e_s = mx((time.perf_counter() - t0) / args.steps)
     io1 = llm.io_bytes()
     e2e = job_throughput(replicas, B, pout, e2e_s)
+    log(f"value {value:.0f} tok/s, e2e {e2e:.0f} tok/s")
     toks_e2e = [o.outputs[0].token_ids for o in outs]
     same = sum(a == b for x, y in zip(toks_e2e, toks_res) for a, b in zip(x, y))
 

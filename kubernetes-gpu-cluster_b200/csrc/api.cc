@@ -3,8 +3,10 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <vector>
 
 #include "common.cuh"
@@ -18,6 +20,13 @@ void set_error(const char* fmt, ...) {
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
 }
+static std::atomic<int> g_pdl{-1};   // -1: not decided yet
+bool pdl_enabled() {
+  int v = g_pdl.load(std::memory_order_relaxed);
+  if (v < 0) { v = getenv("KGE_DISABLE_PDL") ? 0 : 1; g_pdl.store(v, std::memory_order_relaxed); }
+  return v != 0;
+}
+void pdl_set_enabled(bool on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
 }  // namespace kge
 
 extern "C" const char* kge_last_error(void) { return kge::g_err; }

@@ -3,11 +3,16 @@
 #include <cuda_bf16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 namespace kge {
 
 // Thread-local error text behind kge_last_error() (api.cc).
 void set_error(const char* fmt, ...);
+// Process-wide switch for programmatic dependent launch (api.cc).  On by default; turned off by
+// KGE_DISABLE_PDL and by tensor-parallel engines (see DESIGN.md "known issues").
+bool pdl_enabled();
+void pdl_set_enabled(bool on);
 
 #define KGE_CUDA_OK(expr)                                                              \
   do {                                                                                 \
@@ -44,7 +49,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = 1;
+  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 

@@ -1,6 +1,7 @@
 // Engine construction: weight loading (TP-sliced), dummy weights, activation arena, KV pool.
 #include "engine.h"
 
+#include <stdlib.h>
 #include <string.h>
 
 #include <algorithm>
@@ -267,6 +268,14 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   e->H_loc = s.H / e->tp_size;
   e->KV_loc = std::max(1, s.KV / e->tp_size);
   e->ffn_loc = s.ffn / e->tp_size;
+  if (getenv("KGE_DISABLE_GRAPHS")) e->use_graphs = false;               // diagnostics only
+  if (e->tp_size > 1) {
+    // Known issue (round 1): Llama-70B at TP=4 deadlocks intermittently between ranks when the
+    // forward pass uses programmatic dependent launch around the NCCL all-reduces; TP engines run
+    // with plain stream order and eager decode steps until that is understood.
+    kge::pdl_set_enabled(false);
+    e->use_graphs = false;
+  }
   if (e->cfg.block_size <= 0) e->cfg.block_size = 16;
   if (e->cfg.block_size & (e->cfg.block_size - 1)) ENGINE_FAIL("kge_engine_create: block_size must be a power of two");
   if (e->cfg.max_model_len <= 0) e->cfg.max_model_len = std::min(s.max_pos, 8192);

@@ -111,6 +111,8 @@ CONFIGS: dict[str, ModelConfig] = {
                               "tiny-qwen2", qkv_bias=True),
     "tiny-qwen3": ModelConfig("qwen3", 1024, 256, 2, 2, 1, 128, 512, 4096, 1e-6, True, 1000000.0, None, 1, 2,
                               "tiny-qwen3", qk_norm=True),
+    "tiny-llama-tp": ModelConfig("llama", 1024, 512, 2, 8, 4, 64, 1024, 16384, 1e-5, False,
+                                 500000.0, _llama3_scaling(8.0), 1, 2, "tiny-llama-tp (8 heads / 4 kv heads for TP 2 and 4)"),
     "small-opt": ModelConfig("opt", 50272, 768, 2, 12, 12, 64, 3072, 2048, 1e-5, True,
                              bos=2, eos=2, name="small-opt (opt-125m shape, 2 layers)"),
     "small-llama": ModelConfig("llama", 128256, 2048, 2, 32, 8, 64, 8192, 131072, 1e-5, True,

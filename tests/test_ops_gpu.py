@@ -260,6 +260,12 @@ GEMM_CASES = [
     (2048, 1024, 8192, False, 0),             # long K
     (16, 128, 64, False, 0),                  # smallest: one k-block
     (20, 200, 72, True, 0),                   # K % 64 != 0 (TMA zero fill), N < 128
+    (64, 2560, 8192, False, 0),               # 70B TP4 qkv decode: 20 tiles, cluster of 6 or 7
+    (64, 3584, 8192, True, 0),                # 28 tiles: cluster of 5
+    (64, 1024, 8192, False, 0),               # 8 tiles: cluster of 8
+    (64, 8192, 2048, False, 0),               # 70B TP4 o_proj decode: 64 tiles, cluster of 2
+    (8192, 8192, 2048, False, 0),             # 70B TP4 o_proj prefill: CTA pairs, short K
+    (8192, 2560, 8192, False, 0),             # 70B TP4 qkv prefill: 20 row tiles -> 10 pairs
 ]
 
 
@@ -289,7 +295,8 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
 
 
 @pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048),
-                                   (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024)])
+                                   (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024),
+                                   (64, 7168, 8192), (8192, 7168, 1024)])    # 70B TP4 gate_up: decode, prefill pairs
 def test_gemm_silu_gate_fused(kge, L, T, f, K):
     """Fused gate_up GEMM + SiLU*mul against the oracle's two ops (F.linear then silu_and_mul), incl.
     cluster split-K shapes (f/64 tiles <= 74) and 256-token tiles."""

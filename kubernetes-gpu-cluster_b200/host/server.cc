@@ -29,6 +29,7 @@
 #include "args.h"
 #include "json.h"
 #include "kge.h"
+#include "tokenizer.h"
 
 using namespace kge;
 
@@ -55,6 +56,8 @@ struct Server {
   ServeArgs args;
   std::vector<kge_engine*> engines;       // one per TP rank
   int vocab = 0;
+  Tokenizer tok;                          // loaded when the model directory has a tokenizer.json
+  bool have_tok = false;
   std::mutex mu;
   std::condition_variable cv;
   std::deque<Submit> submits;
@@ -282,11 +285,20 @@ struct ParsedReq {
   std::string model;
 };
 
-// prompt: [int] | [[int]]; strings need a tokenizer, which this build does not carry yet
-std::string parse_prompt(const Json* p, int vocab, std::vector<std::vector<int32_t>>* out) {
+// prompt: str | [str] | [int] | [[int]] (vllm:entrypoints/openai/completion/protocol.py:46-52); strings need
+// the model directory to carry a tokenizer.json
+const char* kNoTokenizer = "string prompts need a tokenizer.json in the model directory (none was found): send token ids "
+                           "(prompt: [int] or [[int]])";
+std::string parse_prompt(const Server& s, const Json* p, std::vector<std::vector<int32_t>>* out) {
+  const int vocab = s.vocab;
   if (!p) return "prompt is required";
-  if (p->is_str()) return "string prompts need a tokenizer, which this engine build does not include yet: send token ids (prompt: [int] or [[int]])";
-  if (!p->is_arr() || p->arr.empty()) return "prompt must be a non-empty array of token ids";
+  if (p->is_str()) {
+    if (!s.have_tok) return kNoTokenizer;
+    out->push_back(s.tok.encode(p->str, true));
+    if (out->back().empty()) return "prompt is empty";
+    return "";
+  }
+  if (!p->is_arr() || p->arr.empty()) return "prompt must be a non-empty string, array of strings or array of token ids";
   auto one = [&](const Json& a, std::vector<int32_t>* v) -> std::string {
     for (auto& t : a.arr) {
       if (!t.is_num()) return "prompt arrays must hold integers";
@@ -301,7 +313,15 @@ std::string parse_prompt(const Json* p, int vocab, std::vector<std::vector<int32
     out->emplace_back();
     return one(*p, &out->back());
   }
-  if (p->arr[0].is_str()) return "string prompts need a tokenizer, which this engine build does not include yet: send token ids";
+  if (p->arr[0].is_str()) {
+    if (!s.have_tok) return kNoTokenizer;
+    for (auto& a : p->arr) {
+      if (!a.is_str()) return "prompt array mixes strings and other types";
+      out->push_back(s.tok.encode(a.str, true));
+      if (out->back().empty()) return "prompt is empty";
+    }
+    return "";
+  }
   for (auto& a : p->arr) {
     if (!a.is_arr()) return "prompt must be [int] or [[int]]";
     out->emplace_back();
@@ -353,19 +373,34 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
   std::string err = parse_sampling(j, &pr, chat);
   if (err.empty()) {
     if (chat) {
-      // chat needs the model's chat template + tokenizer; token ids may be passed in `prompt_token_ids`
-      err = parse_prompt(j.get("prompt_token_ids"), s.vocab, &pr.prompts);
-      if (!err.empty()) err = "chat completions need a tokenizer and chat template, which this engine build does not include yet; "
-                              "pass prompt_token_ids: [int] (" + err + ")";
+      // messages are rendered with the model family's chat format (Llama-3 headers or ChatML) and tokenised;
+      // without a tokenizer / known format, token ids may be passed in `prompt_token_ids`
+      const Json* msgs = j.get("messages");
+      if (msgs && msgs->is_arr() && !msgs->arr.empty() && s.have_tok && s.tok.has_chat_template()) {
+        std::vector<ChatMessage> cm;
+        for (auto& m : msgs->arr) {
+          if (!m.is_obj()) { err = "messages must be objects with role and content"; break; }
+          const Json* c = m.get("content");
+          std::string text;
+          if (c && c->is_str()) text = c->str;
+          else if (c && c->is_arr()) { for (auto& part : c->arr) if (part.is_obj() && part.str_or("type", "") == "text") text += part.str_or("text", ""); }
+          cm.push_back({m.str_or("role", "user"), text});
+        }
+        if (err.empty()) pr.prompts.push_back(s.tok.encode(s.tok.render_chat(cm), false));
+      } else {
+        err = parse_prompt(s, j.get("prompt_token_ids"), &pr.prompts);
+        if (!err.empty()) err = "chat completions need a tokenizer.json and a supported chat template (Llama-3 or ChatML) in the model "
+                                "directory; otherwise pass prompt_token_ids: [int] (" + err + ")";
+      }
     } else {
-      err = parse_prompt(j.get("prompt"), s.vocab, &pr.prompts);
+      err = parse_prompt(s, j.get("prompt"), &pr.prompts);
     }
   }
   if (!err.empty()) return respond_error(fd, 400, err, "BadRequestError", hr.keep_alive);
   if (!pr.model.empty() && pr.model != s.args.served_model_name)
     return respond_error(fd, 404, "The model `" + pr.model + "` does not exist.", "NotFoundError", hr.keep_alive);
 
-  struct Sub { int64_t id; std::shared_ptr<ReqState> st; size_t sent = 0; bool done = false; };
+  struct Sub { int64_t id; std::shared_ptr<ReqState> st; size_t sent = 0; bool done = false; std::string pending; };
   std::vector<Sub> subs;
   int prompt_tokens = 0;
   {
@@ -404,11 +439,12 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       }
       completion += (int)st.tokens.size();
       if (i) choices += ",";
+      const std::string text = s.have_tok ? json_escape(s.tok.decode(st.tokens)) : "";
       if (chat)
-        choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"\"},\"token_ids\":" +
+        choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"" + text + "\"},\"token_ids\":" +
                    ids_json(st.tokens) + ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
       else
-        choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"\",\"token_ids\":" + ids_json(st.tokens) +
+        choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"" + text + "\",\"token_ids\":" + ids_json(st.tokens) +
                    ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
     }
     std::string body = "{\"id\":\"" + rid + "\",\"object\":\"" + (chat ? "chat.completion" : "text_completion") + "\",\"created\":" +
@@ -450,8 +486,9 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         const bool last = fin && k + 1 == fresh.size();
         std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
                         "\",\"choices\":[{\"index\":" + std::to_string(i);
-        if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"\"}";
-        else c += ",\"text\":\"\"";
+        const std::string piece = s.have_tok ? json_escape(s.tok.decode_stream(fresh[k], &sb.pending)) : "";
+        if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"" + piece + "\"}";
+        else c += ",\"text\":\"" + piece + "\"";
         c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (last ? reason(fin) : "null") +
              ",\"stop_reason\":null}]}";
         ok = send_chunk(fd, "data: " + c + "\n\n");
@@ -567,7 +604,44 @@ std::string resolve_model(const std::string& model) {
 
 }  // namespace
 
+// `vllm tokenize DIR`: one JSON object per stdin line, {"text": ...} -> {"ids": [...], "pieces": [...]},
+// {"ids": [...]} -> {"text": ...}, {"messages": [...]} -> {"ids": [...], "text": rendered}.  No GPU.
+int tokenize_main(const std::string& dir) {
+  Tokenizer tok;
+  std::string err;
+  if (!tok.load(dir, &err)) { fprintf(stderr, "error: %s\n", err.c_str()); return 1; }
+  std::string line;
+  char buf[1 << 16];
+  while (fgets(buf, sizeof buf, stdin)) {
+    line = buf;
+    while (!line.empty() && line.back() != '\n' && fgets(buf, sizeof buf, stdin)) line += buf;
+    Json j;
+    if (!json_parse(line, &j, &err) || !j.is_obj()) { printf("{\"error\":\"%s\"}\n", json_escape(err).c_str()); continue; }
+    if (const Json* t = j.get("text")) {
+      auto ids = tok.encode(t->str, j.bool_or("add_special_tokens", true));
+      std::string pieces = "[";
+      bool first = true;
+      for (auto& p : tok.split(t->str)) { pieces += (first ? "\"" : ",\"") + json_escape(p) + "\""; first = false; }
+      printf("{\"ids\":%s,\"pieces\":%s]}\n", ids_json(ids).c_str(), pieces.c_str());
+    } else if (const Json* ids = j.get("ids")) {
+      std::vector<int32_t> v;
+      for (auto& x : ids->arr) v.push_back((int32_t)x.num);
+      std::string streamed, pending;
+      for (int32_t id : v) streamed += tok.decode_stream(id, &pending);
+      printf("{\"text\":\"%s\",\"streamed\":\"%s\"}\n", json_escape(tok.decode(v)).c_str(), json_escape(streamed + pending).c_str());
+    } else if (const Json* ms = j.get("messages")) {
+      std::vector<ChatMessage> cm;
+      for (auto& m : ms->arr) cm.push_back({m.str_or("role", "user"), m.str_or("content", "")});
+      const std::string r = tok.has_chat_template() ? tok.render_chat(cm) : "";
+      printf("{\"text\":\"%s\",\"ids\":%s}\n", json_escape(r).c_str(), ids_json(tok.encode(r, false)).c_str());
+    }
+    fflush(stdout);
+  }
+  return 0;
+}
+
 int main(int argc, char** argv) {
+  if (argc >= 3 && std::string(argv[1]) == "tokenize") return tokenize_main(argv[2]);
   Server s;
   std::string err = parse_serve_args(argc, argv, &s.args);
   if (!err.empty()) {
@@ -626,6 +700,12 @@ int main(int argc, char** argv) {
       if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
   }
   s.vocab = kge_engine_vocab(s.engines[0]);
+  {
+    std::string terr;
+    s.have_tok = s.tok.load(dir, &terr);
+    if (s.have_tok) fprintf(stderr, "INFO: tokenizer loaded (%d entries%s)\n", s.tok.vocab_size(), s.tok.has_chat_template() ? ", chat template" : "");
+    else fprintf(stderr, "INFO: %s - string prompts and chat messages will be refused; token-id prompts work\n", terr.c_str());
+  }
   if (s.args.max_model_len <= 0) s.args.max_model_len = 8192;
   fprintf(stderr, "INFO: model %s loaded: %.2f GB weights/rank, %d KV blocks, tp=%d\n", dir.c_str(),
           kge_engine_weight_bytes(s.engines[0]) / 1e9, kge_engine_num_blocks(s.engines[0]), a.tensor_parallel_size);

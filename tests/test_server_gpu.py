@@ -35,13 +35,15 @@ def http(port, path, body=None, timeout=60):
         return e.code, e.read().decode()
 
 
-@pytest.fixture(scope="module")
-def server(tmp_path_factory):
+def start_server(tmp_path_factory, with_tokenizer):
     assert os.path.exists(BIN), "build the server: make -C kubernetes-gpu-cluster_b200"
     cfg = om.CONFIGS["tiny-llama"]
     w = om.make_weights(cfg, seed=0)
     d = str(tmp_path_factory.mktemp("srv-model"))
     om.save_model_dir(d, cfg, w)
+    if with_tokenizer:
+        from test_tokenizer_cpu import build
+        build("llama3", d)            # a 700-entry Llama-3-style tokenizer.json (vocab fits the 1024-row embedding)
     port = free_port()
     proc = subprocess.Popen([BIN, "serve", d, "--host", "127.0.0.1", "--port", str(port), "--max-model-len", "256",
                              "--max-num-seqs", "8", "--max-num-batched-tokens", "128", "--num-gpu-blocks-override", "128",
@@ -57,12 +59,29 @@ def server(tmp_path_factory):
         assert proc.poll() is None, proc.stderr.read()[-2000:]
         assert time.time() - t0 < 120, "server did not come up"
         time.sleep(0.2)
-    yield port, cfg, w, d
+    return proc, (port, cfg, w, d)
+
+
+def stop_server(proc):
     proc.terminate()
     try:
         proc.wait(timeout=20)
     except subprocess.TimeoutExpired:
         proc.kill()
+
+
+@pytest.fixture(scope="module")
+def server(tmp_path_factory):
+    proc, info = start_server(tmp_path_factory, with_tokenizer=False)
+    yield info
+    stop_server(proc)
+
+
+@pytest.fixture(scope="module")
+def server_tok(tmp_path_factory):
+    proc, info = start_server(tmp_path_factory, with_tokenizer=True)
+    yield info
+    stop_server(proc)
 
 
 def test_models_health_metrics(server):
@@ -138,3 +157,38 @@ def test_errors_use_the_openai_error_shape(server):
     r = json.loads(body)
     assert st == 200 and r["object"] == "chat.completion" and r["choices"][0]["message"]["role"] == "assistant"
     assert len(r["choices"][0]["token_ids"]) >= 1
+
+
+def test_string_prompts_and_chat_with_a_tokenizer(server_tok):
+    """With a tokenizer.json in the model directory the server takes text like the engine it replaces: the ids
+    it generates for a string prompt equal those for the same prompt sent as token ids, `text` is their decoding,
+    and chat messages are rendered with the Llama-3 header format."""
+    from tokenizers import Tokenizer
+    port, cfg, w, d = server_tok
+    tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
+    text = "The GPU cluster's nodes aren't ready yet."
+    ids = tok.encode(text).ids
+    st, a = http(port, "/v1/completions", {"prompt": text, "max_tokens": 8, "temperature": 0, "ignore_eos": True})
+    st2, b = http(port, "/v1/completions", {"prompt": ids, "max_tokens": 8, "temperature": 0, "ignore_eos": True})
+    assert st == 200 and st2 == 200, (a, b)
+    a, b = json.loads(a), json.loads(b)
+    assert a["usage"]["prompt_tokens"] == len(ids)
+    assert a["choices"][0]["token_ids"] == b["choices"][0]["token_ids"]
+    assert a["choices"][0]["text"] == tok.decode(a["choices"][0]["token_ids"], skip_special_tokens=True)
+    st, c = http(port, "/v1/completions", {"prompt": [text, "Hello"], "max_tokens": 4, "temperature": 0})
+    assert st == 200 and len(json.loads(c)["choices"]) == 2
+    msgs = [{"role": "user", "content": "Hi there"}]
+    st, c = http(port, "/v1/chat/completions", {"messages": msgs, "max_tokens": 6, "temperature": 0, "ignore_eos": True})
+    c = json.loads(c)
+    rendered = "<|begin_of_text|><|start_header_id|>user<|end_header_id|>\n\nHi there<|eot_id|><|start_header_id|>assistant<|end_header_id|>\n\n"
+    assert st == 200 and c["object"] == "chat.completion"
+    assert c["usage"]["prompt_tokens"] == len(tok.encode(rendered, add_special_tokens=False).ids)
+    assert c["choices"][0]["message"]["content"] == tok.decode(c["choices"][0]["token_ids"], skip_special_tokens=True)
+    # streamed text pieces concatenate to the non-streamed text
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions",
+                                 data=json.dumps({"prompt": text, "max_tokens": 8, "temperature": 0, "ignore_eos": True,
+                                                  "stream": True}).encode(), headers={"Content-Type": "application/json"})
+    with urllib.request.urlopen(req, timeout=60) as r:
+        raw = r.read().decode()
+    pieces = [json.loads(e[6:])["choices"][0]["text"] for e in raw.split("\n\n") if e.startswith("data: {")]
+    assert "".join(pieces) == a["choices"][0]["text"]

@@ -486,7 +486,9 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         const bool last = fin && k + 1 == fresh.size();
         std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
                         "\",\"choices\":[{\"index\":" + std::to_string(i);
-        const std::string piece = s.have_tok ? json_escape(s.tok.decode_stream(fresh[k], &sb.pending)) : "";
+        std::string piece_raw = s.have_tok ? s.tok.decode_stream(fresh[k], &sb.pending) : "";
+        if (last && s.have_tok) piece_raw += Tokenizer::flush_stream(&sb.pending);
+        const std::string piece = json_escape(piece_raw);
         if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"" + piece + "\"}";
         else c += ",\"text\":\"" + piece + "\"";
         c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (last ? reason(fin) : "null") +
@@ -628,7 +630,8 @@ int tokenize_main(const std::string& dir) {
       for (auto& x : ids->arr) v.push_back((int32_t)x.num);
       std::string streamed, pending;
       for (int32_t id : v) streamed += tok.decode_stream(id, &pending);
-      printf("{\"text\":\"%s\",\"streamed\":\"%s\"}\n", json_escape(tok.decode(v)).c_str(), json_escape(streamed + pending).c_str());
+      streamed += Tokenizer::flush_stream(&pending);
+      printf("{\"text\":\"%s\",\"streamed\":\"%s\"}\n", json_escape(tok.decode(v)).c_str(), json_escape(streamed).c_str());
     } else if (const Json* ms = j.get("messages")) {
       std::vector<ChatMessage> cm;
       for (auto& m : ms->arr) cm.push_back({m.str_or("role", "user"), m.str_or("content", "")});

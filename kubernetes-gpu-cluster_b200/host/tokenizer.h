@@ -116,24 +116,64 @@ class Tokenizer {
     }
     return out;
   }
+  // Bytes -> valid UTF-8, replacing every maximal invalid subpart with U+FFFD exactly as Rust's
+  // String::from_utf8_lossy does (what HF's ByteLevel decoder, and so vLLM's detokenizer, produce).
+  // With final == false a sequence that is still a valid PREFIX at the end of the buffer is left in `*rest`.
+  static std::string utf8_lossy(const std::string& b, bool final, std::string* rest) {
+    std::string out;
+    size_t i = 0;
+    const size_t n = b.size();
+    auto at = [&](size_t k) { return (unsigned char)b[k]; };
+    while (i < n) {
+      const unsigned char c = at(i);
+      if (c < 0x80) { out += (char)c; ++i; continue; }
+      size_t need = 0;
+      unsigned char lo = 0x80, hi = 0xBF;                      // allowed range of the SECOND byte
+      if (c >= 0xC2 && c <= 0xDF) need = 1;
+      else if (c == 0xE0) { need = 2; lo = 0xA0; }
+      else if ((c >= 0xE1 && c <= 0xEC) || c == 0xEE || c == 0xEF) need = 2;
+      else if (c == 0xED) { need = 2; hi = 0x9F; }
+      else if (c == 0xF0) { need = 3; lo = 0x90; }
+      else if (c >= 0xF1 && c <= 0xF3) need = 3;
+      else if (c == 0xF4) { need = 3; hi = 0x8F; }
+      if (need == 0) { out += "\xEF\xBF\xBD"; ++i; continue; }   // not a lead byte
+      size_t k = 1;
+      bool ok = true, cut = false;
+      for (; k <= need; ++k) {
+        if (i + k >= n) { cut = true; break; }
+        const unsigned char d = at(i + k);
+        const unsigned char l2 = k == 1 ? lo : 0x80, h2 = k == 1 ? hi : 0xBF;
+        if (d < l2 || d > h2) { ok = false; break; }
+      }
+      if (cut) {
+        if (!final) { if (rest) *rest = b.substr(i); return out; }
+        out += "\xEF\xBF\xBD";                                // truncated at the very end: one replacement
+        i = n;
+      } else if (ok) {
+        out.append(b, i, need + 1);
+        i += need + 1;
+      } else {
+        out += "\xEF\xBF\xBD";                                // lead + the valid continuation bytes seen so far
+        i += k;
+      }
+    }
+    if (rest) rest->clear();
+    return out;
+  }
   std::string decode(const std::vector<int32_t>& ids) const {
     std::string b;
     for (int32_t id : ids) b += token_bytes(id);
-    return b;
+    return utf8_lossy(b, true, nullptr);
   }
-  // Streaming: append one token's bytes to `pending` and return the longest prefix that is complete UTF-8.
+  // Streaming: append one token's bytes to `pending`, return the text that is final so far (invalid bytes
+  // already replaced), keep a possibly-incomplete sequence pending.  flush_stream() ends the stream.
   std::string decode_stream(int32_t id, std::string* pending) const {
-    *pending += token_bytes(id);
-    size_t n = pending->size(), cut = n;
-    for (size_t back = 1; back <= 3 && back <= n; ++back) {
-      const unsigned char c = (unsigned char)(*pending)[n - back];
-      if ((c & 0xC0) == 0x80) continue;                       // continuation byte: keep looking for the lead
-      const size_t need = c >= 0xF0 ? 4 : c >= 0xE0 ? 3 : c >= 0xC0 ? 2 : 1;
-      if (need > back) cut = n - back;                        // incomplete sequence at the tail
-      break;
-    }
-    std::string out = pending->substr(0, cut);
-    pending->erase(0, cut);
+    const std::string b = *pending + token_bytes(id);
+    return utf8_lossy(b, false, pending);
+  }
+  static std::string flush_stream(std::string* pending) {
+    std::string out = utf8_lossy(*pending, true, nullptr);
+    pending->clear();
     return out;
   }
 

@@ -86,6 +86,21 @@ def test_encode_decode_match_hf_tokenizers(kind, tmp_path):
             assert o["text"] == t
 
 
+def test_lossy_decoding_of_arbitrary_id_sequences(tmp_path):
+    """Random ids decode to arbitrary bytes; invalid UTF-8 must become U+FFFD exactly as in HF's (Rust's lossy)
+    decoding, and streamed pieces must concatenate to the same text."""
+    import random
+    tok = build("qwen", str(tmp_path))
+    rng = random.Random(0)
+    seqs = [[rng.randrange(3, tok.get_vocab_size()) for _ in range(rng.randrange(1, 40))] for _ in range(200)]
+    seqs += [tok.encode("日本語 🙂 café").ids[:k] for k in range(1, 12)]        # truncated multi-byte sequences
+    outs = run_cli(str(tmp_path), [{"ids": s} for s in seqs])
+    for s, o in zip(seqs, outs):
+        ref = tok.decode(s, skip_special_tokens=True)
+        assert o["text"] == ref, s
+        assert o["streamed"] == ref, s
+
+
 def test_added_tokens_are_matched_in_text(tmp_path):
     tok = build("qwen", str(tmp_path))
     t = "<|im_start|>user\nhi<|im_end|>\n"

@@ -274,6 +274,11 @@ kge_sched* kge_sched_create(int32_t max_num_seqs, int32_t max_num_batched_tokens
                             int32_t max_model_len, int32_t block_size, int32_t num_blocks,
                             int32_t enable_chunked_prefill, int32_t eos_token_id);
 void kge_sched_destroy(kge_sched* s);
+/* vllm --scheduler-reserve-full-isl / --no-scheduler-reserve-full-isl (vllm:config/scheduler.py, default on;
+ * the admission gate of vllm:v1/core/kv_cache_manager.py:346-360): a waiting request is admitted only when
+ * free blocks cover its whole known sequence.  The engine's scheduler has the same switch. */
+void kge_sched_set_reserve_full_isl(kge_sched* s, int32_t on);
+void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on);
 int kge_sched_add(kge_sched* s, int64_t request_id, const int32_t* prompt_ids, int32_t n,
                   const kge_sampling_params* sp);
 /* Returns the number of scheduled requests; ids/num_tokens [cap]. */

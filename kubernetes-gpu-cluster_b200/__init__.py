@@ -100,6 +100,8 @@ SIGNATURES = {
     "kge_engine_stats": (_I, [_P, _P, _P, _P, _P]),
     "kge_sched_create": (_P, [C.c_int32] * 7),
     "kge_sched_destroy": (None, [_P]),
+    "kge_sched_set_reserve_full_isl": (None, [_P, C.c_int32]),
+    "kge_engine_set_reserve_full_isl": (None, [_P, C.c_int32]),
     "kge_sched_add": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
     "kge_sched_schedule": (_I, [_P, _P, _P, C.c_int32]),
     "kge_sched_update": (_I, [_P, _P, _P, C.c_int32, C.POINTER(StepOutput), C.c_int32]),
@@ -182,7 +184,7 @@ class LLM:
                  max_num_batched_tokens: int = 0, gpu_memory_utilization: float = 0.9,
                  block_size: int = 16, num_gpu_blocks_override: int = 0, tensor_parallel_size: int = 1,
                  tp_rank: int = 0, enable_chunked_prefill: bool = True, load_format: str = "auto",
-                 seed: int = 0, device: int = 0):
+                 seed: int = 0, device: int = 0, scheduler_reserve_full_isl: bool = True):
         require_cuda()
         self.cfg = EngineConfig(max_num_seqs, max_num_batched_tokens, max_model_len, block_size,
                                 num_gpu_blocks_override, gpu_memory_utilization, tp_rank,
@@ -191,6 +193,7 @@ class LLM:
         dummy = seed if load_format == "dummy" else -1
         check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")
         self._h = h
+        lib().kge_engine_set_reserve_full_isl(h, int(scheduler_reserve_full_isl))
         self._next_id = 0
         self._outs = (StepOutput * 4096)()
 

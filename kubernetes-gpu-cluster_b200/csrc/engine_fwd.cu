@@ -392,6 +392,8 @@ extern "C" kge_sched* kge_sched_create(int32_t max_num_seqs, int32_t max_num_bat
   return k;
 }
 extern "C" void kge_sched_destroy(kge_sched* s) { delete s; }
+extern "C" void kge_sched_set_reserve_full_isl(kge_sched* s, int32_t on) { if (s) s->s->set_reserve_full_isl(on != 0); }
+extern "C" void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on) { if (e && e->sched) e->sched->set_reserve_full_isl(on != 0); }
 extern "C" int kge_sched_add(kge_sched* s, int64_t request_id, const int32_t* prompt_ids, int32_t n,
                              const kge_sampling_params* sp) {
   KGE_REQUIRE(s && prompt_ids, "kge_sched_add: null argument");

@@ -96,6 +96,10 @@ const std::vector<Scheduled>& Scheduler::schedule() {
       int32_t n = r->num_tokens() - r->num_computed;
       if (!cfg_.enable_chunked_prefill && n > budget) break;
       n = std::min(n, budget);
+      if (cfg_.reserve_full_isl) {
+        const int32_t full = std::min(r->num_tokens(), cfg_.max_model_len);
+        if ((full + cfg_.block_size - 1) / cfg_.block_size - (int32_t)r->blocks.size() > free_blocks()) break;
+      }
       if (!alloc(r, n)) break;
       waiting_.pop_front();
       r->status = ReqStatus::Running;

@@ -49,6 +49,9 @@ struct SchedConfig {
   int32_t num_blocks = 0;              // including null block 0
   bool enable_chunked_prefill = true;
   int32_t eos_token_id = -1;
+  // vllm --scheduler-reserve-full-isl (default on): a WAITING request is admitted only when the pool has
+  // free blocks for its whole known sequence, not just its first chunk (vllm:v1/core/kv_cache_manager.py:346-360).
+  bool reserve_full_isl = true;
 };
 
 struct Scheduled {
@@ -82,6 +85,7 @@ class Scheduler {
   int32_t usable_blocks() const { return cfg_.num_blocks - 1; }
   int64_t num_preemptions() const { return preemptions_; }
   const SchedConfig& config() const { return cfg_; }
+  void set_reserve_full_isl(bool on) { cfg_.reserve_full_isl = on; }
   Request* find(int64_t id);
 
  private:

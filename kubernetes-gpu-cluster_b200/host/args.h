@@ -26,6 +26,7 @@ struct ServeArgs {
   int block_size = 16;
   int num_gpu_blocks_override = 0;
   bool enable_chunked_prefill = true;
+  bool scheduler_reserve_full_isl = true;
   bool enable_prefix_caching = false;
   bool enforce_eager = false;
   bool disable_custom_all_reduce = false;
@@ -95,6 +96,8 @@ inline std::string parse_serve_args(int argc, char** argv, ServeArgs* a) {
     else if (key == "--num-gpu-blocks-override") err = need_int(&a->num_gpu_blocks_override);
     else if (key == "--enable-chunked-prefill") a->enable_chunked_prefill = true;
     else if (key == "--no-enable-chunked-prefill") a->enable_chunked_prefill = false;
+    else if (key == "--scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = true;
+    else if (key == "--no-scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = false;
     else if (key == "--enable-prefix-caching") a->enable_prefix_caching = true;
     else if (key == "--no-enable-prefix-caching") a->enable_prefix_caching = false;
     else if (key == "--enforce-eager") a->enforce_eager = true;

@@ -684,6 +684,7 @@ int main(int argc, char** argv) {
     c.enable_chunked_prefill = a.enable_chunked_prefill; c.device = r;
     rcs[r] = kge_engine_create(&s.engines[r], dir.c_str(), &c, a.load_format == "dummy" ? a.seed : -1);
     if (rcs[r]) errs[r] = kge_last_error();
+    else kge_engine_set_reserve_full_isl(s.engines[r], a.scheduler_reserve_full_isl);
   };
   {
     std::vector<std::thread> th;

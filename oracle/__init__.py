@@ -8,7 +8,8 @@ This package restates vLLM's published op order and cast points in plain PyTorch
 the CPU (citations are to the vLLM 0.22.0 sources installed in the build container,
 prefix ``vllm:``) and is anchored by fixtures generated in the build container from
 vLLM's own importable pure-PyTorch functions and from HF transformers
-(tests/golden/make_golden.py).
+(tests/golden/make_golden.py), and from step-by-step traces of vLLM's real v1 Scheduler
+(tests/golden/make_sched_golden.py).
 
 Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
 legs may import this package, and only as the checker or the timed CPU baseline.

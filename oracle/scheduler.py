@@ -7,6 +7,8 @@ vllm:v1/core/sched/utils.py:94-130, and the block accounting of
 vllm:v1/core/kv_cache_manager.py:236-430 / block_pool.py (block 0 is the reserved null
 block, so num_blocks-1 are usable).  No prefix caching, no speculative tokens.
 Only WHO runs HOW MANY tokens each step is compared with the product; block ids are free.
+Checked step by step against traces of the real vLLM Scheduler (tests/golden/sched_vllm.json,
+tests/test_scheduler_vllm_golden.py).
 """
 from __future__ import annotations
 
@@ -22,6 +24,9 @@ class SchedConfig:
     block_size: int = 16
     num_blocks: int = 1024              # including the null block 0
     enable_chunked_prefill: bool = True
+    # --scheduler-reserve-full-isl (vLLM default on): admit a waiting request only if free blocks
+    # cover its whole known sequence (kv_cache_manager.py:346-360, full_sequence_must_fit)
+    reserve_full_isl: bool = True
 
 
 @dataclass
@@ -110,6 +115,10 @@ class OracleScheduler:
                 if not c.enable_chunked_prefill and n > budget:
                     break
                 n = min(n, budget)
+                if c.reserve_full_isl:
+                    full = min(r.num_tokens, c.max_model_len)
+                    if -(-full // c.block_size) - r.num_blocks > self.free_blocks:
+                        break
                 if not self._alloc(r, n):
                     break
                 self.waiting.popleft()

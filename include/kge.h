@@ -26,6 +26,15 @@ const char* kge_last_error(void);
 int kge_abi_version(void);
 /* 0 = no usable CUDA device, else the SM count of the current device. */
 int kge_device_sm_count(void);
+/* Launch-shape knobs for tuning and diagnostics (no counterpart in the reference): they change how work is
+ * partitioned over the 148 SMs, never the results.  Process-wide; set them before creating an engine
+ * (captured decode graphs keep the shape they were captured with).
+ *   "pdl" 0/1                 programmatic dependent launch between the kernels of a step
+ *   "gemm_even_grid" 0/1      persistent weight-streaming GEMM: size the grid so every CTA gets the same tile count
+ *   "attn_decode_splits" n    force the split-KV factor of decode attention (0 = heuristic)
+ *   "attn_split_balance" 0/1  heuristic picks the split factor that fills whole waves of resident CTAs
+ * Returns 0, or -1 for an unknown name. */
+int kge_set_tunable(const char* name, int value);
 
 /* ---------------------------------------------------------------- per-op entry points --- */
 

@@ -99,6 +99,7 @@ SIGNATURES = {
     "kge_engine_step": (_I, [_P, C.POINTER(StepOutput), C.c_int32]),
     "kge_engine_stats": (_I, [_P, _P, _P, _P, _P]),
     "kge_sched_create": (_P, [C.c_int32] * 7),
+    "kge_set_tunable": (C.c_int, [C.c_char_p, C.c_int]),
     "kge_sched_destroy": (None, [_P]),
     "kge_sched_set_reserve_full_isl": (None, [_P, C.c_int32]),
     "kge_engine_set_reserve_full_isl": (None, [_P, C.c_int32]),

@@ -284,10 +284,24 @@ static int decode_splits(int B, int KV, int max_seq_len) { return attn_decode_sp
 int attn_decode_splits(int B, int KV, int max_seq_len) {
   const int target = 148 * 4;
   int s = (target + B * KV - 1) / (B * KV);
-  const int max_s = (max_seq_len + 4 * BN - 1) / (4 * BN);   // >= 256 keys per split
+  int max_s = (max_seq_len + 4 * BN - 1) / (4 * BN);   // >= 256 keys per split
+  if (max_s > 32) max_s = 32;
+  if (max_s < 1) max_s = 1;
+  if (const int forced = tunable(TUN_ATTN_DECODE_SPLITS)) return forced < max_s ? forced : max_s;
   if (s > max_s) s = max_s;
-  if (s > 32) s = 32;
   if (s < 1) s = 1;
+  if (tunable(TUN_ATTN_SPLIT_BALANCE)) {
+    // Equal-length requests make equal CTAs, and the kernel is issue-bound per CTA, so the launch runs in
+    // rounds of 148 x 2 resident CTAs: among s..s+3 take the factor whose last round is fullest.
+    const int slots = 148 * 2;
+    int best = s; double best_eff = 0;
+    for (int c = s; c <= s + 3 && c <= max_s; ++c) {
+      const int n = B * KV * c;
+      const double eff = (double)n / (double)(((n + slots - 1) / slots) * slots);
+      if (eff > best_eff + 0.02) { best_eff = eff; best = c; }
+    }
+    s = best;
+  }
   return s;
 }
 

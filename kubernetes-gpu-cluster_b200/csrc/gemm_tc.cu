@@ -495,7 +495,14 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
   } else {
-    cfg.gridDim = dim3(tiles < 148 ? tiles : 148);
+    int grid = tiles < 148 ? tiles : 148;
+    if (tunable(TUN_GEMM_EVEN_GRID) && tiles > 148) {
+      // persistent round-robin: 224 tiles on 148 CTAs leaves 72 CTAs idle for the second half; 112 CTAs with two
+      // tiles each keep every CTA streaming to the end (a weight-streaming GEMM needs bytes in flight, not SMs)
+      const int rounds = (tiles + 147) / 148;
+      grid = (tiles + rounds - 1) / rounds;
+    }
+    cfg.gridDim = dim3(grid);
   }
   KGE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
   return 0;

@@ -33,6 +33,9 @@ int kge_device_sm_count(void);
  *   "gemm_even_grid" 0/1      persistent weight-streaming GEMM: size the grid so every CTA gets the same tile count
  *   "attn_decode_splits" n    force the split-KV factor of decode attention (0 = heuristic)
  *   "attn_split_balance" 0/1  heuristic picks the split factor that fills whole waves of resident CTAs
+ *   "attn_cluster_merge" 0/1  decode attention: 1 = the split-KV CTAs of a (request, kv head) form a thread-block
+ *                             cluster and merge over distributed shared memory instead of workspace + merge kernel
+ *                             (same bits; measured slower, so off by default)
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

@@ -42,6 +42,19 @@ __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], 
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
+// thread-block cluster helpers (split-KV partials are merged through distributed shared memory)
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float ld_dsmem_f32(uint32_t local_addr, uint32_t rank) {
+  uint32_t remote;
+  float v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local_addr), "r"(rank));
+  asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(v) : "r"(remote) : "memory");
+  return v;
+}
+
 // byte offset of 16-byte chunk `c` of row `r` in a [rows][HD] bf16 tile, XOR swizzled
 template <int HD>
 __device__ __forceinline__ uint32_t swz(int r, int c) {
@@ -94,7 +107,10 @@ struct KvLoader {
 // grid (splits, KV, B); 128 threads.  One query token per request; the G (<=16) q heads of the
 // kv head are the M rows.  Warp w handles keys 16w..16w+15 of every 64-key tile.
 // Partial results: part_o [B, H, splits, HD] fp32 (un-normalised), part_ml [B, H, splits, 2].
-template <int HD, int STAGES>
+// CLUSTER: the `splits` CTAs of one (request, kv head) form a thread-block cluster; each leaves its partial in
+// its own shared memory and every rank finishes a slice of the output columns by reading its peers' partials
+// over DSMEM - same arithmetic and summation order as attn_merge_kernel, no workspace, no second kernel.
+template <int HD, int STAGES, bool CLUSTER>
 __global__ void __launch_bounds__(128)
 attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __restrict__ part_ml,
                    const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
@@ -118,6 +134,7 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
   const uint32_t sK = sQ + 16 * HD * 2;
   const uint32_t sV = sK + STAGES * BN * HD * 2;
   float* sRed = reinterpret_cast<float*>(smem + 16 * HD * 2);  // [4][16][HD+2], aliases the K stages after the loop
+  float* sPart = reinterpret_cast<float*>(smem + 16 * HD * 2 + STAGES * BN * HD * 2);   // CLUSTER: [16][HD+2] in the V stages
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const int g = lane >> 2, tg = lane & 3;
 
@@ -244,11 +261,34 @@ attn_decode_kernel(bf16* __restrict__ out, float* __restrict__ part_o, float* __
     const int head = kvh * G + r;
     if (nsplit == 1) {
       out[(int64_t)qrow * H * HD + head * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+    } else if (CLUSTER) {
+      sPart[r * RS + c] = acc;
+      if (c == 0) { sPart[r * RS + HD] = mm; sPart[r * RS + HD + 1] = ll; }
     } else {
       const int64_t pi = ((int64_t)b * H + head) * nsplit + split;
       part_o[pi * HD + c] = acc;
       if (c == 0) { part_ml[pi * 2] = mm; part_ml[pi * 2 + 1] = ll; }
     }
+  }
+  if (CLUSTER && nsplit > 1) {
+    cluster_sync_all();                                   // every rank's partial is in its shared memory
+    const uint32_t sp = smem_u32(sPart);
+    const int total = G * HD, per = (total + nsplit - 1) / nsplit;
+    const int e_end = min(total, (split + 1) * per);
+    for (int i = split * per + tid; i < e_end; i += NT) {
+      const int r = i / HD, c = i % HD;
+      float mm = -INFINITY;
+      for (int sidx = 0; sidx < nsplit; ++sidx) mm = fmaxf(mm, ld_dsmem_f32(sp + (r * RS + HD) * 4, sidx));
+      const float basem = (mm == -INFINITY) ? 0.f : mm;
+      float acc = 0.f, ll = 0.f;
+      for (int sidx = 0; sidx < nsplit; ++sidx) {
+        const float sc = exp2f(ld_dsmem_f32(sp + (r * RS + HD) * 4, sidx) - basem);
+        acc += ld_dsmem_f32(sp + (r * RS + c) * 4, sidx) * sc;
+        ll += ld_dsmem_f32(sp + (r * RS + HD + 1) * 4, sidx) * sc;
+      }
+      out[(int64_t)qrow * H * HD + (kvh * G + r) * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+    }
+    cluster_sync_all();                                   // nobody exits while a peer still reads its partial
   }
 }
 
@@ -316,6 +356,24 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
   const int G = H / KV;
   if (max_q_len == 1 && G <= 16) {
     const int ns = decode_splits(B, KV, max_seq_len);
+    if (ns > 1 && ns <= 8 && tunable(TUN_ATTN_CLUSTER_MERGE)) {
+      // opt-in: split-KV CTAs of one (request, kv head) as a cluster, merged over DSMEM - no workspace and one
+      // kernel, but measured SLOWER than the merge kernel behind programmatic dependent launch (C3 decode step
+      // 7.64 vs 7.38 ms, profiles/r01_knob_sweep.md): cluster co-scheduling costs more than the extra launch
+      auto kern = attn_decode_kernel<HD, kDecodeStages, true>;
+      KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(ns, KV, B); cfg.blockDim = dim3(128); cfg.dynamicSmemBytes = decode_smem<HD>(); cfg.stream = st;
+      cudaLaunchAttribute attr[2];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = ns; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+      attr[1].val.programmaticStreamSerializationAllowed = 1;
+      cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+      KGE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, out, (float*)nullptr, (float*)nullptr, q, q_stride, kc, vc, bt, max_blocks, sl, qsl,
+                                     H, KV, bs_shift, sl2));
+      return 0;
+    }
     float* po = nullptr; float* pml = nullptr;
     if (ns > 1) {
       const int64_t need = (int64_t)B * H * ns * (HD + 2) * 4;
@@ -323,7 +381,7 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
       po = (float*)ws;
       pml = po + (int64_t)B * H * ns * HD;
     }
-    auto kern = attn_decode_kernel<HD, kDecodeStages>;
+    auto kern = attn_decode_kernel<HD, kDecodeStages, false>;
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
     KGE_CUDA_OK(launch_pdl(kern, dim3(ns, KV, B), dim3(128), decode_smem<HD>(), st, out, po, pml, q, q_stride, kc, vc, bt,
                            max_blocks, sl, qsl, H, KV, bs_shift, sl2));

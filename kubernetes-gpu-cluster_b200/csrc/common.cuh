@@ -15,7 +15,7 @@ bool pdl_enabled();
 void pdl_set_enabled(bool on);
 // Launch-shape knobs behind kge_set_tunable() (api.cc): heuristics that only change HOW work is
 // partitioned, never results.  Defaults are the measured-best settings (profiles/).
-enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_COUNT = 3 };
+enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_COUNT = 4 };
 int tunable(Tunable t);
 
 #define KGE_CUDA_OK(expr)                                                              \

@@ -372,6 +372,7 @@ def run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed):
         err = (got[qsl[b]:qsl[b + 1]] - ref).abs()
         tol = 1e-3 * ref.abs().max() + 1.6e-2 * ref.abs() + 4e-3
         assert (err <= tol).all(), f"request {b}: max err {err.max().item():.4g}"
+    return out.cpu()
 
 
 ATTN_CASES = [
@@ -394,6 +395,36 @@ ATTN_CASES = [
 @pytest.mark.parametrize("H,KV,hd,bs,q_lens,seq_lens", ATTN_CASES)
 def test_paged_attention(kge, L, H, KV, hd, bs, q_lens, seq_lens):
     run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed=H * 31 + sum(seq_lens))
+
+
+DECODE_SPLIT_CASES = [
+    # H, KV, hd, q_lens, seq_lens, forced split-KV factor (0 = heuristic)
+    (32, 8, 128, [1] * 3, [2176, 1500, 700], 0),
+    (32, 8, 128, [1] * 3, [2176, 1500, 700], 3),
+    (32, 8, 128, [1] * 2, [4100, 257], 8),
+    (32, 8, 64, [1] * 4, [40, 128, 129, 1000], 2),
+    (12, 12, 64, [1] * 3, [5, 130, 600], 2),
+    (64, 8, 128, [1, 1], [900, 33], 3),
+    (28, 4, 128, [1] * 2, [300, 2000], 5),
+    (32, 8, 128, [1], [6000], 0),                # heuristic picks > 8 splits: workspace + merge kernel path
+]
+
+
+@pytest.mark.parametrize("H,KV,hd,q_lens,seq_lens,splits", DECODE_SPLIT_CASES)
+def test_decode_attention_cluster_merge_equals_workspace_merge(kge, L, H, KV, hd, q_lens, seq_lens, splits):
+    """Split-KV partials merged inside a thread-block cluster over DSMEM (opt-in knob) must give the same BITS as the
+    default workspace + merge-kernel path, and both must match the oracle."""
+    seed = H * 7 + sum(seq_lens) + splits
+    try:
+        check_ok(kge, L.kge_set_tunable(b"attn_decode_splits", splits), "tunable")
+        check_ok(kge, L.kge_set_tunable(b"attn_cluster_merge", 1), "tunable")
+        a = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)
+        check_ok(kge, L.kge_set_tunable(b"attn_cluster_merge", 0), "tunable")
+        b = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)
+    finally:
+        L.kge_set_tunable(b"attn_decode_splits", 0)
+        L.kge_set_tunable(b"attn_cluster_merge", 0)
+    assert torch.equal(a.view(torch.int16), b.view(torch.int16))
 
 
 # ------------------------------------------------------------------------------ sampling

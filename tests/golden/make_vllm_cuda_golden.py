@@ -99,8 +99,22 @@ def perf():
         n = sum(len(o.outputs[0].token_ids) for o in outs)
         runs.append(dict(seconds=dt, output_tokens=n, tok_s=n / dt))
         print("run", runs[-1], flush=True)
+    # where vLLM's time goes: the same prompts with one output token (prefill only) and with 65 (prefill + 64 decode steps
+    # of the last-admitted request), so prefill and decode can be told apart without a profiler
+    split = {}
+    for n_out in (1, 65):
+        spn = SamplingParams(temperature=0.0, max_tokens=n_out, ignore_eos=True, detokenize=False)
+        best = 1e9
+        for _ in range(2):
+            torch.cuda.synchronize()
+            t0 = time.time()
+            llm.generate(prompts, spn, use_tqdm=False)
+            torch.cuda.synchronize()
+            best = min(best, time.time() - t0)
+        split[f"seconds_out{n_out}"] = best
+        print("split", n_out, best, flush=True)
     import vllm
-    json.dump(dict(workload="c3: llama-3.1-8b dummy weights, 64 x 2048-in/256-out, greedy, offline LLM.generate (host prompts)",
+    json.dump(dict(workload="c3: llama-3.1-8b dummy weights, 64 x 2048-in/256-out, greedy, offline LLM.generate (host prompts)", split=split,
                    vllm=vllm.__version__, gpu=torch.cuda.get_device_name(0), init_seconds=t_init, runs=runs,
                    best_tok_s=max(r["tok_s"] for r in runs)), open(os.path.join(OUT, "vllm_cuda_c3.json"), "w"))
 

@@ -71,7 +71,7 @@ def test_engine_reproduces_vllm_cuda(kge, case, tmp_path):
     d = str(tmp_path / case["model"])
     om.save_model_dir(d, cfg, om.make_weights(cfg, seed=0))
     bs = 16
-    llm = kge.LLM(d, max_model_len=256, max_num_seqs=8, max_num_batched_tokens=256, num_gpu_blocks_override=64)
+    llm = kge.LLM(d, max_model_len=256, max_num_seqs=32, max_num_batched_tokens=256, num_gpu_blocks_override=64)   # 16 logits rows
     # teacher-forced: prompt + vLLM's tokens in one prefill step, logits for the rows that predict them
     for r in case["requests"]:
         p = r["prompt"]

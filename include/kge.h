@@ -276,6 +276,11 @@ int kge_has_unfinished(const kge_engine* e);
 /* Schedule + forward + sample + update.  Writes up to cap outputs; returns the count (>= 0)
  * or a negative error. */
 int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap);
+/* kge_engine_step in a loop until no request is left (what LLM.generate does, vllm:entrypoints/llm.py:422, without
+ * a host-language round trip per step).  Appends one event per sampled token / finished request, in step order;
+ * cap >= sum of max_tokens + number of requests is always enough.  Returns 0 or a negative error. */
+int kge_engine_run_to_completion(kge_engine* e, kge_step_output* events, int64_t cap, int64_t* n_events,
+                                 int32_t* n_steps);
 /* Counters for /metrics (vllm:v1/metrics/loggers.py:452-788). */
 int kge_engine_stats(const kge_engine* e, int32_t* num_running, int32_t* num_waiting,
                      float* kv_usage, int64_t* num_preemptions);

@@ -48,6 +48,12 @@ class StepOutput(C.Structure):
                 ("num_scheduled", C.c_int32)]
 
 
+def _event_dtype():
+    import numpy as np
+    return np.dtype({"names": ["request_id", "token", "finished", "num_scheduled"], "formats": ["<i8", "<i4", "<i4", "<i4"],
+                     "offsets": [0, 8, 12, 16], "itemsize": C.sizeof(StepOutput)})
+
+
 class KernelStats(C.Structure):
     _fields_ = [("launches", C.c_int64), ("ms", C.c_double), ("bytes", C.c_double), ("flops", C.c_double)]
 
@@ -96,6 +102,7 @@ SIGNATURES = {
     "kge_add_request": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
     "kge_abort_request": (_I, [_P, _L]),
     "kge_has_unfinished": (_I, [_P]),
+    "kge_engine_run_to_completion": (_I, [_P, _P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
     "kge_engine_step": (_I, [_P, C.POINTER(StepOutput), C.c_int32]),
     "kge_engine_stats": (_I, [_P, _P, _P, _P, _P]),
     "kge_sched_create": (_P, [C.c_int32] * 7),
@@ -283,6 +290,23 @@ class LLM:
         ids = [self.add_request(p, sp) for p, sp in zip(prompt_token_ids, sps)]
         toks = {i: [] for i in ids}
         fin = {}
+        if on_step is None:
+            # the whole job in one C call: no Python between engine steps
+            import numpy as np
+            cap = sum(sp.max_tokens for sp in sps) + len(ids) + 16
+            ev = np.zeros(cap, dtype=_event_dtype())
+            n, steps = C.c_int64(), C.c_int32()
+            check(lib().kge_engine_run_to_completion(self._h, ev.ctypes.data, cap, C.byref(n), C.byref(steps)),
+                  "kge_engine_run_to_completion")
+            ev = ev[:n.value]
+            rid, tok, f = ev["request_id"].tolist(), ev["token"].tolist(), ev["finished"].tolist()
+            for r, t, ff in zip(rid, tok, f):
+                if t >= 0:
+                    toks[r].append(t)
+                if ff:
+                    fin[r] = "stop" if ff == 1 else "length"
+            return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i))])
+                    for i, p in zip(ids, prompt_token_ids)]
         while self.has_unfinished():
             outs = self.step()
             if not outs:

@@ -377,6 +377,28 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   return (int)res.size();
 }
 
+extern "C" int kge_engine_run_to_completion(kge_engine* e, kge_step_output* events, int64_t cap, int64_t* n_events,
+                                            int32_t* n_steps) {
+  KGE_REQUIRE(e && events && n_events, "kge_engine_run_to_completion: null argument");
+  std::vector<kge_step_output> step((size_t)std::max(1, e->cfg.max_num_seqs));
+  int64_t n = 0;
+  int32_t steps = 0;
+  while (e->sched->has_unfinished()) {
+    const int m = kge_engine_step(e, step.data(), (int32_t)step.size());
+    if (m < 0) return m;
+    KGE_REQUIRE(m > 0, "kge_engine_run_to_completion: no request can be scheduled (KV pool too small for the waiting request?)");
+    ++steps;
+    for (int i = 0; i < m; ++i) {
+      if (step[i].token < 0 && !step[i].finished) continue;      // a prefill chunk advanced: nothing to report
+      KGE_REQUIRE(n < cap, "kge_engine_run_to_completion: more than %lld events", (long long)cap);
+      events[n++] = step[i];
+    }
+  }
+  *n_events = n;
+  if (n_steps) *n_steps = steps;
+  return 0;
+}
+
 // ------------------------------------------------------------- scheduler alone (host tests)
 struct kge_sched { std::unique_ptr<Scheduler> s; };
 

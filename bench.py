@@ -298,7 +298,13 @@ def run_ours(args):
     else:
         ach = s["bytes"] / s["ms"] / 1e6
         roof = {"kernel": dom, "bound": "hbm", "achieved": ach, "peak": hbm, "unit": "GB/s", "frac": ach / hbm}
-    roof.update({"traffic": None, "avg_launch_ms": per_launch_ms, "launches": s["launches"],
+    traffic, traffic_of = None, None
+    try:        # DRAM bytes of one launch of this kernel from the committed `ncu --set full` capture (never measured live)
+        t = json.load(open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "ncu_traffic.json")))[dom]
+        traffic, traffic_of = t["traffic"], f"{t['launch']}; algorithmic bytes of that launch {t['algorithmic']}; {t['source']}"
+    except (OSError, KeyError, ValueError):
+        pass
+    roof.update({"traffic": traffic, "traffic_of": traffic_of, "avg_launch_ms": per_launch_ms, "launches": s["launches"],
                  "peak_source": f"MEASURED_PEAKS.json ({src}; sustained bf16 for a kernel inside a long step)"})
     line = {
         "metric": "output tokens/sec at fixed concurrency", "value": value, "unit": "output tokens/s",

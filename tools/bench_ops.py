@@ -123,6 +123,8 @@ if __name__ == "__main__":
             shapes = [shapes[a.only]]
         bench_gemm(shapes, a.cublas)
     elif a.what == "prefill":
-        bench_prefill([(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128), (32, 128, 32, 8, 64), (4, 2048, 12, 12, 64)])
+        cases = [(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128), (32, 128, 32, 8, 64), (4, 2048, 12, 12, 64)]
+        bench_prefill(cases if a.only < 0 else [cases[a.only]])
     else:
-        bench_attn([(64, 2176, 32, 8, 128), (64, 1024, 32, 8, 128), (32, 192, 32, 8, 64), (8, 8192, 32, 8, 128)])
+        cases = [(64, 2176, 32, 8, 128), (64, 1024, 32, 8, 128), (32, 192, 32, 8, 64), (8, 8192, 32, 8, 128)]
+        bench_attn(cases if a.only < 0 else [cases[a.only]])

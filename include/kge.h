@@ -200,6 +200,8 @@ int kge_engine_create(kge_engine** out, const char* model_dir, const kge_engine_
 void kge_engine_destroy(kge_engine* e);
 int kge_engine_num_blocks(const kge_engine* e);
 int kge_engine_vocab(const kge_engine* e);
+/* eos_token_id of config.json (-1 if none): what ends a request unless ignore_eos (vllm:v1/core/sched/utils.py:94-117). */
+int kge_engine_eos_token_id(const kge_engine* e);
 int64_t kge_engine_weight_bytes(const kge_engine* e);
 int64_t kge_engine_launches(const kge_engine* e);
 

@@ -90,6 +90,7 @@ SIGNATURES = {
     "kge_engine_destroy": (None, [_P]),
     "kge_engine_num_blocks": (_I, [_P]),
     "kge_engine_vocab": (_I, [_P]),
+    "kge_engine_eos_token_id": (_I, [_P]),
     "kge_engine_weight_bytes": (_L, [_P]),
     "kge_engine_launches": (_L, [_P]),
     "kge_step": (_I, [_P, C.POINTER(StepBatch), _P, _P]),

@@ -30,6 +30,7 @@
 #include "json.h"
 #include "kge.h"
 #include "tokenizer.h"
+#include "stop_strings.h"
 
 using namespace kge;
 
@@ -56,6 +57,7 @@ struct Server {
   ServeArgs args;
   std::vector<kge_engine*> engines;       // one per TP rank
   int vocab = 0;
+  int eos = -1;
   Tokenizer tok;                          // loaded when the model directory has a tokenizer.json
   bool have_tok = false;
   std::mutex mu;
@@ -280,6 +282,8 @@ struct ParsedReq {
   std::vector<std::vector<int32_t>> prompts;
   kge_sampling_params sp{};
   std::vector<int32_t> stop_ids;
+  std::vector<std::string> stop;            // stop strings (need the tokenizer)
+  bool include_stop = false;                // include_stop_str_in_output
   bool stream = false, include_usage = false, echo = false;
   int n = 1;
   std::string model;
@@ -347,8 +351,12 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   if (const Json* so = j.get("stream_options")) r->include_usage = so->bool_or("include_usage", false);
   if (const Json* st = j.get("stop_token_ids"))
     if (st->is_arr()) for (auto& t : st->arr) if (t.is_num()) r->stop_ids.push_back((int32_t)t.num);
-  if (const Json* st = j.get("stop"))
-    if (!st->is_null() && !(st->is_arr() && st->arr.empty())) return "stop strings need a tokenizer; use stop_token_ids";
+  if (const Json* st = j.get("stop")) {       // str | [str] (vllm:entrypoints/openai/completion/protocol.py:62)
+    if (st->is_str()) { if (!st->str.empty()) r->stop.push_back(st->str); }
+    else if (st->is_arr()) { for (auto& x : st->arr) { if (!x.is_str()) return "stop must be a string or a list of strings"; if (!x.str.empty()) r->stop.push_back(x.str); } }
+    else if (!st->is_null()) return "stop must be a string or a list of strings";
+  }
+  r->include_stop = j.bool_or("include_stop_str_in_output", false);
   if (const Json* lp = j.get("logprobs"))
     if (!lp->is_null() && !(lp->type == Json::Bool && !lp->b)) return "logprobs are not supported";
   if (r->sp.max_tokens < 1) return "max_tokens must be at least 1";
@@ -396,11 +404,19 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       err = parse_prompt(s, j.get("prompt"), &pr.prompts);
     }
   }
+  if (err.empty() && !pr.stop.empty() && !s.have_tok)
+    err = "stop strings need a tokenizer.json in the model directory (none was found); use stop_token_ids";
   if (!err.empty()) return respond_error(fd, 400, err, "BadRequestError", hr.keep_alive);
   if (!pr.model.empty() && pr.model != s.args.served_model_name)
     return respond_error(fd, 404, "The model `" + pr.model + "` does not exist.", "NotFoundError", hr.keep_alive);
 
-  struct Sub { int64_t id; std::shared_ptr<ReqState> st; size_t sent = 0; bool done = false; std::string pending; };
+  // One choice of the response.  Tokens are consumed as the engine produces them, in both modes: the text stream
+  // (detokeniser + stop strings, host/stop_strings.h) decides when a stop string ends the request early.
+  struct Sub {
+    int64_t id; std::shared_ptr<ReqState> st;
+    size_t sent = 0; bool done = false;
+    TextStream ts; std::vector<int32_t> toks; int fin = 0; std::string stop_reason = "null";
+  };
   std::vector<Sub> subs;
   int prompt_tokens = 0;
   {
@@ -416,6 +432,9 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.st = std::make_shared<ReqState>();
         sb.st->prompt_len = (int)p.size();
         subs.push_back({sb.id, sb.st});
+        subs.back().ts.stop = pr.stop;
+        subs.back().ts.include_stop = pr.include_stop;
+        subs.back().ts.min_tokens = pr.sp.min_tokens;
         prompt_tokens += (int)p.size();
         s.submits.push_back(std::move(sb));
       }
@@ -426,26 +445,58 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
   const long created = (long)time(nullptr);
   auto reason = [](int f) { return f == 1 ? "\"stop\"" : f == 2 ? "\"length\"" : "null"; };
 
+  // Feed one engine token into choice `sb`; returns the text that may be handed out now.  `fin` is the engine's
+  // finish flag and applies to the last token of the batch it came with.
+  auto feed = [&](Sub& sb, int32_t tokid, int fin, bool last_of_batch) -> std::string {
+    const bool last = fin != 0 && last_of_batch;
+    sb.toks.push_back(tokid);
+    if (last) {
+      sb.fin = fin;
+      // a stop token id (not EOS) is reported as stop_reason (vllm:v1/core/sched/utils.py:105-112)
+      if (fin == 1 && !(tokid == s.eos && !pr.sp.ignore_eos))
+        for (int32_t x : pr.stop_ids) if (x == tokid) sb.stop_reason = std::to_string(tokid);
+    }
+    if (!s.have_tok) return "";
+    if (sb.ts.push(s.tok, tokid, last && fin == 1, last)) {
+      sb.fin = 1;
+      sb.stop_reason = "\"" + json_escape(sb.ts.stop[sb.ts.matched]) + "\"";
+      if (!last) { push_abort(s, sb.id); ++s.success_stop; }   // the engine still runs this request: free its KV blocks
+    }
+    return sb.ts.next_delta(sb.fin != 0);
+  };
+
   if (!pr.stream) {
     std::string choices;
     int completion = 0;
     for (size_t i = 0; i < subs.size(); ++i) {
-      auto& st = *subs[i].st;
-      std::unique_lock<std::mutex> lk(st.mu);
-      st.cv.wait(lk, [&] { return st.finished != 0; });
-      if (st.finished == 3) {
-        for (auto& o : subs) push_abort(s, o.id);
-        return respond_error(fd, 400, st.error, "BadRequestError", hr.keep_alive);
+      Sub& sb = subs[i];
+      while (!sb.fin) {
+        std::vector<int32_t> fresh;
+        int fin = 0;
+        {
+          std::unique_lock<std::mutex> lk(sb.st->mu);
+          sb.st->cv.wait(lk, [&] { return sb.st->tokens.size() > sb.sent || sb.st->finished != 0; });
+          fresh.assign(sb.st->tokens.begin() + sb.sent, sb.st->tokens.end());
+          fin = sb.st->finished;
+        }
+        if (fin == 3) {
+          std::string e;
+          { std::lock_guard<std::mutex> lk(sb.st->mu); e = sb.st->error; }
+          for (auto& o : subs) push_abort(s, o.id);
+          return respond_error(fd, 400, e, "BadRequestError", hr.keep_alive);
+        }
+        for (size_t k = 0; k < fresh.size() && !sb.fin; ++k) feed(sb, fresh[k], fin, k + 1 == fresh.size());
+        sb.sent += fresh.size();
       }
-      completion += (int)st.tokens.size();
+      completion += (int)sb.toks.size();
       if (i) choices += ",";
-      const std::string text = s.have_tok ? json_escape(s.tok.decode(st.tokens)) : "";
+      const std::string text = json_escape(sb.ts.text);
       if (chat)
         choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"" + text + "\"},\"token_ids\":" +
-                   ids_json(st.tokens) + ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
+                   ids_json(sb.toks) + ",\"logprobs\":null,\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
       else
-        choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"" + text + "\",\"token_ids\":" + ids_json(st.tokens) +
-                   ",\"logprobs\":null,\"finish_reason\":" + reason(st.finished) + ",\"stop_reason\":null}";
+        choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"" + text + "\",\"token_ids\":" + ids_json(sb.toks) +
+                   ",\"logprobs\":null,\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
     }
     std::string body = "{\"id\":\"" + rid + "\",\"object\":\"" + (chat ? "chat.completion" : "text_completion") + "\",\"created\":" +
                        std::to_string(created) + ",\"model\":\"" + model + "\",\"choices\":[" + choices + "],\"usage\":{\"prompt_tokens\":" +
@@ -482,22 +533,19 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.done = true; --remaining;
         continue;
       }
-      for (size_t k = 0; k < fresh.size() && ok; ++k) {
-        const bool last = fin && k + 1 == fresh.size();
+      for (size_t k = 0; k < fresh.size() && ok && !sb.fin; ++k) {
+        const std::string piece = json_escape(feed(sb, fresh[k], fin, k + 1 == fresh.size()));
         std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
                         "\",\"choices\":[{\"index\":" + std::to_string(i);
-        std::string piece_raw = s.have_tok ? s.tok.decode_stream(fresh[k], &sb.pending) : "";
-        if (last && s.have_tok) piece_raw += Tokenizer::flush_stream(&sb.pending);
-        const std::string piece = json_escape(piece_raw);
         if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"" + piece + "\"}";
         else c += ",\"text\":\"" + piece + "\"";
-        c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (last ? reason(fin) : "null") +
-             ",\"stop_reason\":null}]}";
+        c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (sb.fin ? reason(sb.fin) : "null") +
+             ",\"stop_reason\":" + (sb.fin ? sb.stop_reason : std::string("null")) + "}]}";
         ok = send_chunk(fd, "data: " + c + "\n\n");
         ++completion;
       }
       sb.sent += fresh.size();
-      if (fin) { sb.done = true; --remaining; }
+      if (sb.fin) { sb.done = true; --remaining; }
     }
   }
   if (!ok) {                                     // client went away: free the KV blocks
@@ -625,6 +673,26 @@ int tokenize_main(const std::string& dir) {
       bool first = true;
       for (auto& p : tok.split(t->str)) { pieces += (first ? "\"" : ",\"") + json_escape(p) + "\""; first = false; }
       printf("{\"ids\":%s,\"pieces\":%s]}\n", ids_json(ids).c_str(), pieces.c_str());
+    } else if (j.get("ids") && j.get("stop")) {
+      // {"ids", "stop": [str], "include_stop_str_in_output", "min_tokens", "stop_terminated"}: the request's text stream
+      // -> {"text", "deltas": [text handed out after each token], "matched": stop index or -1, "tokens_used"}
+      TextStream ts;
+      for (auto& x : j.get("stop")->arr) ts.stop.push_back(x.str);
+      ts.include_stop = j.bool_or("include_stop_str_in_output", false);
+      ts.min_tokens = (int)j.int_or("min_tokens", 0);
+      const bool stop_term = j.bool_or("stop_terminated", false);
+      const auto& arr = j.get("ids")->arr;
+      std::string deltas = "[";
+      int used = 0;
+      for (size_t i = 0; i < arr.size(); ++i) {
+        const bool last = i + 1 == arr.size();
+        const bool hit = ts.push(tok, (int32_t)arr[i].num, last && stop_term, last);
+        ++used;
+        deltas += (i ? ",\"" : "\"") + json_escape(ts.next_delta(hit || last)) + "\"";
+        if (hit) break;
+      }
+      printf("{\"text\":\"%s\",\"deltas\":%s],\"matched\":%d,\"tokens_used\":%d}\n", json_escape(ts.text).c_str(), deltas.c_str(),
+             ts.matched, used);
     } else if (const Json* ids = j.get("ids")) {
       std::vector<int32_t> v;
       for (auto& x : ids->arr) v.push_back((int32_t)x.num);
@@ -704,6 +772,7 @@ int main(int argc, char** argv) {
       if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
   }
   s.vocab = kge_engine_vocab(s.engines[0]);
+  s.eos = kge_engine_eos_token_id(s.engines[0]);
   {
     std::string terr;
     s.have_tok = s.tok.load(dir, &terr);

@@ -192,3 +192,52 @@ def test_string_prompts_and_chat_with_a_tokenizer(server_tok):
         raw = r.read().decode()
     pieces = [json.loads(e[6:])["choices"][0]["text"] for e in raw.split("\n\n") if e.startswith("data: {")]
     assert "".join(pieces) == a["choices"][0]["text"]
+
+
+def test_stop_strings_and_stop_reason(server_tok):
+    """`stop` strings end a request the way vLLM's detokenizer does (text cut before the stop string, or after it with
+    include_stop_str_in_output; finish_reason "stop", stop_reason = the string; the request is aborted in the engine),
+    in both response modes; a stop TOKEN id is reported as an integer stop_reason and its text is left out."""
+    port, cfg, w, d = server_tok
+    base = {"prompt": "The GPU cluster's nodes", "max_tokens": 24, "temperature": 0, "ignore_eos": True}
+    st, a = http(port, "/v1/completions", base)
+    assert st == 200, a
+    full = json.loads(a)["choices"][0]
+    text, ids = full["text"], full["token_ids"]
+    assert len(ids) == 24 and full["finish_reason"] == "length" and full["stop_reason"] is None and len(text) >= 8
+    mid = len(text) // 2
+    stop = text[mid:mid + 3]
+    cut = text.index(stop)
+    st, b = http(port, "/v1/completions", dict(base, stop=[stop]))
+    b = json.loads(b)
+    c0 = b["choices"][0]
+    assert st == 200 and c0["text"] == text[:cut] and c0["finish_reason"] == "stop" and c0["stop_reason"] == stop
+    assert c0["token_ids"] == ids[:len(c0["token_ids"])] and b["usage"]["completion_tokens"] == len(c0["token_ids"]) <= 24
+    st, b = http(port, "/v1/completions", dict(base, stop=stop, include_stop_str_in_output=True))       # a bare string is accepted
+    c0 = json.loads(b)["choices"][0]
+    assert c0["text"] == text[:cut + len(stop)] and c0["finish_reason"] == "stop" and c0["stop_reason"] == stop
+    st, b = http(port, "/v1/completions", dict(base, stop=["\x00 never there"]))
+    assert json.loads(b)["choices"][0]["text"] == text
+    # streaming: nothing beyond the cut is ever sent, the last chunk carries the reason
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", data=json.dumps(dict(base, stop=[stop], stream=True)).encode(),
+                                 headers={"Content-Type": "application/json"})
+    with urllib.request.urlopen(req, timeout=60) as r:
+        raw = r.read().decode()
+    chunks = [json.loads(e[6:])["choices"][0] for e in raw.split("\n\n") if e.startswith("data: {")]
+    assert "".join(c["text"] for c in chunks) == text[:cut] and raw.rstrip().endswith("data: [DONE]")
+    assert chunks[-1]["finish_reason"] == "stop" and chunks[-1]["stop_reason"] == stop
+    assert all(c["finish_reason"] is None for c in chunks[:-1])
+    # stop token id: first occurrence of the 6th generated token ends the request; its text is not part of the output
+    sid = ids[5]
+    k = ids.index(sid)
+    st, b = http(port, "/v1/completions", dict(base, stop_token_ids=[sid]))
+    c0 = json.loads(b)["choices"][0]
+    assert c0["token_ids"] == ids[:k + 1] and c0["finish_reason"] == "stop" and c0["stop_reason"] == sid
+    from tokenizers import Tokenizer
+    tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
+    assert c0["text"] == tok.decode(ids[:k], skip_special_tokens=True)
+    # the server keeps serving and has released the aborted requests' KV blocks
+    st, m = http(port, "/metrics")
+    assert st == 200 and "vllm:num_requests_running" in m
+    st, a2 = http(port, "/v1/completions", base)
+    assert json.loads(a2)["choices"][0]["token_ids"] == ids

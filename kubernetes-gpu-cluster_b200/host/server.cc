@@ -363,7 +363,6 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   if (r->sp.temperature < 0) return "temperature must be non-negative";
   if (r->sp.top_p <= 0 || r->sp.top_p > 1) return "top_p must be in (0, 1]";
   if (r->n < 1 || r->n > 64) return "n must be in [1, 64]";
-  if (r->echo) return "echo is not supported";
   return "";
 }
 
@@ -404,6 +403,8 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       err = parse_prompt(s, j.get("prompt"), &pr.prompts);
     }
   }
+  if (err.empty() && pr.echo && (!s.have_tok || chat))
+    err = chat ? "echo is a completions parameter" : "echo needs a tokenizer.json in the model directory (none was found)";
   if (err.empty() && !pr.stop.empty() && !s.have_tok)
     err = "stop strings need a tokenizer.json in the model directory (none was found); use stop_token_ids";
   if (!err.empty()) return respond_error(fd, 400, err, "BadRequestError", hr.keep_alive);
@@ -416,6 +417,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
     int64_t id; std::shared_ptr<ReqState> st;
     size_t sent = 0; bool done = false;
     TextStream ts; std::vector<int32_t> toks; int fin = 0; std::string stop_reason = "null";
+    std::string echo;          // echo=true: the prompt's text, sent in front of the completion (completion/serving.py)
   };
   std::vector<Sub> subs;
   int prompt_tokens = 0;
@@ -435,6 +437,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         subs.back().ts.stop = pr.stop;
         subs.back().ts.include_stop = pr.include_stop;
         subs.back().ts.min_tokens = pr.sp.min_tokens;
+        if (pr.echo) subs.back().echo = s.tok.decode(p);
         prompt_tokens += (int)p.size();
         s.submits.push_back(std::move(sb));
       }
@@ -490,7 +493,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       }
       completion += (int)sb.toks.size();
       if (i) choices += ",";
-      const std::string text = json_escape(sb.ts.text);
+      const std::string text = json_escape(sb.echo + sb.ts.text);
       if (chat)
         choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"" + text + "\"},\"token_ids\":" +
                    ids_json(sb.toks) + ",\"logprobs\":null,\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
@@ -534,7 +537,9 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         continue;
       }
       for (size_t k = 0; k < fresh.size() && ok && !sb.fin; ++k) {
-        const std::string piece = json_escape(feed(sb, fresh[k], fin, k + 1 == fresh.size()));
+        std::string piece = feed(sb, fresh[k], fin, k + 1 == fresh.size());
+        if (sb.toks.size() == 1 && !sb.echo.empty()) piece = sb.echo + piece;
+        piece = json_escape(piece);
         std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
                         "\",\"choices\":[{\"index\":" + std::to_string(i);
         if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"" + piece + "\"}";

@@ -236,6 +236,10 @@ def test_stop_strings_and_stop_reason(server_tok):
     from tokenizers import Tokenizer
     tok = Tokenizer.from_file(os.path.join(d, "tokenizer.json"))
     assert c0["text"] == tok.decode(ids[:k], skip_special_tokens=True)
+    # echo: the prompt's text in front of the completion
+    st, b = http(port, "/v1/completions", dict(base, echo=True, max_tokens=4))
+    c0 = json.loads(b)["choices"][0]
+    assert st == 200 and c0["text"] == base["prompt"] + tok.decode(ids[:4], skip_special_tokens=True)
     # the server keeps serving and has released the aborted requests' KV blocks
     st, m = http(port, "/metrics")
     assert st == 200 and "vllm:num_requests_running" in m

@@ -111,6 +111,10 @@ SIGNATURES = {
     "kge_sched_destroy": (None, [_P]),
     "kge_sched_set_reserve_full_isl": (None, [_P, C.c_int32]),
     "kge_engine_set_reserve_full_isl": (None, [_P, C.c_int32]),
+    "kge_sched_set_prefix_caching": (None, [_P, C.c_int32]),
+    "kge_engine_set_prefix_caching": (None, [_P, C.c_int32]),
+    "kge_sched_cached_tokens": (C.c_int32, [_P, C.c_int64]),
+    "kge_engine_prefix_cache_stats": (_I, [_P, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
     "kge_sched_add": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
     "kge_sched_schedule": (_I, [_P, _P, _P, C.c_int32]),
     "kge_sched_update": (_I, [_P, _P, _P, C.c_int32, C.POINTER(StepOutput), C.c_int32]),
@@ -193,7 +197,8 @@ class LLM:
                  max_num_batched_tokens: int = 0, gpu_memory_utilization: float = 0.9,
                  block_size: int = 16, num_gpu_blocks_override: int = 0, tensor_parallel_size: int = 1,
                  tp_rank: int = 0, enable_chunked_prefill: bool = True, load_format: str = "auto",
-                 seed: int = 0, device: int = 0, scheduler_reserve_full_isl: bool = True):
+                 seed: int = 0, device: int = 0, scheduler_reserve_full_isl: bool = True,
+                 enable_prefix_caching: bool = False):
         require_cuda()
         self.cfg = EngineConfig(max_num_seqs, max_num_batched_tokens, max_model_len, block_size,
                                 num_gpu_blocks_override, gpu_memory_utilization, tp_rank,
@@ -203,6 +208,7 @@ class LLM:
         check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")
         self._h = h
         lib().kge_engine_set_reserve_full_isl(h, int(scheduler_reserve_full_isl))
+        lib().kge_engine_set_prefix_caching(h, int(enable_prefix_caching))      # vLLM's own default is True
         self._next_id = 0
         self._outs = (StepOutput * 4096)()
 
@@ -238,6 +244,12 @@ class LLM:
         check(lib().kge_engine_get_timing(self._h, arr), "kge_engine_get_timing")
         return {KERNEL_CATS[i]: dict(launches=arr[i].launches, ms=arr[i].ms, bytes=arr[i].bytes, flops=arr[i].flops)
                 for i in range(NUM_KERNEL_CATS) if arr[i].launches}
+
+    def prefix_cache_stats(self):
+        """(tokens looked up, tokens served from the prefix cache) since the engine was created."""
+        q, h = C.c_int64(), C.c_int64()
+        check(lib().kge_engine_prefix_cache_stats(self._h, C.byref(q), C.byref(h)), "kge_engine_prefix_cache_stats")
+        return q.value, h.value
 
     def io_bytes(self):
         a, b = C.c_int64(), C.c_int64()

@@ -416,6 +416,18 @@ extern "C" kge_sched* kge_sched_create(int32_t max_num_seqs, int32_t max_num_bat
 extern "C" void kge_sched_destroy(kge_sched* s) { delete s; }
 extern "C" void kge_sched_set_reserve_full_isl(kge_sched* s, int32_t on) { if (s) s->s->set_reserve_full_isl(on != 0); }
 extern "C" void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on) { if (e && e->sched) e->sched->set_reserve_full_isl(on != 0); }
+extern "C" void kge_sched_set_prefix_caching(kge_sched* s, int32_t on) { if (s) s->s->set_prefix_caching(on != 0); }
+extern "C" void kge_engine_set_prefix_caching(kge_engine* e, int32_t on) { if (e && e->sched) e->sched->set_prefix_caching(on != 0); }
+extern "C" int32_t kge_sched_cached_tokens(kge_sched* s, int64_t request_id) {
+  Request* r = s ? s->s->find(request_id) : nullptr;
+  return r ? r->num_cached_tokens : -1;
+}
+extern "C" int kge_engine_prefix_cache_stats(const kge_engine* e, int64_t* queries, int64_t* hits) {
+  KGE_REQUIRE(e && e->sched, "kge_engine_prefix_cache_stats: null engine");
+  if (queries) *queries = e->sched->prefix_cache_queries();
+  if (hits) *hits = e->sched->prefix_cache_hits();
+  return 0;
+}
 extern "C" int kge_sched_add(kge_sched* s, int64_t request_id, const int32_t* prompt_ids, int32_t n,
                              const kge_sampling_params* sp) {
   KGE_REQUIRE(s && prompt_ids, "kge_sched_add: null argument");

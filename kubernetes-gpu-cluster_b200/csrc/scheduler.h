@@ -3,6 +3,10 @@
 // budget, tail preemption with recompute when blocks run out, WAITING admission up to
 // max_num_seqs), :1283 update_from_output, stop rules vllm:v1/core/sched/utils.py:94-130 and the
 // block accounting of vllm:v1/core/kv_cache_manager.py:236-430 (block 0 is the null block).
+// Automatic prefix caching (--enable-prefix-caching): block pool with vLLM's free-queue order and hash map
+// (vllm:v1/core/block_pool.py:184-433), longest-hit lookup and the "hits that are eviction candidates count as
+// allocations" rule (vllm:v1/core/single_type_kv_cache_manager.py:88-240,483-528), at most num_tokens-1 cached
+// tokens per admission (vllm:v1/core/kv_cache_manager.py:194-235).
 #pragma once
 #include <stdint.h>
 
@@ -24,6 +28,13 @@ struct SamplingParams {
   std::vector<int32_t> stop_token_ids;
 };
 
+// 128-bit chained hash of a full block: (parent block's hash, the block's token ids).
+struct BlockHash {
+  uint64_t a = 0, b = 0;
+  bool operator==(const BlockHash& o) const { return a == o.a && b == o.b; }
+};
+struct BlockHashHasher { size_t operator()(const BlockHash& h) const { return (size_t)(h.a ^ (h.b * 0x9E3779B97F4A7C15ull)); } };
+
 enum class ReqStatus { Waiting, Running, Preempted, FinishedStop, FinishedLength, Aborted };
 
 struct Request {
@@ -33,6 +44,9 @@ struct Request {
   SamplingParams sp;
   int32_t num_computed = 0;
   std::vector<int32_t> blocks;
+  std::vector<BlockHash> block_hashes;   // of the leading full blocks of prompt + output, extended on demand
+  int32_t num_hashed_blocks = 0;         // leading entries of `blocks` that are registered in the prefix cache
+  int32_t num_cached_tokens = 0;         // tokens taken from the prefix cache at the last admission
   ReqStatus status = ReqStatus::Waiting;
   int32_t num_preemptions = 0;
   int32_t num_tokens() const { return (int32_t)(prompt.size() + output.size()); }
@@ -52,6 +66,33 @@ struct SchedConfig {
   // vllm --scheduler-reserve-full-isl (default on): a WAITING request is admitted only when the pool has
   // free blocks for its whole known sequence, not just its first chunk (vllm:v1/core/kv_cache_manager.py:346-360).
   bool reserve_full_isl = true;
+  // vllm --enable-prefix-caching: full blocks stay addressable by the hash of their token prefix after their request
+  // is gone, and a new request whose prompt starts with the same tokens reuses them instead of recomputing.
+  bool enable_prefix_caching = false;
+};
+
+// Fixed pool of KV blocks: free queue (doubly linked, O(1) removal from the middle), reference counts, and the
+// prefix-cache index hash -> blocks (insertion order; the first one serves lookups).  Block 0 is the null block.
+class BlockPool {
+ public:
+  void init(int32_t num_blocks);
+  int32_t num_free() const { return num_free_; }
+  int32_t ref(int32_t b) const { return ref_[b]; }
+  int32_t cached_block(const BlockHash& h) const;          // -1 = miss
+  void touch(const std::vector<int32_t>& blocks);          // a hit: +1 reference, leaves the free queue if it was there
+  int32_t take();                                          // pops the FRONT of the free queue, evicting its hash
+  void release(const std::vector<int32_t>& blocks_in_eviction_order);
+  void set_hash(int32_t b, const BlockHash& h);
+  int64_t num_cached_hashes() const { return (int64_t)index_.size(); }
+
+ private:
+  void unlink(int32_t b);
+  void push_back(int32_t b);
+  int32_t num_free_ = 0;
+  std::vector<int32_t> prev_, next_, ref_;                 // links use block 0 as the list head
+  std::vector<uint8_t> in_free_, has_hash_;
+  std::vector<BlockHash> hash_;
+  std::unordered_map<BlockHash, std::vector<int32_t>, BlockHashHasher> index_;
 };
 
 struct Scheduled {
@@ -81,19 +122,26 @@ class Scheduler {
   bool has_unfinished() const { return !running_.empty() || !waiting_.empty(); }
   int32_t num_running() const { return (int32_t)running_.size(); }
   int32_t num_waiting() const { return (int32_t)waiting_.size(); }
-  int32_t free_blocks() const { return (int32_t)free_.size(); }
+  int32_t free_blocks() const { return pool_.num_free(); }
   int32_t usable_blocks() const { return cfg_.num_blocks - 1; }
   int64_t num_preemptions() const { return preemptions_; }
   const SchedConfig& config() const { return cfg_; }
   void set_reserve_full_isl(bool on) { cfg_.reserve_full_isl = on; }
+  void set_prefix_caching(bool on) { cfg_.enable_prefix_caching = on; }
+  int64_t prefix_cache_queries() const { return pc_queries_; }   // tokens looked up / tokens served from the cache
+  int64_t prefix_cache_hits() const { return pc_hits_; }
   Request* find(int64_t id);
 
  private:
   bool alloc(Request* r, int32_t n_new);
+  int32_t admit(Request* r, int32_t budget);            // tokens scheduled, or -1: the request has to wait
   void release(Request* r);
   void finish(Request* r, ReqStatus st);
+  void extend_hashes(Request* r, int32_t nblocks);
+  void register_full_blocks(Request* r, int32_t num_tokens);
   SchedConfig cfg_;
-  std::vector<int32_t> free_;          // stack of free block ids
+  BlockPool pool_;
+  int64_t pc_queries_ = 0, pc_hits_ = 0;
   std::deque<Request*> waiting_;
   std::vector<Request*> running_;
   std::unordered_map<int64_t, std::unique_ptr<Request>> reqs_;

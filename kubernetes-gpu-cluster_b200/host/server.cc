@@ -69,7 +69,7 @@ struct Server {
   std::atomic<int64_t> next_id{1};
   std::atomic<int64_t> prompt_tokens{0}, generation_tokens{0}, success_stop{0}, success_length{0}, num_steps{0};
   std::atomic<int> running{0}, waiting{0};
-  std::atomic<int64_t> preemptions{0};
+  std::atomic<int64_t> preemptions{0}, pc_queries{0}, pc_hits{0};
   std::atomic<float> kv_usage{0.f};
   time_t created = time(nullptr);
 };
@@ -166,6 +166,9 @@ void engine_loop(Server* sp) {
     int64_t p = 0;
     kge_engine_stats(s.engines[0], &r, &w, &u, &p);
     s.running = r; s.waiting = w; s.kv_usage = u; s.preemptions = p;
+    int64_t pq = 0, ph = 0;
+    kge_engine_prefix_cache_stats(s.engines[0], &pq, &ph);
+    s.pc_queries = pq; s.pc_hits = ph;
   }
 }
 
@@ -584,6 +587,8 @@ std::string metrics_text(Server& s) {
   counter("vllm:generation_tokens_total", "Number of generation tokens processed.", "", (double)s.generation_tokens, true);
   counter("vllm:request_success_total", "Count of successfully processed requests.", ",finished_reason=\"stop\"", (double)s.success_stop, true);
   counter("vllm:request_success_total", "", ",finished_reason=\"length\"", (double)s.success_length, false);
+  counter("vllm:prefix_cache_queries_total", "Prefix cache queries, in terms of number of queried tokens.", "", (double)s.pc_queries, true);
+  counter("vllm:prefix_cache_hits_total", "Prefix cache hits, in terms of number of cached tokens.", "", (double)s.pc_hits, true);
   counter("kge:engine_steps_total", "Engine steps executed.", "", (double)s.num_steps, true);
   return o;
 }
@@ -737,7 +742,8 @@ int main(int argc, char** argv) {
            a.load_format.c_str(), (long long)a.seed);
     return 0;
   }
-  if (a.enable_prefix_caching) fprintf(stderr, "WARNING: --enable-prefix-caching accepted but prefix caching is not implemented; every prompt is computed\n");
+  if (!a.enable_prefix_caching)
+    fprintf(stderr, "INFO: prefix caching is off (vLLM's V1 default is on): pass --enable-prefix-caching to reuse KV blocks across requests\n");
   if (a.dtype == "float16" || a.dtype == "half" || a.dtype == "float32")
     fprintf(stderr, "WARNING: --dtype %s: this engine computes in bfloat16 (fp32 accumulation); checkpoints are converted at load\n", a.dtype.c_str());
   const int sms = kge_device_sm_count();
@@ -757,7 +763,10 @@ int main(int argc, char** argv) {
     c.enable_chunked_prefill = a.enable_chunked_prefill; c.device = r;
     rcs[r] = kge_engine_create(&s.engines[r], dir.c_str(), &c, a.load_format == "dummy" ? a.seed : -1);
     if (rcs[r]) errs[r] = kge_last_error();
-    else kge_engine_set_reserve_full_isl(s.engines[r], a.scheduler_reserve_full_isl);
+    else {
+      kge_engine_set_reserve_full_isl(s.engines[r], a.scheduler_reserve_full_isl);
+      kge_engine_set_prefix_caching(s.engines[r], a.enable_prefix_caching);
+    }
   };
   {
     std::vector<std::thread> th;

@@ -73,6 +73,22 @@ class OracleScheduler:
         self.free_blocks += r.num_blocks
         r.num_blocks = 0
 
+    def _admit(self, r: Req, budget: int):
+        """WAITING -> RUNNING (scheduler.py:560-760).  Returns the tokens scheduled this step, or None
+        when the request (and so everything behind it) has to wait."""
+        c = self.cfg
+        n = r.num_tokens - r.num_computed
+        if not c.enable_chunked_prefill and n > budget:
+            return None
+        n = min(n, budget)
+        if c.reserve_full_isl:
+            full = min(r.num_tokens, c.max_model_len)
+            if -(-full // c.block_size) - r.num_blocks > self.free_blocks:
+                return None
+        if not self._alloc(r, n):
+            return None
+        return n
+
     def schedule(self) -> dict[int, int]:
         """Returns {rid: num_scheduled_tokens} in scheduling order and advances
         num_computed (scheduler.py _update_after_schedule)."""
@@ -111,15 +127,8 @@ class OracleScheduler:
                 if len(self.running) == c.max_num_seqs:
                     break
                 r = self.waiting[0]
-                n = r.num_tokens - r.num_computed
-                if not c.enable_chunked_prefill and n > budget:
-                    break
-                n = min(n, budget)
-                if c.reserve_full_isl:
-                    full = min(r.num_tokens, c.max_model_len)
-                    if -(-full // c.block_size) - r.num_blocks > self.free_blocks:
-                        break
-                if not self._alloc(r, n):
+                n = self._admit(r, budget)
+                if n is None:
                     break
                 self.waiting.popleft()
                 r.status = "running"

@@ -150,6 +150,36 @@ def test_chunked_prefill_and_preemption_do_not_change_tokens(kge, model_dirs):
         assert diff <= 20, diff
 
 
+def test_prefix_caching_reuses_blocks_and_keeps_tokens(kge, model_dirs):
+    """--enable-prefix-caching: requests that share a prompt prefix (and a second job with the same prompts) take the
+    shared full blocks from the pool instead of recomputing them; the tokens are those of the oracle (near-ties
+    aside) and of the engine without caching."""
+    cfg, w, d = model_dirs("tiny-llama")
+    shared = om.make_prompts(cfg, 1, 48, seed=7)[0]                       # three full blocks of 16
+    prompts = [shared + om.make_prompts(cfg, 1, n, seed=200 + n)[0] for n in (5, 17, 30)] + [shared[:40], list(shared)]
+    sp = kge.SamplingParams(max_tokens=12, temperature=0.0, ignore_eos=True)
+    ref_ids, ref_lg = om.OracleModel(cfg, w, BF).generate_greedy(prompts, 12, return_logits=True)
+    plain = kge.LLM(d, max_model_len=128, max_num_seqs=8, max_num_batched_tokens=64, num_gpu_blocks_override=64)
+    base = [o.outputs[0].token_ids for o in plain.generate(prompts, sp)]
+    assert plain.prefix_cache_stats() == (0, 0)
+    plain.close()
+    llm = kge.LLM(d, max_model_len=128, max_num_seqs=8, max_num_batched_tokens=64, num_gpu_blocks_override=64,
+                  enable_prefix_caching=True)
+    first = [o.outputs[0].token_ids for o in llm.generate(prompts, sp)]
+    q1, h1 = llm.prefix_cache_stats()
+    # a 64-token step admits the first prompt alone; the others arrive after its blocks are registered and hit them
+    assert q1 == sum(len(p) for p in prompts) and h1 >= 48 + 48 + 32 + 32, (q1, h1)
+    second = [o.outputs[0].token_ids for o in llm.generate(prompts, sp)]   # everything but each prompt's last block is cached now
+    q2, h2 = llm.prefix_cache_stats()
+    assert h2 - h1 >= sum((len(p) - 1) // 16 * 16 for p in prompts), (h1, h2)
+    assert llm.stats()["num_running"] == 0
+    llm.close()
+    for got in (first, second):
+        equal, near = compare_greedy(got, ref_ids, ref_lg)      # asserts every mismatch is a near-tie of the oracle
+        assert near <= 2 and equal >= 0.75 * len(prompts) * 12, (equal, near)
+        assert sum(a != b for x, y in zip(base, got) for a, b in zip(x, y)) <= 24
+
+
 def test_stop_rules_eos_and_stop_ids(kge, model_dirs):
     cfg, w, d = model_dirs("tiny-llama")
     prompts = om.make_prompts(cfg, 1, 12, seed=4)

@@ -315,7 +315,8 @@ def run_ours(args):
                                f"paged KV block 16, {pbatch} prompts per prefill step",
                    "parallelism": (f"tp{tp} (NCCL bf16 all-reduce after o_proj and down_proj)" if tp > 1
                                    else f"dp{world} (independent replicas, no collective)"),
-                   "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)"},
+                   "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)",
+                   "prefix_caching": "off: every job recomputes every prompt (the same prompts are replayed each step)"},
         "decode_ms_per_step": dec_ms_step, "decode_ms_per_token_step": dec_ms_step / max(1, pout - 1),
         "e2e": {"value": e2e, "unit": "output tokens/s", "h2d_bytes_per_step": (io1[0] - io0[0]) // args.steps,
                 "d2h_bytes_per_step": (io1[1] - io0[1]) // args.steps, "ms_per_step": e2e_s * 1e3,

@@ -218,7 +218,8 @@ def run_ours(args):
         json.dump(hf, open(os.path.join(d, "config.json"), "w"))
         llm = kge.LLM(d, max_model_len=pin + pout + 16, max_num_seqs=max(B, 8),
                       max_num_batched_tokens=max(pbatch * pin, 256), num_gpu_blocks_override=nblk,
-                      load_format="dummy", seed=1234, device=local, tensor_parallel_size=tp, tp_rank=rank if tp > 1 else 0)
+                      load_format="dummy", seed=1234, device=local, tensor_parallel_size=tp, tp_rank=rank if tp > 1 else 0,
+                      enable_prefix_caching=False)      # the same prompts are replayed every step: a cache hit would skip the prefill
     if tp > 1:
         import ctypes as C
         buf = C.create_string_buffer(128)

@@ -300,8 +300,9 @@ void kge_sched_set_reserve_full_isl(kge_sched* s, int32_t on);
 void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on);
 /* vllm --enable-prefix-caching / --no-enable-prefix-caching (vllm:v1/core/block_pool.py, kv_cache_manager.py:194-235):
  * full KV blocks stay addressable by the hash of their token prefix; a later request (or a preempted one) whose
- * tokens start the same way takes them from the pool instead of recomputing them.  Off unless switched on (vLLM's
- * V1 default is on).  Switch before the first request.  The stats are vllm:prefix_cache_queries / _hits (tokens). */
+ * tokens start the same way takes them from the pool instead of recomputing them.  The C default is off; the
+ * `vllm serve` front end and the Python mirror switch it on unless told otherwise, as vLLM V1 does.  Switch before
+ * the first request.  The stats are vllm:prefix_cache_queries / _hits (tokens). */
 void kge_sched_set_prefix_caching(kge_sched* s, int32_t on);
 void kge_engine_set_prefix_caching(kge_engine* e, int32_t on);
 int32_t kge_sched_cached_tokens(kge_sched* s, int64_t request_id);     /* at its last admission; -1 = unknown id */

@@ -198,7 +198,7 @@ class LLM:
                  block_size: int = 16, num_gpu_blocks_override: int = 0, tensor_parallel_size: int = 1,
                  tp_rank: int = 0, enable_chunked_prefill: bool = True, load_format: str = "auto",
                  seed: int = 0, device: int = 0, scheduler_reserve_full_isl: bool = True,
-                 enable_prefix_caching: bool = False):
+                 enable_prefix_caching: bool = True):
         require_cuda()
         self.cfg = EngineConfig(max_num_seqs, max_num_batched_tokens, max_model_len, block_size,
                                 num_gpu_blocks_override, gpu_memory_utilization, tp_rank,
@@ -208,7 +208,7 @@ class LLM:
         check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")
         self._h = h
         lib().kge_engine_set_reserve_full_isl(h, int(scheduler_reserve_full_isl))
-        lib().kge_engine_set_prefix_caching(h, int(enable_prefix_caching))      # vLLM's own default is True
+        lib().kge_engine_set_prefix_caching(h, int(enable_prefix_caching))      # on by default, as in vLLM V1
         self._next_id = 0
         self._outs = (StepOutput * 4096)()
 

@@ -27,7 +27,7 @@ struct ServeArgs {
   int num_gpu_blocks_override = 0;
   bool enable_chunked_prefill = true;
   bool scheduler_reserve_full_isl = true;
-  bool enable_prefix_caching = false;
+  bool enable_prefix_caching = true;       // vLLM V1 default
   bool enforce_eager = false;
   bool disable_custom_all_reduce = false;
   bool trust_remote_code = false;

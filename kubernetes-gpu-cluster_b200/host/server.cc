@@ -743,7 +743,7 @@ int main(int argc, char** argv) {
     return 0;
   }
   if (!a.enable_prefix_caching)
-    fprintf(stderr, "INFO: prefix caching is off (vLLM's V1 default is on): pass --enable-prefix-caching to reuse KV blocks across requests\n");
+    fprintf(stderr, "INFO: prefix caching is off (--no-enable-prefix-caching): every prompt is computed in full\n");
   if (a.dtype == "float16" || a.dtype == "half" || a.dtype == "float32")
     fprintf(stderr, "WARNING: --dtype %s: this engine computes in bfloat16 (fp32 accumulation); checkpoints are converted at load\n", a.dtype.c_str());
   const int sms = kge_device_sm_count();

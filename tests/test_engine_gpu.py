@@ -159,7 +159,8 @@ def test_prefix_caching_reuses_blocks_and_keeps_tokens(kge, model_dirs):
     prompts = [shared + om.make_prompts(cfg, 1, n, seed=200 + n)[0] for n in (5, 17, 30)] + [shared[:40], list(shared)]
     sp = kge.SamplingParams(max_tokens=12, temperature=0.0, ignore_eos=True)
     ref_ids, ref_lg = om.OracleModel(cfg, w, BF).generate_greedy(prompts, 12, return_logits=True)
-    plain = kge.LLM(d, max_model_len=128, max_num_seqs=8, max_num_batched_tokens=64, num_gpu_blocks_override=64)
+    plain = kge.LLM(d, max_model_len=128, max_num_seqs=8, max_num_batched_tokens=64, num_gpu_blocks_override=64,
+                    enable_prefix_caching=False)
     base = [o.outputs[0].token_ids for o in plain.generate(prompts, sp)]
     assert plain.prefix_cache_stats() == (0, 0)
     plain.close()

@@ -160,6 +160,14 @@ int kge_sample(int32_t* out_ids, const void* logits, int B, int V, int ld,
                int64_t workspace_bytes, void* stream);
 int64_t kge_sample_workspace_bytes(int B, int V);
 
+/* Log-probabilities of sampled tokens, vllm:v1/sample/sampler.py:300-349 (compute_logprobs, gather_logprobs) and
+ * vllm:v1/sample/ops/logprobs.py:11-27: logprobs = log_softmax(fp32(logits)).  Per row: out_vals/out_ids
+ * [R, top_n+1] = the sampled token first, then the top_n most likely tokens (descending; equal values by ascending
+ * id); out_rank [R] = number of vocabulary entries whose logit is >= the sampled token's (1 = it was the argmax).
+ * logits [R, ld] bf16, sampled_ids [R] on the device; 0 <= top_n <= 20. */
+int kge_logprobs(float* out_vals, int32_t* out_ids, int32_t* out_rank, const void* logits,
+                 const int32_t* sampled_ids, int R, int V, int ld, int top_n, void* stream);
+
 /* -------------------------------------------------------------------- engine (model) --- */
 
 typedef struct kge_engine kge_engine;
@@ -274,6 +282,13 @@ typedef struct {
 int kge_add_request(kge_engine* e, int64_t request_id, const int32_t* prompt_ids, int32_t n,
                     const kge_sampling_params* sp);
 int kge_abort_request(kge_engine* e, int64_t request_id);
+/* SamplingParams.logprobs (vllm:sampling_params.py): after kge_add_request, ask for the top_n log-probabilities of
+ * every token the request samples (0 = only the sampled token's, -1 = none).  After each kge_engine_step,
+ * kge_engine_step_logprobs copies what that step produced for the request: entry 0 is the sampled token, then the
+ * top_n; returns the number of entries (0 when the request sampled nothing in that step). */
+int kge_request_set_logprobs(kge_engine* e, int64_t request_id, int32_t top_n);
+int kge_engine_step_logprobs(const kge_engine* e, int64_t request_id, float* vals, int32_t* ids, int32_t* rank,
+                             int32_t cap);
 int kge_has_unfinished(const kge_engine* e);
 /* Schedule + forward + sample + update.  Writes up to cap outputs; returns the count (>= 0)
  * or a negative error. */

@@ -101,6 +101,9 @@ SIGNATURES = {
     "kge_nccl_unique_id": (_I, [_P]),
     "kge_engine_init_tp": (_I, [_P, _P]),
     "kge_add_request": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
+    "kge_request_set_logprobs": (_I, [_P, C.c_int64, C.c_int32]),
+    "kge_engine_step_logprobs": (_I, [_P, C.c_int64, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]),
+    "kge_logprobs": (_I, [_P, _P, _P, _P, _P, _I, _I, _I, _I, _P]),
     "kge_abort_request": (_I, [_P, _L]),
     "kge_has_unfinished": (_I, [_P]),
     "kge_engine_run_to_completion": (_I, [_P, _P, C.c_int64, C.POINTER(C.c_int64), C.POINTER(C.c_int32)]),
@@ -166,6 +169,7 @@ class SamplingParams:
     seed: int | None = None
     ignore_eos: bool = False
     stop_token_ids: list = field(default_factory=list)
+    logprobs: int | None = None         # top-N log-probabilities per sampled token (0: the sampled token's only)
 
     def to_c(self):
         arr = (C.c_int32 * max(1, len(self.stop_token_ids)))(*self.stop_token_ids)
@@ -177,9 +181,17 @@ class SamplingParams:
 
 
 @dataclass
+class Logprob:
+    """vllm:logprobs.py Logprob (decoded_token is left to the caller's tokenizer)."""
+    logprob: float
+    rank: int | None = None
+
+
+@dataclass
 class CompletionOutput:
     token_ids: list
     finish_reason: str | None = None
+    logprobs: list | None = None        # per generated token: {token_id: Logprob}, sampled token first
 
 
 @dataclass
@@ -277,7 +289,20 @@ class LLM:
         arr = (C.c_int32 * len(prompt_token_ids))(*prompt_token_ids)
         c = sp.to_c()
         check(lib().kge_add_request(self._h, rid, arr, len(prompt_token_ids), C.byref(c)), "kge_add_request")
+        if sp.logprobs is not None:
+            check(lib().kge_request_set_logprobs(self._h, rid, int(sp.logprobs)), "kge_request_set_logprobs")
         return rid
+
+    def step_logprobs(self, rid: int):
+        """{token_id: Logprob} of the token request `rid` sampled in the last step (sampled token first), or None."""
+        vals, ids, rank = (C.c_float * 21)(), (C.c_int32 * 21)(), C.c_int32()
+        n = check(lib().kge_engine_step_logprobs(self._h, rid, vals, ids, C.byref(rank), 21), "kge_engine_step_logprobs")
+        if n <= 0:
+            return None
+        d = {ids[0]: Logprob(vals[0], rank.value)}
+        for k in range(1, n):
+            d.setdefault(ids[k], Logprob(vals[k], k))
+        return d
 
     def step(self):
         """One engine step (schedule + forward + sample + update).  Returns a list of
@@ -303,7 +328,9 @@ class LLM:
         ids = [self.add_request(p, sp) for p, sp in zip(prompt_token_ids, sps)]
         toks = {i: [] for i in ids}
         fin = {}
-        if on_step is None:
+        want_lp = {i for i, sp in zip(ids, sps) if sp.logprobs is not None}
+        lps = {i: [] for i in want_lp}
+        if on_step is None and not want_lp:
             # the whole job in one C call: no Python between engine steps
             import numpy as np
             cap = sum(sp.max_tokens for sp in sps) + len(ids) + 16
@@ -327,11 +354,13 @@ class LLM:
             for rid, tok, f, _ in outs:
                 if tok >= 0:
                     toks[rid].append(tok)
+                    if rid in want_lp:
+                        lps[rid].append(self.step_logprobs(rid))
                 if f:
                     fin[rid] = "stop" if f == 1 else "length"
             if on_step:
                 on_step(outs)
-        return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i))])
+        return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i), lps.get(i))])
                 for i, p in zip(ids, prompt_token_ids)]
 
     # raw step with caller-built metadata (tests / bench device-resident leg)

@@ -6,6 +6,7 @@
 
 #include <memory>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "common.cuh"
@@ -65,6 +66,11 @@ struct kge_engine {
   uint8_t *meta_host = nullptr, *meta_dev = nullptr;
   int64_t meta_bytes = 0;
   int32_t* out_host = nullptr;               // pinned [max_num_seqs]
+  // log-probabilities of the last step's sampled rows (only when a request asked): [max_num_seqs, 21] + ranks
+  float* lp_vals = nullptr; int32_t* lp_ids = nullptr; int32_t* lp_rank = nullptr;        // device
+  float* lp_vals_host = nullptr; int32_t* lp_ids_host = nullptr; int32_t* lp_rank_host = nullptr;   // pinned
+  int lp_last_n = -1;                                          // top-N the last step computed, -1 = none
+  std::unordered_map<int64_t, std::pair<int, int>> lp_last;    // request id -> (row of the last step, its own N)
 
   // CUDA graphs of pure decode steps, keyed by what is baked into the launches
   struct DecodeGraph { int B, ns, stride; bool rnd; cudaGraphExec_t exec; int64_t launches; };

@@ -189,7 +189,7 @@ __global__ void bf16_to_f32_kernel(float* o, const bf16* x, int64_t n) {
 
 // Copy the caller's host metadata into the pinned block, ship it, run, read the ids back.
 static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, const int32_t* top_k,
-                    const float* top_p, const uint64_t* seeds, int32_t* out_ids_host, float* out_logits_host) {
+                    const float* top_p, const uint64_t* seeds, int32_t* out_ids_host, float* out_logits_host, int lp_n = -1) {
   const int T = b->T, B = b->B, R = b->R;
   KGE_REQUIRE(T > 0 && B > 0, "kge_step: empty batch");
   KGE_REQUIRE(T <= e->cfg.max_num_batched_tokens, "kge_step: T=%d exceeds max_num_batched_tokens=%d", T, e->cfg.max_num_batched_tokens);
@@ -256,8 +256,20 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
     if (int rc = engine_forward(e, T, B, R, stride, max_q, max_seq, dm, any_random, sum_seq, attn_flops)) return rc;
   }
   ++e->step_count;
+  e->lp_last_n = -1;
   if (R > 0) {
     KGE_CUDA_OK(cudaMemcpyAsync(e->out_host, e->d_out, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));
+    if (lp_n >= 0) {
+      // raw log-probabilities of the sampled tokens (vllm:v1/sample/sampler.py:300-349), for the rows that asked
+      if (int rc = kge_logprobs(e->lp_vals, e->lp_ids, e->lp_rank, e->logits, e->d_out, R, e->spec.vocab, e->spec.vocab, lp_n, e->stream)) return rc;
+      ++e->launches;
+      const size_t n = (size_t)R * (lp_n + 1) * 4;
+      KGE_CUDA_OK(cudaMemcpyAsync(e->lp_vals_host, e->lp_vals, n, cudaMemcpyDeviceToHost, e->stream));
+      KGE_CUDA_OK(cudaMemcpyAsync(e->lp_ids_host, e->lp_ids, n, cudaMemcpyDeviceToHost, e->stream));
+      KGE_CUDA_OK(cudaMemcpyAsync(e->lp_rank_host, e->lp_rank, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));
+      e->d2h_bytes += (int64_t)(2 * n + (size_t)R * 4);
+      e->lp_last_n = lp_n;
+    }
     if (out_logits_host) {
       // debug/parity path: logits as fp32 through a scratch carved from the (idle) gate_up buffer
       float* tmp = reinterpret_cast<float*>(e->gu);
@@ -309,6 +321,28 @@ extern "C" int kge_add_request(kge_engine* e, int64_t request_id, const int32_t*
   return 0;
 }
 
+extern "C" int kge_request_set_logprobs(kge_engine* e, int64_t request_id, int32_t top_n) {
+  KGE_REQUIRE(e, "kge_request_set_logprobs: null engine");
+  KGE_REQUIRE(top_n >= -1 && top_n <= 20, "kge_request_set_logprobs: top_n=%d must be in [-1, 20]", top_n);
+  Request* r = e->sched->find(request_id);
+  KGE_REQUIRE(r, "kge_request_set_logprobs: unknown request %lld", (long long)request_id);
+  r->sp.logprobs = top_n;
+  return 0;
+}
+
+extern "C" int kge_engine_step_logprobs(const kge_engine* e, int64_t request_id, float* vals, int32_t* ids, int32_t* rank,
+                                        int32_t cap) {
+  KGE_REQUIRE(e && vals && ids, "kge_engine_step_logprobs: null argument");
+  auto it = e->lp_last.find(request_id);
+  if (it == e->lp_last.end() || e->lp_last_n < 0) return 0;
+  const int row = it->second.first, n = std::min(it->second.second, e->lp_last_n) + 1;
+  KGE_REQUIRE(cap >= n, "kge_engine_step_logprobs: cap=%d < %d entries", cap, n);
+  const int stride = e->lp_last_n + 1;
+  for (int k = 0; k < n; ++k) { vals[k] = e->lp_vals_host[(size_t)row * stride + k]; ids[k] = e->lp_ids_host[(size_t)row * stride + k]; }
+  if (rank) *rank = e->lp_rank_host[row];
+  return n;
+}
+
 extern "C" int kge_abort_request(kge_engine* e, int64_t request_id) {
   KGE_REQUIRE(e, "kge_abort_request: null engine");
   return e->sched->abort(request_id) ? 0 : -1;
@@ -337,6 +371,8 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   std::vector<int64_t> slots;
   std::vector<float> temp, top_p;
   std::vector<uint64_t> seeds;
+  int lp_n = -1;
+  e->lp_last.clear();
   int max_blocks = 1;
   for (auto& s : sc) max_blocks = std::max(max_blocks, (int)s.req->blocks.size());
   std::vector<int32_t> btab((size_t)B * max_blocks, 0);
@@ -357,6 +393,10 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
       top_k.push_back(r->sp.top_k);
       top_p.push_back(r->sp.top_p);
       seeds.push_back(r->sp.seed ? r->sp.seed : (uint64_t)r->id * 0x9E3779B97F4A7C15ull + 1);
+      if (r->sp.logprobs >= 0) {
+        lp_n = std::max(lp_n, r->sp.logprobs);
+        e->lp_last[r->id] = {(int)rows.size() - 1, r->sp.logprobs};
+      }
     }
   }
   kge_step_batch b;
@@ -365,7 +405,7 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   b.seq_lens = seq_lens.data(); b.block_table = btab.data(); b.max_blocks = max_blocks;
   b.slot_mapping = slots.data(); b.logits_rows = rows.data(); b.R = (int)rows.size();
   std::vector<int32_t> sampled(rows.size());
-  if (int rc = run_step(e, &b, temp.data(), top_k.data(), top_p.data(), seeds.data(), sampled.data(), nullptr)) return rc;
+  if (int rc = run_step(e, &b, temp.data(), top_k.data(), top_p.data(), seeds.data(), sampled.data(), nullptr, lp_n)) return rc;
   std::vector<StepResult> res;
   e->sched->update(sampled, &res);
   for (size_t i = 0; i < res.size(); ++i) {

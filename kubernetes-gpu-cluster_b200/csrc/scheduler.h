@@ -26,6 +26,7 @@ struct SamplingParams {
   float top_p = 1.0f;
   uint64_t seed = 0;
   std::vector<int32_t> stop_token_ids;
+  int32_t logprobs = -1;               // top-N log-probabilities per sampled token (0 = the sampled token's only), -1 = none
 };
 
 // 128-bit chained hash of a full block: (parent block's hash, the block's token ids).

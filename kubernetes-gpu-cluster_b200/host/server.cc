@@ -40,6 +40,8 @@ struct ReqState {
   std::mutex mu;
   std::condition_variable cv;
   std::vector<int32_t> tokens;
+  // logprobs requested: per generated token, (token id, logprob) with the sampled token first, then the top-N
+  std::vector<std::vector<std::pair<int32_t, float>>> lps;
   int finished = 0;            // 0 running, 1 stop, 2 length, 3 error/aborted
   std::string error;
   int prompt_len = 0;
@@ -50,6 +52,7 @@ struct Submit {
   std::vector<int32_t> prompt;
   kge_sampling_params sp;
   std::vector<int32_t> stop_ids;
+  int logprobs = -1;           // SamplingParams.logprobs: top-N per token, -1 = none
   std::shared_ptr<ReqState> st;
 };
 
@@ -114,6 +117,7 @@ void engine_loop(Server* sp) {
       int rc = 0;
       for (auto* e : s.engines) {
         rc = kge_add_request(e, sub.id, sub.prompt.data(), (int)sub.prompt.size(), &sub.sp);
+        if (!rc && sub.logprobs >= 0) rc = kge_request_set_logprobs(e, sub.id, sub.logprobs);
         if (rc) break;
       }
       if (rc) {
@@ -152,7 +156,16 @@ void engine_loop(Server* sp) {
       auto st = it->second;
       {
         std::lock_guard<std::mutex> lk(st->mu);
-        if (outs[i].token >= 0) { st->tokens.push_back(outs[i].token); ++s.generation_tokens; }
+        if (outs[i].token >= 0) {
+          float lv[21]; int32_t li[21], rk = 0;
+          const int m = kge_engine_step_logprobs(s.engines[0], outs[i].request_id, lv, li, &rk, 21);
+          if (m > 0) {
+            st->lps.emplace_back();
+            for (int k = 0; k < m; ++k) st->lps.back().push_back({li[k], lv[k]});
+          }
+          st->tokens.push_back(outs[i].token);
+          ++s.generation_tokens;
+        }
         if (outs[i].finished) st->finished = outs[i].finished;
       }
       st->cv.notify_all();
@@ -287,6 +300,7 @@ struct ParsedReq {
   std::vector<int32_t> stop_ids;
   std::vector<std::string> stop;            // stop strings (need the tokenizer)
   bool include_stop = false;                // include_stop_str_in_output
+  int logprobs = -1;                        // top-N log-probabilities per token, -1 = none
   bool stream = false, include_usage = false, echo = false;
   int n = 1;
   std::string model;
@@ -360,8 +374,13 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
     else if (!st->is_null()) return "stop must be a string or a list of strings";
   }
   r->include_stop = j.bool_or("include_stop_str_in_output", false);
-  if (const Json* lp = j.get("logprobs"))
-    if (!lp->is_null() && !(lp->type == Json::Bool && !lp->b)) return "logprobs are not supported";
+  // completions: logprobs = N (vllm:entrypoints/openai/completion/protocol.py:57); chat: logprobs = true + top_logprobs = N
+  if (const Json* lp = j.get("logprobs")) {
+    if (chat) { if (lp->type == Json::Bool && lp->b) r->logprobs = (int)j.int_or("top_logprobs", 0); }
+    else if (lp->is_num()) r->logprobs = (int)lp->num;
+    else if (!lp->is_null() && !(lp->type == Json::Bool && !lp->b)) return "logprobs must be an integer";
+  }
+  if (r->logprobs < -1 || r->logprobs > 20) return "logprobs / top_logprobs must be in [0, 20]";
   if (r->sp.max_tokens < 1) return "max_tokens must be at least 1";
   if (r->sp.temperature < 0) return "temperature must be non-negative";
   if (r->sp.top_p <= 0 || r->sp.top_p > 1) return "top_p must be in (0, 1]";
@@ -373,6 +392,54 @@ void push_abort(Server& s, int64_t id) {
   std::lock_guard<std::mutex> lk(s.mu);
   s.aborts.push_back(id);
   s.cv.notify_all();
+}
+
+// --- logprobs in the OpenAI response shapes (vllm:entrypoints/openai/completion/serving.py _create_completion_logprobs,
+// chat_completion/serving.py _create_chat_logprobs).  Token strings come from the tokenizer, or are "token_id:N".
+using LpEntry = std::vector<std::pair<int32_t, float>>;
+std::string lp_token(const Server& s, int32_t id) {
+  return s.have_tok ? s.tok.decode(std::vector<int32_t>{id}) : "token_id:" + std::to_string(id);
+}
+std::string lp_num(float v) {
+  char b[32];
+  snprintf(b, sizeof b, "%.9g", (double)(v < -9999.f ? -9999.f : v));
+  return b;
+}
+std::string lp_bytes(const std::string& t) {
+  std::string o = "[";
+  for (size_t i = 0; i < t.size(); ++i) o += (i ? "," : "") + std::to_string((int)(unsigned char)t[i]);
+  return o + "]";
+}
+// completions: {"text_offset","token_logprobs","tokens","top_logprobs"} for entries [from, lps.size())
+std::string lp_completion_json(const Server& s, const std::vector<LpEntry>& lps, size_t from, size_t* offset) {
+  std::string off = "[", tl = "[", tk = "[", top = "[";
+  for (size_t i = from; i < lps.size(); ++i) {
+    const std::string sep = i > from ? "," : "";
+    const std::string t = lp_token(s, lps[i][0].first);
+    off += sep + std::to_string(*offset);
+    *offset += utf8_chars(t);
+    tl += sep + lp_num(lps[i][0].second);
+    tk += sep + "\"" + json_escape(t) + "\"";
+    top += sep + "{";
+    for (size_t k = 0; k < lps[i].size(); ++k)
+      top += (k ? ",\"" : "\"") + json_escape(lp_token(s, lps[i][k].first)) + "\":" + lp_num(lps[i][k].second);
+    top += "}";
+  }
+  return "{\"text_offset\":" + off + "],\"token_logprobs\":" + tl + "],\"tokens\":" + tk + "],\"top_logprobs\":" + top + "]}";
+}
+// chat: {"content":[{"token","logprob","bytes","top_logprobs":[{"token","logprob","bytes"}...]}]}
+std::string lp_chat_json(const Server& s, const std::vector<LpEntry>& lps, size_t from, int top_n) {
+  std::string c = "{\"content\":[";
+  for (size_t i = from; i < lps.size(); ++i) {
+    auto one = [&](const std::pair<int32_t, float>& e) {
+      const std::string t = lp_token(s, e.first);
+      return "\"token\":\"" + json_escape(t) + "\",\"logprob\":" + lp_num(e.second) + ",\"bytes\":" + lp_bytes(t);
+    };
+    c += (i > from ? ",{" : "{") + one(lps[i][0]) + ",\"top_logprobs\":[";
+    for (size_t k = 0; k < lps[i].size() && (int)k < top_n; ++k) c += (k ? ",{" : "{") + one(lps[i][k]) + "}";
+    c += "]}";
+  }
+  return c + "]}";
 }
 
 bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
@@ -421,6 +488,8 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
     size_t sent = 0; bool done = false;
     TextStream ts; std::vector<int32_t> toks; int fin = 0; std::string stop_reason = "null";
     std::string echo;          // echo=true: the prompt's text, sent in front of the completion (completion/serving.py)
+    std::vector<std::vector<std::pair<int32_t, float>>> lps;   // per consumed token: sampled first, then the top-N, no duplicates
+    size_t lp_chars = 0;       // text_offset of the next token (characters of the token strings so far)
   };
   std::vector<Sub> subs;
   int prompt_tokens = 0;
@@ -434,6 +503,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.sp = pr.sp;
         if (pr.n > 1 && sb.sp.seed) sb.sp.seed += (uint64_t)k;
         sb.stop_ids = pr.stop_ids;
+        sb.logprobs = pr.logprobs;
         sb.st = std::make_shared<ReqState>();
         sb.st->prompt_len = (int)p.size();
         subs.push_back({sb.id, sb.st});
@@ -453,9 +523,14 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
 
   // Feed one engine token into choice `sb`; returns the text that may be handed out now.  `fin` is the engine's
   // finish flag and applies to the last token of the batch it came with.
-  auto feed = [&](Sub& sb, int32_t tokid, int fin, bool last_of_batch) -> std::string {
+  auto feed = [&](Sub& sb, int32_t tokid, int fin, bool last_of_batch, const LpEntry* lp) -> std::string {
     const bool last = fin != 0 && last_of_batch;
     sb.toks.push_back(tokid);
+    if (lp && !lp->empty()) {                       // the sampled token first; drop its duplicate among the top-N
+      sb.lps.emplace_back();
+      for (size_t k = 0; k < lp->size(); ++k)
+        if (k == 0 || (*lp)[k].first != (*lp)[0].first) sb.lps.back().push_back((*lp)[k]);
+    }
     if (last) {
       sb.fin = fin;
       // a stop token id (not EOS) is reported as stop_reason (vllm:v1/core/sched/utils.py:105-112)
@@ -478,11 +553,13 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       Sub& sb = subs[i];
       while (!sb.fin) {
         std::vector<int32_t> fresh;
+        std::vector<LpEntry> fresh_lp;
         int fin = 0;
         {
           std::unique_lock<std::mutex> lk(sb.st->mu);
           sb.st->cv.wait(lk, [&] { return sb.st->tokens.size() > sb.sent || sb.st->finished != 0; });
           fresh.assign(sb.st->tokens.begin() + sb.sent, sb.st->tokens.end());
+          if (sb.st->lps.size() >= sb.st->tokens.size()) fresh_lp.assign(sb.st->lps.begin() + sb.sent, sb.st->lps.end());
           fin = sb.st->finished;
         }
         if (fin == 3) {
@@ -491,18 +568,24 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
           for (auto& o : subs) push_abort(s, o.id);
           return respond_error(fd, 400, e, "BadRequestError", hr.keep_alive);
         }
-        for (size_t k = 0; k < fresh.size() && !sb.fin; ++k) feed(sb, fresh[k], fin, k + 1 == fresh.size());
+        for (size_t k = 0; k < fresh.size() && !sb.fin; ++k)
+          feed(sb, fresh[k], fin, k + 1 == fresh.size(), k < fresh_lp.size() ? &fresh_lp[k] : nullptr);
         sb.sent += fresh.size();
       }
       completion += (int)sb.toks.size();
       if (i) choices += ",";
       const std::string text = json_escape(sb.echo + sb.ts.text);
+      std::string lpj = "null";
+      if (pr.logprobs >= 0 && !sb.lps.empty()) {
+        size_t off = utf8_chars(sb.echo);
+        lpj = chat ? lp_chat_json(s, sb.lps, 0, pr.logprobs) : lp_completion_json(s, sb.lps, 0, &off);
+      }
       if (chat)
         choices += "{\"index\":" + std::to_string(i) + ",\"message\":{\"role\":\"assistant\",\"content\":\"" + text + "\"},\"token_ids\":" +
-                   ids_json(sb.toks) + ",\"logprobs\":null,\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
+                   ids_json(sb.toks) + ",\"logprobs\":" + lpj + ",\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
       else
         choices += "{\"index\":" + std::to_string(i) + ",\"text\":\"" + text + "\",\"token_ids\":" + ids_json(sb.toks) +
-                   ",\"logprobs\":null,\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
+                   ",\"logprobs\":" + lpj + ",\"finish_reason\":" + reason(sb.fin) + ",\"stop_reason\":" + sb.stop_reason + "}";
     }
     std::string body = "{\"id\":\"" + rid + "\",\"object\":\"" + (chat ? "chat.completion" : "text_completion") + "\",\"created\":" +
                        std::to_string(created) + ",\"model\":\"" + model + "\",\"choices\":[" + choices + "],\"usage\":{\"prompt_tokens\":" +
@@ -524,6 +607,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
       Sub& sb = subs[i];
       if (sb.done) continue;
       std::vector<int32_t> fresh;
+      std::vector<LpEntry> fresh_lp;
       int fin = 0;
       std::string e;
       {
@@ -531,6 +615,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.st->cv.wait_for(lk, std::chrono::milliseconds(subs.size() > 1 ? 2 : 1000),
                            [&] { return sb.st->tokens.size() > sb.sent || sb.st->finished != 0; });
         fresh.assign(sb.st->tokens.begin() + sb.sent, sb.st->tokens.end());
+        if (sb.st->lps.size() >= sb.st->tokens.size()) fresh_lp.assign(sb.st->lps.begin() + sb.sent, sb.st->lps.end());
         fin = sb.st->finished;
         e = sb.st->error;
       }
@@ -540,14 +625,17 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         continue;
       }
       for (size_t k = 0; k < fresh.size() && ok && !sb.fin; ++k) {
-        std::string piece = feed(sb, fresh[k], fin, k + 1 == fresh.size());
-        if (sb.toks.size() == 1 && !sb.echo.empty()) piece = sb.echo + piece;
+        std::string piece = feed(sb, fresh[k], fin, k + 1 == fresh.size(), k < fresh_lp.size() ? &fresh_lp[k] : nullptr);
+        if (sb.toks.size() == 1 && !sb.echo.empty()) { piece = sb.echo + piece; sb.lp_chars = utf8_chars(sb.echo); }
         piece = json_escape(piece);
+        std::string lpj = "null";
+        if (pr.logprobs >= 0 && sb.lps.size() == sb.toks.size())
+          lpj = chat ? lp_chat_json(s, sb.lps, sb.lps.size() - 1, pr.logprobs) : lp_completion_json(s, sb.lps, sb.lps.size() - 1, &sb.lp_chars);
         std::string c = "{\"id\":\"" + rid + "\",\"object\":\"" + obj + "\",\"created\":" + std::to_string(created) + ",\"model\":\"" + model +
                         "\",\"choices\":[{\"index\":" + std::to_string(i);
         if (chat) c += ",\"delta\":{\"role\":\"assistant\",\"content\":\"" + piece + "\"}";
         else c += ",\"text\":\"" + piece + "\"";
-        c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":null,\"finish_reason\":" + (sb.fin ? reason(sb.fin) : "null") +
+        c += ",\"token_ids\":[" + std::to_string(fresh[k]) + "],\"logprobs\":" + lpj + ",\"finish_reason\":" + (sb.fin ? reason(sb.fin) : "null") +
              ",\"stop_reason\":" + (sb.fin ? sb.stop_reason : std::string("null")) + "}]}";
         ok = send_chunk(fd, "data: " + c + "\n\n");
         ++completion;

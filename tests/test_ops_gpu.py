@@ -515,3 +515,40 @@ def test_sample_philox_is_deterministic_and_in_support(kge, L):
     kth = lg.float().topk(10, dim=-1).values[:, -1]
     for b in range(B):
         assert lg[b, outs[0][b]].float() >= kth[b] and lg[b, outs[2][b]].float() >= kth[b]
+
+
+# ------------------------------------------------------------------------------ logprobs
+@pytest.mark.parametrize("R,V,ld,top_n", [(3, 1000, 1000, 5), (5, 50272, 50304, 20), (2, 128256, 128256, 0), (4, 777, 784, 3), (1, 12, 16, 20)])
+def test_logprobs_match_torch(kge, L, R, V, ld, top_n):
+    """kge_logprobs against vLLM's recipe (sampler.py:300-349): log_softmax of fp32(logits), the sampled token's value,
+    the top-N (ties by ascending id, which torch.topk leaves open) and the rank = #{x >= x_sampled}."""
+    g = torch.Generator().manual_seed(R * 1000 + V)
+    logits = (torch.randn(R, ld, generator=g) * 3).to(BF)           # bf16: plenty of exact ties
+    logits[:, V:] = 100.0                                            # padding columns must be ignored
+    sampled = torch.randint(0, V, (R,), generator=g, dtype=torch.int32)
+    sampled[0] = int(logits[0, :V].float().argmax())
+    ld_, sd = dev(logits), dev(sampled)
+    vals = torch.zeros(R, top_n + 1, dtype=torch.float32, device="cuda")
+    ids = torch.zeros(R, top_n + 1, dtype=torch.int32, device="cuda")
+    rank = torch.zeros(R, dtype=torch.int32, device="cuda")
+    check_ok(kge, L.kge_logprobs(p(vals), p(ids), p(rank), p(ld_), p(sd), R, V, ld, top_n, None), "logprobs")
+    sync()
+    x = logits[:, :V].float()
+    lp = torch.log_softmax(x, -1)
+    vals, ids, rank = vals.cpu(), ids.cpu(), rank.cpu()
+    for r in range(R):
+        t = int(sampled[r])
+        assert ids[r, 0] == t and abs(vals[r, 0].item() - lp[r, t].item()) <= 2e-5 * max(1.0, abs(lp[r, t].item()))
+        assert rank[r] == int((x[r] >= x[r, t]).sum())
+        order = sorted(range(V), key=lambda j: (-x[r, j].item(), j))[:top_n] if V <= 2000 else None
+        n_have = min(top_n, V)
+        tv, _ = torch.topk(lp[r], n_have)
+        assert torch.allclose(vals[r, 1:1 + n_have], tv, rtol=2e-5, atol=2e-5)
+        got = ids[r, 1:1 + n_have].tolist()
+        assert len(set(got)) == n_have and all(0 <= j < V for j in got)
+        assert torch.equal(x[r, got], torch.topk(x[r], n_have).values)          # the picked ids carry the top values
+        if order is not None:
+            assert got == order[:n_have]
+        if n_have < top_n:                                                        # fewer than N entries exist
+            assert (ids[r, 1 + n_have:] == -1).all() and torch.isinf(vals[r, 1 + n_have:]).all()
+    assert rank[0] == int((x[0] >= x[0].max()).sum())

@@ -1,6 +1,7 @@
 """The drop-in server end to end on a GPU: `vllm serve <dir>` (kge-serve), OpenAI-compatible HTTP,
 token-id prompts (no tokenizer offline), greedy ids equal to the in-process engine's."""
 import json
+import math
 import os
 import socket
 import subprocess
@@ -245,3 +246,50 @@ def test_stop_strings_and_stop_reason(server_tok):
     assert st == 200 and "vllm:num_requests_running" in m
     st, a2 = http(port, "/v1/completions", base)
     assert json.loads(a2)["choices"][0]["token_ids"] == ids
+
+
+def test_logprobs_in_both_api_shapes(server_tok, server):
+    """`logprobs` (completions: N; chat: logprobs=true + top_logprobs=N) in the OpenAI shapes vLLM emits: the sampled
+    token's log-probability, the top-N alternatives, text offsets; greedy sampling makes the sampled token the most
+    likely one.  Without a tokenizer, tokens are spelled token_id:N."""
+    port, cfg, w, d = server_tok
+    base = {"prompt": "The GPU cluster's nodes", "max_tokens": 6, "temperature": 0, "ignore_eos": True}
+    st, a = http(port, "/v1/completions", dict(base, logprobs=3))
+    assert st == 200, a
+    c0 = json.loads(a)["choices"][0]
+    lp = c0["logprobs"]
+    assert len(lp["tokens"]) == len(lp["token_logprobs"]) == len(lp["top_logprobs"]) == len(lp["text_offset"]) == 6
+    off = 0
+    for t, v, top, o in zip(lp["tokens"], lp["token_logprobs"], lp["top_logprobs"], lp["text_offset"]):
+        assert o == off and v <= 0 and 3 <= len(top) <= 4
+        assert abs(max(top.values()) - v) < 1e-6            # greedy: nothing is more likely than the sampled token
+        assert sum(math.exp(x) for x in top.values()) <= 1.0 + 1e-3
+        off += len(t)
+    st, b = http(port, "/v1/completions", base)
+    assert json.loads(b)["choices"][0]["logprobs"] is None
+    st, b = http(port, "/v1/completions", dict(base, logprobs=0))
+    assert all(len(t) == 1 for t in json.loads(b)["choices"][0]["logprobs"]["top_logprobs"])
+    st, c = http(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "Hi"}], "max_tokens": 4, "temperature": 0,
+                                                "ignore_eos": True, "logprobs": True, "top_logprobs": 2})
+    assert st == 200, c
+    content = json.loads(c)["choices"][0]["logprobs"]["content"]
+    assert len(content) == 4
+    for e in content:
+        assert e["logprob"] <= 0 and bytes(e["bytes"]).decode("utf-8", "replace") == e["token"] and len(e["top_logprobs"]) == 2
+        assert e["top_logprobs"][0]["token"] == e["token"] and abs(e["top_logprobs"][0]["logprob"] - e["logprob"]) < 1e-6
+    # streaming carries one entry per chunk
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", data=json.dumps(dict(base, logprobs=2, stream=True)).encode(),
+                                 headers={"Content-Type": "application/json"})
+    with urllib.request.urlopen(req, timeout=60) as r:
+        raw = r.read().decode()
+    chunks = [json.loads(e[6:])["choices"][0] for e in raw.split("\n\n") if e.startswith("data: {")]
+    assert len(chunks) == 6 and all(len(ch["logprobs"]["tokens"]) == 1 for ch in chunks)
+    assert [ch["logprobs"]["token_logprobs"][0] for ch in chunks] == pytest.approx(lp["token_logprobs"], abs=1e-5)
+    assert [ch["logprobs"]["text_offset"][0] for ch in chunks] == lp["text_offset"]
+    st, e = http(port, "/v1/completions", dict(base, logprobs=50))
+    assert st == 400 and "logprobs" in e
+    # no tokenizer: ids in, token_id:N out
+    port2 = server[0]
+    st, f = http(port2, "/v1/completions", {"prompt": [5, 6, 7], "max_tokens": 3, "temperature": 0, "ignore_eos": True, "logprobs": 1})
+    c1 = json.loads(f)["choices"][0]
+    assert st == 200 and c1["logprobs"]["tokens"] == [f"token_id:{t}" for t in c1["token_ids"]]

@@ -87,14 +87,21 @@ def test_engine_reproduces_vllm_cuda(kge, case, tmp_path):
     # free-running through the scheduler (prefill, then batched decode with the paged KV cache)
     llm = kge.LLM(d, max_model_len=256, max_num_seqs=8, max_num_batched_tokens=256, num_gpu_blocks_override=64)
     outs = llm.generate([r["prompt"] for r in case["requests"]],
-                        kge.SamplingParams(max_tokens=case["new_tokens"], temperature=0.0, ignore_eos=True))
+                        kge.SamplingParams(max_tokens=case["new_tokens"], temperature=0.0, ignore_eos=True, logprobs=5))
     assert llm.kernel_launches > 0
     llm.close()
     equal = 0
     for r, o in zip(case["requests"], outs):
         got = o.outputs[0].token_ids
-        assert len(got) == len(r["ids"])
+        assert len(got) == len(r["ids"]) == len(o.outputs[0].logprobs)
         for s, (a, e) in enumerate(zip(got, r["ids"])):
+            # SamplingParams.logprobs=5 against vLLM's own top-5 of the same step (same history up to here)
+            mine = o.outputs[0].logprobs[s]
+            assert len(mine) in (5, 6) and mine[a].rank >= 1 and next(iter(mine)) == a
+            for t, v in r["top"][s]:
+                if t in mine:
+                    assert abs(mine[t].logprob - v) <= LOGPROB_TOL, (case["model"], s, t, mine[t].logprob, v)
+            assert len({t for t, _ in r["top"][s]} & set(mine)) >= 3, (case["model"], s, r["top"][s], mine)
             if a != e:      # only at a step where vLLM's own top two are a near-tie; later steps have a different history
                 assert vllm_gap(r["top"][s]) <= NEAR_TIE and a in [t for t, _ in r["top"][s]], (case["model"], s, a, r["top"][s])
                 break

@@ -31,6 +31,7 @@
 #include "kge.h"
 #include "tokenizer.h"
 #include "stop_strings.h"
+#include "nfc.h"
 
 using namespace kge;
 
@@ -771,6 +772,8 @@ int tokenize_main(const std::string& dir) {
       bool first = true;
       for (auto& p : tok.split(t->str)) { pieces += (first ? "\"" : ",\"") + json_escape(p) + "\""; first = false; }
       printf("{\"ids\":%s,\"pieces\":%s]}\n", ids_json(ids).c_str(), pieces.c_str());
+    } else if (const Json* n = j.get("nfc")) {
+      printf("{\"text\":\"%s\"}\n", json_escape(nfc_utf8(n->str)).c_str());
     } else if (j.get("ids") && j.get("stop")) {
       // {"ids", "stop": [str], "include_stop_str_in_output", "min_tokens", "stop_terminated"}: the request's text stream
       // -> {"text", "deltas": [text handed out after each token], "matched": stop index or -1, "tokens_used"}

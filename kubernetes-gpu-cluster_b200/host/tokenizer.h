@@ -19,6 +19,7 @@
 #include <vector>
 
 #include "json.h"
+#include "nfc.h"
 #include "unicode_tables.h"
 
 namespace kge {
@@ -69,6 +70,14 @@ class Tokenizer {
         added_ids_.push_back(id);
       }
     std::sort(added_.begin(), added_.end(), [](auto& a, auto& b) { return a.first.size() > b.first.size(); });
+    // normalizer: NFC alone or inside a Sequence (other normalizers are not used by the supported families)
+    if (const Json* nz = j.get("normalizer")) {
+      if (nz->is_obj()) {
+        if (nz->str_or("type", "") == "NFC") nfc_ = true;
+        if (const Json* seq = nz->get("normalizers"))
+          if (seq->is_arr()) for (auto& x : seq->arr) if (x.is_obj() && x.str_or("type", "") == "NFC") nfc_ = true;
+      }
+    }
     // which split pattern?
     pattern_ = GPT2;
     std::string dump = ss.str();
@@ -335,8 +344,9 @@ class Tokenizer {
       if (const Json* cls = pp.get("cls")) if (cls->is_arr() && cls->arr.size() == 2) prefix_.push_back((int)cls->arr[1].num);
     }
   }
-  void encode_plain(const std::string& text, std::vector<int32_t>* out) const {
-    if (text.empty()) return;
+  void encode_plain(const std::string& raw, std::vector<int32_t>* out) const {
+    if (raw.empty()) return;
+    const std::string text = nfc_ ? nfc_utf8(raw) : raw;      // "normalizer": NFC (Qwen2.5 / Qwen3)
     for (const std::string& piece : split(text)) {
       std::vector<std::string> sym;
       std::string whole;
@@ -374,6 +384,7 @@ class Tokenizer {
   std::string byte_to_str_[256];
   std::unordered_map<uint32_t, uint8_t> cp_to_byte_;
   bool ignore_merges_ = false;
+  bool nfc_ = false;
   Pattern pattern_ = GPT2;
   std::string chat_;
 };

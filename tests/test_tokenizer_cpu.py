@@ -11,7 +11,7 @@ import subprocess
 import pytest
 
 tokenizers = pytest.importorskip("tokenizers")
-from tokenizers import Regex, Tokenizer, decoders, models, pre_tokenizers, processors, trainers  # noqa: E402
+from tokenizers import Regex, Tokenizer, decoders, models, normalizers, pre_tokenizers, processors, trainers  # noqa: E402
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 BIN = os.path.join(ROOT, "kubernetes-gpu-cluster_b200", "bin", "vllm")
@@ -37,8 +37,10 @@ TEXTS = [
 ]
 
 
-def build(kind, d):
+def build(kind, d, nfc=False):
     tok = Tokenizer(models.BPE(ignore_merges=(kind == "llama3")))
+    if nfc:
+        tok.normalizer = normalizers.NFC()          # what Qwen2.5 / Qwen3 tokenizer.json carries
     if kind == "gpt2":
         tok.pre_tokenizer = pre_tokenizers.ByteLevel(add_prefix_space=False, use_regex=True)
         specials = ["</s>", "<pad>"]
@@ -63,7 +65,7 @@ def run_cli(d, objs):
     inp = "".join(json.dumps(o) + "\n" for o in objs)
     p = subprocess.run([BIN, "tokenize", d], input=inp, capture_output=True, text=True, timeout=60)
     assert p.returncode == 0, p.stderr
-    return [json.loads(line) for line in p.stdout.splitlines()]
+    return [json.loads(line) for line in p.stdout.split("\n") if line]
 
 
 @pytest.mark.parametrize("kind", ["gpt2", "llama3", "qwen"])
@@ -125,3 +127,27 @@ def test_chat_formats(tmp_path):
     o = run_cli(str(d2), [{"messages": msgs}])[0]
     assert o["text"] == "<|im_start|>system\nBe brief.<|im_end|>\n<|im_start|>user\nHi there<|im_end|>\n<|im_start|>assistant\n"
     assert o["ids"] == tok.encode(o["text"], add_special_tokens=False).ids
+
+
+def test_nfc_normalizer_like_qwen(tmp_path):
+    """Qwen's tokenizer.json has "normalizer": NFC.  The C++ normaliser must agree with unicodedata on every code point,
+    on decomposed / reordered mark sequences and Hangul, and the tokenizer must apply it before pre-tokenisation."""
+    import random
+    import unicodedata
+    tok = build("qwen", str(tmp_path), nfc=True)
+    rng = random.Random(1)
+    singles = ["".join(chr(c) for c in range(a, min(a + 64, 0x110000)) if not 0xD800 <= c <= 0xDFFF) for a in range(0, 0x110000, 64)]
+    pool = [chr(c) for c in list(range(0x20, 0x7F)) + list(range(0xC0, 0x250)) + list(range(0x300, 0x370)) + list(range(0x1E00, 0x1F00))
+            + list(range(0x1100, 0x1200)) + list(range(0xAC00, 0xAC80)) + [0x212B, 0x2126, 0xFB1D, 0x958, 0xF43, 0x1D15E, 0x2ADC, 0x344, 0x3099,
+                                                                            0x304B, 0xB47, 0xB3E, 0xB56, 0xDD9, 0xDCA, 0xDCF, 0x1B05, 0x1B35, 0x11099, 0x110BA]]
+    mixes = ["".join(rng.choice(pool) for _ in range(rng.randrange(1, 24))) for _ in range(3000)]
+    texts = [t for t in singles if t] + mixes + [unicodedata.normalize("NFD", t) for t in mixes[:1000]]
+    outs = run_cli(str(tmp_path), [{"nfc": t} for t in texts])
+    for t, o in zip(texts, outs):
+        assert o["text"] == unicodedata.normalize("NFC", t), [hex(ord(c)) for c in t][:12]
+    samples = ["cafe\u0301 nai\u0308ve", unicodedata.normalize("NFD", "Ünïcödé Ελληνικά 한국어 が ぱ"), "A\u030a \u212b \u1100\u1161\u11a8", "plain ascii"]
+    outs = run_cli(str(tmp_path), [{"text": t} for t in samples])
+    for t, o in zip(samples, outs):
+        assert o["ids"] == tok.encode(t).ids, t
+    plain = build("qwen", str(tmp_path / "x") if (tmp_path / "x").mkdir() is None else "", nfc=False)
+    assert plain.encode(samples[0]).ids != tok.encode(samples[0]).ids      # the normaliser matters for this input

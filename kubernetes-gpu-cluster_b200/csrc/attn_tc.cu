@@ -101,6 +101,7 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
 // maximum grows by more than 2^8 since its reference maximum was fixed ("lazy rescale": P stays
 // <= 256, well inside bf16/fp32 range), so most tiles never touch O from the softmax side.
 constexpr float kRescaleThreshold = 8.0f;
+__device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
 template <int HD>
 __global__ void __launch_bounds__(160, 2)
@@ -263,13 +264,22 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
       uint32_t sv[BNK];
 #pragma unroll
       for (int c = 0; c < BNK; c += 32) tmem_ld32(t_row + (j & 1) * BNK + c, *reinterpret_cast<uint32_t(*)[32]>(&sv[c]));
-      float mx = -INFINITY;
+      // The softmax warps are issue-bound: keep the per-score work to max, one FMA, one MUFU, one add.  Scores stay
+      // unscaled (scale > 0 keeps the order); the scale is folded into the exponent's FMA.  Only tiles that reach
+      // past some row's last visible key (the diagonal) pay for masking.
+      float mx_raw = -INFINITY;
+      if (__all_sync(0xffffffffu, kbase + BNK - 1 <= lim)) {
 #pragma unroll
-      for (int i = 0; i < BNK; ++i) {
-        const float x = (kbase + i <= lim) ? __uint_as_float(sv[i]) * scale_log2 : -INFINITY;
-        sv[i] = __float_as_uint(x);
-        mx = fmaxf(mx, x);
+        for (int i = 0; i < BNK; ++i) mx_raw = fmaxf(mx_raw, __uint_as_float(sv[i]));
+      } else {
+#pragma unroll
+        for (int i = 0; i < BNK; ++i) {
+          const float x = (kbase + i <= lim) ? __uint_as_float(sv[i]) : -INFINITY;
+          sv[i] = __float_as_uint(x);
+          mx_raw = fmaxf(mx_raw, x);
+        }
       }
+      const float mx = mx_raw * scale_log2;                     // -inf stays -inf
       // PV_{j-1} must be done before O is rescaled, sP is overwritten or V stage (j+1)&1 is refilled
       if (j > 0) { mbar_wait(o_full, (uint32_t)((j - 1) & 1)); tc_after(); }
       load_tile(j + 1, false);
@@ -299,8 +309,8 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         uint32_t pk[4];
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-          const float p0 = exp2f(__uint_as_float(sv[c8 * 8 + i * 2]) - base);        // masked entries are -inf -> 0
-          const float p1 = exp2f(__uint_as_float(sv[c8 * 8 + i * 2 + 1]) - base);
+          const float p0 = ex2_ftz(fmaf(__uint_as_float(sv[c8 * 8 + i * 2]), scale_log2, -base));       // masked: -inf -> 0
+          const float p1 = ex2_ftz(fmaf(__uint_as_float(sv[c8 * 8 + i * 2 + 1]), scale_log2, -base));
           rs += p0 + p1;
           pk[i] = pack_bf2(p0, p1);
         }

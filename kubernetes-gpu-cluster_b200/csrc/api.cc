@@ -27,6 +27,13 @@ bool pdl_enabled() {
   return v != 0;
 }
 void pdl_set_enabled(bool on) { g_pdl.store(on ? 1 : 0, std::memory_order_relaxed); }
+static thread_local bool g_pdl_break = false;
+void pdl_break_next() { g_pdl_break = true; }
+bool pdl_for_this_launch() {
+  const bool brk = g_pdl_break;
+  g_pdl_break = false;
+  return pdl_enabled() && !brk;
+}
 
 static std::atomic<int> g_tun[TUN_COUNT] = {{1}, {0}, {0}, {0}};   // even grid measured +6.5 % on the C3 gate_up GEMM (profiles/r01_knob_sweep.md)
 static const char* const kTunNames[TUN_COUNT] = {"gemm_even_grid", "attn_decode_splits", "attn_split_balance", "attn_cluster_merge"};

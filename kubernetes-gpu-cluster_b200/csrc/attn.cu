@@ -369,7 +369,7 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
       attr[0].val.clusterDim.x = ns; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
       attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
       attr[1].val.programmaticStreamSerializationAllowed = 1;
-      cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 2 : 1;
+      cfg.attrs = attr; cfg.numAttrs = pdl_for_this_launch() ? 2 : 1;
       KGE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, out, (float*)nullptr, (float*)nullptr, q, q_stride, kc, vc, bt, max_blocks, sl, qsl,
                                      H, KV, bs_shift, sl2));
       return 0;

@@ -13,6 +13,10 @@ void set_error(const char* fmt, ...);
 // KGE_DISABLE_PDL and by tensor-parallel engines (see DESIGN.md "known issues").
 bool pdl_enabled();
 void pdl_set_enabled(bool on);
+// pdl_break_next(): the next launch from this thread is an ordinary stream-ordered launch (it neither starts early nor
+// relies on griddepcontrol.wait).  Used right after a kernel that is not ours (NCCL).  pdl_for_this_launch() consumes it.
+void pdl_break_next();
+bool pdl_for_this_launch();
 // Launch-shape knobs behind kge_set_tunable() (api.cc): heuristics that only change HOW work is
 // partitioned, never results.  Defaults are the measured-best settings (profiles/).
 enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_COUNT = 4 };
@@ -53,7 +57,7 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   cudaLaunchAttribute attr[1];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = 1;
-  cfg.attrs = attr; cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = pdl_for_this_launch() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
 }
 

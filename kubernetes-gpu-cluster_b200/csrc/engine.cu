@@ -273,7 +273,9 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
     // Known issue (round 1): Llama-70B at TP=4 deadlocks intermittently between ranks when the
     // forward pass uses programmatic dependent launch around the NCCL all-reduces; TP engines run
     // with plain stream order and eager decode steps until that is understood.
-    kge::pdl_set_enabled(false);
+    // KGE_TP_PDL=1 (experiment for the next round, untested at scale): keep programmatic dependent launch between our
+    // own kernels and launch only the kernel that follows each all-reduce in plain stream order (tp.cu).
+    if (!getenv("KGE_TP_PDL")) kge::pdl_set_enabled(false);
     e->use_graphs = false;
   }
   if (e->cfg.block_size <= 0) e->cfg.block_size = 16;

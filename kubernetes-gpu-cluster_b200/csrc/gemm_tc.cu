@@ -481,7 +481,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
-  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_for_this_launch() ? 1 : 0;
   cfg.attrs = attr; cfg.numAttrs = 1;
   if (SPLIT) {
     cfg.gridDim = dim3(tiles * p.splits);

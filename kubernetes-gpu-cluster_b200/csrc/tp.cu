@@ -48,6 +48,7 @@ int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n) {
   if (!api) return -1;
   ncclResult_t r = api->AllReduce(buf, buf, (size_t)n, ncclBfloat16, ncclSum, e->comm, e->stream);
   KGE_REQUIRE(r == ncclSuccess, "ncclAllReduce: %s", api->GetErrorString(r));
+  pdl_break_next();        // whatever follows the NCCL kernel is launched in plain stream order
   return 0;
 }
 

@@ -213,6 +213,17 @@ int kge_engine_eos_token_id(const kge_engine* e);
 int64_t kge_engine_weight_bytes(const kge_engine* e);
 int64_t kge_engine_launches(const kge_engine* e);
 
+/* Host-only view of a model directory - what kge_engine_create reads, without a GPU (tests, tooling):
+ * config.json -> the model description as JSON; *.safetensors tensors (all shards, BF16 / F16 / F32) sliced and
+ * converted to bf16 bits with round-to-nearest-even, exactly as the engine uploads them.  r1 / c1 = -1 mean "to the end";
+ * returns the number of elements written, -1 on error. */
+typedef struct kge_model_dir kge_model_dir;
+kge_model_dir* kge_model_open(const char* dir);
+void kge_model_close(kge_model_dir* m);
+int kge_model_spec_json(const kge_model_dir* m, char* out, int cap);
+int64_t kge_model_read_bf16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
+                            uint16_t* out, int64_t cap);
+
 /* One forward pass + greedy sampling of the R requested rows (the GPUModelRunner.execute_model
  * + Sampler path, vllm:v1/worker/gpu_model_runner.py:3955, vllm:v1/sample/sampler.py:67).
  * out_ids_host [R]; out_logits_host [R, vocab] fp32 or NULL.  Synchronous. */

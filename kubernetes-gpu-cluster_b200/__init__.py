@@ -89,6 +89,10 @@ SIGNATURES = {
     "kge_engine_create": (_I, [C.POINTER(_P), C.c_char_p, C.POINTER(EngineConfig), _L]),
     "kge_engine_destroy": (None, [_P]),
     "kge_engine_num_blocks": (_I, [_P]),
+    "kge_model_open": (_P, [C.c_char_p]),
+    "kge_model_close": (None, [_P]),
+    "kge_model_spec_json": (_I, [_P, C.c_char_p, _I]),
+    "kge_model_read_bf16": (C.c_int64, [_P, C.c_char_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _P, C.c_int64]),
     "kge_engine_vocab": (_I, [_P]),
     "kge_engine_eos_token_id": (_I, [_P]),
     "kge_engine_weight_bytes": (_L, [_P]),

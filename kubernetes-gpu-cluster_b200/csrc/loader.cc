@@ -207,3 +207,43 @@ bool ModelDir::read_bf16(const std::string& name, int64_t r0, int64_t r1, int64_
 }
 
 }  // namespace kge
+
+// ---------------------------------------------------------------- host-only C view (tests, tooling)
+#include "common.cuh"
+#include "kge.h"
+
+struct kge_model_dir { kge::ModelDir md; };
+
+extern "C" kge_model_dir* kge_model_open(const char* dir) {
+  if (!dir) { kge::set_error("kge_model_open: null directory"); return nullptr; }
+  auto* m = new kge_model_dir();
+  std::string err;
+  if (!m->md.open(dir, &err)) { kge::set_error("kge_model_open: %s", err.c_str()); delete m; return nullptr; }
+  return m;
+}
+extern "C" void kge_model_close(kge_model_dir* m) { delete m; }
+
+extern "C" int kge_model_spec_json(const kge_model_dir* m, char* out, int cap) {
+  KGE_REQUIRE(m && out && cap > 0, "kge_model_spec_json: bad arguments");
+  const kge::ModelSpec& s = m->md.spec();
+  const int n = snprintf(out, (size_t)cap,
+                         "{\"model_type\":\"%s\",\"qkv_bias\":%s,\"qk_norm\":%s,\"vocab\":%d,\"d\":%d,\"L\":%d,\"H\":%d,\"KV\":%d,\"hd\":%d,"
+                         "\"ffn\":%d,\"max_pos\":%d,\"eps\":%.9g,\"tied\":%s,\"rope_theta\":%.17g,\"rope_factor\":%.17g,\"rope_low\":%.17g,"
+                         "\"rope_high\":%.17g,\"rope_orig_max\":%d,\"bos\":%d,\"eos\":%d,\"has_weights\":%s}",
+                         s.model_type.c_str(), s.qkv_bias ? "true" : "false", s.qk_norm ? "true" : "false", s.vocab, s.d, s.L, s.H, s.KV,
+                         s.hd, s.ffn, s.max_pos, (double)s.eps, s.tied ? "true" : "false", s.rope_theta, s.rope_factor, s.rope_low,
+                         s.rope_high, s.rope_orig_max, s.bos, s.eos, m->md.has_weights() ? "true" : "false");
+  KGE_REQUIRE(n > 0 && n < cap, "kge_model_spec_json: buffer of %d bytes too small", cap);
+  return n;
+}
+
+extern "C" int64_t kge_model_read_bf16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
+                                       uint16_t* out, int64_t cap) {
+  if (!m || !name || !out) { kge::set_error("kge_model_read_bf16: null argument"); return -1; }
+  std::vector<uint16_t> v;
+  std::string err;
+  if (!m->md.read_bf16(name, r0, r1, c0, c1, &v, &err)) { kge::set_error("kge_model_read_bf16: %s", err.c_str()); return -1; }
+  if ((int64_t)v.size() > cap) { kge::set_error("kge_model_read_bf16: %lld elements > capacity %lld", (long long)v.size(), (long long)cap); return -1; }
+  memcpy(out, v.data(), v.size() * 2);
+  return (int64_t)v.size();
+}

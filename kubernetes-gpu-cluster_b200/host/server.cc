@@ -302,6 +302,7 @@ struct ParsedReq {
   std::vector<std::string> stop;            // stop strings (need the tokenizer)
   bool include_stop = false;                // include_stop_str_in_output
   int logprobs = -1;                        // top-N log-probabilities per token, -1 = none
+  bool max_tokens_given = true;
   bool stream = false, include_usage = false, echo = false;
   int n = 1;
   std::string model;
@@ -354,6 +355,9 @@ std::string parse_prompt(const Server& s, const Json* p, std::vector<std::vector
 }
 
 std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
+  // completions default to 16 tokens (completion/protocol.py:55); chat requests without a limit may use the rest of the
+  // context (chat_completion/protocol.py: max_tokens = None -> max_model_len - prompt length), resolved once the prompt is known
+  r->max_tokens_given = j.get("max_tokens") || (chat && j.get("max_completion_tokens"));
   r->sp.max_tokens = (int)j.int_or(chat ? "max_completion_tokens" : "max_tokens", j.int_or("max_tokens", 16));
   r->sp.min_tokens = (int)j.int_or("min_tokens", 0);
   r->sp.ignore_eos = j.bool_or("ignore_eos", false) ? 1 : 0;
@@ -502,6 +506,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.id = s.next_id++;
         sb.prompt = p;
         sb.sp = pr.sp;
+        if (chat && !pr.max_tokens_given) sb.sp.max_tokens = std::max(1, s.args.max_model_len - (int)p.size());
         if (pr.n > 1 && sb.sp.seed) sb.sp.seed += (uint64_t)k;
         sb.stop_ids = pr.stop_ids;
         sb.logprobs = pr.logprobs;

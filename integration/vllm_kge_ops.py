@@ -82,3 +82,32 @@ def fused_add_rms_norm_kge(x: Tensor, x_residual: Tensor, weight: Tensor | None,
         _check(_lib().kge_add_rmsnorm(y.data_ptr(), res.data_ptr(), x.data_ptr(), weight.data_ptr(), x.numel() // d, d, float(epsilon),
                                       _stream()), "kge_add_rmsnorm")
     return y, res
+
+
+# ---- SwiGLU activation: vLLM's out-of-tree layer registry (vllm/model_executor/custom_op.py: CustomOp.register_oot).
+# Every `SiluAndMul()` a model builds after this import is a KgeSiluAndMul; inputs the kernel does not cover use vLLM's own
+# forward.
+from vllm.model_executor.custom_op import CustomOp  # noqa: E402
+from vllm.model_executor.layers.activation import SiluAndMul  # noqa: E402
+
+
+def _silu_covered(x):
+    f = x.shape[-1] // 2 if x.dim() else 0
+    return x.is_cuda and x.dtype == torch.bfloat16 and x.is_contiguous() and x.shape[-1] % 2 == 0 and f % 8 == 0 and f > 0
+
+
+@CustomOp.register_oot(name="SiluAndMul")
+class KgeSiluAndMul(SiluAndMul):
+    def forward_cuda(self, x: Tensor) -> Tensor:
+        if not _silu_covered(x):
+            return SiluAndMul.forward_cuda(self, x)
+        f = x.shape[-1] // 2
+        out = torch.empty(x.shape[:-1] + (f,), dtype=x.dtype, device=x.device)
+        if x.numel():
+            lib = _lib()
+            lib.kge_silu_mul.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p]
+            lib.kge_silu_mul.restype = C.c_int
+            _check(lib.kge_silu_mul(out.data_ptr(), x.data_ptr(), x.numel() // (2 * f), f, _stream()), "kge_silu_mul")
+        return out
+
+    forward_oot = forward_cuda

@@ -29,6 +29,28 @@ def test_provider_registers_and_falls_through_on_cpu(ops):
         assert torch.equal(y, rms_norm(x, w, 1e-5))
 
 
+def test_silu_and_mul_layer_is_replaced(ops):
+    from vllm.model_executor.custom_op import op_registry_oot
+    plug = ops[0]
+    assert op_registry_oot["SiluAndMul"] is plug.KgeSiluAndMul
+    assert not plug._silu_covered(torch.zeros(2, 32, dtype=torch.bfloat16))          # CPU tensor
+    assert not plug._silu_covered(torch.zeros(2, 20, dtype=torch.bfloat16))          # half width not a multiple of 8
+
+
+@pytest.mark.gpu
+def test_kge_silu_and_mul_matches_vllm_native(ops):
+    from vllm.model_executor.layers.activation import SiluAndMul
+    plug = ops[0]
+    g = torch.Generator().manual_seed(3)
+    for shape in [(64, 2 * 14336), (5, 2 * 512), (2, 3, 2 * 64)]:
+        x = (torch.randn(*shape, generator=g) * 2).to(torch.bfloat16).cuda()
+        assert plug._silu_covered(x)
+        got = plug.KgeSiluAndMul.forward_cuda(None, x)
+        ref = SiluAndMul.forward_native(x)
+        diff = (got.view(torch.int16).int() - ref.view(torch.int16).int()).abs()
+        assert got.shape == ref.shape and int(diff.max()) <= 1 and float((diff > 0).float().mean()) < 5e-3
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("T,d", [(1, 4096), (64, 4096), (7, 768), (300, 8192)])
 def test_vllm_dispatches_to_kge_kernels(ops, T, d):

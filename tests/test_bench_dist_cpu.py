@@ -66,3 +66,18 @@ def test_reference_arm_line_shape():
     assert line["impl"] == "reference" and line["unit"] == "output tokens/s" and line["value"] > 0
     assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
     assert line["e2e"] == {"value": line["value"], "unit": "output tokens/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}
+
+
+def test_latency_probe_uses_vllm_bench_definitions():
+    """TTFT = first token - send time; ITL = gaps between a request's following tokens; medians."""
+    import bench
+
+    class FakeLLM:
+        def generate(self, prompts, sp, on_step=None):
+            for step in range(1, 7):                      # request 2's prompt needs two steps
+                on_step([(rid, 5, 0, 1) if step >= (1 if rid < 2 else 2) else (rid, -1, 0, 8) for rid in range(3)])
+
+    ticks = iter([0.0] + [0.010 * i + (0.005 if i == 4 else 0.0) for i in range(1, 8)])
+    r = bench.latency_probe(FakeLLM(), None, None, clock=lambda: next(ticks))
+    assert r["requests"] == 3 and abs(r["p50_ttft_ms"] - 10.0) < 1e-9           # first tokens at 10, 10, 20 ms
+    assert abs(r["p50_itl_ms"] - 10.0) < 1e-6                                   # gaps: mostly 10 ms, one 15 and one 5

@@ -35,9 +35,17 @@ struct Json {
     const Json* j = get(k);
     return (j && j->type == Num) ? j->num : d;
   }
+  // number -> integer without undefined behaviour on hostile input: NaN -> 0, out of range -> saturated
+  static int64_t to_i64(double v) {
+    if (!(v == v)) return 0;
+    if (v >= 9.2e18) return INT64_MAX;
+    if (v <= -9.2e18) return INT64_MIN;
+    return (int64_t)v;
+  }
+  int64_t as_i64() const { return type == Num ? to_i64(num) : 0; }
   int64_t int_or(const std::string& k, int64_t d) const {
     const Json* j = get(k);
-    return (j && j->type == Num) ? (int64_t)j->num : d;
+    return (j && j->type == Num) ? to_i64(j->num) : d;
   }
   bool bool_or(const std::string& k, bool d) const {
     const Json* j = get(k);

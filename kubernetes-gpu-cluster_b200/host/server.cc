@@ -325,7 +325,7 @@ std::string parse_prompt(const Server& s, const Json* p, std::vector<std::vector
   auto one = [&](const Json& a, std::vector<int32_t>* v) -> std::string {
     for (auto& t : a.arr) {
       if (!t.is_num()) return "prompt arrays must hold integers";
-      const int64_t id = (int64_t)t.num;
+      const int64_t id = t.as_i64();
       if (id < 0 || id >= vocab) return "token id " + std::to_string(id) + " is out of vocabulary";
       v->push_back((int32_t)id);
     }
@@ -357,22 +357,23 @@ std::string parse_prompt(const Server& s, const Json* p, std::vector<std::vector
 std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   // completions default to 16 tokens (completion/protocol.py:55); chat requests without a limit may use the rest of the
   // context (chat_completion/protocol.py: max_tokens = None -> max_model_len - prompt length), resolved once the prompt is known
+  auto I = [&](const char* k, int64_t d) { return (int)std::max<int64_t>(INT32_MIN, std::min<int64_t>(j.int_or(k, d), INT32_MAX)); };
   r->max_tokens_given = j.get("max_tokens") || (chat && j.get("max_completion_tokens"));
-  r->sp.max_tokens = (int)j.int_or(chat ? "max_completion_tokens" : "max_tokens", j.int_or("max_tokens", 16));
-  r->sp.min_tokens = (int)j.int_or("min_tokens", 0);
+  r->sp.max_tokens = I(chat ? "max_completion_tokens" : "max_tokens", I("max_tokens", 16));
+  r->sp.min_tokens = I("min_tokens", 0);
   r->sp.ignore_eos = j.bool_or("ignore_eos", false) ? 1 : 0;
   r->sp.temperature = (float)j.num_or("temperature", 1.0);     // omitted => 1.0 (vllm:sampling_params.py:205)
   r->sp.top_p = (float)j.num_or("top_p", 1.0);
-  r->sp.top_k = (int)j.int_or("top_k", 0);
+  r->sp.top_k = I("top_k", 0);
   if (r->sp.top_k < 0) r->sp.top_k = 0;
   r->sp.seed = (uint64_t)j.int_or("seed", 0);
-  r->n = (int)j.int_or("n", 1);
+  r->n = I("n", 1);
   r->stream = j.bool_or("stream", false);
   r->echo = j.bool_or("echo", false);
   r->model = j.str_or("model", "");
   if (const Json* so = j.get("stream_options")) r->include_usage = so->bool_or("include_usage", false);
   if (const Json* st = j.get("stop_token_ids"))
-    if (st->is_arr()) for (auto& t : st->arr) if (t.is_num()) r->stop_ids.push_back((int32_t)t.num);
+    if (st->is_arr()) for (auto& t : st->arr) if (t.is_num()) r->stop_ids.push_back((int32_t)std::max<int64_t>(-1, std::min<int64_t>(t.as_i64(), INT32_MAX)));
   if (const Json* st = j.get("stop")) {       // str | [str] (vllm:entrypoints/openai/completion/protocol.py:62)
     if (st->is_str()) { if (!st->str.empty()) r->stop.push_back(st->str); }
     else if (st->is_arr()) { for (auto& x : st->arr) { if (!x.is_str()) return "stop must be a string or a list of strings"; if (!x.str.empty()) r->stop.push_back(x.str); } }
@@ -381,8 +382,8 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   r->include_stop = j.bool_or("include_stop_str_in_output", false);
   // completions: logprobs = N (vllm:entrypoints/openai/completion/protocol.py:57); chat: logprobs = true + top_logprobs = N
   if (const Json* lp = j.get("logprobs")) {
-    if (chat) { if (lp->type == Json::Bool && lp->b) r->logprobs = (int)j.int_or("top_logprobs", 0); }
-    else if (lp->is_num()) r->logprobs = (int)lp->num;
+    if (chat) { if (lp->type == Json::Bool && lp->b) r->logprobs = I("top_logprobs", 0); }
+    else if (lp->is_num()) r->logprobs = (int)std::max<int64_t>(-2, std::min<int64_t>(lp->as_i64(), 1000));
     else if (!lp->is_null() && !(lp->type == Json::Bool && !lp->b)) return "logprobs must be an integer";
   }
   if (r->logprobs < -1 || r->logprobs > 20) return "logprobs / top_logprobs must be in [0, 20]";
@@ -801,7 +802,7 @@ int tokenize_main(const std::string& dir) {
              ts.matched, used);
     } else if (const Json* ids = j.get("ids")) {
       std::vector<int32_t> v;
-      for (auto& x : ids->arr) v.push_back((int32_t)x.num);
+      for (auto& x : ids->arr) v.push_back((int32_t)std::max<int64_t>(-1, std::min<int64_t>(x.as_i64(), INT32_MAX)));
       std::string streamed, pending;
       for (int32_t id : v) streamed += tok.decode_stream(id, &pending);
       streamed += Tokenizer::flush_stream(&pending);

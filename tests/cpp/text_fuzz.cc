@@ -51,6 +51,31 @@ int main(int argc, char** argv) {
     }
     if (out != ts.text && !ids.empty()) { fprintf(stderr, "deltas do not add up to the text at %d\n", it); return 1; }
   }
+  // JSON bodies as a client might send them, mutated: the parser must reject or accept, never crash; numbers convert
+  // to integers without undefined behaviour
+  const std::string sample = "{\"model\":\"m\",\"prompt\":[1,2,3,1e30,-1e30,0.5],\"max_tokens\":1e99,\"stop\":[\"a\",\"\\u00e9\\ud83d\\ude00\"],"
+                             "\"stream_options\":{\"include_usage\":true},\"nested\":[[[[[[[[1]]]]]]]],\"seed\":-0,\"x\":null}";
+  for (int it = 0; it < 20000; ++it) {
+    std::string b = sample;
+    const int muts = 1 + (int)(rng() % 4);
+    for (int m = 0; m < muts; ++m) {
+      const size_t pos = rng() % b.size();
+      switch (rng() % 4) {
+        case 0: b[pos] = (char)(rng() % 256); break;
+        case 1: b.erase(pos, 1 + rng() % 3); break;
+        case 2: b.insert(pos, std::string(1 + rng() % 200, "[{\"\\"[rng() % 4])); break;
+        default: b.insert(pos, std::to_string((double)rng() * 1e300)); break;
+      }
+      if (b.empty()) b = "x";
+    }
+    Json j;
+    std::string e;
+    if (json_parse(b, &j, &e) && j.is_obj()) {
+      total += (size_t)(j.int_or("max_tokens", 1) & 1) + (size_t)(j.int_or("seed", 0) & 1);
+      if (const Json* p = j.get("prompt")) if (p->is_arr()) for (auto& t : p->arr) total += (size_t)(t.as_i64() & 1);
+      total += json_escape(j.str_or("model", "")).size();
+    }
+  }
   printf("ok %zu\n", total);
   return 0;
 }

@@ -27,6 +27,7 @@ struct ServeArgs {
   int num_gpu_blocks_override = 0;
   bool enable_chunked_prefill = true;
   bool scheduler_reserve_full_isl = true;
+  std::string generation_config = "auto";     // auto: defaults from the model's generation_config.json; vllm: none
   bool enable_prefix_caching = true;       // vLLM V1 default
   bool enforce_eager = false;
   bool disable_custom_all_reduce = false;
@@ -96,6 +97,7 @@ inline std::string parse_serve_args(int argc, char** argv, ServeArgs* a) {
     else if (key == "--num-gpu-blocks-override") err = need_int(&a->num_gpu_blocks_override);
     else if (key == "--enable-chunked-prefill") a->enable_chunked_prefill = true;
     else if (key == "--no-enable-chunked-prefill") a->enable_chunked_prefill = false;
+    else if (key == "--generation-config") { if (!need(&a->generation_config)) return key + " expects a value"; }
     else if (key == "--scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = true;
     else if (key == "--no-scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = false;
     else if (key == "--enable-prefix-caching") a->enable_prefix_caching = true;

@@ -32,6 +32,7 @@
 #include "tokenizer.h"
 #include "stop_strings.h"
 #include "nfc.h"
+#include "genconfig.h"
 
 using namespace kge;
 
@@ -62,6 +63,7 @@ struct Server {
   std::vector<kge_engine*> engines;       // one per TP rank
   int vocab = 0;
   int eos = -1;
+  GenDefaults gen;                        // generation_config.json defaults and extra end-of-sequence ids
   Tokenizer tok;                          // loaded when the model directory has a tokenizer.json
   bool have_tok = false;
   std::mutex mu;
@@ -303,6 +305,7 @@ struct ParsedReq {
   bool include_stop = false;                // include_stop_str_in_output
   int logprobs = -1;                        // top-N log-probabilities per token, -1 = none
   bool max_tokens_given = true;
+  bool given_temperature = true, given_top_p = true, given_top_k = true;
   bool stream = false, include_usage = false, echo = false;
   int n = 1;
   std::string model;
@@ -362,9 +365,12 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   r->sp.max_tokens = I(chat ? "max_completion_tokens" : "max_tokens", I("max_tokens", 16));
   r->sp.min_tokens = I("min_tokens", 0);
   r->sp.ignore_eos = j.bool_or("ignore_eos", false) ? 1 : 0;
-  r->sp.temperature = (float)j.num_or("temperature", 1.0);     // omitted => 1.0 (vllm:sampling_params.py:205)
+  r->sp.temperature = (float)j.num_or("temperature", 1.0);     // omitted => 1.0 (vllm:sampling_params.py:205) unless the model says otherwise
   r->sp.top_p = (float)j.num_or("top_p", 1.0);
   r->sp.top_k = I("top_k", 0);
+  r->given_temperature = j.get("temperature") && j.get("temperature")->is_num();
+  r->given_top_p = j.get("top_p") && j.get("top_p")->is_num();
+  r->given_top_k = j.get("top_k") && j.get("top_k")->is_num();
   if (r->sp.top_k < 0) r->sp.top_k = 0;
   r->sp.seed = (uint64_t)j.int_or("seed", 0);
   r->n = I("n", 1);
@@ -454,6 +460,15 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
   if (!json_parse(hr.body, &j, &perr) || !j.is_obj()) return respond_error(fd, 400, "invalid JSON body: " + perr, "BadRequestError", hr.keep_alive);
   ParsedReq pr;
   std::string err = parse_sampling(j, &pr, chat);
+  if (err.empty()) {
+    // what the model's generation_config.json supplies when the request is silent (vLLM: --generation-config auto)
+    if (!pr.given_temperature && s.gen.has_temperature) pr.sp.temperature = (float)s.gen.temperature;
+    if (!pr.given_top_p && s.gen.has_top_p) pr.sp.top_p = (float)s.gen.top_p;
+    if (!pr.given_top_k && s.gen.has_top_k) pr.sp.top_k = s.gen.top_k;
+    if (!pr.sp.ignore_eos)
+      for (int32_t id : s.gen.extra_eos)
+        if (std::find(pr.stop_ids.begin(), pr.stop_ids.end(), id) == pr.stop_ids.end()) pr.stop_ids.push_back(id);
+  }
   if (err.empty()) {
     if (chat) {
       // messages are rendered with the model family's chat format (Llama-3 headers or ChatML) and tokenised;
@@ -831,12 +846,15 @@ int main(int argc, char** argv) {
     printf("{\"model\":\"%s\",\"served_model_name\":\"%s\",\"host\":\"%s\",\"port\":%d,\"max_model_len\":%d,\"dtype\":\"%s\","
            "\"tensor_parallel_size\":%d,\"pipeline_parallel_size\":%d,\"gpu_memory_utilization\":%.4f,\"max_num_seqs\":%d,"
            "\"max_num_batched_tokens\":%d,\"block_size\":%d,\"enable_chunked_prefill\":%s,\"enable_prefix_caching\":%s,"
-           "\"enforce_eager\":%s,\"disable_custom_all_reduce\":%s,\"trust_remote_code\":%s,\"load_format\":\"%s\",\"seed\":%lld}\n",
+           "\"enforce_eager\":%s,\"disable_custom_all_reduce\":%s,\"trust_remote_code\":%s,\"load_format\":\"%s\",\"seed\":%lld,"
+           "\"generation_config\":\"%s\",\"generation_defaults\":%s}\n",
            json_escape(a.model).c_str(), json_escape(a.served_model_name).c_str(), a.host.c_str(), a.port, a.max_model_len, a.dtype.c_str(),
            a.tensor_parallel_size, a.pipeline_parallel_size, a.gpu_memory_utilization, a.max_num_seqs, a.max_num_batched_tokens,
            a.block_size, a.enable_chunked_prefill ? "true" : "false", a.enable_prefix_caching ? "true" : "false",
            a.enforce_eager ? "true" : "false", a.disable_custom_all_reduce ? "true" : "false", a.trust_remote_code ? "true" : "false",
-           a.load_format.c_str(), (long long)a.seed);
+           a.load_format.c_str(), (long long)a.seed, json_escape(a.generation_config).c_str(),
+           load_gen_defaults(a.generation_config == "auto" || a.generation_config == "vllm" ? a.model : a.generation_config,
+                             a.generation_config != "vllm").to_json().c_str());
     return 0;
   }
   if (!a.enable_prefix_caching)
@@ -882,6 +900,13 @@ int main(int argc, char** argv) {
     for (int r = 0; r < a.tensor_parallel_size; ++r)
       if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
   }
+  // sampling defaults and extra end-of-sequence ids the model ships (--generation-config auto | vllm | DIR)
+  s.gen = load_gen_defaults(a.generation_config == "auto" || a.generation_config == "vllm" ? dir : a.generation_config, a.generation_config != "vllm");
+  if (s.gen.has_temperature && s.gen.temperature < 0) s.gen.has_temperature = false;
+  if (s.gen.has_top_p && !(s.gen.top_p > 0 && s.gen.top_p <= 1)) s.gen.has_top_p = false;
+  if (s.gen.has_temperature || s.gen.has_top_p || s.gen.has_top_k || !s.gen.extra_eos.empty())
+    fprintf(stderr, "INFO: model defaults applied to requests that leave them out: %s\n", s.gen.to_json().c_str());
+  for (auto& k : s.gen.ignored) fprintf(stderr, "WARNING: generation_config.json sets %s, which this engine does not implement\n", k.c_str());
   s.vocab = kge_engine_vocab(s.engines[0]);
   s.eos = kge_engine_eos_token_id(s.engines[0]);
   {

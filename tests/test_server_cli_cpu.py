@@ -87,3 +87,26 @@ def test_deploy_values_keep_gpu_count_and_tp_consistent():
         rc, out = dry(*argv)
         assert rc == 0, (f, out)
         assert out["tensor_parallel_size"] == m["requestGPU"], f
+
+
+def test_generation_config_defaults_and_extra_eos(tmp_path):
+    """vLLM's server takes sampling defaults and extra end-of-sequence ids from the model directory (--generation-config auto):
+    Llama-3.1-Instruct stops at <|eot_id|> only because generation_config.json lists it."""
+    (tmp_path / "config.json").write_text(json.dumps({"model_type": "llama", "eos_token_id": [128001, 128008, 128009]}))
+    (tmp_path / "generation_config.json").write_text(json.dumps({"temperature": 0.6, "top_p": 0.9, "top_k": 20, "do_sample": True,
+                                                                  "eos_token_id": [128001, 128008, 128009], "repetition_penalty": 1.05}))
+    rc, d = dry("serve", str(tmp_path))
+    assert rc == 0 and d["generation_config"] == "auto"
+    g = d["generation_defaults"]
+    assert (g["temperature"], g["top_p"], g["top_k"]) == (0.6, 0.9, 20) and g["extra_eos_token_ids"] == [128008, 128009]
+    assert g["ignored"] == ["repetition_penalty"]
+    rc, d = dry("serve", str(tmp_path), "--generation-config", "vllm")
+    g = d["generation_defaults"]
+    assert (g["temperature"], g["top_p"], g["top_k"]) == (None, None, None) and g["extra_eos_token_ids"] == [128008, 128009]
+    other = tmp_path / "gen"
+    other.mkdir()
+    (other / "generation_config.json").write_text(json.dumps({"temperature": 0.2, "eos_token_id": 7}))
+    rc, d = dry("serve", str(tmp_path), f"--generation-config={other}")
+    assert d["generation_defaults"]["temperature"] == 0.2 and d["generation_defaults"]["extra_eos_token_ids"] == [7]
+    rc, d = dry("serve", "facebook/opt-125m")
+    assert d["generation_defaults"] == {"temperature": None, "top_p": None, "top_k": None, "extra_eos_token_ids": [], "ignored": []}

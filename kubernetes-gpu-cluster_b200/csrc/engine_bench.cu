@@ -46,6 +46,7 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   KGE_REQUIRE(e && prompts_host && out_tokens_host && ms, "kge_engine_run_resident: null argument");
   KGE_REQUIRE(B > 0 && prompt_len > 0 && out_len > 0 && prefill_batch > 0, "kge_engine_run_resident: bad sizes");
   KGE_REQUIRE(!e->sched->has_unfinished(), "kge_engine_run_resident: the scheduler must be idle");
+  e->sched->invalidate_prefix_cache();        // this replay writes KV blocks of its own choosing
   KGE_REQUIRE(B <= e->cfg.max_num_seqs, "kge_engine_run_resident: B=%d > max_num_seqs=%d", B, e->cfg.max_num_seqs);
   KGE_REQUIRE(prompt_len + out_len <= e->cfg.max_model_len, "kge_engine_run_resident: sequence exceeds max_model_len");
   KGE_REQUIRE(prefill_batch * prompt_len <= e->cfg.max_num_batched_tokens, "kge_engine_run_resident: prefill step exceeds max_num_batched_tokens");

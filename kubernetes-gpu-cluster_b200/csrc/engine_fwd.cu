@@ -290,6 +290,7 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
 
 extern "C" int kge_step(kge_engine* e, const kge_step_batch* batch, int32_t* out_ids_host, float* out_logits_host) {
   KGE_REQUIRE(e && batch, "kge_step: null argument");
+  e->sched->invalidate_prefix_cache();        // the caller's block tables may overwrite blocks the scheduler has cached
   return run_step(e, batch, nullptr, nullptr, nullptr, nullptr, out_ids_host, out_logits_host);
 }
 

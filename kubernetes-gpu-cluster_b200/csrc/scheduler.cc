@@ -65,6 +65,11 @@ void BlockPool::release(const std::vector<int32_t>& order) {
     if (ref_[b] == 0 && !in_free_[b]) push_back(b);          // hashes stay: the blocks remain cache hits until reused
 }
 
+void BlockPool::forget_hashes() {
+  index_.clear();
+  std::fill(has_hash_.begin(), has_hash_.end(), (uint8_t)0);
+}
+
 void BlockPool::set_hash(int32_t b, const BlockHash& h) {
   hash_[b] = h;
   has_hash_[b] = 1;
@@ -127,6 +132,12 @@ bool Scheduler::add(int64_t id, const int32_t* prompt, int32_t n, const Sampling
   waiting_.push_back(r.get());
   reqs_[id] = std::move(r);
   return true;
+}
+
+void Scheduler::invalidate_prefix_cache() {
+  if (!cfg_.enable_prefix_caching) return;
+  pool_.forget_hashes();
+  for (auto& kv : reqs_) kv.second->num_hashed_blocks = (int32_t)kv.second->blocks.size();   // nothing of theirs gets registered later
 }
 
 bool Scheduler::alloc(Request* r, int32_t n_new) {          // a RUNNING request grows

@@ -85,6 +85,7 @@ class BlockPool {
   void release(const std::vector<int32_t>& blocks_in_eviction_order);
   void set_hash(int32_t b, const BlockHash& h);
   int64_t num_cached_hashes() const { return (int64_t)index_.size(); }
+  void forget_hashes();                                    // drop every cache entry (block contents were overwritten behind the pool's back)
 
  private:
   void unlink(int32_t b);
@@ -129,6 +130,9 @@ class Scheduler {
   const SchedConfig& config() const { return cfg_; }
   void set_reserve_full_isl(bool on) { cfg_.reserve_full_isl = on; }
   void set_prefix_caching(bool on) { cfg_.enable_prefix_caching = on; }
+  // KV blocks were written without going through schedule() (kge_step with caller-built tables, the resident replay):
+  // nothing cached can be trusted any more.  Requests that are running keep their blocks but register no more hashes.
+  void invalidate_prefix_cache();
   int64_t prefix_cache_queries() const { return pc_queries_; }   // tokens looked up / tokens served from the cache
   int64_t prefix_cache_hits() const { return pc_hits_; }
   Request* find(int64_t id);

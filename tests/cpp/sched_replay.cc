@@ -76,6 +76,8 @@ int main(int argc, char** argv) {
     // abort path: fill the scheduler again and abort everything mid-flight
     for (auto& r : reqs.arr) add(r);
     for (int i = 0; i < 3 && s.has_unfinished(); ++i) { s.schedule(); std::vector<int32_t> t(4096, 7); std::vector<StepResult> rr; s.update(t, &rr); }
+    s.invalidate_prefix_cache();                 // blocks written behind the scheduler's back: forget every hash, keep running
+    for (int i = 0; i < 3 && s.has_unfinished(); ++i) { s.schedule(); std::vector<int32_t> t(4096, 7); std::vector<StepResult> rr; s.update(t, &rr); }
     for (auto& r : reqs.arr) s.abort((int64_t)r.int_or("rid", 0));
     if (s.has_unfinished() || s.free_blocks() != sc.num_blocks - 1) { fprintf(stderr, "abort left state behind\n"); return 1; }
   }

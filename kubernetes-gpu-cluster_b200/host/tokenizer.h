@@ -32,7 +32,7 @@ class Tokenizer {
 
   bool load(const std::string& dir, std::string* err) {
     std::ifstream f(dir + "/tokenizer.json", std::ios::binary);
-    if (!f) { *err = "no tokenizer.json in " + dir; return false; }
+    if (!f) return load_vocab_merges(dir, err);      // GPT-2 layout (facebook/opt-125m ships vocab.json + merges.txt only)
     std::stringstream ss;
     ss << f.rdbuf();
     Json j;
@@ -89,6 +89,65 @@ class Tokenizer {
     // chat format
     if (vocab_.count("<|start_header_id|>") || has_added("<|start_header_id|>")) chat_ = "llama3";
     else if (has_added("<|im_start|>")) chat_ = "chatml";
+    return true;
+  }
+
+  // vocab.json + merges.txt (+ tokenizer_config.json / special_tokens_map.json): the slow-tokenizer layout of GPT-2 style
+  // models.  Byte-level BPE with the GPT-2 split pattern; bos/eos/pad/unk named in the config become special tokens and,
+  // with add_bos_token (OPT), the bos id is put in front of every prompt - what GPT2TokenizerFast does with these files.
+  bool load_vocab_merges(const std::string& dir, std::string* err) {
+    std::ifstream fv(dir + "/vocab.json", std::ios::binary), fm(dir + "/merges.txt", std::ios::binary);
+    if (!fv || !fm) { *err = "no tokenizer.json (or vocab.json + merges.txt) in " + dir; return false; }
+    std::stringstream ss;
+    ss << fv.rdbuf();
+    Json v;
+    std::string perr;
+    if (!json_parse(ss.str(), &v, &perr) || !v.is_obj()) { *err = "vocab.json: " + perr; return false; }
+    for (auto& kv : v.obj) {
+      if (!kv.second.is_num()) continue;
+      const int id = (int)kv.second.as_i64();
+      if (id < 0) continue;
+      vocab_[kv.first] = id;
+      if (id >= (int)id_to_tok_.size()) id_to_tok_.resize(id + 1);
+      id_to_tok_[id] = kv.first;
+    }
+    std::string line;
+    int rank = 0;
+    while (std::getline(fm, line)) {
+      if (!line.empty() && line.back() == '\r') line.pop_back();
+      if (line.empty() || line.compare(0, 9, "#version:") == 0) continue;
+      const size_t sp = line.find(' ');
+      if (sp == std::string::npos) continue;
+      ranks_[line] = rank++;                          // "a b"
+    }
+    pattern_ = GPT2;
+    auto special = [&](const Json& cfg, const char* key) -> int {
+      const Json* t = cfg.get(key);
+      std::string name;
+      if (t && t->is_str()) name = t->str;
+      else if (t && t->is_obj()) name = t->str_or("content", "");
+      auto it = vocab_.find(name);
+      if (name.empty() || it == vocab_.end()) return -1;
+      if (std::find(added_ids_.begin(), added_ids_.end(), it->second) == added_ids_.end()) {
+        added_.push_back({name, it->second});
+        added_ids_.push_back(it->second);
+        special_ids_.push_back(it->second);
+      }
+      return it->second;
+    };
+    for (const char* file : {"/special_tokens_map.json", "/tokenizer_config.json"}) {
+      std::ifstream fc(dir + file, std::ios::binary);
+      if (!fc) continue;
+      std::stringstream sc;
+      sc << fc.rdbuf();
+      Json cfg;
+      if (!json_parse(sc.str(), &cfg, &perr) || !cfg.is_obj()) continue;
+      const int bos = special(cfg, "bos_token");
+      special(cfg, "eos_token"); special(cfg, "pad_token"); special(cfg, "unk_token");
+      if (cfg.bool_or("add_bos_token", false) && bos >= 0 && prefix_.empty()) prefix_.push_back(bos);
+    }
+    std::sort(added_.begin(), added_.end(), [](auto& a, auto& b) { return a.first.size() > b.first.size(); });
+    build_byte_maps();
     return true;
   }
 

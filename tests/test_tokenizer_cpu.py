@@ -151,3 +151,33 @@ def test_nfc_normalizer_like_qwen(tmp_path):
         assert o["ids"] == tok.encode(t).ids, t
     plain = build("qwen", str(tmp_path / "x") if (tmp_path / "x").mkdir() is None else "", nfc=False)
     assert plain.encode(samples[0]).ids != tok.encode(samples[0]).ids      # the normaliser matters for this input
+
+
+def test_gpt2_layout_vocab_json_and_merges_txt(tmp_path):
+    """facebook/opt-125m (the reference's first values file) ships vocab.json + merges.txt, no tokenizer.json: the server
+    must read that layout the way transformers' GPT-2 tokenizer does, OPT's leading </s> included."""
+    transformers = pytest.importorskip("transformers")
+    src = tmp_path / "src"
+    src.mkdir()
+    tok = build("gpt2", str(src))
+    d = tmp_path / "opt"
+    d.mkdir()
+    tok.model.save(str(d))                                   # vocab.json + merges.txt
+    (d / "tokenizer_config.json").write_text(json.dumps({"bos_token": "</s>", "eos_token": "</s>", "pad_token": "<pad>", "unk_token": "</s>",
+                                                         "add_bos_token": True, "add_prefix_space": False, "tokenizer_class": "GPT2Tokenizer"}))
+    (d / "special_tokens_map.json").write_text(json.dumps({"bos_token": "</s>", "eos_token": "</s>", "pad_token": "<pad>", "unk_token": "</s>"}))
+    hf = transformers.AutoTokenizer.from_pretrained(str(d))
+    if (d / "tokenizer.json").exists():                      # from_pretrained does not write files; keep the layout pure
+        os.remove(d / "tokenizer.json")
+    texts = [t for t in TEXTS if "<|special|>" not in t]
+    outs = run_cli(str(d), [{"text": t} for t in texts])
+    bos = hf.convert_tokens_to_ids("</s>")
+    for t, o in zip(texts, outs):
+        ref = hf(t)["input_ids"]
+        assert ref[0] == bos and o["ids"] == ref, (t, o["ids"], ref)
+    outs = run_cli(str(d), [{"text": "a</s>b<pad>", "add_special_tokens": False}])
+    assert outs[0]["ids"] == hf("a</s>b<pad>", add_special_tokens=False)["input_ids"]
+    ids = [hf(t)["input_ids"] for t in texts]
+    outs = run_cli(str(d), [{"ids": i} for i in ids])
+    for t, i, o in zip(texts, ids, outs):
+        assert o["text"] == hf.decode(i, skip_special_tokens=True) == t

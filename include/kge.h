@@ -224,6 +224,19 @@ int kge_model_spec_json(const kge_model_dir* m, char* out, int cap);
 int64_t kge_model_read_bf16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
                             uint16_t* out, int64_t cap);
 
+/* The model directory's tokenizer (tokenizer.json byte-level BPE of the GPT-2 / Llama-3 / Qwen families, or GPT-2's
+ * vocab.json + merges.txt), for front ends that take and return text like the engine they replace
+ * (vllm:entrypoints/llm.py accepts str prompts).  Host only.  encode / decode return the length and copy only when the
+ * result fits `cap` (call with cap = 0 to size a buffer); decode skips special tokens and replaces invalid UTF-8 the way
+ * HF's byte-level decoder does. */
+typedef struct kge_tokenizer kge_tokenizer;
+kge_tokenizer* kge_tokenizer_open(const char* model_dir);
+void kge_tokenizer_close(kge_tokenizer* t);
+int kge_tokenizer_vocab_size(const kge_tokenizer* t);
+int64_t kge_tokenizer_encode(const kge_tokenizer* t, const char* text, int64_t text_bytes, int add_special_tokens,
+                             int32_t* out_ids, int64_t cap);
+int64_t kge_tokenizer_decode(const kge_tokenizer* t, const int32_t* ids, int64_t n, char* out, int64_t cap);
+
 /* One forward pass + greedy sampling of the R requested rows (the GPUModelRunner.execute_model
  * + Sampler path, vllm:v1/worker/gpu_model_runner.py:3955, vllm:v1/sample/sampler.py:67).
  * out_ids_host [R]; out_logits_host [R, vocab] fp32 or NULL.  Synchronous. */

@@ -89,6 +89,11 @@ SIGNATURES = {
     "kge_engine_create": (_I, [C.POINTER(_P), C.c_char_p, C.POINTER(EngineConfig), _L]),
     "kge_engine_destroy": (None, [_P]),
     "kge_engine_num_blocks": (_I, [_P]),
+    "kge_tokenizer_open": (_P, [C.c_char_p]),
+    "kge_tokenizer_close": (None, [_P]),
+    "kge_tokenizer_vocab_size": (_I, [_P]),
+    "kge_tokenizer_encode": (C.c_int64, [_P, C.c_char_p, C.c_int64, _I, _P, C.c_int64]),
+    "kge_tokenizer_decode": (C.c_int64, [_P, _P, C.c_int64, _P, C.c_int64]),
     "kge_model_open": (_P, [C.c_char_p]),
     "kge_model_close": (None, [_P]),
     "kge_model_spec_json": (_I, [_P, C.c_char_p, _I]),
@@ -196,6 +201,47 @@ class CompletionOutput:
     token_ids: list
     finish_reason: str | None = None
     logprobs: list | None = None        # per generated token: {token_id: Logprob}, sampled token first
+    text: str = ""                      # decoded token_ids when the model directory has a tokenizer
+
+
+class Tokenizer:
+    """The model directory's tokenizer through the C ABI (kge_tokenizer_*): what lets `LLM.generate` take text."""
+
+    def __init__(self, model_dir: str):
+        self._h = lib().kge_tokenizer_open(str(model_dir).encode())
+        if not self._h:
+            raise KgeError("kge_tokenizer_open: " + lib().kge_last_error().decode())
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().kge_tokenizer_close(self._h)
+            self._h = None
+
+    __del__ = close
+
+    @property
+    def vocab_size(self) -> int:
+        return lib().kge_tokenizer_vocab_size(self._h)
+
+    def encode(self, text: str, add_special_tokens: bool = True) -> list:
+        import numpy as np
+        b = text.encode("utf-8")
+        n = lib().kge_tokenizer_encode(self._h, b, len(b), int(add_special_tokens), None, 0)
+        if n < 0:
+            raise KgeError("kge_tokenizer_encode: " + lib().kge_last_error().decode())
+        out = np.zeros(max(1, n), dtype=np.int32)
+        lib().kge_tokenizer_encode(self._h, b, len(b), int(add_special_tokens), out.ctypes.data, n)
+        return out[:n].tolist()
+
+    def decode(self, ids) -> str:
+        import numpy as np
+        a = np.ascontiguousarray(ids, dtype=np.int32)
+        n = lib().kge_tokenizer_decode(self._h, a.ctypes.data, int(a.size), None, 0)
+        if n < 0:
+            raise KgeError("kge_tokenizer_decode: " + lib().kge_last_error().decode())
+        buf = C.create_string_buffer(max(1, n))
+        lib().kge_tokenizer_decode(self._h, a.ctypes.data, int(a.size), buf, n)
+        return buf.raw[:n].decode("utf-8")
 
 
 @dataclass
@@ -223,6 +269,8 @@ class LLM:
         dummy = seed if load_format == "dummy" else -1
         check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")
         self._h = h
+        self._model = model
+        self._tok = None                # opened on first use; False = the directory has no tokenizer
         lib().kge_engine_set_reserve_full_isl(h, int(scheduler_reserve_full_isl))
         lib().kge_engine_set_prefix_caching(h, int(enable_prefix_caching))      # on by default, as in vLLM V1
         self._next_id = 0
@@ -324,9 +372,34 @@ class LLM:
         check(lib().kge_engine_stats(self._h, C.byref(r), C.byref(w), C.byref(u), C.byref(p)), "kge_engine_stats")
         return {"num_running": r.value, "num_waiting": w.value, "kv_usage": u.value, "num_preemptions": p.value}
 
+    def get_tokenizer(self):
+        """The model directory's tokenizer, or None when it has none (token-id prompts still work)."""
+        if self._tok is None:
+            try:
+                self._tok = Tokenizer(self._model)
+            except KgeError:
+                self._tok = False
+        return self._tok or None
+
+    def _prompt_ids(self, p):
+        """vLLM's prompt forms: token ids, text, {"prompt_token_ids": [...]} or {"prompt": "..."}."""
+        if isinstance(p, dict):
+            p = p["prompt_token_ids"] if "prompt_token_ids" in p else p["prompt"]
+        if isinstance(p, str):
+            tok = self.get_tokenizer()
+            if tok is None:
+                raise KgeError("text prompts need a tokenizer.json (or vocab.json + merges.txt) in the model directory; pass token ids")
+            return tok.encode(p)
+        return p
+
     def generate(self, prompt_token_ids, sampling_params: SamplingParams | list | None = None,
                  on_step=None):
-        """prompt_token_ids: list of token-id lists.  Returns RequestOutput per prompt, in order."""
+        """prompt_token_ids: one prompt or a list of prompts, each a list of token ids, a string, or vLLM's dict forms.
+        Returns a RequestOutput per prompt, in order."""
+        if isinstance(prompt_token_ids, (str, dict)) or (isinstance(prompt_token_ids, (list, tuple)) and prompt_token_ids
+                                                          and isinstance(prompt_token_ids[0], int)):
+            prompt_token_ids = [prompt_token_ids]
+        prompt_token_ids = [self._prompt_ids(p) for p in prompt_token_ids]
         sps = sampling_params or SamplingParams()
         if not isinstance(sps, list):
             sps = [sps] * len(prompt_token_ids)
@@ -350,8 +423,7 @@ class LLM:
                     toks[r].append(t)
                 if ff:
                     fin[r] = "stop" if ff == 1 else "length"
-            return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i))])
-                    for i, p in zip(ids, prompt_token_ids)]
+            return self._outputs(ids, prompt_token_ids, toks, fin, {})
         while self.has_unfinished():
             outs = self.step()
             if not outs:
@@ -365,8 +437,12 @@ class LLM:
                     fin[rid] = "stop" if f == 1 else "length"
             if on_step:
                 on_step(outs)
-        return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i), lps.get(i))])
-                for i, p in zip(ids, prompt_token_ids)]
+        return self._outputs(ids, prompt_token_ids, toks, fin, lps)
+
+    def _outputs(self, ids, prompts, toks, fin, lps):
+        tok = self.get_tokenizer()
+        return [RequestOutput(i, list(p), [CompletionOutput(toks[i], fin.get(i), lps.get(i), tok.decode(toks[i]) if tok else "")])
+                for i, p in zip(ids, prompts)]
 
     # raw step with caller-built metadata (tests / bench device-resident leg)
     def raw_step(self, token_ids, positions, query_start_loc, seq_lens, block_table, max_blocks,

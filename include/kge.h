@@ -36,6 +36,8 @@ int kge_device_sm_count(void);
  *   "attn_cluster_merge" 0/1  decode attention: 1 = the split-KV CTAs of a (request, kv head) form a thread-block
  *                             cluster and merge over distributed shared memory instead of workspace + merge kernel
  *                             (same bits; measured slower, so off by default)
+ *   "gemm_shallow" 0/1        experiment: decode-sized GEMMs (T <= 64) as twice as many CTAs with half the shared memory
+ *                             each (two per SM), so the next kernel's CTAs move in as this one's retire; off by default
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

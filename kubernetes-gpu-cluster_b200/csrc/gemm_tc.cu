@@ -463,12 +463,21 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
   return 0;
 }
 
-template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false, bool PAIR = false>
+// SHALLOW (experiment, knob "gemm_shallow", off by default): at most half an SM's shared memory per CTA and twice as
+// many CTAs, so every SM holds TWO streaming CTAs - the same bytes in flight per SM as the deep pipeline, but when the
+// CTAs of one GEMM finish one by one, CTAs of the next kernel (launched early by PDL) move into the freed half and
+// start streaming their weights: HBM does not idle across the kernel boundary.  Round 1 measured only half of this
+// idea (shallow pipeline with ONE CTA per SM: slower); this is the full configuration, to be measured next round.
+constexpr int gemm_smem_budget(bool shallow) { return shallow ? 112 * 1024 : 224 * 1024; }
+static bool gemm_shallow(int tokn) { return tunable(TUN_GEMM_SHALLOW) != 0 && tokn <= 64; }
+constexpr int kSlotsShallow = 2 * 148;
+
+template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false, bool PAIR = false, bool SHALLOW = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
   constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
-  constexpr int budget = 224 * 1024 - 1024 - extra;
+  constexpr int budget = gemm_smem_budget(SHALLOW) - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
@@ -495,8 +504,9 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
   } else {
-    int grid = tiles < 148 ? tiles : 148;
-    if (tunable(TUN_GEMM_EVEN_GRID) && tiles > 148) {
+    constexpr int slots = SHALLOW ? kSlotsShallow : 148;
+    int grid = tiles < slots ? tiles : slots;
+    if (!SHALLOW && tunable(TUN_GEMM_EVEN_GRID) && tiles > 148) {
       // persistent round-robin: 224 tiles on 148 CTAs leaves 72 CTAs idle for the second half; 112 CTAs with two
       // tiles each keep every CTA streaming to the end (a weight-streaming GEMM needs bytes in flight, not SMs)
       const int rounds = (tiles + 147) / 148;
@@ -508,11 +518,11 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   return 0;
 }
 
-template <int TOKN>
+template <int TOKN, bool SHALLOW>
 static int query_max_clusters(int S) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
   constexpr int extra = 2048 + xbuf_bytes(TOKN);
-  constexpr int budget = 224 * 1024 - 1024 - extra;
+  constexpr int budget = gemm_smem_budget(SHALLOW) - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   constexpr int smem = STAGES * stage_bytes + 1024 + extra;
   auto kern = gemm_tc_kernel<TOKN, STAGES, true, false, false>;   // the gated variant has the same footprint
@@ -531,15 +541,17 @@ static int query_max_clusters(int S) {
 // How many clusters of size S of the split kernel can be co-resident (GPC packing decides: 148 SMs
 // hold e.g. 34 clusters of 4 but fewer than 148/3 clusters of 3).  Cached per (token tile, S).
 static int max_clusters(int tokn, int S) {
-  static int cache[4][9];
-  static bool have[4][9];
+  static int cache[2][4][9];
+  static bool have[2][4][9];
   const int ti = tokn == 16 ? 0 : tokn == 32 ? 1 : tokn == 64 ? 2 : 3;
-  if (!have[ti][S]) {
-    cache[ti][S] = ti == 0 ? query_max_clusters<16>(S) : ti == 1 ? query_max_clusters<32>(S)
-                 : ti == 2 ? query_max_clusters<64>(S) : query_max_clusters<128>(S);
-    have[ti][S] = true;
+  const int sh = gemm_shallow(tokn) ? 1 : 0;
+  if (!have[sh][ti][S]) {
+    if (sh) cache[sh][ti][S] = ti == 0 ? query_max_clusters<16, true>(S) : ti == 1 ? query_max_clusters<32, true>(S) : query_max_clusters<64, true>(S);
+    else cache[sh][ti][S] = ti == 0 ? query_max_clusters<16, false>(S) : ti == 1 ? query_max_clusters<32, false>(S)
+                          : ti == 2 ? query_max_clusters<64, false>(S) : query_max_clusters<128, false>(S);
+    have[sh][ti][S] = true;
   }
-  return cache[ti][S];
+  return cache[sh][ti][S];
 }
 
 struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; };
@@ -552,8 +564,9 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
   g.kb_total = (K + BLK_K - 1) / BLK_K;
   const int tiles = g.m_tiles * g.n_tiles;
   int splits = 1;
-  if (tiles <= 74 && g.tokn <= 128) {
-    int smax = 148 / tiles;                     // never more CTAs than SMs
+  const int slots = gemm_shallow(g.tokn) ? kSlotsShallow : 148;      // CTAs that can be resident at once
+  if (tiles <= slots / 2 && g.tokn <= 128) {
+    int smax = slots / tiles;                   // never more CTAs than resident slots
     const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
     if (smax > max_by_k) smax = max_by_k;
     if (smax > 8) smax = 8;                     // portable cluster size
@@ -570,6 +583,20 @@ static bool gemm_uses_pair(const GemmPlan& g) { return g.tokn == 256 && g.splits
 
 template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  if (gemm_shallow(g.tokn)) {
+    if (g.splits > 1) {
+      switch (g.tokn) {
+        case 16: return launch_gemm<16, true, GATED, false, false, true>(tw, tx, p, st);
+        case 32: return launch_gemm<32, true, GATED, false, false, true>(tw, tx, p, st);
+        default: return launch_gemm<64, true, GATED, false, false, true>(tw, tx, p, st);
+      }
+    }
+    switch (g.tokn) {
+      case 16: return launch_gemm<16, false, GATED, false, false, true>(tw, tx, p, st);
+      case 32: return launch_gemm<32, false, GATED, false, false, true>(tw, tx, p, st);
+      default: return launch_gemm<64, false, GATED, false, false, true>(tw, tx, p, st);
+    }
+  }
   if (g.splits > 1) {
     switch (g.tokn) {
       case 16: return launch_gemm<16, true, GATED>(tw, tx, p, st);

@@ -294,6 +294,21 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
         assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 3e-3
 
 
+EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
+                                  reason="default-off experiments prepared for the next round; set KGE_TEST_EXPERIMENTAL=1 to run them")
+
+
+@EXPERIMENTAL
+@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 64])
+def test_gemm_shallow_variant(kge, L, T, N, K, bias, act):
+    """knob gemm_shallow: two half-footprint CTAs per SM (more, shorter split-K ranges): same tolerance as the default."""
+    try:
+        check_ok(kge, L.kge_set_tunable(b"gemm_shallow", 1), "tunable")
+        test_gemm_bf16(kge, L, T, N, K, bias, act)
+    finally:
+        L.kge_set_tunable(b"gemm_shallow", 0)
+
+
 @pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048),
                                    (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024),
                                    (64, 7168, 8192), (8192, 7168, 1024)])    # 70B TP4 gate_up: decode, prefill pairs

@@ -1,0 +1,315 @@
+"""The HTTP server (the unmodified bin/vllm = kge-serve) on a machine without a GPU: tests/cpp/mock_kge.cc - test
+infrastructure, a stand-in libkge.so that runs the REAL scheduler and "samples" with a fixed formula - is built into a
+temporary directory and put first on LD_LIBRARY_PATH.  What is under test is everything above the C ABI: routes, request
+parsing and validation, the OpenAI response shapes, SSE framing, tokenizer / chat rendering, stop strings and stop_reason,
+echo, logprobs shapes, generation_config defaults, chat max_tokens default, n > 1, aborts on disconnect, /metrics.
+(The same routes run against the real engine in tests/test_server_gpu.py.)  CPU only."""
+import json
+import os
+import shutil
+import socket
+import subprocess
+import time
+import urllib.error
+import urllib.request
+
+import pytest
+
+from oracle import model as om
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+PKG = os.path.join(ROOT, "kubernetes-gpu-cluster_b200")
+BIN = os.path.join(PKG, "bin", "vllm")
+pytestmark = pytest.mark.skipif(not os.path.exists(BIN) or shutil.which("g++") is None, reason="needs the server binary and g++")
+VOCAB = om.CONFIGS["tiny-llama"].vocab_size
+
+
+def mock_next(last, pos):
+    return (7 * last + 3 * pos + 11) % VOCAB
+
+
+def mock_generate(prompt_ids, n):
+    seq = list(prompt_ids)
+    for _ in range(n):
+        seq.append(mock_next(seq[-1], len(seq)))
+    return seq[len(prompt_ids):]
+
+
+def free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+@pytest.fixture(scope="module")
+def mock_lib(tmp_path_factory):
+    d = tmp_path_factory.mktemp("mocklib")
+    cmd = ["g++", "-O1", "-std=c++17", "-shared", "-fPIC", f"-I{os.path.join(ROOT, 'include')}", f"-I{os.path.join(PKG, 'csrc')}",
+           os.path.join(ROOT, "tests", "cpp", "mock_kge.cc"), os.path.join(PKG, "csrc", "scheduler.cc"), "-o", str(d / "libkge.so")]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=300)
+    assert p.returncode == 0, p.stderr[-2000:]
+    return str(d)
+
+
+def start(mock_lib, model_dir, log, *extra, env_extra=None):
+    port = free_port()
+    env = dict(os.environ, LD_LIBRARY_PATH=mock_lib, MOCK_KGE_LOG=str(log), **(env_extra or {}))
+    proc = subprocess.Popen([BIN, "serve", str(model_dir), "--host", "127.0.0.1", "--port", str(port), "--max-model-len", "256",
+                             "--served-model-name", "m", *extra], stderr=subprocess.PIPE, env=env)
+    for _ in range(200):
+        try:
+            with urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=1) as r:
+                if r.status == 200:
+                    return proc, port
+        except Exception:
+            if proc.poll() is not None:
+                break
+            time.sleep(0.03)
+    proc.kill()
+    raise RuntimeError("server did not start: " + proc.stderr.read().decode()[-2000:])
+
+
+def stop(proc):
+    proc.terminate()
+    try:
+        proc.wait(timeout=10)
+    except subprocess.TimeoutExpired:
+        proc.kill()
+
+
+def http(port, path, body=None, timeout=30):
+    req = urllib.request.Request(f"http://127.0.0.1:{port}{path}", data=None if body is None else json.dumps(body).encode(),
+                                 headers={"Content-Type": "application/json"})
+    try:
+        with urllib.request.urlopen(req, timeout=timeout) as r:
+            return r.status, r.read().decode()
+    except urllib.error.HTTPError as e:
+        return e.code, e.read().decode()
+
+
+def sse(port, path, body):
+    req = urllib.request.Request(f"http://127.0.0.1:{port}{path}", data=json.dumps(body).encode(), headers={"Content-Type": "application/json"})
+    with urllib.request.urlopen(req, timeout=30) as r:
+        assert r.headers["Content-Type"].startswith("text/event-stream")
+        raw = r.read().decode()
+    events = [e[6:] for e in raw.split("\n\n") if e.startswith("data: ")]
+    assert events[-1] == "[DONE]"
+    return [json.loads(e) for e in events[:-1]]
+
+
+@pytest.fixture(scope="module")
+def srv(mock_lib, tmp_path_factory):
+    """Server on a model directory WITH a Llama-3-style tokenizer; yields (port, tokenizer, log path)."""
+    from test_tokenizer_cpu import build
+    d = tmp_path_factory.mktemp("model")
+    (d / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    tok = build("llama3", str(d))
+    log = d / "requests.log"
+    proc, port = start(mock_lib, d, log)
+    yield port, tok, log
+    stop(proc)
+
+
+def last_logged(log):
+    return json.loads(open(log).read().strip().splitlines()[-1])
+
+
+def test_routes_and_token_id_completions(srv):
+    port, tok, log = srv
+    st, body = http(port, "/v1/models")
+    m = json.loads(body)["data"][0]
+    assert st == 200 and m["id"] == "m" and m["object"] == "model" and m["owned_by"] == "vllm" and m["max_model_len"] == 256
+    assert http(port, "/health")[0] == 200 and http(port, "/ping")[0] == 200
+    st, body = http(port, "/v1/completions", {"model": "m", "prompt": [5, 6, 7], "max_tokens": 5, "temperature": 0})
+    r = json.loads(body)
+    assert st == 200 and r["object"] == "text_completion" and r["id"].startswith("cmpl-") and r["model"] == "m"
+    c = r["choices"][0]
+    assert c["token_ids"] == mock_generate([5, 6, 7], 5) and c["finish_reason"] == "length" and c["stop_reason"] is None and c["logprobs"] is None
+    assert c["text"] == tok.decode(c["token_ids"], skip_special_tokens=True)
+    assert r["usage"] == {"prompt_tokens": 3, "total_tokens": 8, "completion_tokens": 5}
+    lg = last_logged(log)
+    assert (lg["max_tokens"], lg["temperature"], lg["top_k"], lg["top_p"], lg["ignore_eos"]) == (5, 0, 0, 1, 0)
+    # defaults: 16 tokens, temperature 1.0 (vllm:sampling_params.py)
+    st, body = http(port, "/v1/completions", {"prompt": [5, 6, 7]})
+    assert len(json.loads(body)["choices"][0]["token_ids"]) == 16 and last_logged(log)["temperature"] == 1
+    # batch of prompts and n > 1: choices in order, indices 0..
+    st, body = http(port, "/v1/completions", {"prompt": [[5, 6], [9]], "n": 2, "max_tokens": 2, "temperature": 0, "seed": 7})
+    ch = json.loads(body)["choices"]
+    assert [c["index"] for c in ch] == [0, 1, 2, 3]
+    assert [c["token_ids"] for c in ch] == [mock_generate([5, 6], 2)] * 2 + [mock_generate([9], 2)] * 2
+    st, m = http(port, "/metrics")
+    for name in ("vllm:num_requests_running", "vllm:num_requests_waiting", "vllm:kv_cache_usage_perc", "vllm:prompt_tokens_total",
+                 "vllm:generation_tokens_total", "vllm:request_success_total", "vllm:prefix_cache_queries_total", "vllm:prefix_cache_hits_total"):
+        assert name in m, name
+
+
+def test_errors(srv):
+    port, tok, log = srv
+    for body, code, needle in [({"prompt": [5, 10 ** 7]}, 400, "out of vocabulary"), ({"prompt": [5, 1e30]}, 400, "out of vocabulary"),
+                               ({"prompt": []}, 400, "prompt"), ({"prompt": [5], "max_tokens": 0}, 400, "max_tokens"),
+                               ({"prompt": [5], "top_p": 0}, 400, "top_p"), ({"prompt": [5], "temperature": -1}, 400, "temperature"),
+                               ({"prompt": [5], "n": 1000}, 400, "n must"), ({"prompt": [5], "logprobs": 50}, 400, "logprobs"),
+                               ({"prompt": [5], "stop": 3}, 400, "stop"), ({"prompt": list(range(3, 300)), "max_tokens": 4}, 400, "max_model_len"),
+                               ({"model": "other", "prompt": [5]}, 404, "does not exist"), ({"max_tokens": 3}, 400, "prompt")]:
+        st, out = http(port, "/v1/completions", body)
+        e = json.loads(out)["error"]
+        assert st == code and e["code"] == code and needle in e["message"] and e["type"] in ("BadRequestError", "NotFoundError"), (body, out)
+    req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", data=b"{not json", headers={"Content-Type": "application/json"})
+    with pytest.raises(urllib.error.HTTPError) as ei:
+        urllib.request.urlopen(req, timeout=10)
+    assert ei.value.code == 400 and "invalid JSON" in ei.value.read().decode()
+    assert http(port, "/nope")[0] == 404
+    st, out = http(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "x"}], "echo": True})
+    assert st == 400 and "echo" in out
+
+
+def test_text_prompts_chat_and_defaults(srv):
+    port, tok, log = srv
+    text = "The GPU cluster's nodes"
+    ids = tok.encode(text).ids
+    st, body = http(port, "/v1/completions", {"prompt": text, "max_tokens": 4, "temperature": 0})
+    c = json.loads(body)
+    assert st == 200 and c["usage"]["prompt_tokens"] == len(ids) and c["choices"][0]["token_ids"] == mock_generate(ids, 4)
+    st, body = http(port, "/v1/completions", {"prompt": text, "max_tokens": 3, "temperature": 0, "echo": True})
+    assert json.loads(body)["choices"][0]["text"] == text + tok.decode(mock_generate(ids, 3), skip_special_tokens=True)
+    msgs = [{"role": "system", "content": "Be brief."}, {"role": "user", "content": [{"type": "text", "text": "Hi "}, {"type": "text", "text": "there"}]}]
+    rendered = ("<|begin_of_text|><|start_header_id|>system<|end_header_id|>\n\nBe brief.<|eot_id|><|start_header_id|>user<|end_header_id|>\n\n"
+                "Hi there<|eot_id|><|start_header_id|>assistant<|end_header_id|>\n\n")
+    pids = tok.encode(rendered, add_special_tokens=False).ids
+    st, body = http(port, "/v1/chat/completions", {"messages": msgs, "max_completion_tokens": 5, "temperature": 0})
+    r = json.loads(body)
+    assert st == 200 and r["object"] == "chat.completion" and r["id"].startswith("chatcmpl-") and r["usage"]["prompt_tokens"] == len(pids)
+    ch = r["choices"][0]
+    assert ch["message"]["role"] == "assistant" and ch["token_ids"] == mock_generate(pids, 5)
+    assert ch["message"]["content"] == tok.decode(ch["token_ids"], skip_special_tokens=True)
+    # a chat request without a token limit may use the rest of the context (vLLM: max_model_len - prompt length)
+    st, body = http(port, "/v1/chat/completions", {"messages": msgs, "temperature": 0})
+    assert last_logged(log)["max_tokens"] == 256 - len(pids)
+    assert json.loads(body)["choices"][0]["finish_reason"] == "length"
+
+
+def test_streaming_sse(srv):
+    port, tok, log = srv
+    base = {"prompt": [5, 6, 7], "max_tokens": 6, "temperature": 0}
+    ev = sse(port, "/v1/completions", dict(base, stream=True, stream_options={"include_usage": True}))
+    chunks, usage = ev[:-1], ev[-1]
+    want = mock_generate([5, 6, 7], 6)
+    assert [c["choices"][0]["token_ids"][0] for c in chunks] == want and all(c["object"] == "text_completion" for c in chunks)
+    assert "".join(c["choices"][0]["text"] for c in chunks) == tok.decode(want, skip_special_tokens=True)
+    assert [c["choices"][0]["finish_reason"] for c in chunks] == [None] * 5 + ["length"]
+    assert usage["choices"] == [] and usage["usage"] == {"prompt_tokens": 3, "total_tokens": 9, "completion_tokens": 6}
+    ev = sse(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "Hi"}], "max_tokens": 3, "temperature": 0, "stream": True})
+    assert len(ev) == 3 and all(c["object"] == "chat.completion.chunk" and c["choices"][0]["delta"]["role"] == "assistant" for c in ev)
+    ev = sse(port, "/v1/completions", dict(base, stream=True, n=2))
+    assert sorted(c["choices"][0]["index"] for c in ev) == [0] * 6 + [1] * 6
+
+
+def test_stop_strings_stop_ids_and_logprobs(srv):
+    port, tok, log = srv
+    base = {"prompt": "The GPU cluster's nodes", "max_tokens": 24, "temperature": 0, "ignore_eos": True}
+    full = json.loads(http(port, "/v1/completions", base)[1])["choices"][0]
+    text, ids = full["text"], full["token_ids"]
+    assert len(ids) == 24 and len(text) >= 8
+    mid = len(text) // 2
+    stop_s = text[mid:mid + 3]
+    cut = text.index(stop_s)
+    c0 = json.loads(http(port, "/v1/completions", dict(base, stop=[stop_s]))[1])["choices"][0]
+    assert c0["text"] == text[:cut] and c0["finish_reason"] == "stop" and c0["stop_reason"] == stop_s and c0["token_ids"] == ids[:len(c0["token_ids"])]
+    c0 = json.loads(http(port, "/v1/completions", dict(base, stop=stop_s, include_stop_str_in_output=True))[1])["choices"][0]
+    assert c0["text"] == text[:cut + len(stop_s)] and c0["stop_reason"] == stop_s
+    ev = sse(port, "/v1/completions", dict(base, stop=[stop_s], stream=True))
+    assert "".join(c["choices"][0]["text"] for c in ev) == text[:cut]
+    assert ev[-1]["choices"][0]["finish_reason"] == "stop" and ev[-1]["choices"][0]["stop_reason"] == stop_s
+    sid = ids[5]
+    k = ids.index(sid)
+    c0 = json.loads(http(port, "/v1/completions", dict(base, stop_token_ids=[sid]))[1])["choices"][0]
+    assert c0["token_ids"] == ids[:k + 1] and c0["finish_reason"] == "stop" and c0["stop_reason"] == sid
+    assert c0["text"] == tok.decode(ids[:k], skip_special_tokens=True)           # the stop token's text is left out
+    # min_tokens keeps both kinds of stop from firing early
+    c0 = json.loads(http(port, "/v1/completions", dict(base, stop_token_ids=[sid], min_tokens=k + 2, max_tokens=k + 4))[1])["choices"][0]
+    assert len(c0["token_ids"]) > k + 1
+    # logprobs: the completions and the chat shape, streamed too (values are the mock's: -0.5 for the sampled token)
+    lp = json.loads(http(port, "/v1/completions", dict(base, max_tokens=4, logprobs=2))[1])["choices"][0]["logprobs"]
+    assert lp["token_logprobs"] == [-0.5] * 4 and len(lp["tokens"]) == len(lp["top_logprobs"]) == 4
+    offs, acc = [], 0
+    for t in lp["tokens"]:
+        offs.append(acc)
+        acc += len(t)
+    assert lp["text_offset"] == offs and all(1 <= len(t) <= 3 for t in lp["top_logprobs"])
+    assert all(len(t) == 1 for t in json.loads(http(port, "/v1/completions", dict(base, max_tokens=3, logprobs=0))[1])["choices"][0]["logprobs"]["top_logprobs"])
+    content = json.loads(http(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "Hi"}], "max_tokens": 3, "temperature": 0,
+                                                             "logprobs": True, "top_logprobs": 2})[1])["choices"][0]["logprobs"]["content"]
+    assert len(content) == 3
+    for e in content:
+        assert e["logprob"] == -0.5 and bytes(e["bytes"]).decode("utf-8", "replace") == e["token"] and len(e["top_logprobs"]) == 2
+        assert e["top_logprobs"][0]["token"] == e["token"]
+    ev = sse(port, "/v1/completions", dict(base, max_tokens=4, logprobs=1, stream=True))
+    assert [c["choices"][0]["logprobs"]["text_offset"][0] for c in ev] == offs
+    assert json.loads(http(port, "/v1/completions", dict(base, max_tokens=2))[1])["choices"][0]["logprobs"] is None
+
+
+def test_generation_config_defaults_and_extra_eos(mock_lib, tmp_path):
+    """generation_config.json: sampling defaults for silent requests, and extra end-of-sequence ids that end a request like
+    a stop token (Llama-3.1-Instruct's <|eot_id|>), unless ignore_eos."""
+    prompt = [5, 6, 7]
+    want = mock_generate(prompt, 12)
+    eos2 = want[4]
+    cfg = dict(om.CONFIGS["tiny-llama"].to_hf(), eos_token_id=[want[9], eos2])
+    (tmp_path / "config.json").write_text(json.dumps(cfg))
+    (tmp_path / "generation_config.json").write_text(json.dumps({"temperature": 0.6, "top_p": 0.9, "top_k": 20, "eos_token_id": [want[9], eos2, want[7]]}))
+    log = tmp_path / "log"
+    proc, port = start(mock_lib, tmp_path, log)
+    try:
+        c0 = json.loads(http(port, "/v1/completions", {"prompt": prompt, "max_tokens": 12})[1])["choices"][0]
+        lg = last_logged(log)
+        assert (round(lg["temperature"], 3), round(lg["top_p"], 3), lg["top_k"]) == (0.6, 0.9, 20)
+        assert sorted(lg["stop_token_ids"]) == sorted([eos2, want[7]])
+        assert c0["token_ids"] == want[:5] and c0["finish_reason"] == "stop" and c0["stop_reason"] == eos2
+        http(port, "/v1/completions", {"prompt": prompt, "max_tokens": 2, "temperature": 0, "top_p": 0.5, "top_k": 3})
+        lg = last_logged(log)
+        assert (lg["temperature"], lg["top_p"], lg["top_k"]) == (0, 0.5, 3)           # what the request says wins
+        c0 = json.loads(http(port, "/v1/completions", {"prompt": prompt, "max_tokens": 12, "ignore_eos": True})[1])["choices"][0]
+        assert c0["token_ids"] == want and last_logged(log)["stop_token_ids"] == []
+    finally:
+        stop(proc)
+    proc, port = start(mock_lib, tmp_path, log, "--generation-config", "vllm")
+    try:
+        http(port, "/v1/completions", {"prompt": prompt, "max_tokens": 2})
+        lg = last_logged(log)
+        assert (lg["temperature"], lg["top_p"], lg["top_k"]) == (1, 1, 0) and sorted(lg["stop_token_ids"]) == sorted([eos2, want[7]])
+    finally:
+        stop(proc)
+
+
+def test_without_a_tokenizer_and_client_disconnect(mock_lib, tmp_path):
+    (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    log = tmp_path / "log"
+    proc, port = start(mock_lib, tmp_path, log, env_extra={"MOCK_KGE_STEP_US": "20000"})
+    try:
+        st, out = http(port, "/v1/completions", {"prompt": "hello", "max_tokens": 2})
+        assert st == 400 and "tokenizer" in out
+        st, out = http(port, "/v1/completions", {"prompt": [5], "max_tokens": 2, "stop": ["x"]})
+        assert st == 400 and "tokenizer" in out
+        st, out = http(port, "/v1/chat/completions", {"messages": [{"role": "user", "content": "hi"}]})
+        assert st == 400 and "chat template" in out
+        c0 = json.loads(http(port, "/v1/completions", {"prompt": [5, 6], "max_tokens": 3, "temperature": 0, "logprobs": 1})[1])["choices"][0]
+        assert c0["text"] == "" and c0["logprobs"]["tokens"] == [f"token_id:{t}" for t in c0["token_ids"]]
+        # a streaming client that goes away: the request is aborted and its KV blocks are released
+        s = socket.create_connection(("127.0.0.1", port), timeout=5)
+        body = json.dumps({"prompt": [5, 6, 7], "max_tokens": 200, "temperature": 0, "ignore_eos": True, "stream": True}).encode()
+        s.sendall(b"POST /v1/completions HTTP/1.1\r\nHost: x\r\nContent-Type: application/json\r\nContent-Length: %d\r\n\r\n%s" % (len(body), body))
+        assert b"200 OK" in s.recv(4096)
+        s.close()
+        for _ in range(100):
+            m = http(port, "/metrics")[1]
+            running = float([ln for ln in m.splitlines() if ln.startswith("vllm:num_requests_running")][0].split()[-1])
+            usage = float([ln for ln in m.splitlines() if ln.startswith("vllm:kv_cache_usage_perc")][0].split()[-1])
+            if running == 0 and usage == 0:
+                break
+            time.sleep(0.05)
+        assert running == 0 and usage == 0
+        assert json.loads(http(port, "/v1/completions", {"prompt": [5, 6], "max_tokens": 2, "temperature": 0})[1])["choices"][0]["token_ids"] == mock_generate([5, 6], 2)
+    finally:
+        stop(proc)

@@ -27,6 +27,7 @@ struct ServeArgs {
   int num_gpu_blocks_override = 0;
   bool enable_chunked_prefill = true;
   bool scheduler_reserve_full_isl = true;
+  std::string api_key;                          // --api-key or $VLLM_API_KEY: Bearer token required on /v1 routes
   std::string generation_config = "auto";     // auto: defaults from the model's generation_config.json; vllm: none
   bool enable_prefix_caching = true;       // vLLM V1 default
   bool enforce_eager = false;
@@ -97,6 +98,7 @@ inline std::string parse_serve_args(int argc, char** argv, ServeArgs* a) {
     else if (key == "--num-gpu-blocks-override") err = need_int(&a->num_gpu_blocks_override);
     else if (key == "--enable-chunked-prefill") a->enable_chunked_prefill = true;
     else if (key == "--no-enable-chunked-prefill") a->enable_chunked_prefill = false;
+    else if (key == "--api-key") { if (!need(&a->api_key)) return key + " expects a value"; }
     else if (key == "--generation-config") { if (!need(&a->generation_config)) return key + " expects a value"; }
     else if (key == "--scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = true;
     else if (key == "--no-scheduler-reserve-full-isl") a->scheduler_reserve_full_isl = false;
@@ -122,6 +124,7 @@ inline std::string parse_serve_args(int argc, char** argv, ServeArgs* a) {
   if (a->tensor_parallel_size < 1) return "--tensor-parallel-size must be >= 1";
   if (a->port <= 0 || a->port > 65535) return "--port out of range";
   if (a->served_model_name.empty()) a->served_model_name = a->model;
+  if (a->api_key.empty()) if (const char* k = getenv("VLLM_API_KEY")) a->api_key = k;
   return "";
 }
 

@@ -190,7 +190,7 @@ void engine_loop(Server* sp) {
 
 // ---------------------------------------------------------------------------------- HTTP helpers
 struct HttpReq {
-  std::string method, path, body;
+  std::string method, path, body, authorization;
   bool keep_alive = true;
 };
 
@@ -238,6 +238,7 @@ int read_request(int fd, std::string& buf, HttpReq* r) {
     for (auto& ch : k) ch = (char)tolower(ch);
     while (!v.empty() && v[0] == ' ') v.erase(0, 1);
     if (k == "content-length") clen = (size_t)strtoull(v.c_str(), nullptr, 10);
+    if (k == "authorization") r->authorization = v;
     if (k == "connection") {
       for (auto& ch : v) ch = (char)tolower(ch);
       if (v.find("close") != std::string::npos) r->keep_alive = false;
@@ -261,6 +262,7 @@ const char* status_text(int code) {
   switch (code) {
     case 200: return "OK";
     case 400: return "Bad Request";
+    case 401: return "Unauthorized";
     case 404: return "Not Found";
     case 405: return "Method Not Allowed";
     case 500: return "Internal Server Error";
@@ -703,6 +705,38 @@ std::string metrics_text(Server& s) {
   return o;
 }
 
+// POST /tokenize {"prompt": str, "add_special_tokens": true} | {"messages": [...]} -> {"count", "max_model_len", "tokens"}
+// POST /detokenize {"tokens": [...]} -> {"prompt"}   (vllm:entrypoints/serve/tokenize/api_router.py, protocol.py)
+bool handle_tokenize(Server& s, int fd, const HttpReq& hr, bool detok) {
+  Json j;
+  std::string perr;
+  if (!json_parse(hr.body, &j, &perr) || !j.is_obj()) return respond_error(fd, 400, "invalid JSON body: " + perr, "BadRequestError", hr.keep_alive);
+  if (!s.have_tok) return respond_error(fd, 400, kNoTokenizer, "BadRequestError", hr.keep_alive);
+  if (detok) {
+    const Json* t = j.get("tokens");
+    if (!t || !t->is_arr()) return respond_error(fd, 400, "tokens must be an array of integers", "BadRequestError", hr.keep_alive);
+    std::vector<int32_t> ids;
+    for (auto& x : t->arr) {
+      if (!x.is_num()) return respond_error(fd, 400, "tokens must be an array of integers", "BadRequestError", hr.keep_alive);
+      ids.push_back((int32_t)std::max<int64_t>(-1, std::min<int64_t>(x.as_i64(), INT32_MAX)));
+    }
+    return respond(fd, 200, "application/json", "{\"prompt\":\"" + json_escape(s.tok.decode(ids)) + "\"}", hr.keep_alive);
+  }
+  std::vector<int32_t> ids;
+  if (const Json* msgs = j.get("messages")) {
+    if (!msgs->is_arr() || !s.tok.has_chat_template()) return respond_error(fd, 400, "messages need a supported chat template", "BadRequestError", hr.keep_alive);
+    std::vector<ChatMessage> cm;
+    for (auto& m : msgs->arr) if (m.is_obj()) cm.push_back({m.str_or("role", "user"), m.str_or("content", "")});
+    ids = s.tok.encode(s.tok.render_chat(cm), false);
+  } else {
+    const Json* p = j.get("prompt");
+    if (!p || !p->is_str()) return respond_error(fd, 400, "prompt must be a string", "BadRequestError", hr.keep_alive);
+    ids = s.tok.encode(p->str, j.bool_or("add_special_tokens", true));
+  }
+  return respond(fd, 200, "application/json", "{\"count\":" + std::to_string(ids.size()) + ",\"max_model_len\":" + std::to_string(s.args.max_model_len) +
+                 ",\"tokens\":" + ids_json(ids) + ",\"token_strs\":null}", hr.keep_alive);
+}
+
 void serve_conn(Server* sp, int fd) {
   Server& s = *sp;
   int one = 1;
@@ -713,6 +747,12 @@ void serve_conn(Server* sp, int fd) {
     const int rc = read_request(fd, buf, &r);
     if (rc <= 0) break;
     bool ok = true;
+    // --api-key / VLLM_API_KEY guards the /v1 routes (vllm:entrypoints/openai/server_utils.py AuthenticationMiddleware)
+    if (!s.args.api_key.empty() && r.path.compare(0, 3, "/v1") == 0 && r.method != "OPTIONS" && r.authorization != "Bearer " + s.args.api_key) {
+      ok = respond(fd, 401, "application/json", "{\"error\":\"Unauthorized\"}", r.keep_alive);
+      if (!ok || !r.keep_alive) break;
+      continue;
+    }
     if (r.path == "/health" || r.path == "/ping") {
       ok = respond(fd, s.healthy ? 200 : 503, "", "", r.keep_alive);
     } else if (r.path == "/v1/models" && r.method == "GET") {
@@ -726,6 +766,8 @@ void serve_conn(Server* sp, int fd) {
       ok = respond(fd, 200, "text/plain; version=0.0.4; charset=utf-8", metrics_text(s), r.keep_alive);
     } else if (r.path == "/version") {
       ok = respond(fd, 200, "application/json", "{\"version\":\"kge-b200-0.1\"}", r.keep_alive);
+    } else if ((r.path == "/tokenize" || r.path == "/detokenize") && r.method == "POST") {
+      ok = handle_tokenize(s, fd, r, r.path == "/detokenize");
     } else if (r.path == "/v1/completions" || r.path == "/v1/chat/completions") {
       if (r.method != "POST") ok = respond_error(fd, 405, "Method Not Allowed", "MethodNotAllowed", r.keep_alive);
       else if (!s.healthy) ok = respond_error(fd, 503, "engine is not healthy", "ServiceUnavailable", r.keep_alive);

@@ -378,3 +378,42 @@ def test_server_survives_garbage_under_sanitizers(mock_lib, tmp_path):
         stop(proc)
         err = proc.stderr.read().decode()
     assert "AddressSanitizer" not in err and "runtime error" not in err, err[-3000:]
+
+
+def test_tokenize_detokenize_and_api_key(mock_lib, tmp_path):
+    from test_tokenizer_cpu import build
+    (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    tok = build("llama3", str(tmp_path))
+    proc, port = start(mock_lib, tmp_path, tmp_path / "log", "--api-key", "s3cret")
+    try:
+        text = "The GPU cluster's nodes aren't ready."
+        st, out = http(port, "/tokenize", {"prompt": text})                      # outside /v1: no key needed, as in vLLM
+        r = json.loads(out)
+        assert st == 200 and r["tokens"] == tok.encode(text).ids and r["count"] == len(r["tokens"]) and r["max_model_len"] == 256
+        assert json.loads(http(port, "/tokenize", {"prompt": text, "add_special_tokens": False})[1])["tokens"] == tok.encode(text, add_special_tokens=False).ids
+        st, out = http(port, "/detokenize", {"tokens": r["tokens"]})
+        assert st == 200 and json.loads(out)["prompt"] == text
+        msgs = [{"role": "user", "content": "Hi"}]
+        rendered = "<|begin_of_text|><|start_header_id|>user<|end_header_id|>\n\nHi<|eot_id|><|start_header_id|>assistant<|end_header_id|>\n\n"
+        assert json.loads(http(port, "/tokenize", {"messages": msgs})[1])["tokens"] == tok.encode(rendered, add_special_tokens=False).ids
+        assert http(port, "/tokenize", {"prompt": 5})[0] == 400 and http(port, "/detokenize", {"tokens": "x"})[0] == 400
+        # /v1 routes need the key
+        st, out = http(port, "/v1/completions", {"prompt": [5], "max_tokens": 1})
+        assert st == 401 and json.loads(out) == {"error": "Unauthorized"}
+        assert http(port, "/v1/models")[0] == 401 and http(port, "/health")[0] == 200 and http(port, "/metrics")[0] == 200
+        for key, code in (("s3cret", 200), ("wrong", 401)):
+            req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", data=json.dumps({"prompt": [5], "max_tokens": 1}).encode(),
+                                         headers={"Content-Type": "application/json", "Authorization": f"Bearer {key}"})
+            try:
+                with urllib.request.urlopen(req, timeout=10) as resp:
+                    got = resp.status
+            except urllib.error.HTTPError as e:
+                got = e.code
+            assert got == code
+    finally:
+        stop(proc)
+    proc, port = start(mock_lib, tmp_path, tmp_path / "log", env_extra={"VLLM_API_KEY": "envkey"})
+    try:
+        assert http(port, "/v1/models")[0] == 401
+    finally:
+        stop(proc)

@@ -38,6 +38,36 @@ using namespace kge;
 
 namespace {
 
+// Prometheus histogram with vLLM's metric names and bucket edges (vllm:v1/metrics/loggers.py).
+struct Histogram {
+  std::vector<double> edges;
+  std::vector<uint64_t> counts;      // per bucket, not cumulative; last = +Inf
+  double sum = 0;
+  uint64_t n = 0;
+  std::mutex mu;
+  explicit Histogram(std::vector<double> e) : edges(std::move(e)), counts(edges.size() + 1, 0) {}
+  void observe(double v) {
+    std::lock_guard<std::mutex> lk(mu);
+    size_t i = 0;
+    while (i < edges.size() && v > edges[i]) ++i;
+    ++counts[i]; sum += v; ++n;
+  }
+  std::string text(const char* name, const char* help, const std::string& label) {
+    std::lock_guard<std::mutex> lk(mu);
+    std::string o = std::string("# HELP ") + name + " " + help + "\n# TYPE " + name + " histogram\n";
+    uint64_t cum = 0;
+    char b[64];
+    for (size_t i = 0; i <= edges.size(); ++i) {
+      cum += counts[i];
+      if (i < edges.size()) snprintf(b, sizeof b, "%g", edges[i]); else snprintf(b, sizeof b, "+Inf");
+      o += std::string(name) + "_bucket{" + label + ",le=\"" + b + "\"} " + std::to_string(cum) + "\n";
+    }
+    snprintf(b, sizeof b, "%.9g", sum);
+    o += std::string(name) + "_sum{" + label + "} " + b + "\n" + name + "_count{" + label + "} " + std::to_string(n) + "\n";
+    return o;
+  }
+};
+
 struct ReqState {
   std::mutex mu;
   std::condition_variable cv;
@@ -47,6 +77,7 @@ struct ReqState {
   int finished = 0;            // 0 running, 1 stop, 2 length, 3 error/aborted
   std::string error;
   int prompt_len = 0;
+  std::chrono::steady_clock::time_point t_arrival = std::chrono::steady_clock::now(), t_last;   // latency metrics
 };
 
 struct Submit {
@@ -76,6 +107,9 @@ struct Server {
   std::atomic<int64_t> prompt_tokens{0}, generation_tokens{0}, success_stop{0}, success_length{0}, num_steps{0};
   std::atomic<int> running{0}, waiting{0};
   std::atomic<int64_t> preemptions{0}, pc_queries{0}, pc_hits{0};
+  Histogram h_ttft{{0.001, 0.005, 0.01, 0.02, 0.04, 0.06, 0.08, 0.1, 0.25, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0, 160.0, 640.0, 2560.0}};
+  Histogram h_itl{{0.01, 0.025, 0.05, 0.075, 0.1, 0.15, 0.2, 0.3, 0.4, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0}};
+  Histogram h_e2e{{0.3, 0.5, 0.8, 1.0, 1.5, 2.0, 2.5, 5.0, 10.0, 15.0, 20.0, 30.0, 40.0, 50.0, 60.0, 120.0, 240.0, 480.0, 960.0, 1920.0, 7680.0}};
   std::atomic<float> kv_usage{0.f};
   time_t created = time(nullptr);
 };
@@ -166,10 +200,17 @@ void engine_loop(Server* sp) {
             st->lps.emplace_back();
             for (int k = 0; k < m; ++k) st->lps.back().push_back({li[k], lv[k]});
           }
+          const auto now = std::chrono::steady_clock::now();
+          if (st->tokens.empty()) s.h_ttft.observe(std::chrono::duration<double>(now - st->t_arrival).count());
+          else s.h_itl.observe(std::chrono::duration<double>(now - st->t_last).count());
+          st->t_last = now;
           st->tokens.push_back(outs[i].token);
           ++s.generation_tokens;
         }
-        if (outs[i].finished) st->finished = outs[i].finished;
+        if (outs[i].finished) {
+          st->finished = outs[i].finished;
+          s.h_e2e.observe(std::chrono::duration<double>(std::chrono::steady_clock::now() - st->t_arrival).count());
+        }
       }
       st->cv.notify_all();
       if (outs[i].finished) {
@@ -701,6 +742,10 @@ std::string metrics_text(Server& s) {
   counter("vllm:request_success_total", "", ",finished_reason=\"length\"", (double)s.success_length, false);
   counter("vllm:prefix_cache_queries_total", "Prefix cache queries, in terms of number of queried tokens.", "", (double)s.pc_queries, true);
   counter("vllm:prefix_cache_hits_total", "Prefix cache hits, in terms of number of cached tokens.", "", (double)s.pc_hits, true);
+  o += s.h_ttft.text("vllm:time_to_first_token_seconds", "Histogram of time to first token in seconds.", m);
+  o += s.h_itl.text("vllm:inter_token_latency_seconds", "Histogram of inter-token latency in seconds.", m);
+  o += s.h_itl.text("vllm:time_per_output_token_seconds", "Histogram of time per output token in seconds (v0.8 name of inter_token_latency).", m);
+  o += s.h_e2e.text("vllm:e2e_request_latency_seconds", "Histogram of end to end request latency in seconds.", m);
   counter("kge:engine_steps_total", "Engine steps executed.", "", (double)s.num_steps, true);
   return o;
 }

@@ -417,3 +417,31 @@ def test_tokenize_detokenize_and_api_key(mock_lib, tmp_path):
         assert http(port, "/v1/models")[0] == 401
     finally:
         stop(proc)
+
+
+def test_latency_histograms_in_metrics(mock_lib, tmp_path):
+    """vllm:time_to_first_token_seconds, inter_token_latency_seconds (and its v0.8 name), e2e_request_latency_seconds:
+    Prometheus histograms with vLLM's names; counts follow the traffic."""
+    (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    proc, port = start(mock_lib, tmp_path, tmp_path / "log", env_extra={"MOCK_KGE_STEP_US": "2000"})
+    try:
+        for n in (3, 5, 1):
+            assert http(port, "/v1/completions", {"prompt": [5, 6, 7], "max_tokens": n, "temperature": 0, "ignore_eos": True})[0] == 200
+        m = http(port, "/metrics")[1]
+
+        def series(name):
+            rows = [ln for ln in m.splitlines() if ln.startswith(name)]
+            buckets = [(ln.split('le="')[1].split('"')[0], int(ln.split()[-1])) for ln in rows if "_bucket" in ln]
+            count = int([ln for ln in rows if ln.startswith(name + "_count")][0].split()[-1])
+            total = float([ln for ln in rows if ln.startswith(name + "_sum")][0].split()[-1])
+            return buckets, count, total
+        for name, want in (("vllm:time_to_first_token_seconds", 3), ("vllm:inter_token_latency_seconds", 6),
+                           ("vllm:time_per_output_token_seconds", 6), ("vllm:e2e_request_latency_seconds", 3)):
+            assert f"# TYPE {name} histogram" in m
+            buckets, count, total = series(name)
+            assert count == want and buckets[-1] == ("+Inf", want) and total > 0
+            assert all(a[1] <= b[1] for a, b in zip(buckets, buckets[1:]))
+        b, c, total = series("vllm:inter_token_latency_seconds")
+        assert 0.002 * 6 <= total < 1.0                                   # six gaps of one 2 ms mock step each
+    finally:
+        stop(proc)

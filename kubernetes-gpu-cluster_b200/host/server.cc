@@ -105,7 +105,7 @@ struct Server {
   std::atomic<bool> stop{false}, healthy{true};
   std::atomic<int64_t> next_id{1};
   std::atomic<int64_t> prompt_tokens{0}, generation_tokens{0}, success_stop{0}, success_length{0}, num_steps{0};
-  std::atomic<int> running{0}, waiting{0};
+  std::atomic<int> running{0}, waiting{0}, active_conns{0};
   std::atomic<int64_t> preemptions{0}, pc_queries{0}, pc_hits{0};
   Histogram h_ttft{{0.001, 0.005, 0.01, 0.02, 0.04, 0.06, 0.08, 0.1, 0.25, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0, 160.0, 640.0, 2560.0}};
   Histogram h_itl{{0.01, 0.025, 0.05, 0.075, 0.1, 0.15, 0.2, 0.3, 0.4, 0.5, 0.75, 1.0, 2.5, 5.0, 7.5, 10.0, 20.0, 40.0, 80.0}};
@@ -227,6 +227,18 @@ void engine_loop(Server* sp) {
     kge_engine_prefix_cache_stats(s.engines[0], &pq, &ph);
     s.pc_queries = pq; s.pc_hits = ph;
   }
+  // shutting down: wake every connection that is still waiting for tokens, and the ones that were never admitted
+  {
+    std::lock_guard<std::mutex> lk(s.mu);
+    for (auto& sub : s.submits) s.live[sub.id] = sub.st;
+    s.submits.clear();
+  }
+  for (auto& kv : s.live) {
+    std::lock_guard<std::mutex> lk(kv.second->mu);
+    if (!kv.second->finished) { kv.second->error = "the server is shutting down"; kv.second->finished = 3; }
+    kv.second->cv.notify_all();
+  }
+  s.live.clear();
 }
 
 // ---------------------------------------------------------------------------------- HTTP helpers
@@ -784,6 +796,7 @@ bool handle_tokenize(Server& s, int fd, const HttpReq& hr, bool detok) {
 
 void serve_conn(Server* sp, int fd) {
   Server& s = *sp;
+  struct Live { std::atomic<int>& n; ~Live() { n.fetch_sub(1, std::memory_order_release); } } live{s.active_conns};   // counted in main before the thread starts
   int one = 1;
   setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
   std::string buf;
@@ -1028,12 +1041,18 @@ int main(int argc, char** argv) {
     if (select(lfd + 1, &rf, nullptr, nullptr, &tv) <= 0) continue;
     int fd = accept(lfd, nullptr, nullptr);
     if (fd < 0) continue;
+    s.active_conns.fetch_add(1);
     std::thread(serve_conn, &s, fd).detach();
   }
   s.stop = true;
   { std::lock_guard<std::mutex> lk(s.mu); s.cv.notify_all(); }
   eng.join();
   ::close(lfd);
+  // connection threads are detached: give them a moment to send their last bytes and leave before the state they use
+  // goes away; whatever is still parked on an idle keep-alive socket after that ends with the process
+  for (int i = 0; i < 300 && s.active_conns.load(std::memory_order_acquire) > 0; ++i) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+  const int code = s.healthy ? 0 : 1;
+  if (s.active_conns.load(std::memory_order_acquire) > 0) { fflush(nullptr); _exit(code); }
   for (auto* e : s.engines) kge_engine_destroy(e);
-  return s.healthy ? 0 : 1;
+  return code;
 }

@@ -445,3 +445,71 @@ def test_latency_histograms_in_metrics(mock_lib, tmp_path):
         assert 0.002 * 6 <= total < 1.0                                   # six gaps of one 2 ms mock step each
     finally:
         stop(proc)
+
+
+def test_concurrent_clients_under_thread_sanitizer(mock_lib, tmp_path):
+    """host/server.cc built with ThreadSanitizer: 24 clients at once - blocking, streaming, some disconnecting mid-stream,
+    /metrics and /health polled meanwhile.  Every complete answer is right and TSan reports no data race."""
+    import threading
+    exe = str(tmp_path / "kge-serve-tsan")
+    p = subprocess.run(["g++", "-fsanitize=thread", "-g", "-O1", "-std=c++17", f"-I{os.path.join(ROOT, 'include')}", f"-I{os.path.join(PKG, 'csrc')}",
+                        f"-I{os.path.join(PKG, 'host')}", os.path.join(PKG, "host", "server.cc"), "-o", exe, f"-L{mock_lib}", "-lkge", "-lpthread", "-ldl"],
+                       capture_output=True, text=True, timeout=900)
+    if p.returncode and "cannot find" in p.stderr:
+        pytest.skip("sanitizer runtime not installed")
+    assert p.returncode == 0, p.stderr[-3000:]
+    (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    port = free_port()
+    env = dict(os.environ, LD_LIBRARY_PATH=mock_lib, MOCK_KGE_STEP_US="500", TSAN_OPTIONS="halt_on_error=0")
+    proc = subprocess.Popen([exe, "serve", str(tmp_path), "--host", "127.0.0.1", "--port", str(port), "--max-model-len", "256", "--served-model-name", "m",
+                             "--max-num-seqs", "8"], stderr=subprocess.PIPE, env=env)
+    errors = []
+    try:
+        for _ in range(400):
+            try:
+                if http(port, "/health", timeout=1)[0] == 200:
+                    break
+            except Exception:
+                time.sleep(0.05)
+
+        def client(i):
+            try:
+                prompt = [5 + i, 6, 7 + i % 3]
+                n = 5 + i % 7
+                if i % 3 == 0:
+                    ev = sse(port, "/v1/completions", {"prompt": prompt, "max_tokens": n, "temperature": 0, "ignore_eos": True, "stream": True})
+                    got = [c["choices"][0]["token_ids"][0] for c in ev]
+                elif i % 3 == 1:
+                    got = json.loads(http(port, "/v1/completions", {"prompt": prompt, "max_tokens": n, "temperature": 0, "ignore_eos": True})[1])["choices"][0]["token_ids"]
+                else:                                    # goes away mid-stream
+                    s = socket.create_connection(("127.0.0.1", port), timeout=5)
+                    body = json.dumps({"prompt": prompt, "max_tokens": 150, "temperature": 0, "ignore_eos": True, "stream": True}).encode()
+                    s.sendall(b"POST /v1/completions HTTP/1.1\r\nContent-Length: %d\r\n\r\n%s" % (len(body), body))
+                    s.recv(512)
+                    s.close()
+                    return
+                if got != mock_generate(prompt, n):
+                    errors.append((i, got))
+            except Exception as ex:
+                errors.append((i, repr(ex)))
+
+        def poller():
+            for _ in range(40):
+                http(port, "/metrics")
+                http(port, "/health")
+        threads = [threading.Thread(target=client, args=(i,)) for i in range(24)] + [threading.Thread(target=poller)]
+        for t in threads:
+            t.start()
+        for t in threads:
+            t.join(timeout=120)
+        assert not errors, errors[:3]
+        for _ in range(200):                              # the abandoned requests are gone
+            m = http(port, "/metrics")[1]
+            if float([ln for ln in m.splitlines() if ln.startswith("vllm:num_requests_running")][0].split()[-1]) == 0:
+                break
+            time.sleep(0.05)
+        assert proc.poll() is None
+    finally:
+        stop(proc)
+        err = proc.stderr.read().decode()
+    assert "WARNING: ThreadSanitizer" not in err, err[-4000:]

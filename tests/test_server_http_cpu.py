@@ -513,3 +513,38 @@ def test_concurrent_clients_under_thread_sanitizer(mock_lib, tmp_path):
         stop(proc)
         err = proc.stderr.read().decode()
     assert "WARNING: ThreadSanitizer" not in err, err[-4000:]
+
+
+def test_replicas_behind_the_router(mock_lib, tmp_path):
+    """BASELINE config 5 in miniature, without GPUs: two server processes (mock engines) behind kge-router - requests
+    alternate between the replicas, SSE passes through, /v1/models is merged."""
+    router = os.path.join(PKG, "bin", "kge-router")
+    if not os.path.exists(router):
+        pytest.skip("router binary not built")
+    (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
+    servers = [start(mock_lib, tmp_path, tmp_path / f"log{i}") for i in range(2)]
+    rport = free_port()
+    rproc = subprocess.Popen([router, "--host", "127.0.0.1", "--port", str(rport), "--service-discovery", "static", "--static-backends",
+                              ",".join(f"http://127.0.0.1:{p}" for _, p in servers), "--static-models", "m,m"], stderr=subprocess.PIPE)
+    try:
+        for _ in range(100):
+            try:
+                if http(rport, "/health", timeout=1)[0] == 200:
+                    break
+            except Exception:
+                time.sleep(0.05)
+        for i in range(6):
+            st, body = http(rport, "/v1/completions", {"model": "m", "prompt": [5, 6, 7 + i], "max_tokens": 3, "temperature": 0})
+            assert st == 200 and json.loads(body)["choices"][0]["token_ids"] == mock_generate([5, 6, 7 + i], 3)
+        ev = sse(rport, "/v1/completions", {"model": "m", "prompt": [9, 9], "max_tokens": 4, "temperature": 0, "stream": True})
+        assert [c["choices"][0]["token_ids"][0] for c in ev] == mock_generate([9, 9], 4)
+        assert [m["id"] for m in json.loads(http(rport, "/v1/models")[1])["data"]] == ["m"]
+        served = []
+        for _, p in servers:
+            m = http(p, "/metrics")[1]
+            served.append(sum(float(ln.split()[-1]) for ln in m.splitlines() if ln.startswith("vllm:request_success_total")))
+        assert sorted(served) == [3, 4]                       # 7 requests, round-robin over two replicas
+    finally:
+        stop(rproc)
+        for proc, _ in servers:
+            stop(proc)

@@ -47,6 +47,7 @@ struct Router {
   std::atomic<uint64_t> rr{0};
   std::atomic<bool> stop{false};
   std::atomic<int64_t> no_backend{0};
+  std::atomic<int> active_conns{0};                  // detached connection threads still running
 };
 Router* g_router = nullptr;
 void on_signal(int) { if (g_router) g_router->stop = true; }
@@ -267,6 +268,7 @@ std::string metrics_text(Router& r) {
 
 void serve_conn(Router* rp, int fd) {
   Router& r = *rp;
+  struct Live { std::atomic<int>& n; ~Live() { n.fetch_sub(1, std::memory_order_release); } } live{r.active_conns};
   int one = 1;
   setsockopt(fd, IPPROTO_TCP, TCP_NODELAY, &one, sizeof one);
   HttpReq req;
@@ -382,9 +384,13 @@ int main(int argc, char** argv) {
   while (!r.stop) {
     const int fd = accept(lfd, nullptr, nullptr);
     if (fd < 0) continue;
+    r.active_conns.fetch_add(1);
     std::thread(serve_conn, &r, fd).detach();
   }
   close(lfd);
   hc.join();
+  // let the detached connection threads finish before the state they use goes away
+  for (int i = 0; i < 300 && r.active_conns.load(std::memory_order_acquire) > 0; ++i) std::this_thread::sleep_for(std::chrono::milliseconds(10));
+  if (r.active_conns.load(std::memory_order_acquire) > 0) { fflush(nullptr); _exit(0); }
   return 0;
 }

@@ -212,6 +212,8 @@ int kge_engine_num_blocks(const kge_engine* e);
 int kge_engine_vocab(const kge_engine* e);
 /* eos_token_id of config.json (-1 if none): what ends a request unless ignore_eos (vllm:v1/core/sched/utils.py:94-117). */
 int kge_engine_eos_token_id(const kge_engine* e);
+/* The context length in force: --max-model-len, or min(max_position_embeddings, 8192) when it was left out. */
+int kge_engine_max_model_len(const kge_engine* e);
 int64_t kge_engine_weight_bytes(const kge_engine* e);
 int64_t kge_engine_launches(const kge_engine* e);
 

@@ -100,6 +100,7 @@ SIGNATURES = {
     "kge_model_read_bf16": (C.c_int64, [_P, C.c_char_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _P, C.c_int64]),
     "kge_engine_vocab": (_I, [_P]),
     "kge_engine_eos_token_id": (_I, [_P]),
+    "kge_engine_max_model_len": (_I, [_P]),
     "kge_engine_weight_bytes": (_L, [_P]),
     "kge_engine_launches": (_L, [_P]),
     "kge_step": (_I, [_P, C.POINTER(StepBatch), _P, _P]),

@@ -392,5 +392,6 @@ extern "C" void kge_engine_destroy(kge_engine* e) {
 extern "C" int kge_engine_num_blocks(const kge_engine* e) { return e ? e->num_blocks : 0; }
 extern "C" int kge_engine_vocab(const kge_engine* e) { return e ? e->spec.vocab : 0; }
 extern "C" int kge_engine_eos_token_id(const kge_engine* e) { return e ? e->spec.eos : -1; }
+extern "C" int kge_engine_max_model_len(const kge_engine* e) { return e ? e->cfg.max_model_len : 0; }
 extern "C" int64_t kge_engine_weight_bytes(const kge_engine* e) { return e ? e->weight_bytes : 0; }
 extern "C" int64_t kge_engine_launches(const kge_engine* e) { return e ? e->launches : 0; }

@@ -1015,7 +1015,7 @@ int main(int argc, char** argv) {
     if (s.have_tok) fprintf(stderr, "INFO: tokenizer loaded (%d entries%s)\n", s.tok.vocab_size(), s.tok.has_chat_template() ? ", chat template" : "");
     else fprintf(stderr, "INFO: %s - string prompts and chat messages will be refused; token-id prompts work\n", terr.c_str());
   }
-  if (s.args.max_model_len <= 0) s.args.max_model_len = 8192;
+  s.args.max_model_len = kge_engine_max_model_len(s.engines[0]);      // what the engine settled on when the flag was left out
   fprintf(stderr, "INFO: model %s loaded: %.2f GB weights/rank, %d KV blocks, tp=%d\n", dir.c_str(),
           kge_engine_weight_bytes(s.engines[0]) / 1e9, kge_engine_num_blocks(s.engines[0]), a.tensor_parallel_size);
 

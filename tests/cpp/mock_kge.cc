@@ -14,6 +14,7 @@
 #include <string.h>
 #include <unistd.h>
 
+#include <algorithm>
 #include <fstream>
 #include <map>
 #include <memory>
@@ -37,7 +38,7 @@ static void set_err(const char* fmt, ...) {
 
 struct kge_engine {
   std::unique_ptr<Scheduler> sched;
-  int vocab = 1024, eos = -1, num_blocks = 0;
+  int vocab = 1024, eos = -1, num_blocks = 0, max_model_len = 0;
   std::map<int64_t, int> want_lp;                       // request id -> top-N
   std::map<int64_t, std::pair<int32_t, int>> last_lp;    // request id -> (token sampled in the last step, top-N)
 };
@@ -64,7 +65,7 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   SchedConfig sc;
   sc.max_num_seqs = cfg->max_num_seqs > 0 ? cfg->max_num_seqs : 1024;
   sc.max_num_batched_tokens = cfg->max_num_batched_tokens > 0 ? cfg->max_num_batched_tokens : 8192;
-  sc.max_model_len = cfg->max_model_len > 0 ? cfg->max_model_len : 2048;
+  sc.max_model_len = e->max_model_len = cfg->max_model_len > 0 ? cfg->max_model_len : (int)std::min<int64_t>(j.int_or("max_position_embeddings", 2048), 8192);
   sc.block_size = cfg->block_size > 0 ? cfg->block_size : 16;
   sc.num_blocks = e->num_blocks = cfg->num_blocks > 0 ? cfg->num_blocks : 4096;
   sc.enable_chunked_prefill = cfg->enable_chunked_prefill != 0;
@@ -77,6 +78,7 @@ extern "C" void kge_engine_destroy(kge_engine* e) { delete e; }
 extern "C" int kge_engine_num_blocks(const kge_engine* e) { return e ? e->num_blocks : 0; }
 extern "C" int kge_engine_vocab(const kge_engine* e) { return e ? e->vocab : 0; }
 extern "C" int kge_engine_eos_token_id(const kge_engine* e) { return e ? e->eos : -1; }
+extern "C" int kge_engine_max_model_len(const kge_engine* e) { return e ? e->max_model_len : 0; }
 extern "C" int64_t kge_engine_weight_bytes(const kge_engine*) { return 0; }
 extern "C" void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on) { if (e) e->sched->set_reserve_full_isl(on != 0); }
 extern "C" void kge_engine_set_prefix_caching(kge_engine* e, int32_t on) { if (e) e->sched->set_prefix_caching(on != 0); }

@@ -53,10 +53,11 @@ def mock_lib(tmp_path_factory):
     return str(d)
 
 
-def start(mock_lib, model_dir, log, *extra, env_extra=None):
+def start(mock_lib, model_dir, log, *extra, env_extra=None, max_model_len=256):
     port = free_port()
     env = dict(os.environ, LD_LIBRARY_PATH=mock_lib, MOCK_KGE_LOG=str(log), **(env_extra or {}))
-    proc = subprocess.Popen([BIN, "serve", str(model_dir), "--host", "127.0.0.1", "--port", str(port), "--max-model-len", "256",
+    mml = ["--max-model-len", str(max_model_len)] if max_model_len else []
+    proc = subprocess.Popen([BIN, "serve", str(model_dir), "--host", "127.0.0.1", "--port", str(port), *mml,
                              "--served-model-name", "m", *extra], stderr=subprocess.PIPE, env=env)
     for _ in range(200):
         try:
@@ -548,3 +549,16 @@ def test_replicas_behind_the_router(mock_lib, tmp_path):
         stop(rproc)
         for proc, _ in servers:
             stop(proc)
+
+
+def test_context_length_comes_from_the_engine(mock_lib, tmp_path):
+    cfg = dict(om.CONFIGS["tiny-llama"].to_hf(), max_position_embeddings=4096)
+    (tmp_path / "config.json").write_text(json.dumps(cfg))
+    proc, port = start(mock_lib, tmp_path, tmp_path / "log", max_model_len=None)
+    try:
+        assert json.loads(http(port, "/v1/models")[1])["data"][0]["max_model_len"] == 4096
+        http(port, "/v1/chat/completions", {"prompt_token_ids": [5, 6, 7], "temperature": 0, "max_tokens": 2})
+        st, out = http(port, "/v1/completions", {"prompt": list(range(3, 5003)), "max_tokens": 1})
+        assert st == 400 and "max_model_len" in out
+    finally:
+        stop(proc)

@@ -115,14 +115,6 @@ __device__ __forceinline__ float silu_gate_bf16(float g_acc, float u_acc) {
   return sg * u;                                          // caller rounds the product once
 }
 
-__device__ __forceinline__ void tma_load_2d_mcast(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, uint16_t mask) {
-  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;"
-               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1), "h"(mask) : "memory");
-}
-__device__ __forceinline__ void tc_commit_mcast(uint32_t bar, uint16_t mask) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 [%0], %1;" ::"r"(bar), "h"(mask) : "memory");
-}
-
 __device__ __forceinline__ void tma_load_2d_cg2(uint32_t dst, const CUtensorMap* map, uint32_t bar_cluster, int c0, int c1) {
   asm volatile("cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
                ::"r"(dst), "l"(map), "r"(bar_cluster), "r"(c0), "r"(c1) : "memory");
@@ -145,16 +137,11 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
 // All TMA loads of a stage complete on the LEADER's full barrier; tcgen05.commit multicasts the
 // "stage free" and "accumulator ready" arrivals to both CTAs; both epilogues release the accumulator
 // on the leader's tmem_empty barrier.
-// MCAST (prefill, TOKN = 256): the two CTAs of a cluster work on two adjacent weight-row tiles of the
-// SAME token tile in lockstep; each loads half of the X tile and TMA-multicasts it into both CTAs'
-// shared memory, so the X tile crosses L2 -> SM once per pair (32 KB instead of 48 KB per CTA and
-// k-block).  A stage is free only when BOTH CTAs' MMAs on it have retired (empty barrier count 2,
-// tcgen05.commit multicast to both).
-template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool MCAST, bool PAIR = false>
+template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool PAIR = false>
 __global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
-  static_assert(!(MCAST && PAIR) && !(PAIR && SPLIT), "one cluster scheme at a time");
+  static_assert(!(PAIR && SPLIT), "one cluster scheme at a time");
   constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = (PAIR ? 128 : TOKN) * BLK_K * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
@@ -183,7 +170,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
   }
   if (warp == 1 && lane == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), MCAST ? 2 : 1); }
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
     for (int s = 0; s < 2; ++s) { mbar_init(tfull_bar(s), 1); mbar_init(tempty_bar(s), PAIR ? 8 : 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -200,7 +187,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  if (MCAST || PAIR) { cluster_arrive(); cluster_wait(); }   // peer barriers are initialised before any remote signal
+  if (PAIR) { cluster_arrive(); cluster_wait(); }   // peer barriers are initialised before any remote signal
   // TMEM is held: the next kernel may start arriving now (see attn_tc.cu for why not earlier)
   pdl_launch_dependents();
   if (warp != 0) pdl_wait();          // warp 0 (TMA producer) prefetches weights first, then waits
@@ -209,7 +196,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   // the cluster rank selecting the K range
   const int S = SPLIT ? (int)cluster_nctarank() : 1;
   const int crank = SPLIT ? (int)cluster_ctarank() : 0;
-  constexpr bool TWO = MCAST || PAIR;
+  constexpr bool TWO = PAIR;
   const int mrank = TWO ? (int)cluster_ctarank() : 0;            // which tile of the weight-row pair
   const int total = (TWO ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
   const int w_first = SPLIT ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
@@ -250,8 +237,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       int pre = 0;
       auto load_b = [&](int st, int kb, int n_tile) {
         const uint32_t b_dst = smem_base + st * STAGE_BYTES + A_BYTES;
-        if (MCAST) tma_load_2d_mcast(b_dst + mrank * (128 * BLK_K * 2), &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN + mrank * 128, (uint16_t)3);
-        else if (PAIR) tma_load_2d_cg2(b_dst, &tmap_x, lead_full(st), kb * BLK_K, n_tile * TOKN + mrank * 128);
+        if (PAIR) tma_load_2d_cg2(b_dst, &tmap_x, lead_full(st), kb * BLK_K, n_tile * TOKN + mrank * 128);
         else tma_load_2d(b_dst, &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN);
       };
       if (w_first < total) {
@@ -297,8 +283,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
             if (PAIR) tc_mma_bf16_cg2(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
             else tc_mma_bf16(d_tmem, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
           }
-          if (MCAST) tc_commit_mcast(empty_bar(stage), (uint16_t)3);   // both CTAs' producers wait for both MMAs
-          else if (PAIR) tc_commit_cg2(empty_bar(stage), (uint16_t)3); // frees the stage in both CTAs
+          if (PAIR) tc_commit_cg2(empty_bar(stage), (uint16_t)3); // frees the stage in both CTAs
           else tc_commit(empty_bar(stage));     // frees the smem slot when these MMAs retire
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
@@ -423,7 +408,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
-  if (MCAST || PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
+  if (PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
   if (warp == 2) {
     tc_fence_after();
     if (PAIR) asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
@@ -472,7 +457,7 @@ constexpr int gemm_smem_budget(bool shallow) { return shallow ? 112 * 1024 : 224
 static bool gemm_shallow(int tokn) { return tunable(TUN_GEMM_SHALLOW) != 0 && tokn <= 64; }
 constexpr int kSlotsShallow = 2 * 148;
 
-template <int TOKN, bool SPLIT, bool GATED, bool MCAST = false, bool PAIR = false, bool SHALLOW = false>
+template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool SHALLOW = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
@@ -481,7 +466,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, MCAST, PAIR>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, PAIR>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -497,7 +482,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
-  } else if (MCAST || PAIR) {
+  } else if (PAIR) {
     const int pairs = ((p.m_tiles + 1) / 2) * p.n_tiles;
     cfg.gridDim = dim3(2 * (pairs < 74 ? pairs : 74));
     attr[1].id = cudaLaunchAttributeClusterDimension;
@@ -525,7 +510,7 @@ static int query_max_clusters(int S) {
   constexpr int budget = gemm_smem_budget(SHALLOW) - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   constexpr int smem = STAGES * stage_bytes + 1024 + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, true, false, false>;   // the gated variant has the same footprint
+  auto kern = gemm_tc_kernel<TOKN, STAGES, true, false>;   // the gated variant has the same footprint
   if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem) != cudaSuccess) return 0;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = dim3(S * 64); cfg.blockDim = dim3(kGemmThreads); cfg.dynamicSmemBytes = smem;
@@ -586,15 +571,15 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
   if (gemm_shallow(g.tokn)) {
     if (g.splits > 1) {
       switch (g.tokn) {
-        case 16: return launch_gemm<16, true, GATED, false, false, true>(tw, tx, p, st);
-        case 32: return launch_gemm<32, true, GATED, false, false, true>(tw, tx, p, st);
-        default: return launch_gemm<64, true, GATED, false, false, true>(tw, tx, p, st);
+        case 16: return launch_gemm<16, true, GATED, false, true>(tw, tx, p, st);
+        case 32: return launch_gemm<32, true, GATED, false, true>(tw, tx, p, st);
+        default: return launch_gemm<64, true, GATED, false, true>(tw, tx, p, st);
       }
     }
     switch (g.tokn) {
-      case 16: return launch_gemm<16, false, GATED, false, false, true>(tw, tx, p, st);
-      case 32: return launch_gemm<32, false, GATED, false, false, true>(tw, tx, p, st);
-      default: return launch_gemm<64, false, GATED, false, false, true>(tw, tx, p, st);
+      case 16: return launch_gemm<16, false, GATED, false, true>(tw, tx, p, st);
+      case 32: return launch_gemm<32, false, GATED, false, true>(tw, tx, p, st);
+      default: return launch_gemm<64, false, GATED, false, true>(tw, tx, p, st);
     }
   }
   if (g.splits > 1) {
@@ -611,7 +596,7 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
     case 64: return launch_gemm<64, false, GATED>(tw, tx, p, st);
     case 128: return launch_gemm<128, false, GATED>(tw, tx, p, st);
     default:
-      if (gemm_uses_pair(g)) return launch_gemm<256, false, GATED, false, true>(tw, tx, p, st);
+      if (gemm_uses_pair(g)) return launch_gemm<256, false, GATED, true>(tw, tx, p, st);
       return launch_gemm<256, false, GATED>(tw, tx, p, st);
   }
 }

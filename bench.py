@@ -146,6 +146,40 @@ def latency_probe(llm, prompts, sp, clock=time.perf_counter):
             "requests": len(ttft), "definition": "all requests sent at t0 through LLM.generate; tokens of a step share its completion time"}
 
 
+NEAR_TIE = 0.0625      # two bf16 steps of a logit in [4, 8): what two fp32 summation orders can legitimately flip
+
+
+def classify_divergences(kge, llm, prompts, pout, toks_e2e, toks_res):
+    """The two legs run the same prompts on the same weights but batch them differently (whole prompts per step vs the
+    scheduler's chunked / mixed steps), so rows go through different kernels and fp32 summation orders and a greedy
+    choice between two almost equal logits can flip; after the first flip a request follows another path by
+    construction.  This replays the e2e job once more with per-token log-probabilities, requires it to reproduce the
+    timed job's tokens exactly (the engine is deterministic), and for every request's FIRST token that differs between
+    the legs records the engine's own top-1/top-2 log-probability gap at that step and whether the other leg's token
+    is that runner-up.  not_near_tie counts first divergences that this does not explain."""
+    sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True, logprobs=2)
+    outs = llm.generate(prompts, sp)
+    toks_lp = [o.outputs[0].token_ids for o in outs]
+    gaps, bad, first_steps = [], 0, []
+    for b, (x, y) in enumerate(zip(toks_e2e, toks_res)):
+        s = next((i for i, (a, c) in enumerate(zip(x, y)) if a != c), None)
+        if s is None:
+            continue
+        first_steps.append(s)
+        lp = outs[b].outputs[0].logprobs[s]                    # {token: Logprob}, sampled first, then the top-2
+        top = sorted(((v.logprob, t) for t, v in lp.items()), reverse=True)
+        gap = top[0][0] - top[1][0] if len(top) > 1 else float("inf")
+        runner_up = {t for _, t in top[:2]}
+        gaps.append(gap)
+        if not (gap <= NEAR_TIE and y[s] in runner_up):
+            bad += 1
+    gaps.sort()
+    return {"deterministic_replay": toks_lp == toks_e2e, "requests": len(toks_e2e), "first_divergences": len(gaps),
+            "not_near_tie": bad, "near_tie_threshold": NEAR_TIE, "max_gap": gaps[-1] if gaps else None,
+            "median_gap": gaps[len(gaps) // 2] if gaps else None,
+            "median_first_divergent_step": sorted(first_steps)[len(first_steps) // 2] if first_steps else None}
+
+
 def peaks():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(p):
@@ -163,8 +197,9 @@ def cpu_reference(workload, threads=None):
     (outside the timed region)."""
     import torch
     from oracle import model as om
-    if threads:
-        torch.set_num_threads(threads)
+    # every core this process may run on, whatever OMP_NUM_THREADS says (torchrun exports OMP_NUM_THREADS=1, which made
+    # the reference arm of a multi-rank launch run on one core)
+    torch.set_num_threads(threads or len(os.sched_getaffinity(0)))
     cores = torch.get_num_threads()
     name = WORKLOADS[workload][0]
     n, pin, pout = CPU_SAMPLE[workload]
@@ -297,6 +332,8 @@ def run_ours(args):
     log(f"value {value:.0f} tok/s, e2e {e2e:.0f} tok/s")
     toks_e2e = [o.outputs[0].token_ids for o in outs]
     same = sum(a == b for x, y in zip(toks_e2e, toks_res) for a, b in zip(x, y))
+    divergence = classify_divergences(kge, llm, prompts, pout, toks_e2e, toks_res)
+    log(f"legs: {divergence}")
 
     # ---- latency (extra job through the public API; BASELINE.json's metric also names p50 TTFT and ITL)
     try:
@@ -349,7 +386,7 @@ def run_ours(args):
         "e2e": {"value": e2e, "unit": "output tokens/s", "h2d_bytes_per_step": (io1[0] - io0[0]) // args.steps,
                 "d2h_bytes_per_step": (io1[1] - io0[1]) // args.steps, "ms_per_step": e2e_s * 1e3,
                 "timer": "host wall clock between device synchronisations; includes the C++ scheduler",
-                "tokens_equal_to_resident_leg": f"{same}/{B * pout}"},
+                "tokens_equal_to_resident_leg": f"{same}/{B * pout}", "leg_divergence": divergence},
         "latency": latency, "gpu_launches": launches, "clocks": clk, "roofline": roof, "kernels": kernels,
         "resident_wall_s": wall_resident,
     }
@@ -388,7 +425,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
-    args.warmup_ref = min(args.warmup, 1)
+    args.warmup_ref = args.warmup        # same warm-up count as the GPU arm
     protect_stdout()
     if args.impl == "reference":
         run_reference(args)

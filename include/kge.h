@@ -75,8 +75,8 @@ int kge_silu_mul(void* y, const void* x, int T, int f, void* stream);
 /* Dense projection y[T,N] = act(x[T,K] * w[N,K]^T + bias[N]); bf16 in/out, fp32 accumulate,
  * one rounding.  act: 0 none, 1 relu.  Replaces F.linear in QKV/O/MLP/LM-head
  * (vllm:model_executor/models/llama.py:94-121,164-180; opt.py:92-106,151-165;
- * layers/logits_processor.py:89-99).  tcgen05/TMEM/TMA kernel; K % 64 == 0, 16-byte aligned
- * rows.  `workspace` (>= kge_gemm_workspace_bytes) is device scratch for split-K. */
+ * layers/logits_processor.py:89-99).  tcgen05/TMEM/TMA kernel; K % 8 == 0 (16-byte rows; a partial last
+ * 64-wide k-block is zero-filled by TMA), x and w 16-byte aligned.  `workspace` (>= kge_gemm_workspace_bytes) is device scratch for split-K. */
 int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                   int act, void* workspace, int64_t workspace_bytes, void* stream);
 int64_t kge_gemm_workspace_bytes(int T, int N, int K);
@@ -292,9 +292,11 @@ typedef struct {
   float temperature;     /* < 1e-5 => greedy (vllm:sampling_params.py:25) */
   int32_t top_k;         /* <= 0 => off */
   float top_p;           /* >= 1 => off */
-  uint64_t seed;
+  uint64_t seed;         /* used when has_seed != 0 (0 is a valid seed) */
   const int32_t* stop_token_ids;
   int32_t num_stop_token_ids;
+  int32_t has_seed;      /* request carries its own seed: its random tokens depend only on (seed, output index),
+                            not on batch composition or arrival time (vllm:v1/sample/ops/topk_topp_sampler.py:180-184) */
 } kge_sampling_params;
 
 typedef struct {

@@ -40,7 +40,7 @@ class StepBatch(C.Structure):
 class CSamplingParams(C.Structure):
     _fields_ = [("max_tokens", C.c_int32), ("min_tokens", C.c_int32), ("ignore_eos", C.c_int32),
                 ("temperature", C.c_float), ("top_k", C.c_int32), ("top_p", C.c_float), ("seed", C.c_uint64),
-                ("stop_token_ids", C.c_void_p), ("num_stop_token_ids", C.c_int32)]
+                ("stop_token_ids", C.c_void_p), ("num_stop_token_ids", C.c_int32), ("has_seed", C.c_int32)]
 
 
 class StepOutput(C.Structure):
@@ -185,7 +185,7 @@ class SamplingParams:
         arr = (C.c_int32 * max(1, len(self.stop_token_ids)))(*self.stop_token_ids)
         c = CSamplingParams(self.max_tokens, self.min_tokens, int(self.ignore_eos), self.temperature,
                             self.top_k, self.top_p, self.seed or 0,
-                            C.cast(arr, C.c_void_p), len(self.stop_token_ids))
+                            C.cast(arr, C.c_void_p), len(self.stop_token_ids), int(self.seed is not None))
         c._keep = arr
         return c
 

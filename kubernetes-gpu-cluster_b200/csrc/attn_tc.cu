@@ -7,8 +7,9 @@
 //                   max/sum in fp32 (no shuffles), bf16 P written straight into the swizzled A-operand
 //                   layout in shared memory
 //   O_t = P V       tcgen05.mma, A = P, B = V tile as stored ([key][hd] = MN-major), D in TMEM [128,128+hd)
-//   O  = O*alpha + O_t in registers (exact online softmax, no lazy rescale)
-// K/V tiles are gathered from the paged cache with cp.async (double-buffered, 16-byte chunks placed at
+//   O accumulates in TMEM across tiles; it is rescaled (tcgen05.ld / st) only when a row's running maximum has grown
+//   by more than 2^8 since its reference maximum was fixed (lazy rescale, see kRescaleThreshold below)
+// K/V tiles are gathered from the paged cache with cp.async (K two tiles ahead, V one; 16-byte chunks placed at
 // their 128B-swizzled positions, block-table lookup once per row), made visible to the tensor-core
 // (async) proxy with fence.proxy.async, and handed over with mbarriers; tcgen05.commit signals the
 // softmax warps.  Tensor-bound: 4 * hd * sum_b q_b (ctx0_b + (q_b+1)/2) flop per q head.

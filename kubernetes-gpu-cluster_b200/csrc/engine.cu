@@ -42,6 +42,21 @@ struct Builder {
     return (bf16*)p;
   }
   bool dummy() const { return !md->has_weights(); }
+  // The device buffers are sized from config.json; a checkpoint tensor of another shape would be copied past the end of
+  // its buffer (or leave part of it unset), so every tensor's shape is checked against the config before anything loads.
+  bool expect(const std::string& name, int64_t rows, int64_t cols /* 0: 1-D */) {
+    const HostTensor* t = md->find(name);
+    if (!t) { err = "missing tensor " + name; return false; }
+    const bool ok = cols == 0 ? (t->shape.size() == 1 && t->shape[0] == rows)
+                              : (t->shape.size() == 2 && t->shape[0] == rows && t->shape[1] == cols);
+    if (!ok) {
+      std::string got;
+      for (auto s : t->shape) got += (got.empty() ? "" : "x") + std::to_string(s);
+      err = name + ": checkpoint shape " + got + " does not match config.json (expected " + std::to_string(rows) +
+            (cols ? "x" + std::to_string(cols) : "") + ")";
+    }
+    return ok;
+  }
   // dst rows [dst_r0, ...) of a [.., ncols] device matrix <- tensor slice
   bool put(bf16* dst, int64_t dst_off, const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1) {
     std::vector<uint16_t> buf;
@@ -70,6 +85,23 @@ static bool build_llama(Builder& b) {
   const int Hl = e->H_loc, KVl = e->KV_loc, fl = e->ffn_loc;
   const int kv_rep = tp > s.KV ? tp / s.KV : 1;
   const int kv0 = (rk / kv_rep) * KVl;                 // first kv head of this rank
+  if (!b.dummy()) {
+    if (!b.expect("model.embed_tokens.weight", s.vocab, d) || !b.expect("model.norm.weight", d, 0)) return false;
+    if (!s.tied && !b.expect("lm_head.weight", s.vocab, d)) return false;
+    for (int i = 0; i < s.L; ++i) {
+      const std::string p = "model.layers." + std::to_string(i) + ".";
+      if (!b.expect(p + "self_attn.q_proj.weight", (int64_t)s.H * hd, d) || !b.expect(p + "self_attn.k_proj.weight", (int64_t)s.KV * hd, d) ||
+          !b.expect(p + "self_attn.v_proj.weight", (int64_t)s.KV * hd, d) || !b.expect(p + "self_attn.o_proj.weight", d, (int64_t)s.H * hd) ||
+          !b.expect(p + "mlp.gate_proj.weight", s.ffn, d) || !b.expect(p + "mlp.up_proj.weight", s.ffn, d) ||
+          !b.expect(p + "mlp.down_proj.weight", d, s.ffn) || !b.expect(p + "input_layernorm.weight", d, 0) ||
+          !b.expect(p + "post_attention_layernorm.weight", d, 0))
+        return false;
+      if (s.qkv_bias && (!b.expect(p + "self_attn.q_proj.bias", (int64_t)s.H * hd, 0) || !b.expect(p + "self_attn.k_proj.bias", (int64_t)s.KV * hd, 0) ||
+                         !b.expect(p + "self_attn.v_proj.bias", (int64_t)s.KV * hd, 0)))
+        return false;
+      if (s.qk_norm && (!b.expect(p + "self_attn.q_norm.weight", hd, 0) || !b.expect(p + "self_attn.k_norm.weight", hd, 0))) return false;
+    }
+  }
   if (!(e->embed = b.dalloc((int64_t)s.vocab * d))) return false;
   if (b.dummy()) b.rnd(e->embed, (int64_t)s.vocab * d, kDummyScale);
   else if (!b.put(e->embed, 0, "model.embed_tokens.weight", 0, -1, 0, -1)) return false;
@@ -147,6 +179,21 @@ static bool build_opt(Builder& b) {
   const int Hl = e->H_loc, fl = e->ffn_loc;
   (void)tp;
   const std::string dp = "model.decoder.";
+  if (!b.dummy()) {
+    if (!b.expect(dp + "embed_tokens.weight", s.vocab, d) || !b.expect(dp + "embed_positions.weight", s.max_pos + 2, d) ||
+        !b.expect(dp + "final_layer_norm.weight", d, 0) || !b.expect(dp + "final_layer_norm.bias", d, 0))
+      return false;
+    for (int i = 0; i < s.L; ++i) {
+      const std::string p = dp + "layers." + std::to_string(i) + ".";
+      for (const char* nm : {"q_proj", "k_proj", "v_proj", "out_proj"})
+        if (!b.expect(p + "self_attn." + nm + ".weight", d, d) || !b.expect(p + "self_attn." + nm + ".bias", d, 0)) return false;
+      if (!b.expect(p + "fc1.weight", s.ffn, d) || !b.expect(p + "fc1.bias", s.ffn, 0) || !b.expect(p + "fc2.weight", d, s.ffn) ||
+          !b.expect(p + "fc2.bias", d, 0) || !b.expect(p + "self_attn_layer_norm.weight", d, 0) ||
+          !b.expect(p + "self_attn_layer_norm.bias", d, 0) || !b.expect(p + "final_layer_norm.weight", d, 0) ||
+          !b.expect(p + "final_layer_norm.bias", d, 0))
+        return false;
+    }
+  }
   if (!(e->embed = b.dalloc((int64_t)s.vocab * d)) || !(e->pos_embed = b.dalloc((int64_t)(s.max_pos + 2) * d)) ||
       !(e->final_w = b.dalloc(d)) || !(e->final_b = b.dalloc(d)))
     return false;
@@ -347,6 +394,13 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
     if (nb > cap) nb = (int)cap;
   }
   if (nb < 2) ENGINE_FAIL("kge_engine_create: no memory left for the KV cache (gpu_memory_utilization=%.2f)", e->cfg.gpu_memory_utilization);
+  // One request of max_model_len tokens must fit the pool (block 0 is the null block), or a request that outgrows it
+  // would preempt itself for ever; vLLM refuses to start in the same situation (vllm:v1/core/kv_cache_utils.py
+  // check_enough_kv_cache_memory).
+  if ((int64_t)(nb - 1) * e->cfg.block_size < e->cfg.max_model_len)
+    ENGINE_FAIL("kge_engine_create: the model's max seq len (%d) is larger than the maximum number of tokens that can be stored in "
+                "KV cache (%lld). Try increasing gpu_memory_utilization or decreasing max_model_len when initializing the engine.",
+                e->cfg.max_model_len, (long long)(nb - 1) * e->cfg.block_size);
   e->num_blocks = nb;
   e->kv_bytes = blk_bytes * nb;
   e->kc.resize(s.L); e->vc.resize(s.L);

@@ -143,7 +143,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
     LINEAR(e->logits, e->xsel, head, R, 0);
     if (any_random)
       FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
-                     e->step_count, nullptr, 0, st));
+                     0 /* the step is folded into the per-row seeds */, nullptr, 0, st));
     else
       FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
   }
@@ -153,7 +153,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
 int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const StepMeta& dm, bool any_random, double sum_seq) {
   const double attn_flops = 4.0 * sum_seq;
   const int ns = attn_decode_splits(B, e->KV_loc, max_seq_len);
-  if (!e->use_graphs || e->timing || any_random)      // the Philox step counter is a launch argument: no replay
+  if (!e->use_graphs || e->timing)
     return engine_forward(e, B, B, B, stride, 1, max_seq_len, dm, any_random, sum_seq, attn_flops);
   for (auto& g : e->graphs)
     if (g.B == B && g.ns == ns && g.stride == stride && g.rnd == any_random) {
@@ -304,6 +304,7 @@ static SamplingParams to_sp(const kge_sampling_params* p) {
   sp.top_k = p->top_k;
   sp.top_p = p->top_p;
   sp.seed = p->seed;
+  sp.has_seed = p->has_seed != 0;
   if (p->stop_token_ids && p->num_stop_token_ids > 0)
     sp.stop_token_ids.assign(p->stop_token_ids, p->stop_token_ids + p->num_stop_token_ids);
   return sp;
@@ -393,7 +394,13 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
       temp.push_back(r->sp.temperature);
       top_k.push_back(r->sp.top_k);
       top_p.push_back(r->sp.top_p);
-      seeds.push_back(r->sp.seed ? r->sp.seed : (uint64_t)r->id * 0x9E3779B97F4A7C15ull + 1);
+      // noise stream of this row: a seeded request draws from (seed, index of the token being sampled) only, so the same
+      // seeded request gives the same tokens whatever else is in flight; unseeded ones also mix in the engine step
+      uint64_t z = r->sp.has_seed ? r->sp.seed : ((uint64_t)r->id * 0x9E3779B97F4A7C15ull + 1) ^ (e->step_count * 0xD1B54A32D192ED03ull);
+      z += (uint64_t)r->output.size() * 0x9E3779B97F4A7C15ull + 0x632BE59BD9B4E019ull;
+      z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+      z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+      seeds.push_back(z ^ (z >> 31));
       if (r->sp.logprobs >= 0) {
         lp_n = std::max(lp_n, r->sp.logprobs);
         e->lp_last[r->id] = {(int)rows.size() - 1, r->sp.logprobs};

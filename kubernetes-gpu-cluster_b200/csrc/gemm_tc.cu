@@ -22,6 +22,9 @@
 #include <cuda.h>
 #include <stdlib.h>
 
+#include <mutex>
+#include <unordered_map>
+
 #include "common.cuh"
 #include "kge.h"
 
@@ -434,7 +437,7 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // 2-D row-major bf16 [rows, cols] with a {64 x box_rows} box and 128B swizzle.
-static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
+static int encode_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
   EncodeTiledFn enc = get_encode_fn();
   KGE_REQUIRE(enc, "cuTensorMapEncodeTiled unavailable (no CUDA driver?)");
   cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
@@ -445,6 +448,33 @@ static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   KGE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld", (int)r, (long long)rows, (long long)cols);
+  return 0;
+}
+
+// A tensor map is a pure function of (address, shape, box): the engine's weights and activation buffers keep their
+// addresses, so each map is encoded once and looked up afterwards (two host-side driver calls per GEMM launch otherwise,
+// which is what an un-graphed step pays on every one of its ~200 GEMMs).
+struct TmapKey {
+  const void* p; int64_t rows, cols; int box;
+  bool operator==(const TmapKey& o) const { return p == o.p && rows == o.rows && cols == o.cols && box == o.box; }
+};
+struct TmapKeyHash {
+  size_t operator()(const TmapKey& k) const {
+    uint64_t h = (uint64_t)(uintptr_t)k.p * 0x9E3779B97F4A7C15ull;
+    h ^= ((uint64_t)k.rows * 0xBF58476D1CE4E5B9ull) ^ ((uint64_t)k.cols << 20) ^ (uint64_t)k.box;
+    return (size_t)(h ^ (h >> 29));
+  }
+};
+static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
+  static std::mutex mu;
+  static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
+  const TmapKey key{ptr, rows, cols, box_rows};
+  std::lock_guard<std::mutex> lock(mu);
+  auto it = cache.find(key);
+  if (it != cache.end()) { *m = it->second; return 0; }
+  if (int rc = encode_tmap(m, ptr, rows, cols, box_rows)) return rc;
+  if (cache.size() >= 16384) cache.clear();       // callers that cycle through fresh buffers (tests) stay bounded
+  cache.emplace(key, *m);
   return 0;
 }
 

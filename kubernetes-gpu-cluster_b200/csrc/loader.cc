@@ -119,7 +119,7 @@ bool ModelDir::open(const std::string& dir, std::string* err) {
     const uint8_t* p = (const uint8_t*)base;
     uint64_t hlen;
     memcpy(&hlen, p, 8);
-    if (8 + hlen > (uint64_t)st.st_size) { *err = path + ": bad header length"; return false; }
+    if (hlen > (uint64_t)st.st_size - 8) { /* compared this way round: 8 + hlen could wrap */ *err = path + ": bad header length"; return false; }
     Json hdr;
     JsonParser jp((const char*)p + 8, hlen);
     if (!jp.parse(&hdr, &perr) || !hdr.is_obj()) { *err = path + ": header " + perr; return false; }

@@ -25,6 +25,7 @@ struct SamplingParams {
   int32_t top_k = 0;
   float top_p = 1.0f;
   uint64_t seed = 0;
+  bool has_seed = false;
   std::vector<int32_t> stop_token_ids;
   int32_t logprobs = -1;               // top-N log-probabilities per sampled token (0 = the sampled token's only), -1 = none
 };

@@ -138,6 +138,7 @@ int step_all(Server& s, kge_step_output* outs, int cap) {
 void engine_loop(Server* sp) {
   Server& s = *sp;
   std::vector<kge_step_output> outs(8192);
+  int idle_steps = 0;
   while (!s.stop) {
     std::deque<Submit> subs;
     std::deque<int64_t> abs_;
@@ -186,6 +187,27 @@ void engine_loop(Server* sp) {
       s.stop = true;
       break;
     }
+    if (n == 0) {
+      // Unfinished requests but nothing could be scheduled.  kge_engine_create guarantees that one request always fits the
+      // KV pool, so this should not happen; if it does, spinning here would hang every client while /health stays 200.
+      // Fail the requests that are stuck and carry on serving.
+      if (++idle_steps >= 3) {
+        fprintf(stderr, "engine made no progress with %zu live requests: failing them\n", s.live.size());
+        for (auto& kv : s.live) {
+          for (auto* e : s.engines) kge_abort_request(e, kv.first);
+          std::lock_guard<std::mutex> lk(kv.second->mu);
+          kv.second->error = "the engine could not schedule this request (KV cache too small for it)";
+          kv.second->finished = 3;
+          kv.second->cv.notify_all();
+        }
+        s.live.clear();
+        idle_steps = 0;
+      } else {
+        std::this_thread::sleep_for(std::chrono::milliseconds(1));
+      }
+      continue;
+    }
+    idle_steps = 0;
     ++s.num_steps;
     for (int i = 0; i < n; ++i) {
       auto it = s.live.find(outs[i].request_id);
@@ -428,6 +450,7 @@ std::string parse_sampling(const Json& j, ParsedReq* r, bool chat) {
   r->given_top_k = j.get("top_k") && j.get("top_k")->is_num();
   if (r->sp.top_k < 0) r->sp.top_k = 0;
   r->sp.seed = (uint64_t)j.int_or("seed", 0);
+  r->sp.has_seed = (j.get("seed") && j.get("seed")->is_num()) ? 1 : 0;     // "seed": 0 is a seed
   r->n = I("n", 1);
   r->stream = j.bool_or("stream", false);
   r->echo = j.bool_or("echo", false);
@@ -578,7 +601,7 @@ bool handle_generate(Server& s, int fd, const HttpReq& hr, bool chat) {
         sb.prompt = p;
         sb.sp = pr.sp;
         if (chat && !pr.max_tokens_given) sb.sp.max_tokens = std::max(1, s.args.max_model_len - (int)p.size());
-        if (pr.n > 1 && sb.sp.seed) sb.sp.seed += (uint64_t)k;
+        if (pr.n > 1 && sb.sp.has_seed) sb.sp.seed += (uint64_t)k;
         sb.stop_ids = pr.stop_ids;
         sb.logprobs = pr.logprobs;
         sb.st = std::make_shared<ReqState>();

@@ -91,7 +91,7 @@ extern "C" int kge_add_request(kge_engine* e, int64_t id, const int32_t* prompt,
     if (prompt[i] < 0 || prompt[i] >= e->vocab) { set_err("kge_add_request: token id %d out of vocabulary", prompt[i]); return -1; }
   SamplingParams sp;
   sp.max_tokens = p->max_tokens; sp.min_tokens = p->min_tokens; sp.ignore_eos = p->ignore_eos != 0;
-  sp.temperature = p->temperature; sp.top_k = p->top_k; sp.top_p = p->top_p; sp.seed = p->seed;
+  sp.temperature = p->temperature; sp.top_k = p->top_k; sp.top_p = p->top_p; sp.seed = p->seed; sp.has_seed = p->has_seed != 0;
   if (p->stop_token_ids && p->num_stop_token_ids > 0) sp.stop_token_ids.assign(p->stop_token_ids, p->stop_token_ids + p->num_stop_token_ids);
   const char* why = nullptr;
   if (!e->sched->add(id, prompt, n, sp, &why)) { set_err("kge_add_request: %s", why ? why : "rejected"); return -1; }

@@ -348,7 +348,17 @@ def test_gemm_rejects_bad_arguments(kge, L):
 # ------------------------------------------------------------------------------ attention
 
 
-def run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed):
+def oracle_attention_chunked(q, k, v, scale, q_pos0, chunk=256):
+    """om.causal_attention over query chunks (same function, same values): keeps the fp32 score matrix of a
+    2048- or 8192-token prefill small enough for the host."""
+    outs = []
+    for c0 in range(0, q.shape[0], chunk):
+        c1 = min(q.shape[0], c0 + chunk)
+        outs.append(om.causal_attention(q[c0:c1], k[:q_pos0 + c1], v[:q_pos0 + c1], scale, q_pos0 + c0))
+    return torch.cat(outs, 0)
+
+
+def run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed, ramp=False):
     g = torch.Generator().manual_seed(seed)
     B = len(q_lens)
     T = sum(q_lens)
@@ -363,6 +373,16 @@ def run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed):
             bt[b, j] = free.pop()
     qkv_w = (H + 2 * KV) * hd
     qkv = torch.randn(T, qkv_w, generator=g).to(BF)
+    if ramp:
+        # growing row maximum: every query has a positive component along a fixed direction u and key j carries
+        # (j / ctx) * 40 * u, so the scaled score rises by ~85 (in log2 units) across the context and the running
+        # maximum of every row grows tile after tile - the case a lazily rescaled accumulator has to get right
+        u = torch.nn.functional.normalize(torch.randn(hd, generator=g), dim=0)
+        qkv[:, :H * hd] = (qkv[:, :H * hd].float().view(T, H, hd) + 6.0 * hd ** 0.5 * 0.25 * u).reshape(T, H * hd).to(BF)
+        for b, s_len in enumerate(seq_lens):
+            for j in range((s_len + bs - 1) // bs):
+                pos = (torch.arange(bs) + j * bs).float() / max(1, s_len)
+                kc[bt[b, j]] = (kc[bt[b, j]].float() + (40.0 * pos).view(1, bs, 1) * u.view(1, 1, hd)).to(BF)
     qsl = [0]
     for ql in q_lens:
         qsl.append(qsl[-1] + ql)
@@ -383,7 +403,7 @@ def run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed):
         k = kc[blocks].permute(0, 2, 1, 3).reshape(-1, KV, hd)[:s]
         v = vc[blocks].permute(0, 2, 1, 3).reshape(-1, KV, hd)[:s]
         q = qkv[qsl[b]:qsl[b + 1], :H * hd].reshape(ql, H, hd)
-        ref = om.causal_attention(q, k, v, scale, s - ql).float()
+        ref = oracle_attention_chunked(q, k, v, scale, s - ql).float()
         err = (got[qsl[b]:qsl[b + 1]] - ref).abs()
         tol = 1e-3 * ref.abs().max() + 1.6e-2 * ref.abs() + 4e-3
         assert (err <= tol).all(), f"request {b}: max err {err.max().item():.4g}"
@@ -410,6 +430,26 @@ ATTN_CASES = [
 @pytest.mark.parametrize("H,KV,hd,bs,q_lens,seq_lens", ATTN_CASES)
 def test_paged_attention(kge, L, H, KV, hd, bs, q_lens, seq_lens):
     run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed=H * 31 + sum(seq_lens))
+
+
+# The shapes the C3 bench runs the tcgen05 prefill kernel at (32 and 128 key tiles per row, where its K/V pipeline and
+# its lazy accumulator rescale actually cycle), the mixed step vLLM's scheduling policy produces, and both head sizes.
+ATTN_LONG_CASES = [
+    # H, KV, hd, q_lens, seq_lens, growing row maximum
+    (32, 8, 128, [2048] * 4, [2048] * 4, False),                         # a C3 prefill step: four whole prompts
+    (32, 8, 128, [8192], [8192], False),                                 # one 8192-token prompt
+    (32, 8, 128, [1] * 7 + [2037, 4], [2100 + 7 * i for i in range(7)] + [2037, 2048], False),   # 7 decodes + head + tail chunk
+    (32, 8, 64, [2048, 2048], [2048, 2048], False),                      # 1B head size
+    (32, 8, 64, [1] * 3 + [1000, 48], [300, 2000, 77, 1000, 2048], False),
+    (32, 8, 128, [2048], [2048], True),                                  # row maximum grows through every key tile
+    (32, 8, 64, [1500, 1], [1500, 1800], True),
+    (8, 1, 128, [512], [4096], True),                                    # a late chunk of a long context, group of 8
+]
+
+
+@pytest.mark.parametrize("H,KV,hd,q_lens,seq_lens,ramp", ATTN_LONG_CASES)
+def test_paged_attention_bench_shapes(kge, L, H, KV, hd, q_lens, seq_lens, ramp):
+    run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed=H * 17 + sum(q_lens) + int(ramp), ramp=ramp)
 
 
 DECODE_SPLIT_CASES = [

@@ -1,0 +1,163 @@
+"""Same-box table: this repo's kernels next to the sm_100 libraries installed in the image, on the C3 shapes.
+  GEMM    gemm_tc_kernel (through kge_gemm_bf16) vs cuBLAS (torch.matmul), prefill and decode shapes
+  prefill attn_tc_kernel (through kge_paged_attn) vs FlashInfer's trtllm-gen fmha (trtllm_batch_context_with_kv_cache)
+  decode  attn_decode_kernel vs FlashInfer's trtllm-gen decode (trtllm_batch_decode_with_kv_cache)
+CUDA events on the launching (default) stream, buffers rotated past L2 for the HBM-bound cases.  The library calls are
+comparison points only (tools/, never the product).  Writes one JSON document to --out.
+  python tools/bench_vs_libs.py --out gpurun_out/r02_vs_libs.json"""
+import argparse
+import json
+import os
+import sys
+import traceback
+
+import torch
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+from kge_loader import load  # noqa: E402
+
+kge = load()
+L = kge.lib()
+BF = torch.bfloat16
+
+
+def time_ms(fn, iters, warm=3):
+    for i in range(warm):
+        fn(i)
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(iters):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def gemm_rows():
+    rows = []
+    shapes = [(8192, 6144, 4096), (8192, 4096, 4096), (8192, 28672, 4096), (8192, 4096, 14336),
+              (64, 6144, 4096), (64, 4096, 4096), (64, 28672, 4096), (64, 4096, 14336), (64, 128256, 4096)]
+    for (T, N, K) in shapes:
+        ncopies = min(12, max(2, int(400e6 // (N * K * 2)) + 1))
+        ws = [torch.randn(N, K, device="cuda", dtype=BF) * 0.02 for _ in range(ncopies)]
+        x = torch.randn(T, K, device="cuda", dtype=BF)
+        y = torch.empty(T, N, device="cuda", dtype=BF)
+
+        def ours(i):
+            kge.check(L.kge_gemm_bf16(y.data_ptr(), x.data_ptr(), ws[i % ncopies].data_ptr(), None, T, N, K, 0, None, 0, None), "gemm")
+        it = 20 if T > 256 else 60
+        ms = time_ms(ours, it)
+        ms2 = time_ms(lambda i: torch.matmul(x, ws[i % ncopies].t(), out=y), it)
+        by, fl = 2.0 * (N * K + T * K + T * N), 2.0 * T * N * K
+        rows.append({"T": T, "N": N, "K": K, "kge_ms": round(ms, 4), "cublas_ms": round(ms2, 4),
+                     "kge_TFLOP/s": round(fl / ms / 1e9, 1), "cublas_TFLOP/s": round(fl / ms2 / 1e9, 1),
+                     "kge_GB/s": round(by / ms / 1e6, 1), "cublas_GB/s": round(by / ms2 / 1e6, 1),
+                     "winner": "kge" if ms <= ms2 else "cublas"})
+        print(json.dumps(rows[-1]), flush=True)
+        del ws
+    return rows
+
+
+def paged_setup(B, ctx, KV, hd, copies):
+    bs = 16
+    nb_seq = (ctx + bs - 1) // bs
+    nblk = B * nb_seq + 1
+    kv = [torch.randn(nblk, 2, KV, bs, hd, device="cuda", dtype=BF) for _ in range(copies)]   # FlashInfer HND: [page, 2, KV, page_size, hd]
+    bt = (torch.arange(B * nb_seq, dtype=torch.int32).view(B, nb_seq) + 1).cuda()
+    return bs, nb_seq, nblk, kv, bt
+
+
+def prefill_rows():
+    rows = []
+    for (B, qlen, H, KV, hd) in [(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128)]:
+        bs, nb_seq, nblk, kvs, bt = paged_setup(B, qlen, KV, hd, 1)
+        kv = kvs[0]
+        kc, vc = kv[:, 0].contiguous(), kv[:, 1].contiguous()
+        sl = torch.full((B,), qlen, dtype=torch.int32, device="cuda")
+        qsl = (torch.arange(B + 1, dtype=torch.int32) * qlen).cuda()
+        qw = (H + 2 * KV) * hd
+        qkv = torch.randn(B * qlen, qw, device="cuda", dtype=BF)
+        out = torch.empty(B * qlen, H * hd, device="cuda", dtype=BF)
+
+        def ours(i):
+            kge.check(L.kge_paged_attn(out.data_ptr(), qkv.data_ptr(), qw, kc.data_ptr(), vc.data_ptr(), bt.data_ptr(), nb_seq,
+                                       sl.data_ptr(), qsl.data_ptr(), B, B * qlen, qlen, qlen, H, KV, hd, bs, hd ** -0.5, None, 0, None), "attn")
+        ms = time_ms(ours, 10)
+        flops = 4.0 * H * hd * B * qlen * (qlen + 1) / 2
+        row = {"B": B, "q_len": qlen, "H": H, "KV": KV, "hd": hd, "kge_ms": round(ms, 4), "kge_TFLOP/s": round(flops / ms / 1e9, 1)}
+        try:
+            import flashinfer
+            q = qkv[:, :H * hd].reshape(B * qlen, H, hd).contiguous()
+            wsb = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+            o2 = torch.empty(B * qlen, H, hd, device="cuda", dtype=BF)
+
+            def fi(i):
+                flashinfer.prefill.trtllm_batch_context_with_kv_cache(
+                    q, kv, wsb, bt, sl, qlen, qlen, hd ** -0.5, 1.0, B, qsl, qsl, out=o2, kv_layout="HND")
+            ms2 = time_ms(fi, 10)
+            err = (o2.reshape(B * qlen, H * hd).float() - out.float()).abs().max().item()
+            row.update({"flashinfer_trtllm_gen_ms": round(ms2, 4), "flashinfer_TFLOP/s": round(flops / ms2 / 1e9, 1),
+                        "max_abs_diff_between_the_two": err, "winner": "kge" if ms <= ms2 else "flashinfer"})
+        except Exception as ex:      # comparison point only: record why it is missing
+            row["flashinfer_error"] = f"{type(ex).__name__}: {ex}"[:400]
+            traceback.print_exc()
+        rows.append(row)
+        print(json.dumps(row), flush=True)
+    return rows
+
+
+def decode_rows():
+    rows = []
+    for (B, ctx, H, KV, hd) in [(64, 2176, 32, 8, 128)]:
+        bs, nb_seq, nblk, kvs, bt = paged_setup(B, ctx, KV, hd, 3)
+        kcs = [kv[:, 0].contiguous() for kv in kvs]
+        vcs = [kv[:, 1].contiguous() for kv in kvs]
+        sl = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
+        qsl = torch.arange(B + 1, dtype=torch.int32, device="cuda")
+        qw = (H + 2 * KV) * hd
+        qkv = torch.randn(B, qw, device="cuda", dtype=BF)
+        out = torch.empty(B, H * hd, device="cuda", dtype=BF)
+        nws = L.kge_attn_workspace_bytes(B, H, hd, ctx)
+        ws = torch.empty(nws, dtype=torch.uint8, device="cuda")
+
+        def ours(i):
+            kge.check(L.kge_paged_attn(out.data_ptr(), qkv.data_ptr(), qw, kcs[i % 3].data_ptr(), vcs[i % 3].data_ptr(), bt.data_ptr(),
+                                       nb_seq, sl.data_ptr(), qsl.data_ptr(), B, B, 1, ctx, H, KV, hd, bs, hd ** -0.5, ws.data_ptr(), nws, None), "attn")
+        ms = time_ms(ours, 60)
+        by = B * ctx * KV * hd * 4.0
+        row = {"B": B, "ctx": ctx, "H": H, "KV": KV, "hd": hd, "kge_ms": round(ms, 4), "kge_GB/s": round(by / ms / 1e6, 1)}
+        try:
+            import flashinfer
+            q = qkv[:, :H * hd].reshape(B, H, hd).contiguous()
+            wsb = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+            o2 = torch.empty(B, H, hd, device="cuda", dtype=BF)
+
+            def fi(i):
+                flashinfer.decode.trtllm_batch_decode_with_kv_cache(q, kvs[i % 3], wsb, bt, sl, ctx, hd ** -0.5, 1.0, out=o2, kv_layout="HND")
+            ms2 = time_ms(fi, 60)
+            row.update({"flashinfer_trtllm_gen_ms": round(ms2, 4), "flashinfer_GB/s": round(by / ms2 / 1e6, 1),
+                        "winner": "kge" if ms <= ms2 else "flashinfer"})
+        except Exception as ex:
+            row["flashinfer_error"] = f"{type(ex).__name__}: {ex}"[:400]
+            traceback.print_exc()
+        rows.append(row)
+        print(json.dumps(row), flush=True)
+    return rows
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--out", default="gpurun_out/r02_vs_libs.json")
+    ap.add_argument("--skip", default="")
+    a = ap.parse_args()
+    kge.require_cuda()
+    doc = {"gpu": torch.cuda.get_device_name(0), "torch": torch.__version__}
+    if "gemm" not in a.skip:
+        doc["gemm_vs_cublas"] = gemm_rows()
+    if "prefill" not in a.skip:
+        doc["prefill_attention_vs_flashinfer"] = prefill_rows()
+    if "decode" not in a.skip:
+        doc["decode_attention_vs_flashinfer"] = decode_rows()
+    os.makedirs(os.path.dirname(a.out) or ".", exist_ok=True)
+    json.dump(doc, open(a.out, "w"), indent=1)

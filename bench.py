@@ -245,6 +245,83 @@ def run_reference(args):
     })
 
 
+def connect_tp(kge, llm, how, rank):
+    """Join the ranks of one tensor-parallel engine: peer-memory exchange (default) or NCCL (--tp-exchange nccl, what the
+    reference's --disable-custom-all-reduce selects)."""
+    import torch
+    import torch.distributed as dist
+    if how == "nccl":
+        import ctypes as C
+        buf = C.create_string_buffer(128)
+        if rank == 0:
+            kge.check(kge.lib().kge_nccl_unique_id(buf), "kge_nccl_unique_id")
+        t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        llm.init_tp(bytes(t.cpu().numpy().tobytes()))
+    else:
+        llm.tp_connect_torch()
+
+
+# decode-only HBM ceilings of Llama-3.1-70B on the C3 load, output tok/s (BASELINE.md section 3)
+C4_DECODE_CEILING = {2: 4540.0, 4: 9080.0, 8: 18160.0}
+
+
+def tp_subrecord(kge, args, world, rank, local, mx, barrier):
+    """BASELINE config 4 on the same ranks: ONE Llama-3.1-70B engine sharded over all `world` GPUs (tensor parallel,
+    strong scaling), same 64 x 2048-in/256-out load, device-resident replay like the headline `value`, plus one job
+    through the public API and the per-category device times of an instrumented job."""
+    import tempfile
+    name, B, pin, pout, pbatch = WORKLOADS["c4"]
+    hf = model_cfg(name)
+    prompts = rank_prompts(hf["vocab_size"], B, pin, rank, world)
+    nblk = B * ((pin + pout + 15) // 16) + 2
+    with tempfile.TemporaryDirectory() as d:
+        json.dump(hf, open(os.path.join(d, "config.json"), "w"))
+        llm = kge.LLM(d, max_model_len=pin + pout + 16, max_num_seqs=B, max_num_batched_tokens=pbatch * pin,
+                      num_gpu_blocks_override=nblk, load_format="dummy", seed=1234, device=local, tensor_parallel_size=world,
+                      tp_rank=rank, enable_prefix_caching=False)
+    connect_tp(kge, llm, args.tp_exchange, rank)
+    log(f"tp{world} engine ready: {llm.weight_bytes / 1e9:.1f} GB weights/rank")
+    llm.run_resident(prompts, pout, pbatch)
+    barrier()
+    ms = dms = 0.0
+    steps = max(1, min(2, args.steps))
+    for _ in range(steps):
+        _, m, dm = llm.run_resident(prompts, pout, pbatch)
+        ms += m
+        dms += dm
+    barrier()
+    ms, dms = mx(ms / steps), mx(dms / steps)
+    sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True)
+    barrier()
+    t0 = time.perf_counter()
+    llm.generate(prompts, sp)
+    barrier()
+    e2e_s = mx(time.perf_counter() - t0)
+    llm.set_timing(True)
+    llm.generate(prompts, sp)
+    stats = llm.kernel_stats()
+    llm.set_timing(False)
+    barrier()
+    llm.close()
+    total = sum(s["ms"] for s in stats.values())
+    ar = stats.get("all_reduce", {"ms": 0.0, "launches": 0})
+    value = B * pout / (ms * 1e-3)
+    dec_step = dms / (pout - 1)
+    ceil = C4_DECODE_CEILING.get(world)
+    return {"workload": f"c4: {name}, {B} concurrent requests, {pin}-in/{pout}-out, greedy, tensor parallel over {world} GPUs",
+            "parallelism": f"tp{world}", "exchange": ("peer memory: fused all-reduce + residual + norm kernel, vocab-sharded LM head + logits all-gather"
+                                                     if args.tp_exchange == "peer" else "NCCL all-reduce / all-gather"),
+            "scaling": "strong", "value": value, "unit": "output tokens/s", "ms_per_job": ms, "steps": steps,
+            "decode_ms_per_step": dec_step, "decode_tokens_per_s": B / (dec_step * 1e-3),
+            "decode_hbm_ceiling_tokens_per_s": ceil, "decode_frac_of_hbm_ceiling": (B / (dec_step * 1e-3) / ceil) if ceil else None,
+            "prefill_ms_per_8192_token_step": (ms - dms) / (B / pbatch),
+            "e2e": {"value": B * pout / e2e_s, "unit": "output tokens/s", "ms_per_job": e2e_s * 1e3},
+            "exchange_ms_of_instrumented_job": ar["ms"], "exchange_launches": ar["launches"],
+            "exchange_share_of_kernel_time": ar["ms"] / total if total else None,
+            "kernels_ms": {k: round(s["ms"], 1) for k, s in stats.items()}}
+
+
 def log(msg):
     sys.stderr.write(f"[bench {time.strftime('%H:%M:%S')} rank {os.environ.get('RANK', '0')}] {msg}\n")
     sys.stderr.flush()
@@ -277,13 +354,7 @@ def run_ours(args):
                       load_format="dummy", seed=1234, device=local, tensor_parallel_size=tp, tp_rank=rank if tp > 1 else 0,
                       enable_prefix_caching=False)      # the same prompts are replayed every step: a cache hit would skip the prefill
     if tp > 1:
-        import ctypes as C
-        buf = C.create_string_buffer(128)
-        if rank == 0:
-            kge.check(kge.lib().kge_nccl_unique_id(buf), "kge_nccl_unique_id")
-        t = torch.frombuffer(bytearray(buf.raw), dtype=torch.uint8).cuda()
-        dist.broadcast(t, 0)
-        llm.init_tp(bytes(t.cpu().numpy().tobytes()))
+        connect_tp(kge, llm, args.tp_exchange, rank)
     sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True)
     log(f"engine ready: {llm.weight_bytes / 1e9:.1f} GB weights, {llm.num_gpu_blocks} KV blocks, tp={tp}")
 
@@ -378,7 +449,7 @@ def run_ours(args):
         "data": "synthetic token-id prompts U[1000,V-1000), hash-random weights (--load-format dummy)",
         "config": {"workload": f"{args.workload}: {name}, {B} concurrent requests, {pin}-in/{pout}-out, greedy, "
                                f"paged KV block 16, {pbatch} prompts per prefill step",
-                   "parallelism": (f"tp{tp} (NCCL bf16 all-reduce after o_proj and down_proj)" if tp > 1
+                   "parallelism": (f"tp{tp} ({'peer-memory fused all-reduce + residual + norm' if args.tp_exchange == 'peer' else 'NCCL bf16 all-reduce'} after o_proj and down_proj)" if tp > 1
                                    else f"dp{world} (independent replicas, no collective)"),
                    "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)",
                    "prefix_caching": "off: every job recomputes every prompt (the same prompts are replayed each step)"},
@@ -390,13 +461,34 @@ def run_ours(args):
         "latency": latency, "gpu_launches": launches, "clocks": clk, "roofline": roof, "kernels": kernels,
         "resident_wall_s": wall_resident,
     }
+    llm.close()
+    if world > 1 and tp == 1 and not args.no_tp:
+        # BASELINE config 4 on the same ranks.  Guarded: whatever happens in this leg, the headline line is printed -
+        # a watchdog prints it without the sub-record and ends the process if the leg does not finish in time.
+        import threading
+
+        def give_up():
+            if rank == 0:
+                line["tp"] = {"error": f"tensor-parallel leg did not finish within {args.tp_timeout} s"}
+                emit(line)
+            os._exit(0)
+        dog = threading.Timer(args.tp_timeout, give_up)
+        dog.daemon = True
+        dog.start()
+        try:
+            line["tp"] = tp_subrecord(kge, args, world, rank, local, mx, barrier)
+        except Exception as ex:
+            line["tp"] = {"error": f"{type(ex).__name__}: {ex}"[:500]}
+        dog.cancel()
     if rank == 0:
         if world == 1 and not args.no_cpu:
             _, line["cpu_baseline"] = cpu_reference(args.workload)
         emit(line)
-    llm.close()
     if world > 1:
-        dist.destroy_process_group()
+        try:
+            dist.destroy_process_group()
+        except Exception:
+            pass
 
 
 _REAL_STDOUT = None
@@ -424,6 +516,9 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-tp", action="store_true", help="at N > 1, skip the tensor-parallel (config 4) sub-record")
+    ap.add_argument("--tp-exchange", default="peer", choices=["peer", "nccl"], help="TP data path: peer memory (default) or NCCL")
+    ap.add_argument("--tp-timeout", type=float, default=420.0, help="seconds the tensor-parallel leg may take at N > 1")
     args = ap.parse_args()
     args.warmup_ref = args.warmup        # same warm-up count as the GPU arm
     protect_stdout()

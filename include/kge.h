@@ -283,6 +283,51 @@ int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_host, int32_t 
 int kge_nccl_unique_id(char* out128);
 int kge_engine_init_tp(kge_engine* e, const char* id128);
 
+/* Tensor-parallel exchange over peer memory (NVLink / NVSwitch) - the default TP data path; the NCCL path above is what
+ * --disable-custom-all-reduce selects (ref:values-01-minimal-example8.yaml:32).
+ *
+ * Every rank owns one window of device memory; all ranks map all windows (CUDA IPC between processes, peer access
+ * between threads of one process).  kge_tp_comm_info fills the record a rank publishes; after every rank has collected
+ * all `world` records (any transport: a file, torch.distributed, MPI) it calls kge_tp_comm_connect.  Offsets below are
+ * relative to kge_tp_comm_data() and must be the same on every rank.
+ *
+ * kge_tp_reduce_add_norm: x[T,d] (bf16 partial sums, one per rank, at x_off of each window) are summed in fp32 in rank
+ *   order and rounded once to bf16 - what ncclAllReduce(sum, bf16) of vllm:model_executor/layers/linear.py:1559 returns -
+ *   then, fused, what always follows it:
+ *     mode 1  fused add + RMSNorm  (vllm:ir/ops/layernorm.py:40-58; llama.py:323-331,430)
+ *     mode 3  residual add + LayerNorm of the rounded sum  (vllm:model_executor/models/opt.py:181-196)
+ *     mode 0  nothing (plain all-reduce; y_off may equal x_off)
+ *   The result y[T,d] lands at y_off of EVERY rank's window.  Rows are partitioned over ranks: rank r reduces and
+ *   normalises rows [r*ceil(T/N), (r+1)*ceil(T/N)) only, so `residual` (a local [T,d] buffer, read and updated) is
+ *   maintained for a rank's OWN rows only; the other rows of it are never read.  Every rank must make the same call.
+ * kge_tp_all_gather_cols: dst[r, col0 + c] at dst_off of every rank's window <- src[r, c] (local [R, cols]); the
+ *   all-gather of vocab-sharded logits (vllm:model_executor/layers/logits_processor.py:83).
+ * A peer that never arrives makes the kernel trap after ~20 s (an error on the stream) instead of hanging the GPU. */
+typedef struct kge_tp_comm kge_tp_comm;
+typedef struct {
+  char ipc_handle[64];   /* cudaIpcMemHandle_t of the window                                   */
+  uint64_t ptr;          /* its device address in the owning process (used by same-process peers) */
+  int64_t pid;
+  int64_t bytes;
+  int32_t device;
+  int32_t rank;
+} kge_tp_peer_info;
+int kge_tp_comm_create(kge_tp_comm** out, int rank, int world, int device, int64_t data_bytes);
+void kge_tp_comm_destroy(kge_tp_comm* c);
+int kge_tp_comm_info(kge_tp_comm* c, kge_tp_peer_info* out);
+int kge_tp_comm_connect(kge_tp_comm* c, const kge_tp_peer_info* all /* [world], indexed by rank */);
+int kge_tp_comm_connected(const kge_tp_comm* c);
+void* kge_tp_comm_data(kge_tp_comm* c);
+int kge_tp_reduce_add_norm(kge_tp_comm* c, int64_t y_off, void* residual, int64_t x_off, const void* w, const void* b,
+                           int T, int d, float eps, int mode, void* stream);
+int kge_tp_all_gather_cols(kge_tp_comm* c, int64_t dst_off, const void* src, int R, int cols, int ld_dst, int col0,
+                           void* stream);
+/* The engine's own communicator (created with the engine when tp_size > 1): publish / connect as above.  Once
+ * connected, the forward pass uses the fused exchange, programmatic dependent launch and decode CUDA graphs; an
+ * engine that was only given kge_engine_init_tp keeps the NCCL all-reduce path. */
+int kge_engine_tp_info(kge_engine* e, kge_tp_peer_info* out);
+int kge_engine_tp_connect(kge_engine* e, const kge_tp_peer_info* all);
+
 /* ----------------------------------------------- scheduler + serving loop (host side) --- */
 
 typedef struct {

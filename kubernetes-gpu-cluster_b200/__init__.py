@@ -54,6 +54,12 @@ def _event_dtype():
                      "offsets": [0, 8, 12, 16], "itemsize": C.sizeof(StepOutput)})
 
 
+class TpPeerInfo(C.Structure):
+    """kge_tp_peer_info: what a tensor-parallel rank publishes so that its peers can map its exchange window."""
+    _fields_ = [("ipc_handle", C.c_char * 64), ("ptr", C.c_uint64), ("pid", C.c_int64), ("bytes", C.c_int64),
+                ("device", C.c_int32), ("rank", C.c_int32)]
+
+
 class KernelStats(C.Structure):
     _fields_ = [("launches", C.c_int64), ("ms", C.c_double), ("bytes", C.c_double), ("flops", C.c_double)]
 
@@ -110,6 +116,16 @@ SIGNATURES = {
     "kge_engine_run_resident": (_I, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
     "kge_nccl_unique_id": (_I, [_P]),
     "kge_engine_init_tp": (_I, [_P, _P]),
+    "kge_tp_comm_create": (_I, [C.POINTER(_P), _I, _I, _I, _L]),
+    "kge_tp_comm_destroy": (None, [_P]),
+    "kge_tp_comm_info": (_I, [_P, C.POINTER(TpPeerInfo)]),
+    "kge_tp_comm_connect": (_I, [_P, C.POINTER(TpPeerInfo)]),
+    "kge_tp_comm_connected": (_I, [_P]),
+    "kge_tp_comm_data": (_P, [_P]),
+    "kge_tp_reduce_add_norm": (_I, [_P, _L, _P, _L, _P, _P, _I, _I, _F, _I, _P]),
+    "kge_tp_all_gather_cols": (_I, [_P, _L, _P, _I, _I, _I, _I, _P]),
+    "kge_engine_tp_info": (_I, [_P, C.POINTER(TpPeerInfo)]),
+    "kge_engine_tp_connect": (_I, [_P, C.POINTER(TpPeerInfo)]),
     "kge_add_request": (_I, [_P, _L, _P, C.c_int32, C.POINTER(CSamplingParams)]),
     "kge_request_set_logprobs": (_I, [_P, C.c_int64, C.c_int32]),
     "kge_engine_step_logprobs": (_I, [_P, C.c_int64, C.POINTER(C.c_float), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.c_int32]),
@@ -334,7 +350,33 @@ class LLM:
         return out.tolist(), ms.value, dms.value
 
     def init_tp(self, unique_id: bytes):
+        """NCCL exchange (what --disable-custom-all-reduce selects): every rank passes rank 0's kge_nccl_unique_id."""
         check(lib().kge_engine_init_tp(self._h, unique_id), "kge_engine_init_tp")
+
+    def tp_info(self) -> bytes:
+        """This rank's exchange-window record (96 bytes) to hand to every peer, by any transport."""
+        info = TpPeerInfo()
+        check(lib().kge_engine_tp_info(self._h, C.byref(info)), "kge_engine_tp_info")
+        return bytes(info)
+
+    def tp_connect(self, infos):
+        """infos: every rank's tp_info(), indexed by rank.  Switches the forward pass to the peer-memory exchange
+        (fused all-reduce + residual + norm, logits all-gather), programmatic dependent launch and decode graphs."""
+        arr = (TpPeerInfo * len(infos))()
+        for i, b in enumerate(infos):
+            C.memmove(C.addressof(arr[i]), bytes(b), C.sizeof(TpPeerInfo))
+        check(lib().kge_engine_tp_connect(self._h, arr), "kge_engine_tp_connect")
+
+    def tp_connect_torch(self, group=None):
+        """tp_info / tp_connect over an initialised torch.distributed process group (rank order = TP rank order)."""
+        import torch
+        import torch.distributed as dist
+        dev = "cuda" if dist.get_backend(group) == "nccl" else "cpu"
+        mine = torch.frombuffer(bytearray(self.tp_info()), dtype=torch.uint8).to(dev)
+        outs = [torch.empty_like(mine) for _ in range(dist.get_world_size(group))]
+        dist.all_gather(outs, mine, group=group)
+        self.tp_connect([bytes(o.cpu().numpy().tobytes()) for o in outs])
+        dist.barrier(group=group)        # nobody starts a step before every rank has mapped every window
 
     def add_request(self, prompt_token_ids, sp: SamplingParams) -> int:
         rid = self._next_id

@@ -67,9 +67,12 @@ struct Builder {
     }
     return true;
   }
-  void rnd(bf16* p, int64_t n, float scale) {
+  // `shard`: this rank's slice of a sharded tensor draws its own values (replicated tensors must agree on every rank,
+  // which the common counter order guarantees)
+  void rnd(bf16* p, int64_t n, float scale, bool shard = false) {
+    const uint64_t salt = shard ? (uint64_t)e->tp_rank * 0xA24BAED4963EE407ull : 0;
     fill_uniform_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, e->stream>>>(
-        p, n, (uint64_t)dummy_seed * 0x100000001B3ull + (counter++) * 0x9E3779B9ull, scale);
+        p, n, ((uint64_t)dummy_seed * 0x100000001B3ull + (counter++) * 0x9E3779B9ull) ^ salt, scale);
   }
   void cst(bf16* p, int64_t n, float v) {
     fill_const_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, e->stream>>>(p, n, v);
@@ -105,11 +108,13 @@ static bool build_llama(Builder& b) {
   if (!(e->embed = b.dalloc((int64_t)s.vocab * d))) return false;
   if (b.dummy()) b.rnd(e->embed, (int64_t)s.vocab * d, kDummyScale);
   else if (!b.put(e->embed, 0, "model.embed_tokens.weight", 0, -1, 0, -1)) return false;
-  if (s.tied) e->lm_head = e->embed;
+  // LM head: under tensor parallelism each rank holds the rows (vocabulary entries) [vocab_col0, vocab_col0 + vocab_loc)
+  // (vllm:model_executor/layers/vocab_parallel_embedding.py:81-83; the embedding itself stays replicated here)
+  if (s.tied) e->lm_head = e->embed + (int64_t)e->vocab_col0 * d;
   else {
-    if (!(e->lm_head = b.dalloc((int64_t)s.vocab * d))) return false;
-    if (b.dummy()) b.rnd(e->lm_head, (int64_t)s.vocab * d, kDummyScale);
-    else if (!b.put(e->lm_head, 0, "lm_head.weight", 0, -1, 0, -1)) return false;
+    if (!(e->lm_head = b.dalloc((int64_t)e->vocab_loc * d))) return false;
+    if (b.dummy()) b.rnd(e->lm_head, (int64_t)e->vocab_loc * d, kDummyScale, tp > 1);
+    else if (!b.put(e->lm_head, 0, "lm_head.weight", e->vocab_col0, e->vocab_col0 + e->vocab_loc, 0, -1)) return false;
   }
   if (!(e->final_w = b.dalloc(d))) return false;
   if (b.dummy()) b.cst(e->final_w, d, 1.f);
@@ -132,10 +137,10 @@ static bool build_llama(Builder& b) {
     if (b.dummy()) {
       if (s.qkv_bias) b.cst(L.qkv.b, L.qkv.N, 0.f);
       if (s.qk_norm) { b.cst(L.q_norm, hd, 1.f); b.cst(L.k_norm, hd, 1.f); }
-      b.rnd(L.qkv.w, (int64_t)L.qkv.N * d, kDummyScale);
-      b.rnd(L.o.w, (int64_t)d * nq, kDummyScale);
-      b.rnd(L.up.w, (int64_t)2 * fl * d, kDummyScale);
-      b.rnd(L.down.w, (int64_t)d * fl, kDummyScale);
+      b.rnd(L.qkv.w, (int64_t)L.qkv.N * d, kDummyScale, tp > 1);
+      b.rnd(L.o.w, (int64_t)d * nq, kDummyScale, tp > 1);
+      b.rnd(L.up.w, (int64_t)2 * fl * d, kDummyScale, tp > 1);
+      b.rnd(L.down.w, (int64_t)d * fl, kDummyScale, tp > 1);
       b.cst(L.ln1_w, d, 1.f);
       b.cst(L.ln2_w, d, 1.f);
       continue;
@@ -197,7 +202,7 @@ static bool build_opt(Builder& b) {
   if (!(e->embed = b.dalloc((int64_t)s.vocab * d)) || !(e->pos_embed = b.dalloc((int64_t)(s.max_pos + 2) * d)) ||
       !(e->final_w = b.dalloc(d)) || !(e->final_b = b.dalloc(d)))
     return false;
-  e->lm_head = e->embed;
+  e->lm_head = e->embed + (int64_t)e->vocab_col0 * d;
   if (b.dummy()) {
     b.rnd(e->embed, (int64_t)s.vocab * d, kDummyScale);
     b.rnd(e->pos_embed, (int64_t)(s.max_pos + 2) * d, kDummyScale);
@@ -315,13 +320,17 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   e->H_loc = s.H / e->tp_size;
   e->KV_loc = std::max(1, s.KV / e->tp_size);
   e->ffn_loc = s.ffn / e->tp_size;
+  // vocabulary shard of the LM head: equal widths, a multiple of 8 so gathered rows move as 16-byte vectors
+  e->vocab_shard = e->tp_size == 1 ? s.vocab : ((s.vocab + e->tp_size - 1) / e->tp_size + 7) / 8 * 8;
+  e->vocab_col0 = e->tp_rank * e->vocab_shard;
+  e->vocab_loc = std::min(e->vocab_shard, s.vocab - e->vocab_col0);
+  if (e->vocab_loc <= 0) ENGINE_FAIL("kge_engine_create: vocabulary of %d is too small to shard over %d ranks", s.vocab, e->tp_size);
   if (getenv("KGE_DISABLE_GRAPHS")) e->use_graphs = false;               // diagnostics only
   if (e->tp_size > 1) {
-    // Known issue (round 1): Llama-70B at TP=4 deadlocks intermittently between ranks when the
-    // forward pass uses programmatic dependent launch around the NCCL all-reduces; TP engines run
-    // with plain stream order and eager decode steps until that is understood.
-    // KGE_TP_PDL=1 (experiment for the next round, untested at scale): keep programmatic dependent launch between our
-    // own kernels and launch only the kernel that follows each all-reduce in plain stream order (tp.cu).
+    // Until the ranks are connected over peer memory (kge_engine_tp_connect, which switches both back on) the exchange
+    // is NCCL's: plain stream order and eager decode steps there (with programmatic dependent
+    // launch around the NCCL kernels, Llama-70B at TP=4 deadlocked between ranks in round 1).
+    // KGE_TP_PDL=1 keeps programmatic dependent launch between the engine's own kernels on that path as well.
     if (!getenv("KGE_TP_PDL")) kge::pdl_set_enabled(false);
     e->use_graphs = false;
   }
@@ -350,15 +359,31 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
     act_bytes += elems * esz;
     return p;
   };
-  e->h = (bf16*)aalloc((int64_t)Tm * d, 2);
+  if (e->tp_size > 1) {
+    // the exchange window: [h | xn | gathered logits], same offsets on every rank
+    e->off_h = 0;
+    e->off_xn = align_up((int64_t)Tm * d * 2, 256);
+    e->off_logits = e->off_xn + align_up((int64_t)Tm * d * 2, 256);
+    const int64_t win = e->off_logits + align_up((int64_t)Rm * e->ld_logits * 2, 256);
+    if (kge_tp_comm_create(&e->tpc, e->tp_rank, e->tp_size, e->cfg.device, win)) { kge_engine_destroy(e); return -2; }
+    uint8_t* base = (uint8_t*)kge_tp_comm_data(e->tpc);
+    e->h = (bf16*)(base + e->off_h);
+    e->xn = (bf16*)(base + e->off_xn);
+    e->logits = (bf16*)(base + e->off_logits);
+    act_bytes += win;
+    e->logits_loc = (bf16*)aalloc((int64_t)Rm * e->vocab_shard, 2);
+    if (!e->logits_loc) ENGINE_FAIL("kge_engine_create: activation arena allocation failed");
+  } else {
+    e->h = (bf16*)aalloc((int64_t)Tm * d, 2);
+    e->xn = (bf16*)aalloc((int64_t)Tm * d, 2);
+    e->logits = (bf16*)aalloc((int64_t)Rm * e->ld_logits, 2);
+  }
   e->res = (bf16*)aalloc((int64_t)Tm * d, 2);
-  e->xn = (bf16*)aalloc((int64_t)Tm * d, 2);
   e->qkv = (bf16*)aalloc((int64_t)Tm * qkv_n, 2);
   e->attn = (bf16*)aalloc((int64_t)Tm * e->H_loc * s.hd, 2);
   e->gu = (bf16*)aalloc((int64_t)Tm * up_n, 2);
   e->act = (bf16*)aalloc((int64_t)Tm * e->ffn_loc, 2);
   e->xsel = (bf16*)aalloc((int64_t)Rm * d, 2);
-  e->logits = (bf16*)aalloc((int64_t)Rm * e->ld_logits, 2);
   e->logits_f32 = nullptr;
   e->d_out = (int32_t*)aalloc(Rm, 4);
   e->lp_vals = (float*)aalloc((int64_t)Rm * 21, 4);
@@ -434,6 +459,7 @@ extern "C" void kge_engine_destroy(kge_engine* e) {
   if (e->stream) cudaStreamSynchronize(e->stream);
   for (auto& g : e->graphs) cudaGraphExecDestroy(g.exec);
   for (void* p : e->allocs) cudaFree(p);
+  if (e->tpc) kge_tp_comm_destroy(e->tpc);
   if (e->meta_host) cudaFreeHost(e->meta_host);
   if (e->out_host) cudaFreeHost(e->out_host);
   if (e->lp_vals_host) cudaFreeHost(e->lp_vals_host);

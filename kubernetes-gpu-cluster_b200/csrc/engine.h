@@ -44,6 +44,14 @@ struct kge_engine {
   kge_engine_config cfg;
   int tp_rank = 0, tp_size = 1;
   ncclComm_t comm = nullptr;
+  // peer-memory exchange (tp_peer.cu): created with the engine when tp_size > 1; h, xn and the gathered logits live in
+  // its window at the offsets below (the same on every rank)
+  kge_tp_comm* tpc = nullptr;
+  int64_t off_h = 0, off_xn = 0, off_logits = 0;
+  kge::bf16* logits_loc = nullptr;           // [max_num_seqs, vocab_shard]: this rank's columns of the logits
+  kge::bf16* logits_gather = nullptr;        // NCCL path: [tp, max_num_seqs, vocab_shard] before the reorder
+  int vocab_shard = 0, vocab_loc = 0, vocab_col0 = 0;   // shard width (multiple of 8), columns really held, first column
+  bool tp_peer() const { return tpc && tp_size > 1 && kge_tp_comm_connected(tpc); }
   int H_loc = 0, KV_loc = 0, ffn_loc = 0;
   cudaStream_t stream = nullptr;
 

@@ -58,6 +58,19 @@ static int linear_rc(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int
       2.0 * (T) * (double)(l).N * (l).K, linear_rc(e, y, x, l, T, act))
 
 int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n);   // tp.cu
+int tp_all_gather_logits(kge_engine* e, int R);           // tp.cu (NCCL path)
+
+// The row-parallel projection before this point left its output (under TP: this rank's partial sum) in e->h:
+// all-reduce it, add it to the residual stream and normalise into e->xn.  Single GPU: the fused add + norm kernel.
+// TP over peer memory: ONE kernel does all three (tp_peer.cu) and keeps the residual for this rank's rows only.
+// TP over NCCL (--disable-custom-all-reduce): ncclAllReduce, then the norm kernel.
+static int reduce_add_norm(kge_engine* e, int T, const bf16* w, const bf16* b, bool layer_norm, float eps) {
+  const int d = e->spec.d;
+  if (e->tp_peer())
+    return kge_tp_reduce_add_norm(e->tpc, e->off_xn, e->res, e->off_h, w, b, T, d, eps, layer_norm ? 3 : 1, e->stream);
+  if (layer_norm) return kge_layernorm(e->xn, e->res, e->h, w, b, T, d, eps, e->stream);
+  return kge_add_rmsnorm(e->xn, e->res, e->h, w, T, d, eps, e->stream);
+}
 
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
                    const StepMeta& m, bool any_random, double sum_seq, double attn_flops) {
@@ -91,37 +104,42 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
   };
   const double rope_bytes = (double)T * (Hl + 2 * KVl) * hd * 2 * 2;
   const double ar_bytes = Td2;
+  const bool peer = e->tp_peer();
+  // all-reduce (TP) + residual add + norm; the fused peer kernel is booked under all_reduce
+#define REDUCE_NORM(w, b, ln, eps)                                                                      \
+  do {                                                                                                  \
+    if (e->tp_size > 1 && !peer) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));         \
+    FWD(peer ? C_AR : C_NORM, 4 * Td2, 0, reduce_add_norm(e, T, w, b, ln, eps));                        \
+  } while (0)
   if (s.is_opt()) {
     FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
       // first LN of the layer; for i > 0 it also folds in the previous layer's fc2 output
-      FWD(C_NORM, (i ? 4 : 2) * Td2, 0, kge_layernorm(e->xn, e->res, i == 0 ? nullptr : e->h, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
+      if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_layernorm(e->xn, e->res, nullptr, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
+      else REDUCE_NORM(L.ln1_w, L.ln1_b, true, 1e-5f);
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
       FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
       if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
-      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
-      FWD(C_NORM, 4 * Td2, 0, kge_layernorm(e->xn, e->res, e->h, L.ln2_w, L.ln2_b, T, d, 1e-5f, st));
+      REDUCE_NORM(L.ln2_w, L.ln2_b, true, 1e-5f);
       LINEAR(e->act, e->xn, L.up, T, 1);
       LINEAR(e->h, e->act, L.down, T, 0);
-      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
     }
-    FWD(C_NORM, 4 * Td2, 0, kge_layernorm(e->xn, e->res, e->h, e->final_w, e->final_b, T, d, 1e-5f, st));
+    REDUCE_NORM(e->final_w, e->final_b, true, 1e-5f);
   } else {
     FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
       if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
-      else FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln1_w, T, d, s.eps, st));
+      else REDUCE_NORM(L.ln1_w, nullptr, false, s.eps);
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
       if (s.qk_norm)
         FWD(C_NORM, (double)T * (Hl + KVl) * hd * 4, 0, kge_head_rmsnorm(e->qkv, L.q_norm, L.k_norm, T, Hl, KVl, hd, s.eps, st));
       FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
       if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
-      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
-      FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, L.ln2_w, T, d, s.eps, st));
+      REDUCE_NORM(L.ln2_w, nullptr, false, s.eps);
       if (e->ffn_loc % 64 == 0) {
         // gate_up GEMM with the SiLU*mul in its epilogue: [T,2f] never reaches HBM
         FWD(T <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)L.up.N * L.up.K + (double)T * (L.up.K + e->ffn_loc)),
@@ -131,16 +149,25 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
         FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
       }
       LINEAR(e->h, e->act, L.down, T, 0);
-      if (e->tp_size > 1) FWD(C_AR, ar_bytes, 0, tp_all_reduce(e, e->h, (int64_t)T * d));
     }
-    FWD(C_NORM, 4 * Td2, 0, kge_add_rmsnorm(e->xn, e->res, e->h, e->final_w, T, d, s.eps, st));
+    REDUCE_NORM(e->final_w, nullptr, false, s.eps);
   }
+#undef REDUCE_NORM
   if (R > 0) {
     // logits only for the last token of each sampled request (logits_processor.py:54-99)
     FWD(C_EMBED, 2.0 * R * d * 2, 0, kge_embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
     Linear head;
-    head.w = e->lm_head; head.b = nullptr; head.N = s.vocab; head.K = d;
-    LINEAR(e->logits, e->xsel, head, R, 0);
+    head.w = e->lm_head; head.b = nullptr; head.N = e->vocab_loc; head.K = d;
+    if (e->tp_size == 1) {
+      LINEAR(e->logits, e->xsel, head, R, 0);
+    } else {
+      // this rank's vocabulary columns, then the all-gather of vllm:model_executor/layers/logits_processor.py:83
+      LINEAR(e->logits_loc, e->xsel, head, R, 0);
+      if (peer)
+        FWD(C_AR, 2.0 * R * s.vocab, 0, kge_tp_all_gather_cols(e->tpc, e->off_logits, e->logits_loc, R, e->vocab_loc, s.vocab, e->vocab_col0, st));
+      else
+        FWD(C_AR, 2.0 * R * s.vocab, 0, tp_all_gather_logits(e, R));
+    }
     if (any_random)
       FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
                      0 /* the step is folded into the per-row seeds */, nullptr, 0, st));

@@ -16,6 +16,7 @@ struct NcclApi {
   ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
   ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
   ncclResult_t (*AllReduce)(const void*, void*, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+  ncclResult_t (*AllGather)(const void*, void*, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
   ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
   const char* (*GetErrorString)(ncclResult_t) = nullptr;
 };
@@ -32,9 +33,10 @@ static NcclApi* nccl_api() {
   api.GetUniqueId = (decltype(api.GetUniqueId))dlsym(api.lib, "ncclGetUniqueId");
   api.CommInitRank = (decltype(api.CommInitRank))dlsym(api.lib, "ncclCommInitRank");
   api.AllReduce = (decltype(api.AllReduce))dlsym(api.lib, "ncclAllReduce");
+  api.AllGather = (decltype(api.AllGather))dlsym(api.lib, "ncclAllGather");
   api.CommDestroy = (decltype(api.CommDestroy))dlsym(api.lib, "ncclCommDestroy");
   api.GetErrorString = (decltype(api.GetErrorString))dlsym(api.lib, "ncclGetErrorString");
-  if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.CommDestroy || !api.GetErrorString) {
+  if (!api.GetUniqueId || !api.CommInitRank || !api.AllReduce || !api.AllGather || !api.CommDestroy || !api.GetErrorString) {
     set_error("libnccl is missing a required symbol");
     api.lib = nullptr;
     return nullptr;
@@ -43,7 +45,7 @@ static NcclApi* nccl_api() {
 }
 
 int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n) {
-  KGE_REQUIRE(e->comm, "tensor parallel size %d but kge_engine_init_tp was not called", e->tp_size);
+  KGE_REQUIRE(e->comm, "tensor parallel size %d but neither kge_engine_tp_connect nor kge_engine_init_tp was called", e->tp_size);
   NcclApi* api = nccl_api();
   if (!api) return -1;
   ncclResult_t r = api->AllReduce(buf, buf, (size_t)n, ncclBfloat16, ncclSum, e->comm, e->stream);
@@ -52,9 +54,52 @@ int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n) {
   return 0;
 }
 
+// [tp][R][shard] (what ncclAllGather delivers) -> logits [R][vocab]
+__global__ void reorder_logits_kernel(bf16* __restrict__ dst, const bf16* __restrict__ src, int R, int shard, int vocab, int tp) {
+  const int64_t n = (int64_t)tp * R * shard;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int c = (int)(i % shard), r = (int)((i / shard) % R), k = (int)(i / ((int64_t)shard * R));
+    const int col = k * shard + c;
+    if (col < vocab) dst[(int64_t)r * vocab + col] = src[i];
+  }
+}
+
+// NCCL path of the vocab-sharded LM head: all ranks' [R, vocab_shard] blocks gathered, then laid out as [R, vocab].
+int tp_all_gather_logits(kge_engine* e, int R) {
+  KGE_REQUIRE(e->comm, "tensor parallel size %d but neither kge_engine_tp_connect nor kge_engine_init_tp was called", e->tp_size);
+  NcclApi* api = nccl_api();
+  if (!api) return -1;
+  if (!e->logits_gather) {
+    KGE_CUDA_OK(cudaMalloc((void**)&e->logits_gather, (size_t)e->tp_size * e->cfg.max_num_seqs * e->vocab_shard * 2));
+    e->allocs.push_back(e->logits_gather);
+  }
+  ncclResult_t r = api->AllGather(e->logits_loc, e->logits_gather, (size_t)R * e->vocab_shard, ncclBfloat16, e->comm, e->stream);
+  KGE_REQUIRE(r == ncclSuccess, "ncclAllGather: %s", api->GetErrorString(r));
+  reorder_logits_kernel<<<148 * 2, 256, 0, e->stream>>>(e->logits, e->logits_gather, R, e->vocab_shard, e->spec.vocab, e->tp_size);
+  KGE_LAUNCH_OK();
+  pdl_break_next();
+  return 0;
+}
+
 }  // namespace kge
 
 using namespace kge;
+
+extern "C" int kge_engine_tp_info(kge_engine* e, kge_tp_peer_info* out) {
+  KGE_REQUIRE(e && out, "kge_engine_tp_info: null argument");
+  KGE_REQUIRE(e->tpc, "kge_engine_tp_info: the engine was created with tensor_parallel_size 1");
+  return kge_tp_comm_info(e->tpc, out);
+}
+
+extern "C" int kge_engine_tp_connect(kge_engine* e, const kge_tp_peer_info* all) {
+  KGE_REQUIRE(e && all, "kge_engine_tp_connect: null argument");
+  KGE_REQUIRE(e->tpc, "kge_engine_tp_connect: the engine was created with tensor_parallel_size 1");
+  if (int rc = kge_tp_comm_connect(e->tpc, all)) return rc;
+  // the exchange kernels are the engine's own: programmatic dependent launch and captured decode steps are safe again
+  if (!getenv("KGE_DISABLE_PDL")) kge::pdl_set_enabled(true);
+  e->use_graphs = getenv("KGE_DISABLE_GRAPHS") == nullptr;
+  return 0;
+}
 
 extern "C" int kge_nccl_unique_id(char* out128) {
   KGE_REQUIRE(out128, "kge_nccl_unique_id: null argument");

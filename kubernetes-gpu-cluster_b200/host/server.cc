@@ -117,21 +117,65 @@ struct Server {
 Server* g_srv = nullptr;
 
 // ---------------------------------------------------------------------------------- engine thread
+// Tensor parallel: every rank runs the identical step so that the exchanges inside it can meet.  Ranks > 0 live in
+// worker threads that stay for the life of the server (one per rank, started on the first step) and are handed each
+// step through a generation counter; rank 0 steps in the engine-loop thread.
+struct RankWorkers {
+  std::mutex mu;
+  std::condition_variable cv_go, cv_done;
+  uint64_t gen = 0;
+  int pending = 0, cap = 0;
+  bool quit = false;
+  std::vector<int> rcs;
+  std::vector<std::vector<kge_step_output>> tmp;
+  std::vector<std::thread> th;
+  ~RankWorkers() {
+    { std::lock_guard<std::mutex> lk(mu); quit = true; }
+    cv_go.notify_all();
+    for (auto& t : th) t.join();
+  }
+};
+static RankWorkers g_workers;
+
 int step_all(Server& s, kge_step_output* outs, int cap) {
   if (s.engines.size() == 1) return kge_engine_step(s.engines[0], outs, cap);
-  // tensor parallel: every rank runs the identical step; ranks > 0 in helper threads so the NCCL
-  // all-reduces inside the step can meet
-  std::vector<std::thread> th;
-  std::vector<int> rcs(s.engines.size(), 0);
-  std::vector<std::vector<kge_step_output>> tmp(s.engines.size());
-  for (size_t r = 1; r < s.engines.size(); ++r) {
-    tmp[r].resize(cap);
-    th.emplace_back([&, r] { rcs[r] = kge_engine_step(s.engines[r], tmp[r].data(), cap); });
+  RankWorkers& w = g_workers;
+  if (w.th.empty()) {
+    w.rcs.assign(s.engines.size(), 0);
+    w.tmp.resize(s.engines.size());
+    for (size_t r = 1; r < s.engines.size(); ++r) {
+      w.tmp[r].resize(cap);
+      w.th.emplace_back([&w, &s, r] {
+        uint64_t seen = 0;
+        for (;;) {
+          int c;
+          {
+            std::unique_lock<std::mutex> lk(w.mu);
+            w.cv_go.wait(lk, [&] { return w.quit || w.gen != seen; });
+            if (w.quit) return;
+            seen = w.gen;
+            c = w.cap;
+          }
+          const int rc = kge_engine_step(s.engines[r], w.tmp[r].data(), c);
+          std::lock_guard<std::mutex> lk(w.mu);
+          w.rcs[r] = rc;
+          if (--w.pending == 0) w.cv_done.notify_one();
+        }
+      });
+    }
   }
+  {
+    std::lock_guard<std::mutex> lk(w.mu);
+    w.cap = std::min<int>(cap, (int)w.tmp[1].size());
+    w.pending = (int)s.engines.size() - 1;
+    ++w.gen;
+  }
+  w.cv_go.notify_all();
   const int n = kge_engine_step(s.engines[0], outs, cap);
-  for (auto& t : th) t.join();
+  std::unique_lock<std::mutex> lk(w.mu);
+  w.cv_done.wait(lk, [&] { return w.pending == 0; });
   for (size_t r = 1; r < s.engines.size(); ++r)
-    if (rcs[r] < 0 || rcs[r] != n) return -3;
+    if (w.rcs[r] < 0 || w.rcs[r] != n) return -3;
   return n;
 }
 
@@ -1013,7 +1057,17 @@ int main(int argc, char** argv) {
   }
   for (int r = 0; r < a.tensor_parallel_size; ++r)
     if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
-  if (a.tensor_parallel_size > 1) {
+  if (a.tensor_parallel_size > 1 && !a.disable_custom_all_reduce) {
+    // default exchange: the ranks (threads of this process) map each other's windows over NVLink peer access; the
+    // forward pass then runs the fused all-reduce + residual + norm kernel, with decode graphs
+    std::vector<kge_tp_peer_info> infos(a.tensor_parallel_size);
+    for (int r = 0; r < a.tensor_parallel_size; ++r)
+      if (kge_engine_tp_info(s.engines[r], &infos[r])) { fprintf(stderr, "error: rank %d: %s\n", r, kge_last_error()); return 1; }
+    for (int r = 0; r < a.tensor_parallel_size; ++r)
+      if (kge_engine_tp_connect(s.engines[r], infos.data())) { fprintf(stderr, "error: rank %d: %s\n", r, kge_last_error()); return 1; }
+    fprintf(stderr, "INFO: tensor parallel exchange over peer memory (fused all-reduce + residual + norm)\n");
+  } else if (a.tensor_parallel_size > 1) {
+    // --disable-custom-all-reduce (ref:values-01-minimal-example8.yaml:32): NCCL all-reduce, as the reference deploys it
     char id[128];
     if (kge_nccl_unique_id(id)) { fprintf(stderr, "error: %s\n", kge_last_error()); return 1; }
     std::vector<std::thread> th;
@@ -1022,6 +1076,7 @@ int main(int argc, char** argv) {
     for (auto& t : th) t.join();
     for (int r = 0; r < a.tensor_parallel_size; ++r)
       if (rcs[r]) { fprintf(stderr, "error: rank %d: %s\n", r, errs[r].c_str()); return 1; }
+    fprintf(stderr, "INFO: tensor parallel exchange over NCCL (--disable-custom-all-reduce)\n");
   }
   // sampling defaults and extra end-of-sequence ids the model ships (--generation-config auto | vllm | DIR)
   s.gen = load_gen_defaults(a.generation_config == "auto" || a.generation_config == "vllm" ? dir : a.generation_config, a.generation_config != "vllm");

@@ -84,6 +84,8 @@ extern "C" void kge_engine_set_reserve_full_isl(kge_engine* e, int32_t on) { if 
 extern "C" void kge_engine_set_prefix_caching(kge_engine* e, int32_t on) { if (e) e->sched->set_prefix_caching(on != 0); }
 extern "C" int kge_nccl_unique_id(char*) { set_err("mock engine: no tensor parallelism"); return -1; }
 extern "C" int kge_engine_init_tp(kge_engine*, const char*) { set_err("mock engine: no tensor parallelism"); return -1; }
+extern "C" int kge_engine_tp_info(kge_engine*, kge_tp_peer_info*) { set_err("mock engine: no tensor parallelism"); return -1; }
+extern "C" int kge_engine_tp_connect(kge_engine*, const kge_tp_peer_info*) { set_err("mock engine: no tensor parallelism"); return -1; }
 
 extern "C" int kge_add_request(kge_engine* e, int64_t id, const int32_t* prompt, int32_t n, const kge_sampling_params* p) {
   if (!e || !prompt || !p) { set_err("kge_add_request: null argument"); return -1; }

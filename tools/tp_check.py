@@ -1,7 +1,10 @@
-"""Tensor-parallel parity check: one process per rank (RANK / WORLD_SIZE env), each with its own engine on
-GPU `rank`, NCCL unique id passed through a file.  Rank 0 compares the greedy ids with the CPU oracle and
-prints one JSON line.  Used by tests/test_tp_gpu.py and by hand:
-  for r in 0 1; do RANK=$r WORLD_SIZE=2 python tools/tp_check.py tiny-llama /tmp/idfile & done; wait"""
+"""Tensor-parallel parity checks: one process per rank (RANK / WORLD_SIZE env), each on GPU `rank`; the ranks meet
+through files under a scratch prefix (NCCL unique id, peer-window records), so no launcher is needed.
+  tp_check.py engine <model> <prefix> [peer|nccl]   greedy ids of a TP engine vs the CPU oracle (rank 0 prints one JSON line)
+  tp_check.py ops <prefix>                         kge_tp_reduce_add_norm / kge_tp_all_gather_cols vs the oracle's arithmetic
+Used by tests/test_tp_gpu.py and by hand:
+  for r in 0 1; do RANK=$r WORLD_SIZE=2 python tools/tp_check.py engine tiny-llama /tmp/x peer & done; wait"""
+import ctypes as C
 import json
 import os
 import sys
@@ -14,41 +17,64 @@ import torch  # noqa: E402
 from kge_loader import load  # noqa: E402
 from oracle import model as om  # noqa: E402
 
+BF = torch.bfloat16
 
-def main():
-    name, idfile = sys.argv[1], sys.argv[2]
-    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
-    kge = load()
-    L = kge.lib()
-    torch.cuda.set_device(rank)
+
+def publish(prefix, name, rank, data: bytes):
+    tmp = f"{prefix}.{name}.{rank}.tmp"
+    with open(tmp, "wb") as f:
+        f.write(data)
+    os.replace(tmp, f"{prefix}.{name}.{rank}")
+
+
+def collect(prefix, name, world, timeout=180):
+    out = []
+    for r in range(world):
+        p = f"{prefix}.{name}.{r}"
+        t0 = time.time()
+        while not os.path.exists(p):
+            assert time.time() - t0 < timeout, f"rank {r} never published {name}"
+            time.sleep(0.02)
+        out.append(open(p, "rb").read())
+    return out
+
+
+def barrier(prefix, name, rank, world):
+    publish(prefix, name, rank, b"1")
+    collect(prefix, name, world)
+
+
+def engine_mode(kge, L, rank, world, name, prefix, how):
     cfg = om.CONFIGS[name]
     w = om.make_weights(cfg, seed=0)
-    prompts = [om.make_prompts(cfg, 1, n, seed=n)[0] for n in (9, 40, 70)]
+    prompts = [om.make_prompts(cfg, 1, n, seed=n)[0] for n in (9, 40, 70, 1, 33)]
     N = 12
     with tempfile.TemporaryDirectory() as d:
         om.save_model_dir(d, cfg, w)
         llm = kge.LLM(d, max_model_len=128, max_num_seqs=8, max_num_batched_tokens=96, num_gpu_blocks_override=64,
-                      tensor_parallel_size=world, tp_rank=rank, device=rank)
-    if rank == 0:
-        import ctypes as C
-        buf = C.create_string_buffer(128)
-        kge.check(L.kge_nccl_unique_id(buf), "unique id")
-        with open(idfile + ".tmp", "wb") as f:
-            f.write(buf.raw)
-        os.replace(idfile + ".tmp", idfile)
-        uid = buf.raw
+                      tensor_parallel_size=world, tp_rank=rank, device=rank, enable_prefix_caching=False)
+    if how == "nccl":
+        if rank == 0:
+            buf = C.create_string_buffer(128)
+            kge.check(L.kge_nccl_unique_id(buf), "unique id")
+            publish(prefix, "ncclid", 0, buf.raw)
+        llm.init_tp(collect(prefix, "ncclid", 1)[0])
     else:
-        t0 = time.time()
-        while not os.path.exists(idfile):
-            assert time.time() - t0 < 120, "rank 0 never wrote the NCCL id"
-            time.sleep(0.05)
-        uid = open(idfile, "rb").read()
-    llm.init_tp(uid)
-    outs = llm.generate(prompts, kge.SamplingParams(max_tokens=N, temperature=0.0, ignore_eos=True))
-    got = [o.outputs[0].token_ids for o in outs]
+        publish(prefix, "peer", rank, llm.tp_info())
+        llm.tp_connect(collect(prefix, "peer", world))
+        barrier(prefix, "connected", rank, world)
+    sp = kge.SamplingParams(max_tokens=N, temperature=0.0, ignore_eos=True)
+    got = [o.outputs[0].token_ids for o in llm.generate(prompts, sp)]
+    again = [o.outputs[0].token_ids for o in llm.generate(prompts, sp)]       # second job: replayed decode graphs, advanced epochs
+    # a seeded random job must give the same tokens on every rank (they sample the same gathered logits)
+    rnd = [o.outputs[0].token_ids for o in llm.generate(prompts[:2], kge.SamplingParams(max_tokens=6, temperature=1.0, top_p=0.9, seed=7, ignore_eos=True))]
+    publish(prefix, "rnd", rank, json.dumps(rnd).encode())
+    all_rnd = [json.loads(b) for b in collect(prefix, "rnd", world)]
+    launches = llm.kernel_launches
+    barrier(prefix, "done", rank, world)
     llm.close()
     if rank == 0:
-        ref_ids, ref_lg = om.OracleModel(cfg, w, torch.bfloat16).generate_greedy(prompts, N, return_logits=True)
+        ref_ids, ref_lg = om.OracleModel(cfg, w, BF).generate_greedy(prompts, N, return_logits=True)
         equal = near = bad = 0
         for b, (g, r) in enumerate(zip(got, ref_ids)):
             for s, (a, e) in enumerate(zip(g, r)):
@@ -61,8 +87,98 @@ def main():
                 else:
                     bad += 1
                 break
-        print(json.dumps({"model": name, "tp": world, "equal": equal, "near_tie_divergences": near, "bad": bad,
-                          "total": len(prompts) * N}))
+        print(json.dumps({"model": name, "tp": world, "exchange": how, "equal": equal, "near_tie_divergences": near, "bad": bad,
+                          "total": len(prompts) * N, "second_job_identical": again == got,
+                          "ranks_agree_on_random_tokens": all(r == all_rnd[0] for r in all_rnd), "launches": launches}))
+
+
+def ops_mode(kge, L, rank, world, prefix):
+    from cuda.bindings import runtime as cudart
+    D2D = cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice
+    Tmax, dmax, V = 320, 1024, 1000
+    off_x, off_y = 0, Tmax * dmax * 2
+    off_g = 2 * Tmax * dmax * 2
+    comm = C.c_void_p()
+    kge.check(L.kge_tp_comm_create(C.byref(comm), rank, world, rank, off_g + 64 * V * 2), "comm create")
+    info = kge.TpPeerInfo()
+    kge.check(L.kge_tp_comm_info(comm, C.byref(info)), "comm info")
+    publish(prefix, "peer", rank, bytes(info))
+    arr = (kge.TpPeerInfo * world)()
+    for i, b in enumerate(collect(prefix, "peer", world)):
+        C.memmove(C.addressof(arr[i]), b, C.sizeof(kge.TpPeerInfo))
+    kge.check(L.kge_tp_comm_connect(comm, arr), "comm connect")
+    barrier(prefix, "connected", rank, world)
+    base = L.kge_tp_comm_data(comm)
+    results = []
+    it = 0
+    for (T, d, mode) in [(64, 1024, 1), (1, 256, 1), (5, 512, 3), (300, 1024, 1), (64, 768, 3), (7, 1024, 0), (64, 1024, 1)]:
+        it += 1
+        g = torch.Generator().manual_seed(1000 * it)
+        parts = [(torch.randn(T, d, generator=g) * 0.5).to(BF) for _ in range(world)]      # every rank knows every partial
+        res = torch.randn(T, d, generator=g).to(BF)
+        w = (1.0 + 0.1 * torch.randn(d, generator=g)).to(BF)
+        b = (0.1 * torch.randn(d, generator=g)).to(BF)
+        xd, resd, wd, bd = parts[rank].cuda(), res.cuda(), w.cuda(), b.cuda()
+        torch.cuda.synchronize()
+        cudart.cudaMemcpy(base + off_x, xd.data_ptr(), T * d * 2, D2D)
+        kge.check(L.kge_tp_reduce_add_norm(comm, off_y, resd.data_ptr(), off_x, wd.data_ptr(), bd.data_ptr(), T, d, 1e-5, mode, None), "reduce")
+        torch.cuda.synchronize()
+        y = torch.empty(T, d, dtype=BF, device="cuda")
+        cudart.cudaMemcpy(y.data_ptr(), base + off_y, T * d * 2, D2D)
+        torch.cuda.synchronize()
+        hs = parts[0].float()
+        for p in parts[1:]:
+            hs = hs + p.float()                                               # rank order, as the kernel sums
+        h = hs.to(BF)
+        if mode == 1:
+            y_ref, res_ref = om.fused_add_rms_norm(h, res, w, 1e-5)
+        elif mode == 3:
+            res_ref = (res.float() + h.float()).to(BF)
+            y_ref = om.layer_norm(res_ref, w, b)
+        else:
+            y_ref, res_ref = h, res
+        rows_per = (T + world - 1) // world
+        r0, r1 = rank * rows_per, min(T, (rank + 1) * rows_per)
+        yd = (y.cpu().float() - y_ref.float()).abs()
+        ulp_bad = (yd > 1.6e-2 * y_ref.float().abs() + 1e-3).float().mean().item()
+        y_exact = (y.cpu().view(torch.int16) == y_ref.view(torch.int16)).float().mean().item()
+        res_ok = True if r1 <= r0 else torch.equal(resd.cpu()[r0:r1].view(torch.int16), res_ref[r0:r1].view(torch.int16))
+        results.append({"T": T, "d": d, "mode": mode, "y_bit_equal_frac": y_exact, "y_outside_tol_frac": ulp_bad, "own_residual_rows_exact": res_ok})
+    # all-gather of column shards
+    for (R, shard, short) in [(64, 504, 8), (3, 250, 3), (1, 8, 3)]:      # first case: 16-byte vector path
+        vocab = shard * world - short
+        cols = min(shard, vocab - rank * shard)
+        g = torch.Generator().manual_seed(77)
+        full = torch.randn(R, shard * world, generator=g).to(BF)
+        src = full[:, rank * shard: rank * shard + cols].contiguous().cuda()        # [R, cols], row stride = cols
+        torch.cuda.synchronize()
+        kge.check(L.kge_tp_all_gather_cols(comm, off_g, src.data_ptr(), R, cols, vocab, rank * shard, None), "gather")
+        torch.cuda.synchronize()
+        out = torch.empty(R, vocab, dtype=BF, device="cuda")
+        cudart.cudaMemcpy(out.data_ptr(), base + off_g, R * vocab * 2, D2D)
+        torch.cuda.synchronize()
+        ref = torch.cat([full[:, k * shard: k * shard + min(shard, vocab - k * shard)] for k in range(world)], 1)
+        results.append({"gather": [R, shard], "exact": bool(torch.equal(out.cpu().view(torch.int16), ref.view(torch.int16)))})
+    barrier(prefix, "done", rank, world)
+    L.kge_tp_comm_destroy(comm)
+    publish(prefix, "res", rank, json.dumps(results).encode())
+    if rank == 0:
+        allr = [json.loads(b) for b in collect(prefix, "res", world)]
+        ok = all((r.get("exact", True) and r.get("own_residual_rows_exact", True) and r.get("y_outside_tol_frac", 0) == 0
+                  and r.get("y_bit_equal_frac", 1) >= 0.995) for rr in allr for r in rr)
+        print(json.dumps({"ops": "ok" if ok else "MISMATCH", "tp": world, "per_rank": allr}))
+
+
+def main():
+    mode = sys.argv[1]
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    kge = load()
+    L = kge.lib()
+    torch.cuda.set_device(rank)
+    if mode == "ops":
+        ops_mode(kge, L, rank, world, sys.argv[2])
+    else:
+        engine_mode(kge, L, rank, world, sys.argv[2], sys.argv[3], sys.argv[4] if len(sys.argv) > 4 else "peer")
 
 
 if __name__ == "__main__":

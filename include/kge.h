@@ -38,6 +38,9 @@ int kge_device_sm_count(void);
  *                             (same bits; measured slower, so off by default)
  *   "gemm_shallow" 0/1        experiment: decode-sized GEMMs (T <= 64) as twice as many CTAs with half the shared memory
  *                             each (two per SM), so the next kernel's CTAs move in as this one's retire; off by default
+ *   "attn_tma" 1/0            attention K/V tiles fetched by the TMA unit (one producer thread, cp.async.bulk.tensor boxes
+ *                             of one KV block) instead of per-thread 16-byte cp.async gathers; 0 = the round-1 kernels, kept
+ *                             for same-box comparison and for block sizes below 8
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

@@ -9,10 +9,16 @@
 //   O_t = P V       tcgen05.mma, A = P, B = V tile as stored ([key][hd] = MN-major), D in TMEM [128,128+hd)
 //   O accumulates in TMEM across tiles; it is rescaled (tcgen05.ld / st) only when a row's running maximum has grown
 //   by more than 2^8 since its reference maximum was fixed (lazy rescale, see kRescaleThreshold below)
-// K/V tiles are gathered from the paged cache with cp.async (K two tiles ahead, V one; 16-byte chunks placed at
-// their 128B-swizzled positions, block-table lookup once per row), made visible to the tensor-core
-// (async) proxy with fence.proxy.async, and handed over with mbarriers; tcgen05.commit signals the
-// softmax warps.  Tensor-bound: 4 * hd * sum_b q_b (ctx0_b + (q_b+1)/2) flop per q head.
+// K/V tiles (TMA = true, the default): a producer thread fetches every tile from the paged cache with
+// cp.async.bulk.tensor.2d boxes of {64 columns, block_size rows} (the cache of a layer seen as a 2-D tensor [rows, hd],
+// 128-byte swizzle = the layout the MMA descriptors expect), two tiles ahead for K and for V, completion counted by
+// mbarriers; tcgen05.commit tells it when a stage is free.  The softmax warps issue no loads.
+// TMA = false (knob "attn_tma" 0, block sizes below 8): the round-1 path, tiles gathered by the softmax threads with
+// 16-byte cp.async (K two tiles ahead, V one; block-table lookup once per row) and published with fence.proxy.async.
+// Tensor-bound: 4 * hd * sum_b q_b (ctx0_b + (q_b+1)/2) flop per q head.
+#include <cuda.h>
+#include <string.h>
+
 #include "common.cuh"
 #include "kge.h"
 
@@ -38,6 +44,13 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
                  : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
     if (!ok && ++spins > kSpin) __trap();
   } while (!ok);
+}
+__device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile("cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
+               ::"r"(dst), "l"(map), "r"(bar), "r"(c0), "r"(c1) : "memory");
 }
 __device__ __forceinline__ void cp16(uint32_t dst, const void* src, bool valid) {
   const int sz = valid ? 16 : 0;
@@ -104,9 +117,10 @@ __device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32
 constexpr float kRescaleThreshold = 8.0f;
 __device__ __forceinline__ float ex2_ftz(float x) { float y; asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x)); return y; }
 
-template <int HD>
-__global__ void __launch_bounds__(160, 2)
-attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
+template <int HD, bool TMA>
+__global__ void __launch_bounds__(TMA ? 192 : 160, 2)
+attn_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
+               bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride, const bf16* __restrict__ k_cache,
                const bf16* __restrict__ v_cache, const int32_t* __restrict__ block_table, int max_blocks,
                const int32_t* __restrict__ seq_lens, const int32_t* __restrict__ qsl, int H, int KV, int bs_shift,
                float scale_log2) {
@@ -142,22 +156,29 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
   const uint32_t sV = sK + 2 * TILE_BYTES;         // 2 stages
   const uint32_t sP = sV + 2 * TILE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + Q_BYTES + 4 * TILE_BYTES + P_BYTES);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 12);
   const uint32_t bar0 = s_addr(bars);
-  // k_full[2], v_full[2], s_full[2], p_full, o_full
+  // k_full[2], v_full[2], s_full[2], p_full, o_full, q_full, v_empty[2]
   auto k_full = [&](int s) { return bar0 + 8u * s; };
   auto v_full = [&](int s) { return bar0 + 16u + 8u * s; };
   auto s_full = [&](int s) { return bar0 + 32u + 8u * s; };
-  const uint32_t p_full = bar0 + 48, o_full = bar0 + 56;
+  const uint32_t p_full = bar0 + 48, o_full = bar0 + 56, q_full = bar0 + 64;
+  auto v_empty = [&](int s) { return bar0 + 72u + 8u * s; };
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (warp == 4) {
     if (lane == 0) {
-      mbar_init(k_full(0), 128); mbar_init(k_full(1), 128);
-      mbar_init(v_full(0), 128); mbar_init(v_full(1), 128);
+      // TMA: the producer's expect_tx is the one arrival of a K/V barrier; cp.async: every loading thread arrives
+      mbar_init(k_full(0), TMA ? 1 : 128); mbar_init(k_full(1), TMA ? 1 : 128);
+      mbar_init(v_full(0), TMA ? 1 : 128); mbar_init(v_full(1), TMA ? 1 : 128);
       mbar_init(s_full(0), 1); mbar_init(s_full(1), 1);
       mbar_init(p_full, 128); mbar_init(o_full, 1);
+      mbar_init(q_full, 128); mbar_init(v_empty(0), 1); mbar_init(v_empty(1), 1);
       asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+      if (TMA) {
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
+        asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
+      }
     }
     __syncwarp();
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(s_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
@@ -188,6 +209,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         }
         tc_commit(s_full(st));
       };
+      if (TMA) { mbar_wait(q_full, 0u); tc_after(); }      // the Q tile (cp.async by the softmax threads) has landed
       issue_s(0);
       for (int j = 0; j < ntiles; ++j) {
         // S_{j+1} may overwrite S buffer (j+1)&1 = the buffer of S_{j-1}: the softmax warps finished
@@ -204,6 +226,39 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
           tc_mma(tmem + O_COL, desc_kmajor(sP + aoff), desc_mnmajor(vt + boff), IDESC_O, (j > 0 || k > 0) ? 1u : 0u);
         }
         tc_commit(o_full);
+        if (TMA) tc_commit(v_empty(j & 1));      // PV_j has read V stage j&1: the producer may refill it
+      }
+    }
+  } else if (warp == 5) {
+    // ------------------------------------------------------------------ TMA producer (TMA only: 192 threads)
+    if (lane == 0) {
+      const int bs = 1 << bs_shift;
+      const int box_rows = bs < BNK ? bs : BNK;
+      const int boxes = BNK / box_rows;
+      auto fetch = [&](int t, bool is_k) {
+        const int st = t & 1;
+        const uint32_t dst = (is_k ? sK : sV) + st * TILE_BYTES;
+        const uint32_t bar = is_k ? k_full(st) : v_full(st);
+        mbar_expect_tx(bar, TILE_BYTES);
+        for (int i = 0; i < boxes; ++i) {
+          const int key = t * BNK + i * box_rows;
+          const int bi = key >> bs_shift;
+          const int blk = bi < max_blocks ? btab[bi] : 0;      // past the table: block 0 (those keys are masked)
+          const int row = (blk * KV + kvh) * bs + (key & (bs - 1));
+#pragma unroll
+          for (int h = 0; h < HD / 64; ++h)
+            tma_load_2d(dst + (uint32_t)(h * (BNK * 128) + i * box_rows * 128), is_k ? &tm_k : &tm_v, bar, h * 64, row);
+        }
+      };
+      fetch(0, true);
+      if (ntiles > 1) fetch(1, true);
+      fetch(0, false);
+      if (ntiles > 1) fetch(1, false);
+      for (int j = 0; j + 2 < ntiles; ++j) {
+        mbar_wait(s_full(j & 1), (uint32_t)((j >> 1) & 1));      // S_j done: K stage j&1 is free
+        fetch(j + 2, true);
+        mbar_wait(v_empty(j & 1), (uint32_t)((j >> 1) & 1));     // PV_j done: V stage j&1 is free
+        fetch(j + 2, false);
       }
     }
   } else {
@@ -243,14 +298,21 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
       const bf16* src = ok ? q + (int64_t)(q0 + tok0 + t2) * q_stride + (kvh * G + h2) * HD + lc * 8 : q;
       cp16(sQ + tile_off<128>(row, lc), src, ok);
     }
-    // commit order K0 | K1 | V0 | K2 | V1 | K3 | V2 ...: whenever a tile is published, exactly two
-    // younger groups may still be in flight
-    load_tile(0, true);        // group 0: Q + K0 (what S_0 needs)
-    load_tile(1, true);        // group 1: K1
-    load_tile(0, false);       // group 2: V0
-    cp_wait<2>();              // group 0 landed
-    fence_async_smem();
-    mbar_arrive(k_full(0));
+    if (TMA) {
+      cp_commit();
+      cp_wait<0>();              // this thread's part of the Q tile
+      fence_async_smem();
+      mbar_arrive(q_full);
+    } else {
+      // commit order K0 | K1 | V0 | K2 | V1 | K3 | V2 ...: whenever a tile is published, exactly two
+      // younger groups may still be in flight
+      load_tile(0, true);        // group 0: Q + K0 (what S_0 needs)
+      load_tile(1, true);        // group 1: K1
+      load_tile(0, false);       // group 2: V0
+      cp_wait<2>();              // group 0 landed
+      fence_async_smem();
+      mbar_arrive(k_full(0));
+    }
 
     float m_ref = -INFINITY, l = 0.f;
     const uint32_t t_row = tmem + ((uint32_t)(warp * 32) << 16);
@@ -258,9 +320,11 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
     for (int j = 0; j < ntiles; ++j) {
       mbar_wait(s_full(j & 1), (uint32_t)((j >> 1) & 1));
       tc_after();
-      // S_j is complete, so K stage j&1 is free: fetch K_{j+2}; then publish K_{j+1} (two groups back)
-      load_tile(j + 2, true);
-      if (j + 1 < ntiles) { cp_wait<2>(); fence_async_smem(); mbar_arrive(k_full((j + 1) & 1)); }
+      if (!TMA) {
+        // S_j is complete, so K stage j&1 is free: fetch K_{j+2}; then publish K_{j+1} (two groups back)
+        load_tile(j + 2, true);
+        if (j + 1 < ntiles) { cp_wait<2>(); fence_async_smem(); mbar_arrive(k_full((j + 1) & 1)); }
+      }
       const int kbase = j * BNK;
       uint32_t sv[BNK];
 #pragma unroll
@@ -268,22 +332,25 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
       // The softmax warps are issue-bound: keep the per-score work to max, one FMA, one MUFU, one add.  Scores stay
       // unscaled (scale > 0 keeps the order); the scale is folded into the exponent's FMA.  Only tiles that reach
       // past some row's last visible key (the diagonal) pay for masking.
-      float mx_raw = -INFINITY;
+      // four independent running maxima (and, below, sums): with two softmax warps per scheduler there is little
+      // else to hide the latency of a 64-long dependent chain behind
+      float mxa[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
       if (__all_sync(0xffffffffu, kbase + BNK - 1 <= lim)) {
 #pragma unroll
-        for (int i = 0; i < BNK; ++i) mx_raw = fmaxf(mx_raw, __uint_as_float(sv[i]));
+        for (int i = 0; i < BNK; ++i) mxa[i & 3] = fmaxf(mxa[i & 3], __uint_as_float(sv[i]));
       } else {
 #pragma unroll
         for (int i = 0; i < BNK; ++i) {
           const float x = (kbase + i <= lim) ? __uint_as_float(sv[i]) : -INFINITY;
           sv[i] = __float_as_uint(x);
-          mx_raw = fmaxf(mx_raw, x);
+          mxa[i & 3] = fmaxf(mxa[i & 3], x);
         }
       }
+      const float mx_raw = fmaxf(fmaxf(mxa[0], mxa[1]), fmaxf(mxa[2], mxa[3]));
       const float mx = mx_raw * scale_log2;                     // -inf stays -inf
       // PV_{j-1} must be done before O is rescaled, sP is overwritten or V stage (j+1)&1 is refilled
       if (j > 0) { mbar_wait(o_full, (uint32_t)((j - 1) & 1)); tc_after(); }
-      load_tile(j + 1, false);
+      if (!TMA) load_tile(j + 1, false);
       const bool grow = mx > m_ref + kRescaleThreshold;        // includes the first finite maximum
       if (__any_sync(0xffffffffu, grow)) {
         float alpha = 1.f;
@@ -304,7 +371,7 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         }
       }
       const float base = (m_ref == -INFINITY) ? 0.f : m_ref;
-      float rs = 0.f;
+      float rsa[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int c8 = 0; c8 < BNK / 8; ++c8) {
         uint32_t pk[4];
@@ -312,20 +379,20 @@ attn_tc_kernel(bf16* __restrict__ out, const bf16* __restrict__ q, int q_stride,
         for (int i = 0; i < 4; ++i) {
           const float p0 = ex2_ftz(fmaf(__uint_as_float(sv[c8 * 8 + i * 2]), scale_log2, -base));       // masked: -inf -> 0
           const float p1 = ex2_ftz(fmaf(__uint_as_float(sv[c8 * 8 + i * 2 + 1]), scale_log2, -base));
-          rs += p0 + p1;
+          rsa[i] += p0 + p1;
           pk[i] = pack_bf2(p0, p1);
         }
         const uint32_t dst = sP + tile_off<128>(r, c8);
         asm volatile("st.shared.v4.b32 [%0], {%1,%2,%3,%4};" ::"r"(dst), "r"(pk[0]), "r"(pk[1]), "r"(pk[2]), "r"(pk[3]) : "memory");
       }
-      l += rs;
-      cp_wait<2>();                       // V_j (committed one tile ago) has landed
-      fence_async_smem();                 // P and V_j bytes -> tensor-core proxy
+      l += (rsa[0] + rsa[1]) + (rsa[2] + rsa[3]);
+      if (!TMA) cp_wait<2>();             // V_j (committed one tile ago) has landed
+      fence_async_smem();                 // P (and, cp.async path, V_j) bytes -> tensor-core proxy
       tc_before();                        // my TMEM reads/writes are ordered before the MMAs that follow
-      mbar_arrive(v_full(j & 1));
+      if (!TMA) mbar_arrive(v_full(j & 1));
       mbar_arrive(p_full);
     }
-    cp_wait<0>();
+    if (!TMA) cp_wait<0>();
     mbar_wait(o_full, (uint32_t)((ntiles - 1) & 1));
     tc_after();
     {
@@ -362,6 +429,8 @@ template <int HD> constexpr int tc_smem() { return 128 * HD * 2 + 4 * BNK * HD *
 
 }  // namespace atc
 
+int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows);   // gemm_tc.cu (cached)
+
 template <int HD>
 static int launch_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc, const bf16* vc, const int32_t* bt,
                      int max_blocks, const int32_t* sl, const int32_t* qsl, int B, int max_q_len, int H, int KV, int bs,
@@ -370,9 +439,23 @@ static int launch_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc, con
   while ((1 << bs_shift) < bs) ++bs_shift;
   const int G = H / KV;
   const int TT = atc::BM / G;
-  auto kern = atc::attn_tc_kernel<HD>;
+  CUtensorMap tk, tv;
+  const bool tma = tunable(TUN_ATTN_TMA) != 0 && bs >= 8;
+  if (tma) {
+    const int box_rows = bs < atc::BNK ? bs : atc::BNK;
+    const int64_t rows = (int64_t)1 << 30;      // the pool's extent is not known here; it only bounds out-of-range handling, never relied on
+    if (int rc = make_tmap(&tk, kc, rows, HD, box_rows)) return rc;
+    if (int rc = make_tmap(&tv, vc, rows, HD, box_rows)) return rc;
+    auto kern = atc::attn_tc_kernel<HD, true>;
+    KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::tc_smem<HD>()));
+    KGE_CUDA_OK(launch_pdl(kern, dim3((max_q_len + TT - 1) / TT, KV, B), dim3(192), atc::tc_smem<HD>(), st, tk, tv, out, q, q_stride,
+                           kc, vc, bt, max_blocks, sl, qsl, H, KV, bs_shift, scale * atc::kLog2e));
+    return 0;
+  }
+  memset(&tk, 0, sizeof tk); memset(&tv, 0, sizeof tv);
+  auto kern = atc::attn_tc_kernel<HD, false>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, atc::tc_smem<HD>()));
-  KGE_CUDA_OK(launch_pdl(kern, dim3((max_q_len + TT - 1) / TT, KV, B), dim3(160), atc::tc_smem<HD>(), st, out, q, q_stride, kc,
+  KGE_CUDA_OK(launch_pdl(kern, dim3((max_q_len + TT - 1) / TT, KV, B), dim3(160), atc::tc_smem<HD>(), st, tk, tv, out, q, q_stride, kc,
                          vc, bt, max_blocks, sl, qsl, H, KV, bs_shift, scale * atc::kLog2e));
   return 0;
 }

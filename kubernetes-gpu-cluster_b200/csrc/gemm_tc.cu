@@ -465,7 +465,7 @@ struct TmapKeyHash {
     return (size_t)(h ^ (h >> 29));
   }
 };
-static int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
+int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows) {
   static std::mutex mu;
   static std::unordered_map<TmapKey, CUtensorMap, TmapKeyHash> cache;
   const TmapKey key{ptr, rows, cols, box_rows};

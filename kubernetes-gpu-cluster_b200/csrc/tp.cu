@@ -54,13 +54,15 @@ int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n) {
   return 0;
 }
 
-// [tp][R][shard] (what ncclAllGather delivers) -> logits [R][vocab]
+// What ncclAllGather delivers - rank k's block at [k][R * shard], holding its [R, cols_k] logits densely (cols_k = the
+// columns rank k really has: the last rank's shard may be narrower) - laid out as logits [R][vocab].
 __global__ void reorder_logits_kernel(bf16* __restrict__ dst, const bf16* __restrict__ src, int R, int shard, int vocab, int tp) {
-  const int64_t n = (int64_t)tp * R * shard;
+  const int64_t n = (int64_t)R * vocab;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
-    const int c = (int)(i % shard), r = (int)((i / shard) % R), k = (int)(i / ((int64_t)shard * R));
-    const int col = k * shard + c;
-    if (col < vocab) dst[(int64_t)r * vocab + col] = src[i];
+    const int col = (int)(i % vocab), r = (int)(i / vocab);
+    const int k = col / shard, c = col - k * shard;
+    const int cols_k = min(shard, vocab - k * shard);
+    dst[i] = src[(int64_t)k * R * shard + (int64_t)r * cols_k + c];
   }
 }
 

@@ -466,20 +466,47 @@ DECODE_SPLIT_CASES = [
 
 
 @pytest.mark.parametrize("H,KV,hd,q_lens,seq_lens,splits", DECODE_SPLIT_CASES)
-def test_decode_attention_cluster_merge_equals_workspace_merge(kge, L, H, KV, hd, q_lens, seq_lens, splits):
-    """Split-KV partials merged inside a thread-block cluster over DSMEM (opt-in knob) must give the same BITS as the
-    default workspace + merge-kernel path, and both must match the oracle."""
+def test_decode_attention_variants_give_the_same_bits(kge, L, H, KV, hd, q_lens, seq_lens, splits):
+    """Three ways to stage K/V and merge the split-KV partials - TMA boxes + merge by the last CTA (default), per-thread
+    cp.async + merge kernel (knob attn_tma 0), cp.async + cluster/DSMEM merge (attn_cluster_merge 1) - run the same
+    arithmetic in the same order: they must give the same BITS, and each must match the oracle."""
     seed = H * 7 + sum(seq_lens) + splits
     try:
         check_ok(kge, L.kge_set_tunable(b"attn_decode_splits", splits), "tunable")
-        check_ok(kge, L.kge_set_tunable(b"attn_cluster_merge", 1), "tunable")
         a = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)
-        check_ok(kge, L.kge_set_tunable(b"attn_cluster_merge", 0), "tunable")
+        a2 = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)        # arrival counters were reset by the first launch
+        check_ok(kge, L.kge_set_tunable(b"attn_tma", 0), "tunable")
         b = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)
+        check_ok(kge, L.kge_set_tunable(b"attn_cluster_merge", 1), "tunable")
+        c = run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed)
     finally:
         L.kge_set_tunable(b"attn_decode_splits", 0)
         L.kge_set_tunable(b"attn_cluster_merge", 0)
+        L.kge_set_tunable(b"attn_tma", 1)
+    for other in (a2, b, c):
+        assert torch.equal(a.view(torch.int16), other.view(torch.int16))
+
+
+@pytest.mark.parametrize("H,KV,hd,bs,q_lens,seq_lens", [c for c in ATTN_CASES if max(c[4]) > 1][:5] + [ATTN_LONG_CASES[2][:3] + (16,) + ATTN_LONG_CASES[2][3:5]])
+def test_prefill_attention_tma_and_cp_async_agree(kge, L, H, KV, hd, bs, q_lens, seq_lens):
+    """The tcgen05 prefill kernel with TMA-staged K/V (default) and with the round-1 cp.async gathers computes the same
+    tiles in the same order: same bits."""
+    seed = H * 13 + sum(seq_lens)
+    try:
+        a = run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed)
+        check_ok(kge, L.kge_set_tunable(b"attn_tma", 0), "tunable")
+        b = run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed)
+    finally:
+        L.kge_set_tunable(b"attn_tma", 1)
     assert torch.equal(a.view(torch.int16), b.view(torch.int16))
+
+
+def test_attention_block_sizes(kge, L):
+    """Block sizes from 8 (one TMA box per block, eight boxes per tile) to 128 (two tiles per block) and 4 (below the TMA
+    box granularity: cp.async path), decode and prefill."""
+    for bs in (4, 8, 32, 64, 128):
+        run_attn_case(kge, L, 8, 2, 128, bs, [1, 1, 1], [700, 129, 64], seed=bs)
+        run_attn_case(kge, L, 8, 2, 64, bs, [150, 1, 40], [150, 300, 200], seed=bs + 1)
 
 
 # ------------------------------------------------------------------------------ sampling

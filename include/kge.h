@@ -41,6 +41,8 @@ int kge_device_sm_count(void);
  *   "attn_tma" 1/0            attention K/V tiles fetched by the TMA unit (one producer thread, cp.async.bulk.tensor boxes
  *                             of one KV block) instead of per-thread 16-byte cp.async gathers; 0 = the round-1 kernels, kept
  *                             for same-box comparison and for block sizes below 8
+ *   "gemm_ws" 1/0             decode-sized projections split K over ordinary CTAs, two per SM, reduced through the caller's
+ *                             workspace by the last CTA to arrive; 0 = always the cluster / distributed-shared-memory split
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 
@@ -79,7 +81,12 @@ int kge_silu_mul(void* y, const void* x, int T, int f, void* stream);
  * one rounding.  act: 0 none, 1 relu.  Replaces F.linear in QKV/O/MLP/LM-head
  * (vllm:model_executor/models/llama.py:94-121,164-180; opt.py:92-106,151-165;
  * layers/logits_processor.py:89-99).  tcgen05/TMEM/TMA kernel; K % 8 == 0 (16-byte rows; a partial last
- * 64-wide k-block is zero-filled by TMA), x and w 16-byte aligned.  `workspace` (>= kge_gemm_workspace_bytes) is device scratch for split-K. */
+ * 64-wide k-block is zero-filled by TMA), x and w 16-byte aligned.
+ * `workspace`: optional device scratch of >= kge_gemm_workspace_bytes(T, N, K) bytes, 16-byte aligned, whose first
+ * 1024 bytes are ZERO before the first call that uses it (arrival counters; every call leaves them zero again).  With it,
+ * decode-sized shapes split K over two CTAs per SM and reduce through the scratch; without it (NULL, or too small) they
+ * split K inside a thread-block cluster.  Same results either way up to fp32 summation order.  Calls that share one
+ * workspace must not overlap on the GPU. */
 int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                   int act, void* workspace, int64_t workspace_bytes, void* stream);
 int64_t kge_gemm_workspace_bytes(int T, int N, int K);

@@ -81,7 +81,7 @@ __device__ __forceinline__ uint32_t swz_kv(int key, int c /* 16-byte chunk of th
   return (uint32_t)((c >> 3) * (BN * 128) + key * 128 + (((c & 7) ^ (key & 7)) << 4));
 }
 
-// grid (splits, KV, B); 160 threads: warps 0-3 compute, warp 4 = TMA producer (one lane).
+// grid (splits, KV, B); 160 threads: warps 0-3 compute, warp 4 = TMA producer.
 template <int HD>
 __global__ void __launch_bounds__(160, 2)
 attn_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v,
@@ -139,27 +139,41 @@ attn_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_co
   const int g = lane >> 2, tg = lane & 3;
 
   if (warp == 4) {
-    // ---------------------------------------------------------------- producer
-    if (lane == 0) {
-      const int32_t* btab = block_table + (int64_t)b * max_blocks;
-      const int bs = 1 << bs_shift;
-      const int box_rows = bs < BN ? bs : BN;
-      const int boxes = BN / box_rows;
-      for (int kt = t_begin; kt < t_end; ++kt) {
-        const int it = kt - t_begin, st = it % kStages;
+    // ---------------------------------------------------------------- producer (the whole warp)
+    // Block ids are read 32 at a time, one per lane (a coalesced 128-byte load, the next 32 already in flight), and
+    // handed out by shuffle; lane j issues the boxes of block j of the tile.  A single thread that loads one table entry,
+    // waits for it and issues one block's boxes, eight times per tile, cannot keep three stages full.
+    const int32_t* btab = block_table + (int64_t)b * max_blocks;
+    const int bs = 1 << bs_shift;
+    const int box_rows = bs < BN ? bs : BN;
+    const int boxes = BN / box_rows;
+    auto ld_blk = [&](int bi) { return (bi >= 0 && bi < max_blocks) ? btab[bi] : 0; };   // past the table: block 0 (masked keys)
+    int cbase = (t_begin * BN) >> bs_shift;
+    int v = ld_blk(cbase + lane), v_next = ld_blk(cbase + 32 + lane);
+    for (int kt = t_begin; kt < t_end; ++kt) {
+      const int it = kt - t_begin, st = it % kStages;
+      const int key = kt * BN + (lane < boxes ? lane : 0) * box_rows;      // first key of this lane's box
+      const int bi = key >> bs_shift;
+      const int bi_last = (kt * BN + (boxes - 1) * box_rows) >> bs_shift;
+      if (bi_last >= cbase + 32) {                                         // warp-uniform: the tile leaves the held chunk
+        const int nb = (kt * BN) >> bs_shift;
+        if (nb == cbase + 32) { v = v_next; } else { v = ld_blk(nb + lane); }
+        cbase = nb;
+        v_next = ld_blk(cbase + 32 + lane);
+      }
+      const int blk = __shfl_sync(0xffffffffu, v, (bi - cbase) & 31);
+      if (lane == 0) {
         if (it >= kStages) mbar_wait(empty(st), (uint32_t)((it / kStages - 1) & 1));
         mbar_expect_tx(full(st), 2 * TILE);
-        for (int j = 0; j < boxes; ++j) {
-          const int key = kt * BN + j * box_rows;
-          const int bi = key >> bs_shift;
-          const int blk = bi < max_blocks ? btab[bi] : 0;
-          const int row = (blk * KV + kvh) * bs + (key & (bs - 1));
+      }
+      __syncwarp();
+      if (lane < boxes) {
+        const int row = (blk * KV + kvh) * bs + (key & (bs - 1));
 #pragma unroll
-          for (int h = 0; h < HD / 64; ++h) {
-            const uint32_t off = (uint32_t)(h * (BN * 128) + j * box_rows * 128);
-            tma_load_2d(sK + st * TILE + off, &tm_k, full(st), h * 64, row);
-            tma_load_2d(sV + st * TILE + off, &tm_v, full(st), h * 64, row);
-          }
+        for (int h = 0; h < HD / 64; ++h) {
+          const uint32_t off = (uint32_t)(h * (BN * 128) + lane * box_rows * 128);
+          tma_load_2d(sK + st * TILE + off, &tm_k, full(st), h * 64, row);
+          tma_load_2d(sV + st * TILE + off, &tm_v, full(st), h * 64, row);
         }
       }
     }

@@ -16,6 +16,11 @@
 // through distributed shared memory (st.shared::cluster): CTA r receives column slice r of every
 // peer, sums the S partials in rank order (deterministic), adds bias, rounds once and stores.
 // No global scratch, no atomics, no serial tail; the cluster guarantees co-scheduling.
+// Split-K through a workspace (WS; decode-sized projections when the caller provides scratch): the S CTAs of a tile are
+// ordinary CTAs with HALF an SM's shared memory each, so two are resident per SM and one CTA's prologue and epilogue
+// overlap the other's weight streaming (a 1-CTA-per-SM kernel leaves HBM idle for ~8 us per launch, profiles/
+// r02_ncu_full_gemm_split_*.csv).  fp32 partials go to the workspace (they stay in L2), and the CTA that arrives LAST on
+// the tile's counter sums them in split order (deterministic), adds bias, rounds once and stores.
 //
 // Roofline: decode T<=256 -> HBM, algorithmic bytes = N*K*2 (weights) + T*(K+N)*2;
 //           prefill        -> tensor, 2*T*N*K flop.
@@ -89,6 +94,8 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
 struct GemmParams {
   bf16* y;
   const bf16* bias;
+  float* ws_part;            // WS: [tile][split][token column][128 rows] fp32 partial accumulators
+  unsigned int* ws_count;    // WS: per-tile arrival counters (zero before the first launch; the reducing CTA resets its own)
   int T, N, K, act;
   int m_tiles, n_tiles, splits, kb_total, kb_per_split;
 };
@@ -140,11 +147,11 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
 // All TMA loads of a stage complete on the LEADER's full barrier; tcgen05.commit multicasts the
 // "stage free" and "accumulator ready" arrivals to both CTAs; both epilogues release the accumulator
 // on the leader's tmem_empty barrier.
-template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool PAIR = false>
-__global__ void __launch_bounds__(kGemmThreads, 1)
+template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool PAIR = false, bool WS = false>
+__global__ void __launch_bounds__(kGemmThreads, WS ? 2 : 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
-  static_assert(!(PAIR && SPLIT), "one cluster scheme at a time");
+  static_assert(!(PAIR && SPLIT) && !(WS && (SPLIT || PAIR || GATED)), "one split scheme at a time");
   constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = (PAIR ? 128 : TOKN) * BLK_K * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
@@ -197,13 +204,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
 
   // work decomposition: persistent round-robin over tiles, or (SPLIT) one tile per cluster with
   // the cluster rank selecting the K range
-  const int S = SPLIT ? (int)cluster_nctarank() : 1;
-  const int crank = SPLIT ? (int)cluster_ctarank() : 0;
+  const int S = SPLIT ? (int)cluster_nctarank() : WS ? p.splits : 1;
+  const int crank = SPLIT ? (int)cluster_ctarank() : WS ? (int)blockIdx.x % p.splits : 0;
   constexpr bool TWO = PAIR;
   const int mrank = TWO ? (int)cluster_ctarank() : 0;            // which tile of the weight-row pair
   const int total = (TWO ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
-  const int w_first = SPLIT ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
-  const int w_step = SPLIT ? (1 << 30) : TWO ? (int)gridDim.x / 2 : (int)gridDim.x;
+  const int w_first = (SPLIT || WS) ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int w_step = (SPLIT || WS) ? (1 << 30) : TWO ? (int)gridDim.x / 2 : (int)gridDim.x;
   auto m_tile_of = [&](int w) { return TWO ? 2 * (w / p.n_tiles) + mrank : w / p.n_tiles; };
   // PAIR: every TMA of a stage completes on the leader's (rank 0) full barrier
   auto lead_full = [&](int s) { return PAIR ? mapa_u32(full_bar(s), 0u) : full_bar(s); };
@@ -315,7 +322,19 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
       const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
-      if (!SPLIT && !GATED) {
+      if (WS) {
+        // this split's fp32 partial tile -> workspace, [column][128 rows]: a warp stores 128 consecutive bytes per column
+        float* part = p.ws_part + ((int64_t)(w * S + crank) * TOKN) * BLK_M;
+#pragma unroll 1
+        for (int c = 0; c < TOKN; c += 16) {
+          uint32_t r[16];
+          tmem_ld16(taddr + c, r);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) part[(c + j) * BLK_M + et] = __uint_as_float(r[j]);
+        }
+        tc_fence_before();
+        __threadfence();                         // the partial is visible device-wide before this CTA arrives on the counter
+      } else if (!SPLIT && !GATED) {
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
           uint32_t r[16];
@@ -409,6 +428,54 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     cluster_arrive();
     cluster_wait();
   }
+  if (WS) {
+    // Whichever CTA of the tile arrives last reduces it, with all 256 threads: thread = (4 consecutive weight rows,
+    // TOKN/8 token columns); partials are summed in split order, so the result does not depend on who came last.
+    int* s_last = reinterpret_cast<int*>(tmem_slot + 1);
+    __syncthreads();
+    if (threadIdx.x == 0) *s_last = (atomicAdd(p.ws_count + w_first, 1u) == (unsigned)S - 1u) ? 1 : 0;
+    __syncthreads();
+    if (*s_last) {
+      __threadfence();
+      constexpr int CPG = TOKN / 8;
+      const int quad = threadIdx.x & 31, grp = threadIdx.x >> 5;
+      const int m_tile = w_first / p.n_tiles, n_tile = w_first % p.n_tiles;
+      const int n0 = m_tile * BLK_M + quad * 4, t0 = n_tile * TOKN, c0 = grp * CPG;
+      float acc[CPG][4];
+#pragma unroll
+      for (int ci = 0; ci < CPG; ++ci) { acc[ci][0] = acc[ci][1] = acc[ci][2] = acc[ci][3] = 0.f; }
+      const float* base = p.ws_part + ((int64_t)w_first * S * TOKN + c0) * BLK_M + quad * 4;
+      for (int s2 = 0; s2 < S; ++s2) {
+#pragma unroll
+        for (int ci = 0; ci < CPG; ++ci) {
+          const float4 v = __ldcg(reinterpret_cast<const float4*>(base + ((int64_t)s2 * TOKN + ci) * BLK_M));
+          acc[ci][0] += v.x; acc[ci][1] += v.y; acc[ci][2] += v.z; acc[ci][3] += v.w;
+        }
+      }
+      float bv4[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) bv4[k] = (p.bias && n0 + k < p.N) ? bf2f(p.bias[n0 + k]) : 0.f;
+      const bool vec = (p.N & 3) == 0 && n0 + 3 < p.N;
+#pragma unroll
+      for (int ci = 0; ci < CPG; ++ci) {
+        const int t = t0 + c0 + ci;
+        if (t >= p.T) break;
+        float o[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { o[k] = acc[ci][k] + bv4[k]; if (p.act == 1) o[k] = fmaxf(o[k], 0.f); }
+        bf16* dst = p.y + (int64_t)t * p.N + n0;
+        if (vec) {
+          uint2 w2;
+          w2.x = pack_bf2(o[0], o[1]); w2.y = pack_bf2(o[2], o[3]);
+          *reinterpret_cast<uint2*>(dst) = w2;
+        } else {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) if (n0 + k < p.N) dst[k] = f2bf(o[k]);
+        }
+      }
+      if (threadIdx.x == 0) p.ws_count[w_first] = 0;      // ready for the next launch
+    }
+  }
   tc_fence_before();
   __syncthreads();
   if (PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
@@ -487,8 +554,9 @@ constexpr int gemm_smem_budget(bool shallow) { return shallow ? 112 * 1024 : 224
 static bool gemm_shallow(int tokn) { return tunable(TUN_GEMM_SHALLOW) != 0 && tokn <= 64; }
 constexpr int kSlotsShallow = 2 * 148;
 
-template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool SHALLOW = false>
+template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool SHALLOW = false, bool WS = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  static_assert(!WS || SHALLOW, "the workspace split runs two CTAs per SM");
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
   constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
@@ -496,7 +564,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
-  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, PAIR>;
+  auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, PAIR, WS>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
@@ -507,7 +575,9 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
   attr[0].val.programmaticStreamSerializationAllowed = pdl_for_this_launch() ? 1 : 0;
   cfg.attrs = attr; cfg.numAttrs = 1;
-  if (SPLIT) {
+  if (WS) {
+    cfg.gridDim = dim3(tiles * p.splits);        // CTA = (tile, split), no cluster: CTAs are placed wherever a half SM is free
+  } else if (SPLIT) {
     cfg.gridDim = dim3(tiles * p.splits);
     attr[1].id = cudaLaunchAttributeClusterDimension;
     attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
@@ -569,10 +639,14 @@ static int max_clusters(int tokn, int S) {
   return cache[sh][ti][S];
 }
 
-struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; };
+struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; bool ws; };
 
-static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
+constexpr int64_t kWsCounterBytes = 1024;        // per-tile arrival counters at the head of the workspace (<= 256 tiles)
+
+// ws_ok: the caller can provide a workspace, so split-K may go through it (two CTAs per SM) instead of a cluster
+static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M, bool ws_ok = false) {
   GemmPlan g;
+  g.ws = false;
   g.tokn = T <= 16 ? 16 : T <= 32 ? 32 : T <= 64 ? 64 : T <= 128 ? 128 : 256;
   g.m_tiles = (N + rows_out - 1) / rows_out;
   g.n_tiles = (T + g.tokn - 1) / g.tokn;
@@ -580,7 +654,15 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M) {
   const int tiles = g.m_tiles * g.n_tiles;
   int splits = 1;
   const int slots = gemm_shallow(g.tokn) ? kSlotsShallow : 148;      // CTAs that can be resident at once
-  if (tiles <= slots / 2 && g.tokn <= 128) {
+  if (ws_ok && rows_out == BLK_M && g.tokn <= 128 && tiles <= 148 && tunable(TUN_GEMM_WS)) {
+    // about two CTAs per SM in one wave, each with at least 4 k-blocks (256 of K)
+    int s = kSlotsShallow / tiles;
+    const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;
+    if (s > max_by_k) s = max_by_k;
+    if (s > 32) s = 32;
+    if (s >= 2) { g.ws = true; splits = s; }
+  }
+  if (!g.ws && tiles <= slots / 2 && g.tokn <= 128) {
     int smax = slots / tiles;                   // never more CTAs than resident slots
     const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
     if (smax > max_by_k) smax = max_by_k;
@@ -598,6 +680,16 @@ static bool gemm_uses_pair(const GemmPlan& g) { return g.tokn == 256 && g.splits
 
 template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  if constexpr (!GATED) {
+    if (g.ws) {
+      switch (g.tokn) {
+        case 16: return launch_gemm<16, false, false, false, true, true>(tw, tx, p, st);
+        case 32: return launch_gemm<32, false, false, false, true, true>(tw, tx, p, st);
+        case 64: return launch_gemm<64, false, false, false, true, true>(tw, tx, p, st);
+        default: return launch_gemm<128, false, false, false, true, true>(tw, tx, p, st);
+      }
+    }
+  }
   if (gemm_shallow(g.tokn)) {
     if (g.splits > 1) {
       switch (g.tokn) {
@@ -635,22 +727,29 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
 
 using namespace kge;
 
+static int64_t ws_bytes_of(const GemmPlan& g) {
+  return g.ws ? kWsCounterBytes + (int64_t)g.m_tiles * g.n_tiles * g.splits * g.tokn * BLK_M * 4 : 0;
+}
+
 extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
-  (void)T; (void)N; (void)K;
-  return 0;   // split-K partials are exchanged through distributed shared memory
+  if (T <= 0 || N <= 0 || K <= 0) return 0;
+  return ws_bytes_of(plan_gemm(T, N, K, BLK_M, true));      // 0: this shape does not split K through a workspace
 }
 
 extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                              int act, void* workspace, int64_t workspace_bytes, void* stream) {
-  (void)workspace; (void)workspace_bytes;
   KGE_REQUIRE(y && x && w, "kge_gemm_bf16: null pointer");
   KGE_REQUIRE(T >= 0 && N > 0 && K > 0 && K % 8 == 0, "kge_gemm_bf16: K=%d must be a positive multiple of 8", K);
   KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kge_gemm_bf16: x and w must be 16-byte aligned");
   KGE_REQUIRE(act == 0 || act == 1, "kge_gemm_bf16: act=%d unsupported", act);
   if (T == 0) return 0;
-  const GemmPlan g = plan_gemm(T, N, K);
+  GemmPlan g = plan_gemm(T, N, K, BLK_M, workspace != nullptr);
+  if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0 || g.m_tiles * g.n_tiles > (int)(kWsCounterBytes / 4)))
+    g = plan_gemm(T, N, K);                        // scratch too small for this shape: split K inside a cluster instead
   GemmParams p;
   p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
+  p.ws_count = g.ws ? (unsigned int*)workspace : nullptr;
+  p.ws_part = g.ws ? (float*)((uint8_t*)workspace + kWsCounterBytes) : nullptr;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
@@ -670,6 +769,7 @@ extern "C" int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gat
   const GemmPlan g = plan_gemm(T, f, K, 64);
   GemmParams p;
   p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
+  p.ws_count = nullptr; p.ws_part = nullptr;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;

@@ -294,6 +294,31 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
         assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 3e-3
 
 
+@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 128])
+def test_gemm_split_k_variants_agree(kge, L, T, N, K, bias, act):
+    """Decode-sized shapes split K two ways - through the caller's workspace (two CTAs per SM, last CTA reduces) or, with no
+    workspace, inside a thread-block cluster over distributed shared memory.  Both sum fp32 partials in a fixed order, so
+    each is deterministic; they differ from each other only by that order (<= 1 bf16 ulp on a few outputs).  A workspace
+    that is too small must fall back to the cluster split, not fail."""
+    g = torch.Generator().manual_seed(T + N + K)
+    x = dev(torch.randn(T, K, generator=g).to(BF))
+    w = dev((torch.randn(N, K, generator=g) * 0.05).to(BF))
+    b = dev(torch.randn(N, generator=g).to(BF)) if bias else None
+    nws = L.kge_gemm_workspace_bytes(T, N, K)
+    ws = torch.zeros(max(nws, 16), dtype=torch.uint8, device="cuda")
+    outs = []
+    for (wsp, nb) in ((p(ws), nws), (p(ws), nws), (None, 0), (p(ws), 2048 if nws > 2048 else 0)):
+        y = torch.full((T, N), float("nan"), dtype=BF, device="cuda")
+        check_ok(kge, L.kge_gemm_bf16(p(y), p(x), p(w), p(b) if bias else None, T, N, K, act, wsp, nb, None), "gemm")
+        sync()
+        outs.append(y.cpu())
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))          # workspace path: same bits every time
+    assert torch.equal(outs[2].view(torch.int16), outs[3].view(torch.int16))          # too-small scratch == no scratch
+    assert int(ws[:1024].max().item()) == 0                                            # the counters were left at zero
+    d = (outs[0].float() - outs[2].float()).abs()
+    assert (d <= 1.6e-2 * outs[2].float().abs() + 1e-3 * outs[2].float().abs().max()).all()
+
+
 EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
                                   reason="default-off experiments prepared for the next round; set KGE_TEST_EXPERIMENTAL=1 to run them")
 
@@ -342,7 +367,9 @@ def test_gemm_rejects_bad_arguments(kge, L):
     assert L.kge_gemm_bf16(p(x), None, p(x), None, 4, 4, 64, 0, None, 0, None) == -1       # null x
     assert L.kge_gemm_bf16(p(x), p(x), p(x), None, 4, 4, 64, 7, None, 0, None) == -1       # unknown act
     assert b"act" in L.kge_last_error()
-    assert L.kge_gemm_workspace_bytes(1, 768, 4096) == 0        # split-K goes through cluster shared memory
+    assert L.kge_gemm_workspace_bytes(64, 28672, 4096) == 0     # 224 tiles: persistent, no split-K, no scratch
+    assert L.kge_gemm_workspace_bytes(8192, 4096, 4096) == 0    # prefill-sized: CTA pairs
+    assert L.kge_gemm_workspace_bytes(1, 768, 4096) > 1024      # decode-sized: split-K through the workspace
 
 
 # ------------------------------------------------------------------------------ attention

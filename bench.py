@@ -274,12 +274,13 @@ def tp_subrecord(kge, args, world, rank, local, mx, barrier):
     name, B, pin, pout, pbatch = WORKLOADS["c4"]
     hf = model_cfg(name)
     prompts = rank_prompts(hf["vocab_size"], B, pin, rank, world)
-    nblk = B * ((pin + pout + 15) // 16) + 2
+    bs = args.block_size
+    nblk = B * ((pin + pout + bs - 1) // bs) + 2
     with tempfile.TemporaryDirectory() as d:
         json.dump(hf, open(os.path.join(d, "config.json"), "w"))
         llm = kge.LLM(d, max_model_len=pin + pout + 16, max_num_seqs=B, max_num_batched_tokens=pbatch * pin,
                       num_gpu_blocks_override=nblk, load_format="dummy", seed=1234, device=local, tensor_parallel_size=world,
-                      tp_rank=rank, enable_prefix_caching=False)
+                      tp_rank=rank, block_size=bs, enable_prefix_caching=False)
     connect_tp(kge, llm, args.tp_exchange, rank)
     log(f"tp{world} engine ready: {llm.weight_bytes / 1e9:.1f} GB weights/rank")
     llm.run_resident(prompts, pout, pbatch)
@@ -345,14 +346,14 @@ def run_ours(args):
     tp = world if args.workload == "c4" else 1      # c4: ONE model sharded over all ranks; else replicas
     replicas = 1 if tp > 1 else world
     prompts = rank_prompts(vocab, B, pin, rank, tp)
-    bs = 16
+    bs = args.block_size
     nblk = B * ((pin + pout + bs - 1) // bs) + 2
     with tempfile.TemporaryDirectory() as d:
         json.dump(hf, open(os.path.join(d, "config.json"), "w"))
         llm = kge.LLM(d, max_model_len=pin + pout + 16, max_num_seqs=max(B, 8),
                       max_num_batched_tokens=max(pbatch * pin, 256), num_gpu_blocks_override=nblk,
                       load_format="dummy", seed=1234, device=local, tensor_parallel_size=tp, tp_rank=rank if tp > 1 else 0,
-                      enable_prefix_caching=False)      # the same prompts are replayed every step: a cache hit would skip the prefill
+                      block_size=bs, enable_prefix_caching=False)      # the same prompts are replayed every step: a cache hit would skip the prefill
     if tp > 1:
         connect_tp(kge, llm, args.tp_exchange, rank)
     sp = kge.SamplingParams(max_tokens=pout, temperature=0.0, ignore_eos=True)
@@ -448,7 +449,7 @@ def run_ours(args):
         "higher_is_better": True, "scaling": "strong" if tp > 1 else "weak", "vs_baseline": None, "dtype": "bf16",
         "data": "synthetic token-id prompts U[1000,V-1000), hash-random weights (--load-format dummy)",
         "config": {"workload": f"{args.workload}: {name}, {B} concurrent requests, {pin}-in/{pout}-out, greedy, "
-                               f"paged KV block 16, {pbatch} prompts per prefill step",
+                               f"paged KV block {bs}, {pbatch} prompts per prefill step",
                    "parallelism": (f"tp{tp} ({'peer-memory fused all-reduce + residual + norm' if args.tp_exchange == 'peer' else 'NCCL bf16 all-reduce'} after o_proj and down_proj)" if tp > 1
                                    else f"dp{world} (independent replicas, no collective)"),
                    "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)",
@@ -516,6 +517,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--block-size", type=int, default=64, help="tokens per KV block (the server's default, 64)")
     ap.add_argument("--no-tp", action="store_true", help="at N > 1, skip the tensor-parallel (config 4) sub-record")
     ap.add_argument("--tp-exchange", default="peer", choices=["peer", "nccl"], help="TP data path: peer memory (default) or NCCL")
     ap.add_argument("--tp-timeout", type=float, default=420.0, help="seconds the tensor-parallel leg may take at N > 1")

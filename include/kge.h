@@ -41,8 +41,9 @@ int kge_device_sm_count(void);
  *   "attn_tma" 1/0            attention K/V tiles fetched by the TMA unit (one producer thread, cp.async.bulk.tensor boxes
  *                             of one KV block) instead of per-thread 16-byte cp.async gathers; 0 = the round-1 kernels, kept
  *                             for same-box comparison and for block sizes below 8
- *   "gemm_ws" 1/0             decode-sized projections split K over ordinary CTAs, two per SM, reduced through the caller's
- *                             workspace by the last CTA to arrive; 0 = always the cluster / distributed-shared-memory split
+ *   "gemm_ws" 0/1             1 = decode-sized projections split K over ordinary CTAs, two per SM, reduced through the caller's
+ *                             workspace by the last CTA to arrive (faster alone, 19.5 vs 25.5 us on the 8B qkv shape, but not
+ *                             inside the decode step, so off by default); 0 = the cluster / distributed-shared-memory split
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 
@@ -180,6 +181,39 @@ int64_t kge_sample_workspace_bytes(int B, int V);
 int kge_logprobs(float* out_vals, int32_t* out_ids, int32_t* out_rank, const void* logits,
                  const int32_t* sampled_ids, int R, int V, int ld, int top_n, void* stream);
 
+/* ------------------------------------------------------------ float16 twins of the ops ---
+ * `--dtype float16` (ref:values-01-minimal-example8.yaml:30-31, ...example9.yaml:31-32): the same kernels compiled for
+ * IEEE half storage - same arguments, same cast points (every "rounded to the model dtype" step rounds to float16;
+ * accumulation, softmax and norm statistics stay fp32), tcgen05.mma kind::f16 with F16 operands.  Buffers the bfloat16
+ * entry points describe as bf16 are float16 here. */
+int kge_embed_f16(void* out, const int32_t* ids, const void* table, const void* pos_table, const int32_t* positions,
+                  int pos_offset, int T, int d, void* stream);
+int kge_rmsnorm_f16(void* y, const void* x, const void* w, int T, int d, float eps, void* stream);
+int kge_add_rmsnorm_f16(void* y, void* residual, const void* x, const void* w, int T, int d, float eps, void* stream);
+int kge_head_rmsnorm_f16(void* qkv, const void* q_weight, const void* k_weight, int T, int H, int KV, int hd, float eps,
+                         void* stream);
+int kge_layernorm_f16(void* y, void* residual, const void* add, const void* w, const void* b, int T, int d, float eps,
+                      void* stream);
+int kge_silu_mul_f16(void* y, const void* x, int T, int f, void* stream);
+int kge_gemm_f16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K, int act, void* workspace,
+                 int64_t workspace_bytes, void* stream);
+int kge_gemm_silu_gate_f16(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* stream);
+int kge_rope_kvwrite_f16(void* qkv, const void* cos_sin, const int32_t* positions, const int64_t* slot_mapping,
+                         void* k_cache, void* v_cache, int T, int H, int KV, int hd, int block_size, void* stream);
+int kge_rope_cache_host_f16(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                            double low_freq_factor, double high_freq_factor, int orig_max_pos);
+int kge_paged_attn_f16(void* out, const void* q, int q_stride, const void* k_cache, const void* v_cache,
+                       const int32_t* block_table, int max_blocks_per_seq, const int32_t* seq_lens,
+                       const int32_t* query_start_loc, int B, int T, int max_q_len, int max_seq_len, int H, int KV, int hd,
+                       int block_size, float scale, void* workspace, int64_t workspace_bytes, void* stream);
+int kge_argmax_f16(int32_t* out_ids, const void* logits, int B, int V, int ld, void* stream);
+int kge_sample_f16(int32_t* out_ids, const void* logits, int B, int V, int ld, const float* temperature,
+                   const int32_t* top_k, const float* top_p, const float* exp_noise, const uint64_t* seeds, uint64_t step,
+                   void* workspace, int64_t workspace_bytes, void* stream);
+int kge_logprobs_f16(float* out_vals, int32_t* out_ids, int32_t* out_rank, const void* logits, const int32_t* sampled_ids,
+                     int R, int V, int ld, int top_n, void* stream);
+/* (kge_tp_reduce_add_norm_f16 is declared with the tensor-parallel exchange below) */
+
 /* -------------------------------------------------------------------- engine (model) --- */
 
 typedef struct kge_engine kge_engine;
@@ -188,12 +222,14 @@ typedef struct {
   int32_t max_num_seqs;           /* vllm --max-num-seqs                                  */
   int32_t max_num_batched_tokens; /* vllm --max-num-batched-tokens (per-step token budget) */
   int32_t max_model_len;          /* vllm --max-model-len                                 */
-  int32_t block_size;             /* KV block size in tokens (16)                         */
+  int32_t block_size;             /* KV block size in tokens (0: 64; 16 and 32 accepted)  */
   int32_t num_blocks;             /* 0: size from gpu_memory_utilization                  */
   float gpu_memory_utilization;   /* vllm --gpu-memory-utilization                        */
   int32_t tp_rank, tp_size;       /* vllm --tensor-parallel-size                          */
   int32_t enable_chunked_prefill; /* vllm --enable-chunked-prefill                        */
   int32_t device;                 /* CUDA device ordinal                                   */
+  int32_t dtype;                  /* vllm --dtype: 0 auto (config.json torch_dtype: float16 -> float16, else bfloat16),
+                                     1 bfloat16, 2 float16 (ref:values-01-minimal-example8.yaml:30-31)                  */
 } kge_engine_config;
 
 /* One engine step's device-side metadata - what vLLM hands its attention backend
@@ -219,6 +255,7 @@ int kge_engine_create(kge_engine** out, const char* model_dir, const kge_engine_
                       int64_t dummy_seed);
 void kge_engine_destroy(kge_engine* e);
 int kge_engine_num_blocks(const kge_engine* e);
+int kge_engine_dtype(const kge_engine* e);        /* 1 bfloat16, 2 float16: what the engine settled on */
 int kge_engine_vocab(const kge_engine* e);
 /* eos_token_id of config.json (-1 if none): what ends a request unless ignore_eos (vllm:v1/core/sched/utils.py:94-117). */
 int kge_engine_eos_token_id(const kge_engine* e);
@@ -237,6 +274,9 @@ void kge_model_close(kge_model_dir* m);
 int kge_model_spec_json(const kge_model_dir* m, char* out, int cap);
 int64_t kge_model_read_bf16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
                             uint16_t* out, int64_t cap);
+/* the same slice as IEEE half bits: what a float16 engine (--dtype float16) uploads */
+int64_t kge_model_read_f16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
+                           uint16_t* out, int64_t cap);
 
 /* The model directory's tokenizer (tokenizer.json byte-level BPE of the GPT-2 / Llama-3 / Qwen families, or GPT-2's
  * vocab.json + merges.txt), for front ends that take and return text like the engine they replace
@@ -330,6 +370,8 @@ int kge_tp_comm_connected(const kge_tp_comm* c);
 void* kge_tp_comm_data(kge_tp_comm* c);
 int kge_tp_reduce_add_norm(kge_tp_comm* c, int64_t y_off, void* residual, int64_t x_off, const void* w, const void* b,
                            int T, int d, float eps, int mode, void* stream);
+int kge_tp_reduce_add_norm_f16(kge_tp_comm* c, int64_t y_off, void* residual, int64_t x_off, const void* w, const void* b,
+                               int T, int d, float eps, int mode, void* stream);      /* float16 twin */
 int kge_tp_all_gather_cols(kge_tp_comm* c, int64_t dst_off, const void* src, int R, int cols, int ld_dst, int col0,
                            void* stream);
 /* The engine's own communicator (created with the engine when tp_size > 1): publish / connect as above.  Once

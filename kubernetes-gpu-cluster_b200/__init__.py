@@ -27,7 +27,7 @@ class EngineConfig(C.Structure):
     _fields_ = [("max_num_seqs", C.c_int32), ("max_num_batched_tokens", C.c_int32),
                 ("max_model_len", C.c_int32), ("block_size", C.c_int32), ("num_blocks", C.c_int32),
                 ("gpu_memory_utilization", C.c_float), ("tp_rank", C.c_int32), ("tp_size", C.c_int32),
-                ("enable_chunked_prefill", C.c_int32), ("device", C.c_int32)]
+                ("enable_chunked_prefill", C.c_int32), ("device", C.c_int32), ("dtype", C.c_int32)]
 
 
 class StepBatch(C.Structure):
@@ -95,6 +95,7 @@ SIGNATURES = {
     "kge_engine_create": (_I, [C.POINTER(_P), C.c_char_p, C.POINTER(EngineConfig), _L]),
     "kge_engine_destroy": (None, [_P]),
     "kge_engine_num_blocks": (_I, [_P]),
+    "kge_engine_dtype": (_I, [_P]),
     "kge_tokenizer_open": (_P, [C.c_char_p]),
     "kge_tokenizer_close": (None, [_P]),
     "kge_tokenizer_vocab_size": (_I, [_P]),
@@ -104,6 +105,7 @@ SIGNATURES = {
     "kge_model_close": (None, [_P]),
     "kge_model_spec_json": (_I, [_P, C.c_char_p, _I]),
     "kge_model_read_bf16": (C.c_int64, [_P, C.c_char_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _P, C.c_int64]),
+    "kge_model_read_f16": (C.c_int64, [_P, C.c_char_p, C.c_int64, C.c_int64, C.c_int64, C.c_int64, _P, C.c_int64]),
     "kge_engine_vocab": (_I, [_P]),
     "kge_engine_eos_token_id": (_I, [_P]),
     "kge_engine_max_model_len": (_I, [_P]),
@@ -150,6 +152,16 @@ SIGNATURES = {
     "kge_sched_counts": (_I, [_P, _P, _P, _P]),
 }
 
+# float16 twins of the element-type dependent ops: same signatures (include/kge.h)
+for _n, _t in {"kge_embed": "kge_embed_f16", "kge_rmsnorm": "kge_rmsnorm_f16", "kge_add_rmsnorm": "kge_add_rmsnorm_f16",
+               "kge_head_rmsnorm": "kge_head_rmsnorm_f16", "kge_layernorm": "kge_layernorm_f16", "kge_silu_mul": "kge_silu_mul_f16",
+               "kge_gemm_bf16": "kge_gemm_f16", "kge_gemm_silu_gate_bf16": "kge_gemm_silu_gate_f16",
+               "kge_rope_kvwrite": "kge_rope_kvwrite_f16", "kge_rope_cache_host": "kge_rope_cache_host_f16",
+               "kge_paged_attn": "kge_paged_attn_f16", "kge_argmax": "kge_argmax_f16", "kge_sample": "kge_sample_f16",
+               "kge_logprobs": "kge_logprobs_f16", "kge_tp_reduce_add_norm": "kge_tp_reduce_add_norm_f16"}.items():
+    SIGNATURES[_t] = SIGNATURES[_n]
+
+DTYPES = {"auto": 0, "bfloat16": 1, "float16": 2, "half": 2}
 _lib = None
 
 
@@ -237,6 +249,10 @@ class Tokenizer:
     __del__ = close
 
     @property
+    def dtype(self) -> str:
+        return {1: "bfloat16", 2: "float16"}.get(lib().kge_engine_dtype(self._h), "?")
+
+    @property
     def vocab_size(self) -> int:
         return lib().kge_tokenizer_vocab_size(self._h)
 
@@ -277,11 +293,13 @@ class LLM:
                  block_size: int = 16, num_gpu_blocks_override: int = 0, tensor_parallel_size: int = 1,
                  tp_rank: int = 0, enable_chunked_prefill: bool = True, load_format: str = "auto",
                  seed: int = 0, device: int = 0, scheduler_reserve_full_isl: bool = True,
-                 enable_prefix_caching: bool = True):
+                 enable_prefix_caching: bool = True, dtype: str = "auto"):
         require_cuda()
+        if dtype not in DTYPES:
+            raise KgeError(f"dtype {dtype!r}: this engine computes in bfloat16 or float16 (auto, bfloat16, float16)")
         self.cfg = EngineConfig(max_num_seqs, max_num_batched_tokens, max_model_len, block_size,
                                 num_gpu_blocks_override, gpu_memory_utilization, tp_rank,
-                                tensor_parallel_size, int(enable_chunked_prefill), device)
+                                tensor_parallel_size, int(enable_chunked_prefill), device, DTYPES[dtype])
         h = C.c_void_p()
         dummy = seed if load_format == "dummy" else -1
         check(lib().kge_engine_create(C.byref(h), model.encode(), C.byref(self.cfg), dummy), "kge_engine_create")

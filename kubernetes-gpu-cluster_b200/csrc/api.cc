@@ -35,7 +35,7 @@ bool pdl_for_this_launch() {
   return pdl_enabled() && !brk;
 }
 
-static std::atomic<int> g_tun[TUN_COUNT] = {{1}, {0}, {0}, {0}, {0}, {1}, {1}};   // even grid measured +6.5 % on the C3 gate_up GEMM (profiles/r01_knob_sweep.md)
+static std::atomic<int> g_tun[TUN_COUNT] = {{1}, {0}, {0}, {0}, {0}, {1}, {0}};   // even grid measured +6.5 % on the C3 gate_up GEMM (profiles/r01_knob_sweep.md)
 static const char* const kTunNames[TUN_COUNT] = {"gemm_even_grid", "attn_decode_splits", "attn_split_balance", "attn_cluster_merge", "gemm_shallow", "attn_tma", "gemm_ws"};
 int tunable(Tunable t) { return g_tun[t].load(std::memory_order_relaxed); }
 }  // namespace kge
@@ -71,10 +71,34 @@ static inline uint16_t f32_to_bf16_rne(float f) {
 
 // vllm:model_executor/layers/rotary_embedding/base.py:69-93 (fp32 inv_freq, fp32 outer product,
 // fp32 cos/sin, cast to the model dtype) and llama3_rope.py:33-54 (frequency rescale).
-extern "C" int kge_rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
-                                   double low_freq_factor, double high_freq_factor, int orig_max_pos) {
+// fp32 -> IEEE half bits, round to nearest even (the cast base.py:58-61 applies to the cos/sin cache of an fp16 model)
+static inline uint16_t f32_to_f16_rne(float f) {
+  uint32_t x;
+  memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  x &= 0x7fffffffu;
+  if (x >= 0x7f800000u) return (uint16_t)(sign | 0x7c00u | (x > 0x7f800000u ? 0x200u : 0u));   // inf / NaN
+  if (x >= 0x477ff000u) return (uint16_t)(sign | 0x7c00u);                                        // rounds to inf
+  if (x < 0x33000001u) return (uint16_t)sign;                                                     // rounds to zero
+  if (x < 0x38800000u) {                                                                          // subnormal half
+    const int shift = 126 - (int)(x >> 23);                 // 14..24
+    const uint32_t man = (x & 0x7fffffu) | 0x800000u;
+    uint32_t r = man >> shift;
+    const uint32_t rem = man & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
+    if (rem > halfway || (rem == halfway && (r & 1u))) ++r;
+    return (uint16_t)(sign | r);
+  }
+  uint32_t r = ((x - 0x38000000u) >> 13);
+  const uint32_t rem = x & 0x1fffu;
+  if (rem > 0x1000u || (rem == 0x1000u && (r & 1u))) ++r;
+  return (uint16_t)(sign | r);
+}
+
+static int rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                           double low_freq_factor, double high_freq_factor, int orig_max_pos, bool f16) {
   KGE_REQUIRE(out_host && max_pos > 0 && hd > 0 && hd % 2 == 0, "kge_rope_cache_host: bad arguments");
   const int half = hd / 2;
+  auto to16 = [f16](float v) { return f16 ? f32_to_f16_rne(v) : f32_to_bf16_rne(v); };
   std::vector<float> inv(half);
   for (int i = 0; i < half; ++i) {
     const float e = (float)(2 * i) / (float)hd;               // arange(0,rd,2,float)/rd
@@ -102,9 +126,18 @@ extern "C" int kge_rope_cache_host(uint16_t* out_host, int max_pos, int hd, doub
     for (int i = 0; i < half; ++i) {
       const float fr = (float)p * inv[i];
       // correctly rounded fp32 cos/sin of the fp32 angle
-      out_host[(size_t)p * hd + i] = f32_to_bf16_rne((float)cos((double)fr));
-      out_host[(size_t)p * hd + half + i] = f32_to_bf16_rne((float)sin((double)fr));
+      out_host[(size_t)p * hd + i] = to16((float)cos((double)fr));
+      out_host[(size_t)p * hd + half + i] = to16((float)sin((double)fr));
     }
   }
   return 0;
+}
+
+extern "C" int kge_rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                                   double low_freq_factor, double high_freq_factor, int orig_max_pos) {
+  return rope_cache_host(out_host, max_pos, hd, theta, factor, low_freq_factor, high_freq_factor, orig_max_pos, false);
+}
+extern "C" int kge_rope_cache_host_f16(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
+                                       double low_freq_factor, double high_freq_factor, int orig_max_pos) {
+  return rope_cache_host(out_host, max_pos, hd, theta, factor, low_freq_factor, high_freq_factor, orig_max_pos, true);
 }

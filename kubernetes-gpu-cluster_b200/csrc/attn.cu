@@ -13,6 +13,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int BN = 64;            // keys per tile
 constexpr float kLog2e = 1.4426950408889634f;
@@ -37,7 +38,7 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t& r0, uint32_t& r1, uint32_t& 
                : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
 __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32." KGE_MMA_ELT "." KGE_MMA_ELT ".f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
                : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
@@ -386,7 +387,10 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
       pml = po + (int64_t)B * H * ns * HD;
     }
     // default: K/V tiles staged by the TMA unit, splits merged by the last CTA to finish (attn_decode_tma.cu)
-    if (tunable(TUN_ATTN_TMA) && decode_tma_supported(B, KV, bs))
+    // (measured, profiles/r02_attn_block_size.jsonl: with 16-token blocks a TMA box is 2 KB and the TMA unit's request
+    // rate, not HBM, bounds the kernel - 107 us against 102 us for the cp.async gathers; from 32-token blocks on the
+    // boxes are large enough and TMA wins, 96 us at 64)
+    if (tunable(TUN_ATTN_TMA) && bs >= 32 && decode_tma_supported(B, KV, bs))
       return paged_attn_decode_tma(out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, B, H, KV, HD, bs, ns, sl2, po, pml, st);
     auto kern = attn_decode_kernel<HD, kDecodeStages, false>;
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
@@ -404,16 +408,20 @@ int paged_attn_prefill_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc
                           int max_blocks, const int32_t* sl, const int32_t* qsl, int B, int max_q_len, int H, int KV,
                           int hd, int bs, float scale, cudaStream_t st);   // attn_tc.cu
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
 
+#ifndef KGE_HALF
 extern "C" int64_t kge_attn_workspace_bytes(int B, int H, int hd, int max_seq_len) {
   (void)max_seq_len;
   return (int64_t)B * H * 32 * (hd + 2) * 4;
 }
 
-extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void* k_cache,
+#endif
+
+extern "C" int KGE_API(kge_paged_attn)(void* out, const void* q, int q_stride, const void* k_cache,
                               const void* v_cache, const int32_t* block_table, int max_blocks_per_seq,
                               const int32_t* seq_lens, const int32_t* query_start_loc, int B, int T,
                               int max_q_len, int max_seq_len, int H, int KV, int hd, int block_size,
@@ -442,6 +450,7 @@ extern "C" int kge_paged_attn(void* out, const void* q, int q_stride, const void
   return -1;
 }
 
+#ifndef KGE_HALF      // bfloat16 only: one scratch array per library image
 // ---------------------------------------------------------------------------------------------
 // Decode attention for callers that must not allocate.
 //
@@ -524,3 +533,4 @@ extern "C" int kge_paged_attn_decode_noalloc(void* out, const void* q, int q_str
                           max_blocks_per_seq, seq_lens, query_start_loc, B, 1, max_seq_len, H, KV, block_size, scale,
                           ws, kNoAllocScratchBytes, st);
 }
+#endif

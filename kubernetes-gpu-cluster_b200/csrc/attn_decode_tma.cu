@@ -22,6 +22,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int box_rows);   // gemm_tc.cu (cached)
 
@@ -68,7 +69,7 @@ __device__ __forceinline__ void ldsm_x4_t(uint32_t& r0, uint32_t& r1, uint32_t& 
   asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];" : "=r"(r0), "=r"(r1), "=r"(r2), "=r"(r3) : "r"(addr));
 }
 __device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+  asm volatile("mma.sync.aligned.m16n8k16.row.col.f32." KGE_MMA_ELT "." KGE_MMA_ELT ".f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
                : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3]) : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 __device__ __forceinline__ void bar_compute() { asm volatile("bar.sync 1, 128;" ::: "memory"); }   // the four compute warps
@@ -346,4 +347,5 @@ int paged_attn_decode_tma(bf16* out, const bf16* q, int q_stride, const bf16* kc
   return launch_decode_tma<64>(out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, B, H, KV, bs, ns, scale_log2, part_o, part_ml, st);
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge

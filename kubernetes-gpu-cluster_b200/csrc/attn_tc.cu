@@ -23,6 +23,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 namespace atc {
 
@@ -131,8 +132,8 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__
   constexpr uint32_t TMEM_COLS = 256;              // S0 [0,64), S1 [64,128), O [128,128+HD)
   constexpr uint32_t O_COL = 128;
   // S: M=128, N=128, both K-major.  PV: M=128, N=HD, A K-major, B MN-major (bit 16).
-  constexpr uint32_t IDESC_S = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(BNK >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
-  constexpr uint32_t IDESC_O = (1u << 4) | (1u << 7) | (1u << 10) | (1u << 16) | ((uint32_t)(HD >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  constexpr uint32_t IDESC_S = (1u << 4) | KGE_IDESC_AB | ((uint32_t)(BNK >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
+  constexpr uint32_t IDESC_O = (1u << 4) | KGE_IDESC_AB | (1u << 16) | ((uint32_t)(HD >> 3) << 17) | ((uint32_t)(BM >> 4) << 24);
 
   const int b = blockIdx.z, kvh = blockIdx.y;
   const int G = H / KV;
@@ -230,48 +231,39 @@ attn_tc_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_constant__
       }
     }
   } else if (warp == 5) {
-    // ------------------------------------------------------------------ TMA producer (TMA only: 192 threads; whole warp)
-    // Block ids come 32 at a time, one per lane, and are handed out by shuffle; lane i issues the boxes of block i.
-    const int bs = 1 << bs_shift;
-    const int box_rows = bs < BNK ? bs : BNK;
-    const int boxes = BNK / box_rows;
-    auto ld_blk = [&](int bi) { return (bi >= 0 && bi < max_blocks) ? btab[bi] : 0; };   // past the table: block 0 (those keys are masked)
-    int cbase = 0;
-    int v = ld_blk(lane), v_next = ld_blk(32 + lane);
-    auto fetch = [&](int t, bool is_k) {
-      const int st = t & 1;
-      const uint32_t dst = (is_k ? sK : sV) + st * TILE_BYTES;
-      const uint32_t bar = is_k ? k_full(st) : v_full(st);
-      const int key = t * BNK + (lane < boxes ? lane : 0) * box_rows;
-      const int bi = key >> bs_shift;
-      const int bi_last = (t * BNK + (boxes - 1) * box_rows) >> bs_shift;
-      if (bi_last >= cbase + 32) {                                        // warp-uniform
-        const int nb = (t * BNK) >> bs_shift;
-        if (nb == cbase + 32) { v = v_next; } else { v = ld_blk(nb + lane); }
-        cbase = nb;
-        v_next = ld_blk(cbase + 32 + lane);
-      }
-      const int blk = __shfl_sync(0xffffffffu, v, (bi - cbase) & 31);
-      if (lane == 0) mbar_expect_tx(bar, TILE_BYTES);
-      __syncwarp();
-      if (lane < boxes) {
-        const int row = (blk * KV + kvh) * bs + (key & (bs - 1));
+    // ------------------------------------------------------------------ TMA producer (TMA only: 192 threads)
+    // One thread: per tile it reads the tile's block ids and issues one box per (block, 64-column half).  (Spreading the
+    // issue over several lanes with the block ids handed out by shuffle measured SLOWER here: 364 vs 471 TFLOP/s at
+    // 4 x 2048, profiles/r02_vs_libs_*.json; a prefill tile lasts long enough for one thread to stay ahead.)
+    if (lane == 0) {
+      const int bs = 1 << bs_shift;
+      const int box_rows = bs < BNK ? bs : BNK;
+      const int boxes = BNK / box_rows;
+      auto fetch = [&](int t, bool is_k) {
+        const int st = t & 1;
+        const uint32_t dst = (is_k ? sK : sV) + st * TILE_BYTES;
+        const uint32_t bar = is_k ? k_full(st) : v_full(st);
+        mbar_expect_tx(bar, TILE_BYTES);
+        for (int i = 0; i < boxes; ++i) {
+          const int key = t * BNK + i * box_rows;
+          const int bi = key >> bs_shift;
+          const int blk = bi < max_blocks ? btab[bi] : 0;      // past the table: block 0 (those keys are masked)
+          const int row = (blk * KV + kvh) * bs + (key & (bs - 1));
 #pragma unroll
-        for (int h = 0; h < HD / 64; ++h)
-          tma_load_2d(dst + (uint32_t)(h * (BNK * 128) + lane * box_rows * 128), is_k ? &tm_k : &tm_v, bar, h * 64, row);
+          for (int h = 0; h < HD / 64; ++h)
+            tma_load_2d(dst + (uint32_t)(h * (BNK * 128) + i * box_rows * 128), is_k ? &tm_k : &tm_v, bar, h * 64, row);
+        }
+      };
+      fetch(0, true);
+      if (ntiles > 1) fetch(1, true);
+      fetch(0, false);
+      if (ntiles > 1) fetch(1, false);
+      for (int j = 0; j + 2 < ntiles; ++j) {
+        mbar_wait(s_full(j & 1), (uint32_t)((j >> 1) & 1));      // S_j done: K stage j&1 is free
+        fetch(j + 2, true);
+        mbar_wait(v_empty(j & 1), (uint32_t)((j >> 1) & 1));     // PV_j done: V stage j&1 is free
+        fetch(j + 2, false);
       }
-    };
-    fetch(0, true);
-    if (ntiles > 1) fetch(1, true);
-    fetch(0, false);
-    if (ntiles > 1) fetch(1, false);
-    for (int j = 0; j + 2 < ntiles; ++j) {
-      if (lane == 0) mbar_wait(s_full(j & 1), (uint32_t)((j >> 1) & 1));      // S_j done: K stage j&1 is free
-      __syncwarp();
-      fetch(j + 2, true);
-      if (lane == 0) mbar_wait(v_empty(j & 1), (uint32_t)((j >> 1) & 1));     // PV_j done: V stage j&1 is free
-      __syncwarp();
-      fetch(j + 2, false);
     }
   } else {
     // ------------------------------------------------------------------ loaders + softmax (one row per thread)
@@ -481,4 +473,5 @@ int paged_attn_prefill_tc(bf16* out, const bf16* q, int q_stride, const bf16* kc
   return launch_tc<64>(out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, B, max_q_len, H, KV, bs, scale, st);
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge

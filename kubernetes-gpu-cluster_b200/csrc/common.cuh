@@ -41,8 +41,66 @@ int tunable(Tunable t);
 
 #define KGE_LAUNCH_OK() KGE_CUDA_OK(cudaGetLastError())
 
-typedef __nv_bfloat16 bf16;
+}  // namespace kge
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Element type.  The kernel sources are compiled TWICE: as they are (bfloat16) and with -DKGE_HALF (float16, what
+// `--dtype float16` of ref:values-01-minimal-example8.yaml:30-31 asks for).  Everything that depends on the 16-bit format
+// goes through the handful of helpers below; the two builds live in two inline namespaces (so their kernels and host
+// helpers are distinct symbols) and export their C entry points under KGE_API(name): `name` and `name_f16`.
+// In the float16 build `bf16` simply names the 16-bit storage element.
+#ifdef KGE_HALF
+#include <cuda_fp16.h>
+#define KGE_ELT_NS h16
+#define KGE_API(name) name##_f16
+#define KGE_MMA_ELT "f16"
+#define KGE_IDESC_AB 0u                              /* tcgen05 instruction descriptor: A and B are F16 */
+#else
+#define KGE_ELT_NS b16
+#define KGE_API(name) name
+#define KGE_MMA_ELT "bf16"
+#define KGE_IDESC_AB ((1u << 7) | (1u << 10))        /* tcgen05 instruction descriptor: A and B are BF16 */
+#endif
+
+namespace kge {
+inline namespace KGE_ELT_NS {
+
+#ifdef KGE_HALF
+typedef __half bf16;
+#else
+typedef __nv_bfloat16 bf16;
+#endif
+
+#ifdef __CUDACC__
+#ifdef KGE_HALF
+__device__ __forceinline__ float bf2f(bf16 v) { return __half2float(v); }
+__device__ __forceinline__ bf16 f2bf(float v) { return __float2half_rn(v); }
+__device__ __forceinline__ float rbf(float v) { return __half2float(__float2half_rn(v)); }
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __half2float(__ushort_as_half((unsigned short)(u & 0xffffu))); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __half2float(__ushort_as_half((unsigned short)(u >> 16))); }
+__device__ __forceinline__ uint32_t pack_bf2(float lo, float hi) {
+  __half2 p = __floats2half2_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+#else
+__device__ __forceinline__ float bf2f(bf16 v) { return __bfloat162float(v); }
+__device__ __forceinline__ bf16 f2bf(float v) { return __float2bfloat16_rn(v); }
+// round-trip through the element type: the "every op rounds in the model dtype" steps of the reference
+__device__ __forceinline__ float rbf(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
+
+__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
+__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
+__device__ __forceinline__ uint32_t pack_bf2(float lo, float hi) {
+  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
+  return *reinterpret_cast<uint32_t*>(&p);
+}
+#endif
+#endif
+
+}  // namespace KGE_ELT_NS
+}  // namespace kge
+
+namespace kge {
 #ifdef __CUDACC__
 // Programmatic dependent launch: every kernel of the forward pass lets its successor start early
 // (launch latency, prologue and - for the GEMM - the first weight tiles overlap this kernel's
@@ -59,18 +117,6 @@ inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, siz
   attr[0].val.programmaticStreamSerializationAllowed = 1;
   cfg.attrs = attr; cfg.numAttrs = pdl_for_this_launch() ? 1 : 0;
   return cudaLaunchKernelEx(&cfg, kern, KArgs(args)...);
-}
-
-__device__ __forceinline__ float bf2f(bf16 v) { return __bfloat162float(v); }
-__device__ __forceinline__ bf16 f2bf(float v) { return __float2bfloat16_rn(v); }
-// round-trip through bf16: the "every op rounds in the model dtype" steps of the reference
-__device__ __forceinline__ float rbf(float v) { return __bfloat162float(__float2bfloat16_rn(v)); }
-
-__device__ __forceinline__ float bf_lo(uint32_t u) { return __uint_as_float(u << 16); }
-__device__ __forceinline__ float bf_hi(uint32_t u) { return __uint_as_float(u & 0xffff0000u); }
-__device__ __forceinline__ uint32_t pack_bf2(float lo, float hi) {
-  __nv_bfloat162 p = __floats2bfloat162_rn(lo, hi);
-  return *reinterpret_cast<uint32_t*>(&p);
 }
 
 __device__ __forceinline__ uint4 ld_nc_v4(const void* p) {

@@ -5,6 +5,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int kMaxVecPerThread = 4;   // up to 4 x (8 bf16) per thread: d <= 32 * blockDim
 
@@ -286,13 +287,14 @@ argmax_kernel(int32_t* __restrict__ out, const bf16* __restrict__ logits, int V,
   }
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
 
 static inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
-extern "C" int kge_embed(void* out, const int32_t* ids, const void* table, const void* pos_table,
+extern "C" int KGE_API(kge_embed)(void* out, const int32_t* ids, const void* table, const void* pos_table,
                          const int32_t* positions, int pos_offset, int T, int d, void* stream) {
   KGE_REQUIRE(T >= 0 && d > 0 && d % 8 == 0, "kge_embed: d=%d must be a positive multiple of 8", d);
   KGE_REQUIRE(aligned16(out) && aligned16(table) && aligned16(pos_table), "kge_embed: pointers must be 16-byte aligned");
@@ -320,23 +322,23 @@ static int norm_common(int mode, void* y, void* residual, const void* x, const v
   return 0;
 }
 
-extern "C" int kge_rmsnorm(void* y, const void* x, const void* w, int T, int d, float eps, void* stream) {
+extern "C" int KGE_API(kge_rmsnorm)(void* y, const void* x, const void* w, int T, int d, float eps, void* stream) {
   KGE_REQUIRE(y && x && w, "kge_rmsnorm: null pointer");
   return norm_common(0, y, nullptr, x, w, nullptr, T, d, eps, stream);
 }
-extern "C" int kge_add_rmsnorm(void* y, void* residual, const void* x, const void* w, int T, int d,
+extern "C" int KGE_API(kge_add_rmsnorm)(void* y, void* residual, const void* x, const void* w, int T, int d,
                                float eps, void* stream) {
   KGE_REQUIRE(y && residual && x && w, "kge_add_rmsnorm: null pointer");
   return norm_common(1, y, residual, x, w, nullptr, T, d, eps, stream);
 }
-extern "C" int kge_layernorm(void* y, void* residual, const void* add, const void* w, const void* b,
+extern "C" int KGE_API(kge_layernorm)(void* y, void* residual, const void* add, const void* w, const void* b,
                              int T, int d, float eps, void* stream) {
   KGE_REQUIRE(residual && (y || add), "kge_layernorm: null pointer");
   KGE_REQUIRE(!y || (w && b), "kge_layernorm: weight and bias required");
   return norm_common(add ? 3 : 2, y, residual, add, w, b, T, d, eps, stream);
 }
 
-extern "C" int kge_silu_mul(void* y, const void* x, int T, int f, void* stream) {
+extern "C" int KGE_API(kge_silu_mul)(void* y, const void* x, int T, int f, void* stream) {
   KGE_REQUIRE(y && x && f > 0 && f % 8 == 0, "kge_silu_mul: f=%d must be a positive multiple of 8", f);
   KGE_REQUIRE(aligned16(y) && aligned16(x), "kge_silu_mul: pointers must be 16-byte aligned");
   if (T <= 0) return 0;
@@ -347,7 +349,7 @@ extern "C" int kge_silu_mul(void* y, const void* x, int T, int f, void* stream) 
   return 0;
 }
 
-extern "C" int kge_rope_kvwrite(void* qkv, const void* cos_sin, const int32_t* positions,
+extern "C" int KGE_API(kge_rope_kvwrite)(void* qkv, const void* cos_sin, const int32_t* positions,
                                 const int64_t* slot_mapping, void* k_cache, void* v_cache, int T,
                                 int H, int KV, int hd, int block_size, void* stream) {
   KGE_REQUIRE(qkv && slot_mapping && k_cache && v_cache, "kge_rope_kvwrite: null pointer");
@@ -364,7 +366,7 @@ extern "C" int kge_rope_kvwrite(void* qkv, const void* cos_sin, const int32_t* p
   return 0;
 }
 
-extern "C" int kge_head_rmsnorm(void* qkv, const void* q_weight, const void* k_weight, int T, int H, int KV, int hd,
+extern "C" int KGE_API(kge_head_rmsnorm)(void* qkv, const void* q_weight, const void* k_weight, int T, int H, int KV, int hd,
                                 float eps, void* stream) {
   KGE_REQUIRE(qkv && q_weight && k_weight, "kge_head_rmsnorm: null pointer");
   KGE_REQUIRE(hd == 64 || hd == 128, "kge_head_rmsnorm: head_dim=%d unsupported (64, 128)", hd);
@@ -375,7 +377,7 @@ extern "C" int kge_head_rmsnorm(void* qkv, const void* q_weight, const void* k_w
   return 0;
 }
 
-extern "C" int kge_argmax(int32_t* out_ids, const void* logits, int B, int V, int ld, void* stream) {
+extern "C" int KGE_API(kge_argmax)(int32_t* out_ids, const void* logits, int B, int V, int ld, void* stream) {
   KGE_REQUIRE(out_ids && logits && V > 0 && ld >= V, "kge_argmax: bad arguments");
   KGE_REQUIRE(aligned16(logits) && ld % 8 == 0, "kge_argmax: logits rows must be 16-byte aligned");
   if (B <= 0) return 0;

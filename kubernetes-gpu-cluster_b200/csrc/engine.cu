@@ -8,20 +8,35 @@
 
 using namespace kge;
 
+#include <cuda_fp16.h>
+
 namespace kge {
 
-__global__ void fill_uniform_kernel(bf16* p, int64_t n, uint64_t seed, float scale) {
+const Ops kOpsBf16 = {kge_embed, kge_rmsnorm, kge_add_rmsnorm, kge_head_rmsnorm, kge_layernorm, kge_silu_mul, kge_gemm_bf16,
+                      kge_gemm_silu_gate_bf16, kge_rope_kvwrite, kge_rope_cache_host, kge_paged_attn, kge_argmax, kge_sample,
+                      kge_logprobs, kge_tp_reduce_add_norm};
+const Ops kOpsF16 = {kge_embed_f16, kge_rmsnorm_f16, kge_add_rmsnorm_f16, kge_head_rmsnorm_f16, kge_layernorm_f16, kge_silu_mul_f16,
+                     kge_gemm_f16, kge_gemm_silu_gate_f16, kge_rope_kvwrite_f16, kge_rope_cache_host_f16, kge_paged_attn_f16,
+                     kge_argmax_f16, kge_sample_f16, kge_logprobs_f16, kge_tp_reduce_add_norm_f16};
+
+// 16-bit pattern of v in the engine's element type
+__device__ __forceinline__ uint16_t to_elt_bits(float v, bool f16) {
+  return f16 ? __half_as_ushort(__float2half_rn(v)) : __bfloat16_as_ushort(__float2bfloat16_rn(v));
+}
+
+__global__ void fill_uniform_kernel(bf16* p, int64_t n, uint64_t seed, float scale, bool f16) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     uint64_t z = (uint64_t)i * 0x9E3779B97F4A7C15ull + seed;
     z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
     z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
     z ^= z >> 31;
     const float u = (float)(z >> 40) * (1.0f / 16777216.0f);   // [0,1)
-    p[i] = f2bf((2.f * u - 1.f) * scale);
+    reinterpret_cast<uint16_t*>(p)[i] = to_elt_bits((2.f * u - 1.f) * scale, f16);
   }
 }
-__global__ void fill_const_kernel(bf16* p, int64_t n, float v) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) p[i] = f2bf(v);
+__global__ void fill_const_kernel(bf16* p, int64_t n, float v, bool f16) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    reinterpret_cast<uint16_t*>(p)[i] = to_elt_bits(v, f16);
 }
 
 struct Builder {
@@ -60,7 +75,7 @@ struct Builder {
   // dst rows [dst_r0, ...) of a [.., ncols] device matrix <- tensor slice
   bool put(bf16* dst, int64_t dst_off, const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1) {
     std::vector<uint16_t> buf;
-    if (!md->read_bf16(name, r0, r1, c0, c1, &buf, &err)) return false;
+    if (!md->read_16(name, r0, r1, c0, c1, e->f16, &buf, &err)) return false;
     if (cudaMemcpy(dst + dst_off, buf.data(), buf.size() * 2, cudaMemcpyHostToDevice) != cudaSuccess) {
       err = "cudaMemcpy failed for " + name;
       return false;
@@ -72,10 +87,10 @@ struct Builder {
   void rnd(bf16* p, int64_t n, float scale, bool shard = false) {
     const uint64_t salt = shard ? (uint64_t)e->tp_rank * 0xA24BAED4963EE407ull : 0;
     fill_uniform_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, e->stream>>>(
-        p, n, ((uint64_t)dummy_seed * 0x100000001B3ull + (counter++) * 0x9E3779B9ull) ^ salt, scale);
+        p, n, ((uint64_t)dummy_seed * 0x100000001B3ull + (counter++) * 0x9E3779B9ull) ^ salt, scale, e->f16);
   }
   void cst(bf16* p, int64_t n, float v) {
-    fill_const_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, e->stream>>>(p, n, v);
+    fill_const_kernel<<<(int)std::min<int64_t>((n + 255) / 256, 148 * 8), 256, 0, e->stream>>>(p, n, v, e->f16);
   }
 };
 
@@ -168,7 +183,7 @@ static bool build_llama(Builder& b) {
   // RoPE cache (host, vLLM's arithmetic) up to max_model_len positions
   const int max_pos = std::min(e->cfg.max_model_len, s.max_pos);
   std::vector<uint16_t> cs((size_t)max_pos * hd);
-  if (kge_rope_cache_host(cs.data(), max_pos, hd, s.rope_theta, s.rope_factor, s.rope_low, s.rope_high, s.rope_orig_max)) {
+  if (e->op->rope_cache_host(cs.data(), max_pos, hd, s.rope_theta, s.rope_factor, s.rope_low, s.rope_high, s.rope_orig_max)) {
     b.err = kge_last_error();
     return false;
   }
@@ -312,6 +327,10 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   e->spec = md.spec();
   const ModelSpec& s = e->spec;
   if (!md.has_weights() && dummy_seed < 0) ENGINE_FAIL("kge_engine_create: no *.safetensors in %s (use --load-format dummy)", model_dir);
+  // --dtype: auto follows the checkpoint (float16 stays float16; everything else runs in bfloat16), or as told
+  if (cfg->dtype < 0 || cfg->dtype > 2) ENGINE_FAIL("kge_engine_create: dtype %d (0 auto, 1 bfloat16, 2 float16)", cfg->dtype);
+  e->f16 = cfg->dtype == 2 || (cfg->dtype == 0 && (s.torch_dtype == "float16" || s.torch_dtype == "half"));
+  e->op = e->f16 ? &kOpsF16 : &kOpsBf16;
   e->tp_size = cfg->tp_size > 0 ? cfg->tp_size : 1;
   e->tp_rank = cfg->tp_rank;
   if (e->tp_rank < 0 || e->tp_rank >= e->tp_size) ENGINE_FAIL("kge_engine_create: tp_rank %d of %d", e->tp_rank, e->tp_size);
@@ -334,7 +353,9 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
     if (!getenv("KGE_TP_PDL")) kge::pdl_set_enabled(false);
     e->use_graphs = false;
   }
-  if (e->cfg.block_size <= 0) e->cfg.block_size = 16;
+  // default KV block: 64 tokens, so that a (block, kv head) run of the cache is one 8 KB TMA box per 64-column half
+  // (16 and 32, vLLM's other sizes, are accepted; profiles/r02_attn_block_size.jsonl has what they cost)
+  if (e->cfg.block_size <= 0) e->cfg.block_size = 64;
   if (e->cfg.block_size & (e->cfg.block_size - 1)) ENGINE_FAIL("kge_engine_create: block_size must be a power of two");
   if (e->cfg.max_model_len <= 0) e->cfg.max_model_len = std::min(s.max_pos, 8192);
   if (e->cfg.max_model_len > s.max_pos) ENGINE_FAIL("kge_engine_create: max_model_len %d > model max positions %d", e->cfg.max_model_len, s.max_pos);
@@ -470,6 +491,7 @@ extern "C" void kge_engine_destroy(kge_engine* e) {
 }
 
 extern "C" int kge_engine_num_blocks(const kge_engine* e) { return e ? e->num_blocks : 0; }
+extern "C" int kge_engine_dtype(const kge_engine* e) { return e ? (e->f16 ? 2 : 1) : 0; }
 extern "C" int kge_engine_vocab(const kge_engine* e) { return e ? e->spec.vocab : 0; }
 extern "C" int kge_engine_eos_token_id(const kge_engine* e) { return e ? e->spec.eos : -1; }
 extern "C" int kge_engine_max_model_len(const kge_engine* e) { return e ? e->cfg.max_model_len : 0; }

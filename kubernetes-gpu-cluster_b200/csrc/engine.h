@@ -16,6 +16,27 @@
 
 namespace kge {
 
+// The element-type dependent ops behind one table: the engine is compiled once and runs a bfloat16 or a float16 model
+// by calling the C entry points of the matching build of the kernel sources (common.cuh).
+struct Ops {
+  decltype(&kge_embed) embed;
+  decltype(&kge_rmsnorm) rmsnorm;
+  decltype(&kge_add_rmsnorm) add_rmsnorm;
+  decltype(&kge_head_rmsnorm) head_rmsnorm;
+  decltype(&kge_layernorm) layernorm;
+  decltype(&kge_silu_mul) silu_mul;
+  decltype(&kge_gemm_bf16) gemm;
+  decltype(&kge_gemm_silu_gate_bf16) gemm_silu_gate;
+  decltype(&kge_rope_kvwrite) rope_kvwrite;
+  decltype(&kge_rope_cache_host) rope_cache_host;
+  decltype(&kge_paged_attn) paged_attn;
+  decltype(&kge_argmax) argmax;
+  decltype(&kge_sample) sample;
+  decltype(&kge_logprobs) logprobs;
+  decltype(&kge_tp_reduce_add_norm) tp_reduce_add_norm;
+};
+extern const Ops kOpsBf16, kOpsF16;     // engine.cu
+
 struct Linear {
   bf16* w = nullptr;     // [N, K] row-major
   bf16* b = nullptr;     // [N] or null
@@ -43,6 +64,8 @@ struct kge_engine {
   kge::ModelSpec spec;
   kge_engine_config cfg;
   int tp_rank = 0, tp_size = 1;
+  bool f16 = false;                          // float16 model (--dtype float16); bfloat16 otherwise
+  const kge::Ops* op = &kge::kOpsBf16;
   ncclComm_t comm = nullptr;
   // peer-memory exchange (tp_peer.cu): created with the engine when tp_size > 1; h, xn and the gathered logits live in
   // its window at the offsets below (the same on every rank)
@@ -109,7 +132,7 @@ namespace kge {
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
                    const StepMeta& dm, bool any_random, double sum_seq, double attn_flops);
 void collect_timing(kge_engine* e);
-int attn_decode_splits(int B, int KV, int max_seq_len);   // attn.cu
+inline namespace KGE_ELT_NS { int attn_decode_splits(int B, int KV, int max_seq_len); }   // attn.cu (the same in both element builds)
 // A pure decode step (one token per request, metadata at the fixed-stride layout `dm` in meta_dev):
 // eager the first time a (B, splits, stride, sampling) key is seen, captured into a CUDA graph the
 // second time, replayed afterwards.

@@ -5,6 +5,8 @@
 
 #include <algorithm>
 
+#include <cuda_fp16.h>
+
 #include "engine.h"
 
 using namespace kge;
@@ -51,7 +53,7 @@ void collect_timing(kge_engine* e) {
 enum { C_GEMM_S = 0, C_GEMM_L = 1, C_ATT_DEC = 2, C_ATT_GEN = 3, C_NORM = 4, C_ROPE = 5, C_ACT = 6, C_EMBED = 7, C_SAMPLE = 8, C_AR = 9 };
 
 static int linear_rc(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int T, int act) {
-  return kge_gemm_bf16(y, x, l.w, l.b, T, l.N, l.K, act, e->ws_gemm, e->ws_gemm_bytes, e->stream);
+  return e->op->gemm(y, x, l.w, l.b, T, l.N, l.K, act, e->ws_gemm, e->ws_gemm_bytes, e->stream);
 }
 #define LINEAR(y, x, l, T, act)                                                                   \
   FWD((T) <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)(l).N * (l).K + (double)(T) * ((l).K + (l).N)), \
@@ -67,9 +69,9 @@ int tp_all_gather_logits(kge_engine* e, int R);           // tp.cu (NCCL path)
 static int reduce_add_norm(kge_engine* e, int T, const bf16* w, const bf16* b, bool layer_norm, float eps) {
   const int d = e->spec.d;
   if (e->tp_peer())
-    return kge_tp_reduce_add_norm(e->tpc, e->off_xn, e->res, e->off_h, w, b, T, d, eps, layer_norm ? 3 : 1, e->stream);
-  if (layer_norm) return kge_layernorm(e->xn, e->res, e->h, w, b, T, d, eps, e->stream);
-  return kge_add_rmsnorm(e->xn, e->res, e->h, w, T, d, eps, e->stream);
+    return e->op->tp_reduce_add_norm(e->tpc, e->off_xn, e->res, e->off_h, w, b, T, d, eps, layer_norm ? 3 : 1, e->stream);
+  if (layer_norm) return e->op->layernorm(e->xn, e->res, e->h, w, b, T, d, eps, e->stream);
+  return e->op->add_rmsnorm(e->xn, e->res, e->h, w, T, d, eps, e->stream);
 }
 
 int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q_len, int max_seq_len,
@@ -90,15 +92,15 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
   // offset the per-request arrays
   auto attend = [&](int i) -> int {
     if (D == 0) {
-      FWD(c_att, att_bytes, att_fl, kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
+      FWD(c_att, att_bytes, att_fl, e->op->paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, B, T,
                          max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
       return 0;
     }
     FWD(C_ATT_DEC, dec_bytes, 4.0 * e->step_dec_sum_seq * Hl * hd,
-        kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, D, D, 1,
+        e->op->paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab, max_blocks, m.seq_lens, m.qsl, D, D, 1,
                        e->step_dec_max_seq, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
     FWD(C_ATT_GEN, att_bytes - dec_bytes, att_fl - 4.0 * e->step_dec_sum_seq * Hl * hd,
-        kge_paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab + (int64_t)D * max_blocks, max_blocks, m.seq_lens + D,
+        e->op->paged_attn(e->attn, e->qkv, qkv_n, e->kc[i], e->vc[i], m.btab + (int64_t)D * max_blocks, max_blocks, m.seq_lens + D,
                        m.qsl + D, B - D, T - D, max_q_len, max_seq_len, Hl, KVl, hd, bs, scale, e->ws_attn, e->ws_attn_bytes, st));
     return 0;
   };
@@ -112,14 +114,14 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
     FWD(peer ? C_AR : C_NORM, 4 * Td2, 0, reduce_add_norm(e, T, w, b, ln, eps));                        \
   } while (0)
   if (s.is_opt()) {
-    FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
+    FWD(C_EMBED, 2 * Td2, 0, e->op->embed(e->res, m.ids, e->embed, e->pos_embed, m.pos, 2, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
       // first LN of the layer; for i > 0 it also folds in the previous layer's fc2 output
-      if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_layernorm(e->xn, e->res, nullptr, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
+      if (i == 0) FWD(C_NORM, 2 * Td2, 0, e->op->layernorm(e->xn, e->res, nullptr, L.ln1_w, L.ln1_b, T, d, 1e-5f, st));
       else REDUCE_NORM(L.ln1_w, L.ln1_b, true, 1e-5f);
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
-      FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+      FWD(C_ROPE, rope_bytes, 0, e->op->rope_kvwrite(e->qkv, nullptr, nullptr, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
       if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
       REDUCE_NORM(L.ln2_w, L.ln2_b, true, 1e-5f);
@@ -128,25 +130,25 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
     }
     REDUCE_NORM(e->final_w, e->final_b, true, 1e-5f);
   } else {
-    FWD(C_EMBED, 2 * Td2, 0, kge_embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
+    FWD(C_EMBED, 2 * Td2, 0, e->op->embed(e->res, m.ids, e->embed, nullptr, nullptr, 0, T, d, st));
     for (int i = 0; i < s.L; ++i) {
       const LayerW& L = e->layers[i];
-      if (i == 0) FWD(C_NORM, 2 * Td2, 0, kge_rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
+      if (i == 0) FWD(C_NORM, 2 * Td2, 0, e->op->rmsnorm(e->xn, e->res, L.ln1_w, T, d, s.eps, st));
       else REDUCE_NORM(L.ln1_w, nullptr, false, s.eps);
       LINEAR(e->qkv, e->xn, L.qkv, T, 0);
       if (s.qk_norm)
-        FWD(C_NORM, (double)T * (Hl + KVl) * hd * 4, 0, kge_head_rmsnorm(e->qkv, L.q_norm, L.k_norm, T, Hl, KVl, hd, s.eps, st));
-      FWD(C_ROPE, rope_bytes, 0, kge_rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
+        FWD(C_NORM, (double)T * (Hl + KVl) * hd * 4, 0, e->op->head_rmsnorm(e->qkv, L.q_norm, L.k_norm, T, Hl, KVl, hd, s.eps, st));
+      FWD(C_ROPE, rope_bytes, 0, e->op->rope_kvwrite(e->qkv, e->cos_sin, m.pos, m.slots, e->kc[i], e->vc[i], T, Hl, KVl, hd, bs, st));
       if (int rc = attend(i)) return rc;
       LINEAR(e->h, e->attn, L.o, T, 0);
       REDUCE_NORM(L.ln2_w, nullptr, false, s.eps);
       if (e->ffn_loc % 64 == 0) {
         // gate_up GEMM with the SiLU*mul in its epilogue: [T,2f] never reaches HBM
         FWD(T <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)L.up.N * L.up.K + (double)T * (L.up.K + e->ffn_loc)),
-            2.0 * T * (double)L.up.N * L.up.K, kge_gemm_silu_gate_bf16(e->act, e->xn, L.up.w, T, e->ffn_loc, L.up.K, st));
+            2.0 * T * (double)L.up.N * L.up.K, e->op->gemm_silu_gate(e->act, e->xn, L.up.w, T, e->ffn_loc, L.up.K, st));
       } else {
         LINEAR(e->gu, e->xn, L.up, T, 0);
-        FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, kge_silu_mul(e->act, e->gu, T, e->ffn_loc, st));
+        FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, e->op->silu_mul(e->act, e->gu, T, e->ffn_loc, st));
       }
       LINEAR(e->h, e->act, L.down, T, 0);
     }
@@ -155,7 +157,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
 #undef REDUCE_NORM
   if (R > 0) {
     // logits only for the last token of each sampled request (logits_processor.py:54-99)
-    FWD(C_EMBED, 2.0 * R * d * 2, 0, kge_embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
+    FWD(C_EMBED, 2.0 * R * d * 2, 0, e->op->embed(e->xsel, m.rows, e->xn, nullptr, nullptr, 0, R, d, st));
     Linear head;
     head.w = e->lm_head; head.b = nullptr; head.N = e->vocab_loc; head.K = d;
     if (e->tp_size == 1) {
@@ -169,10 +171,10 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
         FWD(C_AR, 2.0 * R * s.vocab, 0, tp_all_gather_logits(e, R));
     }
     if (any_random)
-      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
+      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, e->op->sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
                      0 /* the step is folded into the per-row seeds */, nullptr, 0, st));
     else
-      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, kge_argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
+      FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, e->op->argmax(e->d_out, e->logits, R, s.vocab, s.vocab, st));
   }
   return 0;
 }
@@ -210,8 +212,9 @@ int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const 
   return 0;
 }
 
-__global__ void bf16_to_f32_kernel(float* o, const bf16* x, int64_t n) {
-  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) o[i] = bf2f(x[i]);
+__global__ void elt_to_f32_kernel(float* o, const bf16* x, int64_t n, bool f16) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    o[i] = f16 ? __half2float(reinterpret_cast<const __half*>(x)[i]) : bf2f(x[i]);
 }
 
 // Copy the caller's host metadata into the pinned block, ship it, run, read the ids back.
@@ -288,7 +291,7 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
     KGE_CUDA_OK(cudaMemcpyAsync(e->out_host, e->d_out, (size_t)R * 4, cudaMemcpyDeviceToHost, e->stream));
     if (lp_n >= 0) {
       // raw log-probabilities of the sampled tokens (vllm:v1/sample/sampler.py:300-349), for the rows that asked
-      if (int rc = kge_logprobs(e->lp_vals, e->lp_ids, e->lp_rank, e->logits, e->d_out, R, e->spec.vocab, e->spec.vocab, lp_n, e->stream)) return rc;
+      if (int rc = e->op->logprobs(e->lp_vals, e->lp_ids, e->lp_rank, e->logits, e->d_out, R, e->spec.vocab, e->spec.vocab, lp_n, e->stream)) return rc;
       ++e->launches;
       const size_t n = (size_t)R * (lp_n + 1) * 4;
       KGE_CUDA_OK(cudaMemcpyAsync(e->lp_vals_host, e->lp_vals, n, cudaMemcpyDeviceToHost, e->stream));
@@ -303,7 +306,7 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
       const int64_t n = (int64_t)R * e->spec.vocab;
       KGE_REQUIRE(n * 4 <= (int64_t)e->cfg.max_num_batched_tokens * e->layers[0].up.N * 2,
                   "kge_step: logits read-back needs R*vocab*4 <= gate_up buffer");
-      bf16_to_f32_kernel<<<148 * 4, 256, 0, e->stream>>>(tmp, e->logits, n);
+      elt_to_f32_kernel<<<148 * 4, 256, 0, e->stream>>>(tmp, e->logits, n, e->f16);
       KGE_CUDA_OK(cudaMemcpyAsync(out_logits_host, tmp, (size_t)n * 4, cudaMemcpyDeviceToHost, e->stream));
     }
   }

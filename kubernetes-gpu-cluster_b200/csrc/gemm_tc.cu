@@ -34,6 +34,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int BLK_M = 128;   // weight rows per tile (UMMA M)
 constexpr int BLK_K = 64;    // 64 bf16 = 128 B = one swizzle row
@@ -155,7 +156,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = (PAIR ? 128 : TOKN) * BLK_K * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
-  constexpr uint32_t IDESC = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(TOKN >> 3) << 17) |
+  constexpr uint32_t IDESC = (1u << 4) | KGE_IDESC_AB | ((uint32_t)(TOKN >> 3) << 17) |
                              ((uint32_t)((PAIR ? 2 * BLK_M : BLK_M) >> 4) << 24);
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
@@ -511,7 +512,12 @@ static int encode_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t co
   cuuint64_t strides[1] = {(cuuint64_t)cols * 2};
   cuuint32_t box[2] = {(cuuint32_t)BLK_K, (cuuint32_t)box_rows};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides, box, estr,
+#ifdef KGE_HALF
+  const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_FLOAT16;
+#else
+  const CUtensorMapDataType dt = CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+#endif
+  CUresult r = enc(m, dt, 2, const_cast<void*>(ptr), dims, strides, box, estr,
                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   KGE_REQUIRE(r == CUDA_SUCCESS, "cuTensorMapEncodeTiled failed (%d) rows=%lld cols=%lld", (int)r, (long long)rows, (long long)cols);
@@ -723,6 +729,7 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
   }
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
@@ -731,12 +738,22 @@ static int64_t ws_bytes_of(const GemmPlan& g) {
   return g.ws ? kWsCounterBytes + (int64_t)g.m_tiles * g.n_tiles * g.splits * g.tokn * BLK_M * 4 : 0;
 }
 
+#ifndef KGE_HALF      // the same for both element types: exported once
 extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
   if (T <= 0 || N <= 0 || K <= 0) return 0;
   return ws_bytes_of(plan_gemm(T, N, K, BLK_M, true));      // 0: this shape does not split K through a workspace
 }
 
-extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
+#endif
+
+#ifdef KGE_HALF
+#define KGE_GEMM_NAME kge_gemm_f16
+#define KGE_GEMM_GATE_NAME kge_gemm_silu_gate_f16
+#else
+#define KGE_GEMM_NAME kge_gemm_bf16
+#define KGE_GEMM_GATE_NAME kge_gemm_silu_gate_bf16
+#endif
+extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                              int act, void* workspace, int64_t workspace_bytes, void* stream) {
   KGE_REQUIRE(y && x && w, "kge_gemm_bf16: null pointer");
   KGE_REQUIRE(T >= 0 && N > 0 && K > 0 && K % 8 == 0, "kge_gemm_bf16: K=%d must be a positive multiple of 8", K);
@@ -759,7 +776,7 @@ extern "C" int kge_gemm_bf16(void* y, const void* x, const void* w, const void* 
   return dispatch_gemm<false>(g, tw, tx, p, st);
 }
 
-extern "C" int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
+extern "C" int KGE_GEMM_GATE_NAME(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
                                        void* stream) {
   KGE_REQUIRE(y && x && w_gate_up, "kge_gemm_silu_gate_bf16: null pointer");
   KGE_REQUIRE(T >= 0 && f > 0 && K > 0 && K % 8 == 0, "kge_gemm_silu_gate_bf16: K=%d must be a positive multiple of 8", K);

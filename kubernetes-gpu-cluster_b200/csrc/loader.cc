@@ -36,6 +36,7 @@ static bool parse_config(const Json& j, ModelSpec* s, std::string* err) {
   s->H = (int)j.int_or("num_attention_heads", 0);
   s->max_pos = (int)j.int_or("max_position_embeddings", 2048);
   s->bos = (int)j.int_or("bos_token_id", -1);
+  s->torch_dtype = j.str_or("torch_dtype", j.str_or("dtype", ""));
   if (const Json* e = j.get("eos_token_id")) {
     if (e->is_num()) s->eos = (int)e->num;
     else if (e->is_arr() && !e->arr.empty() && e->arr[0].is_num()) s->eos = (int)e->arr[0].num;
@@ -174,8 +175,37 @@ static inline float f16_f32(uint16_t h) {
   return f;
 }
 
-bool ModelDir::read_bf16(const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
-                         std::vector<uint16_t>* out, std::string* err) const {
+// fp32 -> IEEE half bits, round to nearest even
+static inline uint16_t f32_f16(float f) {
+  uint32_t x;
+  memcpy(&x, &f, 4);
+  const uint32_t sign = (x >> 16) & 0x8000u;
+  x &= 0x7fffffffu;
+  if (x >= 0x7f800000u) return (uint16_t)(sign | 0x7c00u | (x > 0x7f800000u ? 0x200u : 0u));
+  if (x >= 0x477ff000u) return (uint16_t)(sign | 0x7c00u);
+  if (x < 0x33000001u) return (uint16_t)sign;
+  if (x < 0x38800000u) {
+    const int shift = 126 - (int)(x >> 23);
+    const uint32_t man = (x & 0x7fffffu) | 0x800000u;
+    uint32_t r = man >> shift;
+    const uint32_t rem = man & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
+    if (rem > halfway || (rem == halfway && (r & 1u))) ++r;
+    return (uint16_t)(sign | r);
+  }
+  uint32_t r = ((x - 0x38000000u) >> 13);
+  const uint32_t rem = x & 0x1fffu;
+  if (rem > 0x1000u || (rem == 0x1000u && (r & 1u))) ++r;
+  return (uint16_t)(sign | r);
+}
+static inline float bf16_f32(uint16_t b) {
+  const uint32_t u = (uint32_t)b << 16;
+  float f;
+  memcpy(&f, &u, 4);
+  return f;
+}
+
+bool ModelDir::read_16(const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1, bool f16,
+                       std::vector<uint16_t>* out, std::string* err) const {
   const HostTensor* t = find(name);
   if (!t) { *err = "missing tensor " + name; return false; }
   int64_t rows, cols;
@@ -193,14 +223,17 @@ bool ModelDir::read_bf16(const std::string& name, int64_t r0, int64_t r1, int64_
   for (int64_t r = 0; r < nr; ++r) {
     const int64_t src = (r0 + r) * cols + c0;
     uint16_t* dst = out->data() + r * nc;
-    if (t->dtype == "BF16") {
+    if (t->dtype == (f16 ? "F16" : "BF16")) {
       memcpy(dst, t->data + src * 2, (size_t)nc * 2);
     } else if (t->dtype == "F16") {
       const uint16_t* s = (const uint16_t*)t->data + src;
       for (int64_t c = 0; c < nc; ++c) dst[c] = f32_bf16(f16_f32(s[c]));
+    } else if (t->dtype == "BF16") {
+      const uint16_t* s = (const uint16_t*)t->data + src;
+      for (int64_t c = 0; c < nc; ++c) dst[c] = f32_f16(bf16_f32(s[c]));
     } else {
       const float* s = (const float*)t->data + src;
-      for (int64_t c = 0; c < nc; ++c) dst[c] = f32_bf16(s[c]);
+      for (int64_t c = 0; c < nc; ++c) dst[c] = f16 ? f32_f16(s[c]) : f32_bf16(s[c]);
     }
   }
   return true;
@@ -237,12 +270,22 @@ extern "C" int kge_model_spec_json(const kge_model_dir* m, char* out, int cap) {
   return n;
 }
 
+static int64_t model_read_16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1, bool f16,
+                             uint16_t* out, int64_t cap);
 extern "C" int64_t kge_model_read_bf16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
                                        uint16_t* out, int64_t cap) {
+  return model_read_16(m, name, r0, r1, c0, c1, false, out, cap);
+}
+extern "C" int64_t kge_model_read_f16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
+                                      uint16_t* out, int64_t cap) {
+  return model_read_16(m, name, r0, r1, c0, c1, true, out, cap);
+}
+static int64_t model_read_16(const kge_model_dir* m, const char* name, int64_t r0, int64_t r1, int64_t c0, int64_t c1, bool f16,
+                             uint16_t* out, int64_t cap) {
   if (!m || !name || !out) { kge::set_error("kge_model_read_bf16: null argument"); return -1; }
   std::vector<uint16_t> v;
   std::string err;
-  if (!m->md.read_bf16(name, r0, r1, c0, c1, &v, &err)) { kge::set_error("kge_model_read_bf16: %s", err.c_str()); return -1; }
+  if (!m->md.read_16(name, r0, r1, c0, c1, f16, &v, &err)) { kge::set_error("kge_model_read_bf16: %s", err.c_str()); return -1; }
   if ((int64_t)v.size() > cap) { kge::set_error("kge_model_read_bf16: %lld elements > capacity %lld", (long long)v.size(), (long long)cap); return -1; }
   memcpy(out, v.data(), v.size() * 2);
   return (int64_t)v.size();

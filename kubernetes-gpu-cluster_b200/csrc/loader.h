@@ -20,6 +20,7 @@ struct ModelSpec {
   double rope_factor = 0.0, rope_low = 1.0, rope_high = 4.0;   // factor 0 => no llama3 scaling
   int rope_orig_max = 8192;
   int bos = -1, eos = -1;
+  std::string torch_dtype;      // config.json torch_dtype / dtype ("float16", "bfloat16", "float32", or empty)
   bool is_opt() const { return model_type == "opt"; }
 };
 
@@ -40,7 +41,10 @@ class ModelDir {
   const HostTensor* find(const std::string& name) const;
   // Rows [r0, r1) x cols [c0, c1) of a 2-D (or all of a 1-D, r-range only) tensor as bf16 bits.
   bool read_bf16(const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1,
-                 std::vector<uint16_t>* out, std::string* err) const;
+                 std::vector<uint16_t>* out, std::string* err) const { return read_16(name, r0, r1, c0, c1, false, out, err); }
+  // The same slice as bfloat16 bits (f16 = false) or IEEE half bits (f16 = true), converted from whatever the file holds.
+  bool read_16(const std::string& name, int64_t r0, int64_t r1, int64_t c0, int64_t c1, bool f16,
+               std::vector<uint16_t>* out, std::string* err) const;
 
  private:
   struct Map { void* base; size_t len; };

@@ -9,6 +9,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int kLpThreads = 1024;
 constexpr int kLpMaxTop = 20;       // vLLM's default max_logprobs
@@ -115,11 +116,12 @@ logprobs_kernel(float* __restrict__ out_vals, int32_t* __restrict__ out_ids, int
   }
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
 
-extern "C" int kge_logprobs(float* out_vals, int32_t* out_ids, int32_t* out_rank, const void* logits,
+extern "C" int KGE_API(kge_logprobs)(float* out_vals, int32_t* out_ids, int32_t* out_rank, const void* logits,
                             const int32_t* sampled_ids, int R, int V, int ld, int top_n, void* stream) {
   KGE_REQUIRE(out_vals && out_ids && out_rank && logits && sampled_ids, "kge_logprobs: null pointer");
   KGE_REQUIRE(V > 0 && ld >= V, "kge_logprobs: V=%d ld=%d", V, ld);

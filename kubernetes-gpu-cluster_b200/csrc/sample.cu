@@ -7,6 +7,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int kSampleThreads = 1024;
 
@@ -175,16 +176,20 @@ sample_kernel(int32_t* __restrict__ out, const bf16* __restrict__ logits, int V,
   }
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
 
+#ifndef KGE_HALF
 extern "C" int64_t kge_sample_workspace_bytes(int B, int V) {
   (void)B; (void)V;
   return 0;   // thresholds are found in shared memory; kept in the ABI for a future sort path
 }
 
-extern "C" int kge_sample(int32_t* out_ids, const void* logits, int B, int V, int ld,
+#endif
+
+extern "C" int KGE_API(kge_sample)(int32_t* out_ids, const void* logits, int B, int V, int ld,
                           const float* temperature, const int32_t* top_k, const float* top_p,
                           const float* exp_noise, const uint64_t* seeds, uint64_t step, void* workspace,
                           int64_t workspace_bytes, void* stream) {

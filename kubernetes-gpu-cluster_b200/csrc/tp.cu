@@ -48,7 +48,7 @@ int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n) {
   KGE_REQUIRE(e->comm, "tensor parallel size %d but neither kge_engine_tp_connect nor kge_engine_init_tp was called", e->tp_size);
   NcclApi* api = nccl_api();
   if (!api) return -1;
-  ncclResult_t r = api->AllReduce(buf, buf, (size_t)n, ncclBfloat16, ncclSum, e->comm, e->stream);
+  ncclResult_t r = api->AllReduce(buf, buf, (size_t)n, e->f16 ? ncclFloat16 : ncclBfloat16, ncclSum, e->comm, e->stream);
   KGE_REQUIRE(r == ncclSuccess, "ncclAllReduce: %s", api->GetErrorString(r));
   pdl_break_next();        // whatever follows the NCCL kernel is launched in plain stream order
   return 0;

@@ -36,6 +36,7 @@
 #include "kge.h"
 
 namespace kge {
+inline namespace KGE_ELT_NS {
 
 constexpr int kTpMaxRanks = 16;
 constexpr int64_t kTpCtrlBytes = 4096;            // control block at the start of every window
@@ -249,6 +250,7 @@ static inline int tp_row_threads(int d) {
   return t;
 }
 
+}  // namespace KGE_ELT_NS
 }  // namespace kge
 
 using namespace kge;
@@ -263,6 +265,7 @@ struct kge_tp_comm {
   int sm_count = 148;
 };
 
+#ifndef KGE_HALF      // window management and the byte-wise gather do not depend on the element type
 extern "C" int kge_tp_comm_create(kge_tp_comm** out, int rank, int world, int device, int64_t data_bytes) {
   KGE_REQUIRE(out, "kge_tp_comm_create: null argument");
   *out = nullptr;
@@ -350,6 +353,8 @@ extern "C" int kge_tp_comm_connect(kge_tp_comm* c, const kge_tp_peer_info* all) 
 extern "C" void* kge_tp_comm_data(kge_tp_comm* c) { return c ? c->window + kTpCtrlBytes : nullptr; }
 extern "C" int kge_tp_comm_connected(const kge_tp_comm* c) { return c && c->connected ? 1 : 0; }
 
+#endif
+
 static int tp_params(const kge_tp_comm* c, TpParams* p, const char* who) {
   KGE_REQUIRE(c, "%s: null communicator", who);
   KGE_REQUIRE(c->connected, "%s: kge_tp_comm_connect has not been called", who);
@@ -358,7 +363,7 @@ static int tp_params(const kge_tp_comm* c, TpParams* p, const char* who) {
   return 0;
 }
 
-extern "C" int kge_tp_reduce_add_norm(kge_tp_comm* c, int64_t y_off, void* residual, int64_t x_off, const void* w,
+extern "C" int KGE_API(kge_tp_reduce_add_norm)(kge_tp_comm* c, int64_t y_off, void* residual, int64_t x_off, const void* w,
                                       const void* b, int T, int d, float eps, int mode, void* stream) {
   TpParams p;
   if (int rc = tp_params(c, &p, "kge_tp_reduce_add_norm")) return rc;
@@ -388,6 +393,7 @@ extern "C" int kge_tp_reduce_add_norm(kge_tp_comm* c, int64_t y_off, void* resid
   return 0;
 }
 
+#ifndef KGE_HALF
 extern "C" int kge_tp_all_gather_cols(kge_tp_comm* c, int64_t dst_off, const void* src, int R, int cols, int ld_dst, int col0,
                                       void* stream) {
   TpParams p;
@@ -407,3 +413,4 @@ extern "C" int kge_tp_all_gather_cols(kge_tp_comm* c, int64_t dst_off, const voi
   else KGE_CUDA_OK(launch_pdl(tp_all_gather_cols_kernel<false>, dim3(grid), dim3(256), 0, st, p, off, (const bf16*)src, R, cols, ld_dst, col0));
   return 0;
 }
+#endif

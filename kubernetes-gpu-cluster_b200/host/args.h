@@ -23,7 +23,7 @@ struct ServeArgs {
   double gpu_memory_utilization = 0.9;
   int max_num_seqs = 0;
   int max_num_batched_tokens = 0;
-  int block_size = 16;
+  int block_size = 64;      // tokens per KV block: one TMA box per (block, kv head, 64-column half); 16 and 32 are accepted
   int num_gpu_blocks_override = 0;
   bool enable_chunked_prefill = true;
   bool scheduler_reserve_full_isl = true;

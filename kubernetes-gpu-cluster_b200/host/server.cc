@@ -1026,8 +1026,8 @@ int main(int argc, char** argv) {
   }
   if (!a.enable_prefix_caching)
     fprintf(stderr, "INFO: prefix caching is off (--no-enable-prefix-caching): every prompt is computed in full\n");
-  if (a.dtype == "float16" || a.dtype == "half" || a.dtype == "float32")
-    fprintf(stderr, "WARNING: --dtype %s: this engine computes in bfloat16 (fp32 accumulation); checkpoints are converted at load\n", a.dtype.c_str());
+  if (a.dtype == "float32")
+    fprintf(stderr, "WARNING: --dtype float32: this engine computes in 16-bit storage with fp32 accumulation; running in bfloat16\n");
   const int sms = kge_device_sm_count();
   if (sms <= 0) { fprintf(stderr, "error: no CUDA device visible (this engine has no CPU backend)\n"); return 1; }
   const std::string dir = resolve_model(a.model);
@@ -1041,6 +1041,7 @@ int main(int argc, char** argv) {
     kge_engine_config c{};
     c.max_num_seqs = a.max_num_seqs; c.max_num_batched_tokens = a.max_num_batched_tokens;
     c.max_model_len = a.max_model_len; c.block_size = a.block_size; c.num_blocks = a.num_gpu_blocks_override;
+    c.dtype = (a.dtype == "float16" || a.dtype == "half") ? 2 : (a.dtype == "bfloat16" || a.dtype == "float32") ? 1 : 0;
     c.gpu_memory_utilization = (float)a.gpu_memory_utilization; c.tp_rank = r; c.tp_size = a.tensor_parallel_size;
     c.enable_chunked_prefill = a.enable_chunked_prefill; c.device = r;
     rcs[r] = kge_engine_create(&s.engines[r], dir.c_str(), &c, a.load_format == "dummy" ? a.seed : -1);

@@ -278,13 +278,14 @@ def make_shapes(cfg: ModelConfig) -> dict[str, tuple]:
     return s
 
 
-def save_model_dir(path: str, cfg: ModelConfig, weights: dict[str, torch.Tensor]) -> None:
+def save_model_dir(path: str, cfg: ModelConfig, weights: dict[str, torch.Tensor], torch_dtype: str = "bfloat16") -> None:
     """Write an HF-layout directory: config.json + model.safetensors (the layout the
-    reference mounts at /models/<name>, ref:values-01-minimal-example3.yaml:8,22-30)."""
+    reference mounts at /models/<name>, ref:values-01-minimal-example3.yaml:8,22-30).  torch_dtype is what config.json
+    declares (what `--dtype auto` follows); the tensors are stored in whatever dtype `weights` holds."""
     from safetensors.torch import save_file
     os.makedirs(path, exist_ok=True)
     with open(os.path.join(path, "config.json"), "w") as fh:
-        json.dump(cfg.to_hf(), fh, indent=1)
+        json.dump(dict(cfg.to_hf(), torch_dtype=torch_dtype), fh, indent=1)
     save_file({k: v.contiguous() for k, v in weights.items()},
               os.path.join(path, "model.safetensors"))
 

@@ -39,7 +39,7 @@ def test_no_cpu_fallback(kge, tmp_path):
     cfg = om.CONFIGS["tiny-llama"]
     (tmp_path / "config.json").write_text(__import__("json").dumps(cfg.to_hf()))
     h = C.c_void_p()
-    ec = kge.EngineConfig(8, 64, 128, 16, 8, 0.9, 0, 1, 1, 0)
+    ec = kge.EngineConfig(8, 64, 128, 16, 8, 0.9, 0, 1, 1, 0, 0)
     rc = kge.lib().kge_engine_create(C.byref(h), str(tmp_path).encode(), C.byref(ec), 0)
     assert rc == -2 and b"no CUDA device" in kge.lib().kge_last_error()
 
@@ -62,3 +62,19 @@ def test_rope_cache_host_matches_oracle(kge, name):
     # fp32 libm differences can move a value across a bf16 rounding boundary: allow 1 ulp on <0.1 %
     assert diff.max() <= 1, diff.max()
     assert (diff != 0).mean() < 1e-3, (diff != 0).mean()
+
+
+def test_rope_cache_host_float16(kge):
+    """The float16 twin rounds the fp32 cos/sin to IEEE half (base.py:58-61 casts the cache to the model dtype)."""
+    c = om.CONFIGS["llama-3.1-8b"]
+    rs = c.rope_scaling
+    n = 2048
+    out = np.zeros((n, c.head_dim), dtype=np.uint16)
+    rc = kge.lib().kge_rope_cache_host_f16(out.ctypes.data, n, c.head_dim, c.rope_theta, rs["factor"], rs["low_freq_factor"],
+                                           rs["high_freq_factor"], rs["original_max_position_embeddings"])
+    assert rc == 0
+    ref = om.rope_cos_sin_cache(c, n, torch.float16).view(torch.int16).numpy().astype(np.int32) & 0xFFFF
+    diff = np.abs(out.astype(np.int32) - ref)
+    # +-0 differ in the sign bit only; fp32 libm differences can cross a rounding boundary: 1 ulp on < 0.1 %
+    diff[(out.astype(np.int32) & 0x7FFF) + (ref & 0x7FFF) == 0] = 0
+    assert diff.max() <= 1 and (diff != 0).mean() < 1e-3, (diff.max(), (diff != 0).mean())

@@ -99,3 +99,27 @@ def test_bad_directories(kge, tmp_path):
     (tmp_path / "config.json").write_text(json.dumps(om.CONFIGS["tiny-llama"].to_hf()))
     (tmp_path / "model.safetensors").write_bytes(b"\xff" * 64)
     assert not L.kge_model_open(str(tmp_path).encode()) and "header" in L.kge_last_error().decode()
+
+
+def test_float16_view_of_every_source_dtype(kge, tmp_path):
+    """kge_model_read_f16: what a float16 engine uploads.  BF16, F16 and F32 tensors converted to IEEE half with round to
+    nearest even (torch's .to(float16) is the reference), including values that overflow to inf, subnormals and ties."""
+    from safetensors.torch import save_file
+    c = om.CONFIGS["tiny-llama"]
+    g = torch.Generator().manual_seed(5)
+    base = torch.randn(64, 48, generator=g)
+    special = torch.tensor([0.0, -0.0, 65504.0, 65519.9, 65520.0, 1e6, -1e6, 6.1e-5, 5.96e-8, 2.98e-8, 2.99e-8, 1e-9, 1.0009765625, 1.00048828125,
+                            1.0014648438, float("inf"), -float("inf")])
+    f32 = torch.cat([base.flatten(), special, base.flatten()[: 48 - special.numel() % 48]]).reshape(-1, 48)
+    (tmp_path / "config.json").write_text(json.dumps(c.to_hf()))
+    save_file({"a.f32": f32.contiguous(), "a.f16": f32.to(torch.float16).contiguous(), "a.bf16": f32.to(torch.bfloat16).contiguous()},
+              str(tmp_path / "model.safetensors"))
+    h = open_dir(kge, tmp_path)
+    cap = f32.numel()
+    for name, src in (("a.f32", f32), ("a.f16", f32.to(torch.float16)), ("a.bf16", f32.to(torch.bfloat16))):
+        out = np.zeros(cap, dtype=np.uint16)
+        n = kge.lib().kge_model_read_f16(h, name.encode(), 0, -1, 0, -1, out.ctypes.data, cap)
+        assert n == cap
+        ref = src.to(torch.float16).contiguous().view(torch.int16).numpy().astype(np.uint16).ravel()
+        assert np.array_equal(out, ref), (name, np.nonzero(out != ref)[0][:5])
+    kge.lib().kge_model_close(h)

@@ -98,7 +98,7 @@ def measure(gpus, workload, jobs, warm_jobs, log=lambda m: None, startup_timeout
     try:
         json.dump(hf, open(os.path.join(tmp.name, "config.json"), "w"))
         ports = [free_port() for _ in range(gpus)]
-        nblk = B * ((pin + pout + 15) // 16) + 2
+        nblk = B * ((pin + pout + 63) // 64) + 2        # the server's default KV block is 64 tokens
         for g, port in enumerate(ports):
             env = dict(os.environ, CUDA_VISIBLE_DEVICES=str(g), **(env_extra or {}))
             cmd = [os.path.join(PKG, "bin", "vllm"), "serve", tmp.name, "--host", "127.0.0.1", "--port", str(port), "--served-model-name", served,

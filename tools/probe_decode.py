@@ -12,6 +12,7 @@ from kge_loader import load  # noqa: E402
 
 kge = load()
 L = kge.lib()
+BS = int(os.environ.get("PROBE_BLOCK", "64"))
 DEFAULTS = {"gemm_ws": 1, "attn_tma": 1, "pdl": 1, "gemm_even_grid": 1, "attn_decode_splits": 0, "attn_split_balance": 0, "attn_cluster_merge": 0, "gemm_shallow": 0}
 
 
@@ -29,7 +30,7 @@ def main():
         with tempfile.TemporaryDirectory() as d:
             json.dump(hf, open(os.path.join(d, "config.json"), "w"))
             llm = kge.LLM(d, max_model_len=pin + 256 + 16, max_num_seqs=B, max_num_batched_tokens=pbatch * pin,
-                          num_gpu_blocks_override=B * ((pin + 256 + 15) // 16) + 2, load_format="dummy", seed=1234)
+                          num_gpu_blocks_override=B * ((pin + 256 + BS - 1) // BS) + 2, load_format="dummy", seed=1234, block_size=BS)
         llm.run_resident(prompts, pout, pbatch)
         res = []
         for _ in range(2):

@@ -481,6 +481,16 @@ def run_ours(args):
         except Exception as ex:
             line["tp"] = {"error": f"{type(ex).__name__}: {ex}"[:500]}
         dog.cancel()
+    if world == 1 and not args.no_http and args.workload != "c4":
+        # the same job as it is deployed: SSE clients -> kge-router -> `vllm serve` (one engine process on this GPU);
+        # a side measurement, never allowed to take the bench line down
+        try:
+            sys.path.insert(0, os.path.join(ROOT, "tools"))
+            import http_bench
+            line["http"] = http_bench.measure(1, args.workload, jobs=1, warm_jobs=1, log=log, startup_timeout=240)
+            line["http"]["vs_e2e"] = line["http"]["value"] / e2e
+        except Exception as ex:
+            line["http"] = {"error": f"{type(ex).__name__}: {ex}"[:400]}
     if rank == 0:
         if world == 1 and not args.no_cpu:
             _, line["cpu_baseline"] = cpu_reference(args.workload)
@@ -518,6 +528,7 @@ def main():
     ap.add_argument("--workload", default="c3", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--block-size", type=int, default=64, help="tokens per KV block (the server's default, 64)")
+    ap.add_argument("--no-http", action="store_true", help="at N = 1, skip the HTTP (router + server) sub-record")
     ap.add_argument("--no-tp", action="store_true", help="at N > 1, skip the tensor-parallel (config 4) sub-record")
     ap.add_argument("--tp-exchange", default="peer", choices=["peer", "nccl"], help="TP data path: peer memory (default) or NCCL")
     ap.add_argument("--tp-timeout", type=float, default=420.0, help="seconds the tensor-parallel leg may take at N > 1")

@@ -27,8 +27,22 @@ def p(t):
     return C.c_void_p(t.data_ptr()) if t is not None else None
 
 
+_KEEP = []
+
+
 def dev(t):
-    return t.cuda()
+    """Device copy that stays alive until the test ends: the C ABI gets raw pointers, so a temporary freed (and its
+    memory reused) before the kernel runs would feed the kernel somebody else's bytes."""
+    d = t.cuda()
+    _KEEP.append(d)
+    return d
+
+
+@pytest.fixture(autouse=True)
+def _release():
+    yield
+    torch.cuda.synchronize()
+    _KEEP.clear()
 
 
 def ok(kge, rc, what):

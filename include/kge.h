@@ -99,6 +99,9 @@ int64_t kge_gemm_workspace_bytes(int T, int N, int K);
  * [T,2f] intermediate never goes to HBM.  f % 64 == 0. */
 int kge_gemm_silu_gate_bf16(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
                             void* stream);
+/* the same with the optional split-K workspace of kge_gemm_bf16 (kge_gemm_workspace_bytes(T, f, K) bytes) */
+int kge_gemm_silu_gate_ws_bf16(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* workspace,
+                               int64_t workspace_bytes, void* stream);
 
 /* RoPE (neox pairing, Llama-3 scaled cache) on the q and k parts of a packed qkv buffer
  * [T,(H+2KV)*hd], in place, then scatter of k and v rows into the paged cache.
@@ -198,6 +201,8 @@ int kge_silu_mul_f16(void* y, const void* x, int T, int f, void* stream);
 int kge_gemm_f16(void* y, const void* x, const void* w, const void* bias, int T, int N, int K, int act, void* workspace,
                  int64_t workspace_bytes, void* stream);
 int kge_gemm_silu_gate_f16(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* stream);
+int kge_gemm_silu_gate_ws_f16(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* workspace,
+                              int64_t workspace_bytes, void* stream);
 int kge_rope_kvwrite_f16(void* qkv, const void* cos_sin, const int32_t* positions, const int64_t* slot_mapping,
                          void* k_cache, void* v_cache, int T, int H, int KV, int hd, int block_size, void* stream);
 int kge_rope_cache_host_f16(uint16_t* out_host, int max_pos, int hd, double theta, double factor,

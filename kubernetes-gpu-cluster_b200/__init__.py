@@ -83,6 +83,7 @@ SIGNATURES = {
     "kge_gemm_bf16": (_I, [_P, _P, _P, _P, _I, _I, _I, _I, _P, _L, _P]),
     "kge_gemm_workspace_bytes": (_L, [_I, _I, _I]),
     "kge_gemm_silu_gate_bf16": (_I, [_P, _P, _P, _I, _I, _I, _P]),
+    "kge_gemm_silu_gate_ws_bf16": (_I, [_P, _P, _P, _I, _I, _I, _P, _L, _P]),
     "kge_rope_kvwrite": (_I, [_P, _P, _P, _P, _P, _P, _I, _I, _I, _I, _I, _P]),
     "kge_rope_cache_host": (_I, [_P, _I, _I, C.c_double, C.c_double, C.c_double, C.c_double, _I]),
     "kge_paged_attn": (_I, [_P, _P, _I, _P, _P, _P, _I, _P, _P, _I, _I, _I, _I, _I, _I, _I, _I, _F, _P, _L, _P]),
@@ -156,6 +157,7 @@ SIGNATURES = {
 for _n, _t in {"kge_embed": "kge_embed_f16", "kge_rmsnorm": "kge_rmsnorm_f16", "kge_add_rmsnorm": "kge_add_rmsnorm_f16",
                "kge_head_rmsnorm": "kge_head_rmsnorm_f16", "kge_layernorm": "kge_layernorm_f16", "kge_silu_mul": "kge_silu_mul_f16",
                "kge_gemm_bf16": "kge_gemm_f16", "kge_gemm_silu_gate_bf16": "kge_gemm_silu_gate_f16",
+               "kge_gemm_silu_gate_ws_bf16": "kge_gemm_silu_gate_ws_f16",
                "kge_rope_kvwrite": "kge_rope_kvwrite_f16", "kge_rope_cache_host": "kge_rope_cache_host_f16",
                "kge_paged_attn": "kge_paged_attn_f16", "kge_argmax": "kge_argmax_f16", "kge_sample": "kge_sample_f16",
                "kge_logprobs": "kge_logprobs_f16", "kge_tp_reduce_add_norm": "kge_tp_reduce_add_norm_f16"}.items():
@@ -249,10 +251,6 @@ class Tokenizer:
     __del__ = close
 
     @property
-    def dtype(self) -> str:
-        return {1: "bfloat16", 2: "float16"}.get(lib().kge_engine_dtype(self._h), "?")
-
-    @property
     def vocab_size(self) -> int:
         return lib().kge_tokenizer_vocab_size(self._h)
 
@@ -317,6 +315,11 @@ class LLM:
             self._h = None
 
     __del__ = close
+
+    @property
+    def dtype(self) -> str:
+        """What the engine computes in: "bfloat16" or "float16" (what `dtype="auto"` settled on)."""
+        return {1: "bfloat16", 2: "float16"}.get(lib().kge_engine_dtype(self._h), "?")
 
     @property
     def num_gpu_blocks(self) -> int:

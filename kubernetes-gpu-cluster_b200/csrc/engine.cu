@@ -13,10 +13,10 @@ using namespace kge;
 namespace kge {
 
 const Ops kOpsBf16 = {kge_embed, kge_rmsnorm, kge_add_rmsnorm, kge_head_rmsnorm, kge_layernorm, kge_silu_mul, kge_gemm_bf16,
-                      kge_gemm_silu_gate_bf16, kge_rope_kvwrite, kge_rope_cache_host, kge_paged_attn, kge_argmax, kge_sample,
+                      kge_gemm_silu_gate_ws_bf16, kge_rope_kvwrite, kge_rope_cache_host, kge_paged_attn, kge_argmax, kge_sample,
                       kge_logprobs, kge_tp_reduce_add_norm};
 const Ops kOpsF16 = {kge_embed_f16, kge_rmsnorm_f16, kge_add_rmsnorm_f16, kge_head_rmsnorm_f16, kge_layernorm_f16, kge_silu_mul_f16,
-                     kge_gemm_f16, kge_gemm_silu_gate_f16, kge_rope_kvwrite_f16, kge_rope_cache_host_f16, kge_paged_attn_f16,
+                     kge_gemm_f16, kge_gemm_silu_gate_ws_f16, kge_rope_kvwrite_f16, kge_rope_cache_host_f16, kge_paged_attn_f16,
                      kge_argmax_f16, kge_sample_f16, kge_logprobs_f16, kge_tp_reduce_add_norm_f16};
 
 // 16-bit pattern of v in the engine's element type

@@ -26,7 +26,7 @@ struct Ops {
   decltype(&kge_layernorm) layernorm;
   decltype(&kge_silu_mul) silu_mul;
   decltype(&kge_gemm_bf16) gemm;
-  decltype(&kge_gemm_silu_gate_bf16) gemm_silu_gate;
+  decltype(&kge_gemm_silu_gate_ws_bf16) gemm_silu_gate;
   decltype(&kge_rope_kvwrite) rope_kvwrite;
   decltype(&kge_rope_cache_host) rope_cache_host;
   decltype(&kge_paged_attn) paged_attn;

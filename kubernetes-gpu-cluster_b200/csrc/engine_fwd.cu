@@ -145,7 +145,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       if (e->ffn_loc % 64 == 0) {
         // gate_up GEMM with the SiLU*mul in its epilogue: [T,2f] never reaches HBM
         FWD(T <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)L.up.N * L.up.K + (double)T * (L.up.K + e->ffn_loc)),
-            2.0 * T * (double)L.up.N * L.up.K, e->op->gemm_silu_gate(e->act, e->xn, L.up.w, T, e->ffn_loc, L.up.K, st));
+            2.0 * T * (double)L.up.N * L.up.K, e->op->gemm_silu_gate(e->act, e->xn, L.up.w, T, e->ffn_loc, L.up.K, e->ws_gemm, e->ws_gemm_bytes, st));
       } else {
         LINEAR(e->gu, e->xn, L.up, T, 0);
         FWD(C_ACT, (double)T * e->ffn_loc * 2 * 3, 0, e->op->silu_mul(e->act, e->gu, T, e->ffn_loc, st));

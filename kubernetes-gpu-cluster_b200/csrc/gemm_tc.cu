@@ -16,11 +16,13 @@
 // through distributed shared memory (st.shared::cluster): CTA r receives column slice r of every
 // peer, sums the S partials in rank order (deterministic), adds bias, rounds once and stores.
 // No global scratch, no atomics, no serial tail; the cluster guarantees co-scheduling.
-// Split-K through a workspace (WS; decode-sized projections when the caller provides scratch): the S CTAs of a tile are
-// ordinary CTAs with HALF an SM's shared memory each, so two are resident per SM and one CTA's prologue and epilogue
-// overlap the other's weight streaming (a 1-CTA-per-SM kernel leaves HBM idle for ~8 us per launch, profiles/
-// r02_ncu_full_gemm_split_*.csv).  fp32 partials go to the workspace (they stay in L2), and the CTA that arrives LAST on
-// the tile's counter sums them in split order (deterministic), adds bias, rounds once and stores.
+// Stream-K through a workspace (WS; decode-sized projections when the caller provides scratch): the (tile, k-block) units
+// of the whole problem are laid end to end and cut into one contiguous share per CTA, one CTA per SM - every SM streams
+// exactly 1/148 of the weights through ONE uninterrupted TMA ring, whatever the tile count (48 tiles x split 2 used 96 SMs,
+// 224 tiles used 112).  A CTA's share covers at most one partial tile at its start and one at its end: those fp32 partials
+// go to the workspace (they stay in L2) and the CTA that arrives LAST on the tile's counter sums the tile's partials in
+// k order (deterministic), applies bias / activation / SiLU-gate, rounds once and stores; whole tiles in between take the
+// ordinary epilogue.  The accumulators are double-buffered in TMEM, so all of this overlaps the next segment's main loop.
 //
 // Roofline: decode T<=256 -> HBM, algorithmic bytes = N*K*2 (weights) + T*(K+N)*2;
 //           prefill        -> tensor, 2*T*N*K flop.
@@ -149,10 +151,10 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t bar_cluster) {
 // "stage free" and "accumulator ready" arrivals to both CTAs; both epilogues release the accumulator
 // on the leader's tmem_empty barrier.
 template <int TOKN, int STAGES, bool SPLIT, bool GATED, bool PAIR = false, bool WS = false>
-__global__ void __launch_bounds__(kGemmThreads, WS ? 2 : 1)
+__global__ void __launch_bounds__(kGemmThreads, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x,
                const GemmParams p) {
-  static_assert(!(PAIR && SPLIT) && !(WS && (SPLIT || PAIR || GATED)), "one split scheme at a time");
+  static_assert(!(PAIR && SPLIT) && !(WS && (SPLIT || PAIR)), "one split scheme at a time");
   constexpr uint32_t A_BYTES = BLK_M * BLK_K * 2, B_BYTES = (PAIR ? 128 : TOKN) * BLK_K * 2;
   constexpr uint32_t STAGE_BYTES = A_BYTES + B_BYTES;
   constexpr uint32_t TMEM_COLS = (2 * TOKN < 32) ? 32 : 2 * TOKN;
@@ -205,18 +207,41 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
 
   // work decomposition: persistent round-robin over tiles, or (SPLIT) one tile per cluster with
   // the cluster rank selecting the K range
-  const int S = SPLIT ? (int)cluster_nctarank() : WS ? p.splits : 1;
-  const int crank = SPLIT ? (int)cluster_ctarank() : WS ? (int)blockIdx.x % p.splits : 0;
+  const int S = SPLIT ? (int)cluster_nctarank() : 1;
+  const int crank = SPLIT ? (int)cluster_ctarank() : 0;
   constexpr bool TWO = PAIR;
   const int mrank = TWO ? (int)cluster_ctarank() : 0;            // which tile of the weight-row pair
   const int total = (TWO ? (p.m_tiles + 1) / 2 : p.m_tiles) * p.n_tiles;
-  const int w_first = (SPLIT || WS) ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
-  const int w_step = (SPLIT || WS) ? (1 << 30) : TWO ? (int)gridDim.x / 2 : (int)gridDim.x;
+  const int w_first = SPLIT ? (int)blockIdx.x / S : TWO ? (int)blockIdx.x / 2 : (int)blockIdx.x;
+  const int w_step = SPLIT ? (1 << 30) : TWO ? (int)gridDim.x / 2 : (int)gridDim.x;
   auto m_tile_of = [&](int w) { return TWO ? 2 * (w / p.n_tiles) + mrank : w / p.n_tiles; };
   // PAIR: every TMA of a stage completes on the leader's (rank 0) full barrier
   auto lead_full = [&](int s) { return PAIR ? mapa_u32(full_bar(s), 0u) : full_bar(s); };
-  const int kb0 = crank * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+  const int kb0f = crank * p.kb_per_split, kb1f = min(p.kb_total, kb0f + p.kb_per_split);
   const int cols_per = (TOKN + S - 1) / S;               // columns finished by each cluster rank
+  // A CTA's work as a sequence of segments (tile w, k-blocks [kb0, kb1)).  Persistent / split variants: its tiles, each
+  // with the same k range.  WS (stream-K): its contiguous share [u_begin, u_end) of the tiles * kb_total units.
+  const int KB = p.kb_total;
+  const int64_t U = (int64_t)total * KB;
+  const int64_t u_begin = WS ? U * (int64_t)blockIdx.x / (int64_t)gridDim.x : 0;
+  const int64_t u_end = WS ? U * ((int64_t)blockIdx.x + 1) / (int64_t)gridDim.x : 0;
+  struct SegIter {
+    int64_t cur, end;
+    int step, KB, k0, k1;
+    __device__ __forceinline__ bool next(int& w, int& kb0, int& kb1) {
+      if (cur >= end) return false;
+      if (WS) {
+        w = (int)(cur / KB); kb0 = (int)(cur % KB);
+        const int64_t left = end - cur;
+        kb1 = (left < (int64_t)(KB - kb0)) ? kb0 + (int)left : KB;
+        cur += kb1 - kb0;
+      } else {
+        w = (int)cur; kb0 = k0; kb1 = k1; cur += step;
+      }
+      return true;
+    }
+  };
+  auto segments = [&]() { return WS ? SegIter{u_begin, u_end, 0, KB, 0, 0} : SegIter{(int64_t)w_first, (int64_t)total, w_step, KB, kb0f, kb1f}; };
   if (SPLIT) cluster_arrive();                           // phase A: every CTA of the cluster has started
 
   if (warp == 0) {
@@ -251,19 +276,25 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         if (PAIR) tma_load_2d_cg2(b_dst, &tmap_x, lead_full(st), kb * BLK_K, n_tile * TOKN + mrank * 128);
         else tma_load_2d(b_dst, &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN);
       };
-      if (w_first < total) {
-        const int m_tile = m_tile_of(w_first);
-        pre = min(STAGES, kb1 - kb0);
-        for (int i = 0; i < pre; ++i) {
-          expect(i);
-          load_a(i, kb0 + i, m_tile);
+      int w, kb0, kb1;
+      {
+        SegIter peek = segments();
+        if (peek.next(w, kb0, kb1)) {            // the first segment's first stages (a later segment's are loaded in the loop)
+          const int m_tile = m_tile_of(w);
+          pre = min(STAGES, kb1 - kb0);
+          for (int i = 0; i < pre; ++i) {
+            expect(i);
+            load_a(i, kb0 + i, m_tile);
+          }
         }
       }
       pdl_wait();
-      for (int w = w_first; w < total; w += w_step) {
+      SegIter it = segments();
+      bool first_seg = true;
+      while (it.next(w, kb0, kb1)) {
         const int n_tile = w % p.n_tiles, m_tile = m_tile_of(w);
         for (int kb = kb0; kb < kb1; ++kb) {
-          if (w == w_first && kb - kb0 < pre) {
+          if (first_seg && kb - kb0 < pre) {
             load_b(stage, kb, n_tile);
           } else {
             mbar_wait(empty_bar(stage), phase ^ 1);
@@ -273,13 +304,16 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
           }
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
+        first_seg = false;
       }
     }
   } else if (warp == 1) {
     if (lane == 0 && (!PAIR || mrank == 0)) {          // PAIR: the leader issues for both CTAs
       int stage = 0; uint32_t phase = 0;
       int acc = 0; uint32_t acc_phase = 0;
-      for (int w = w_first; w < total; w += w_step) {
+      SegIter it = segments();
+      int w, kb0, kb1;
+      while (it.next(w, kb0, kb1)) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * TOKN;
@@ -315,7 +349,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       }
       asm volatile("bar.sync 1, 128;" ::: "memory");
     }
-    for (int w = w_first; w < total; w += w_step) {
+    SegIter it = segments();
+    int w, kb0, kb1;
+    while (it.next(w, kb0, kb1)) {
       const int n_tile = w % p.n_tiles, m_tile = m_tile_of(w);
       const int n = m_tile * ROWS_OUT + (GATED ? (et & 63) : et);   // output column of this thread's row
       const int t0 = n_tile * TOKN;
@@ -323,9 +359,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       tc_fence_after();
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
       const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
-      if (WS) {
-        // this split's fp32 partial tile -> workspace, [column][128 rows]: a warp stores 128 consecutive bytes per column
-        float* part = p.ws_part + ((int64_t)(w * S + crank) * TOKN) * BLK_M;
+      if (WS && (kb0 != 0 || kb1 != KB)) {
+        // ---- stream-K: this segment is only part of tile w's k range.  Its fp32 partial goes to the workspace
+        // ([column][128 rows]: a warp stores 128 consecutive bytes per column); slot 0 of a CTA holds the partial that
+        // STARTS its share, slot 1 the one that ends it.
+        const int slot = ((int64_t)w * KB + kb0 == u_begin) ? 0 : 1;
+        float* part = p.ws_part + ((int64_t)(blockIdx.x * 2 + slot) * TOKN) * BLK_M;
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
           uint32_t r[16];
@@ -334,7 +373,74 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
           for (int j = 0; j < 16; ++j) part[(c + j) * BLK_M + et] = __uint_as_float(r[j]);
         }
         tc_fence_before();
-        __threadfence();                         // the partial is visible device-wide before this CTA arrives on the counter
+        __syncwarp();
+        if (lane == 0) mbar_arrive(tempty_bar(acc));       // the accumulator is free: the next segment's MMAs may start
+        __threadfence();                                   // the partial is visible device-wide before this CTA arrives
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        // which CTAs hold a part of tile w: the one containing its first unit ... the one containing its last unit
+        const int64_t G = gridDim.x, x0 = (int64_t)w * KB, x1 = x0 + KB - 1;
+        const int c_first = (int)(((x0 + 1) * G + U - 1) / U - 1), c_last = (int)(((x1 + 1) * G + U - 1) / U - 1);
+        int* s_last = reinterpret_cast<int*>(tmem_slot + 1);
+        if (et == 0) *s_last = (atomicAdd(p.ws_count + w, 1u) == (unsigned)(c_last - c_first)) ? 1 : 0;
+        asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (*s_last) {
+          // the LAST contributor to arrive reduces the tile: partials summed in k order (fixed), then the usual epilogue
+          __threadfence();
+          constexpr int QUADS = GATED ? 16 : 32;           // 4 consecutive weight rows per thread (GATED: + their up rows)
+          constexpr int NGRP = 128 / QUADS;                // column groups
+          constexpr int CPG = TOKN / NGRP;                 // columns per group
+          constexpr int CH = CPG < 8 ? CPG : 8;            // columns held in registers at a time
+          const int quad = et % QUADS, grp = et / QUADS;
+          const int n0 = m_tile * ROWS_OUT + quad * 4;
+          float bv4[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) bv4[k] = (p.bias && n0 + k < p.N) ? bf2f(p.bias[n0 + k]) : 0.f;
+          const bool vec = (p.N & 3) == 0 && n0 + 3 < p.N;
+#pragma unroll 1
+          for (int cb = grp * CPG; cb < (grp + 1) * CPG; cb += CH) {
+            float a[CH][4], u[GATED ? CH : 1][4];
+#pragma unroll
+            for (int ci = 0; ci < CH; ++ci) {
+              a[ci][0] = a[ci][1] = a[ci][2] = a[ci][3] = 0.f;
+              if (GATED) { u[ci][0] = u[ci][1] = u[ci][2] = u[ci][3] = 0.f; }
+            }
+            for (int cc = c_first; cc <= c_last; ++cc) {
+              const int sl = (U * cc / G >= x0) ? 0 : 1;     // that CTA's share starts inside this tile: its slot 0
+              const float* src = p.ws_part + ((int64_t)(cc * 2 + sl) * TOKN + cb) * BLK_M + quad * 4;
+#pragma unroll
+              for (int ci = 0; ci < CH; ++ci) {
+                const float4 v = __ldcg(reinterpret_cast<const float4*>(src + ci * BLK_M));
+                a[ci][0] += v.x; a[ci][1] += v.y; a[ci][2] += v.z; a[ci][3] += v.w;
+                if (GATED) {
+                  const float4 v2 = __ldcg(reinterpret_cast<const float4*>(src + ci * BLK_M + 64));
+                  u[ci][0] += v2.x; u[ci][1] += v2.y; u[ci][2] += v2.z; u[ci][3] += v2.w;
+                }
+              }
+            }
+#pragma unroll
+            for (int ci = 0; ci < CH; ++ci) {
+              const int t = t0 + cb + ci;
+              if (t < p.T) {
+                float o[4];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                  if (GATED) o[k] = silu_gate_bf16(a[ci][k], u[ci][k]);
+                  else { o[k] = a[ci][k] + bv4[k]; if (p.act == 1) o[k] = fmaxf(o[k], 0.f); }
+                }
+                bf16* dst = p.y + (int64_t)t * p.N + n0;
+                if (vec) {
+                  uint2 w2;
+                  w2.x = pack_bf2(o[0], o[1]); w2.y = pack_bf2(o[2], o[3]);
+                  *reinterpret_cast<uint2*>(dst) = w2;
+                } else {
+#pragma unroll
+                  for (int k = 0; k < 4; ++k) if (n0 + k < p.N) dst[k] = f2bf(o[k]);
+                }
+              }
+            }
+          }
+          if (et == 0) p.ws_count[w] = 0;                  // ready for the next launch
+        }
       } else if (!SPLIT && !GATED) {
 #pragma unroll 1
         for (int c = 0; c < TOKN; c += 16) {
@@ -429,54 +535,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     cluster_arrive();
     cluster_wait();
   }
-  if (WS) {
-    // Whichever CTA of the tile arrives last reduces it, with all 256 threads: thread = (4 consecutive weight rows,
-    // TOKN/8 token columns); partials are summed in split order, so the result does not depend on who came last.
-    int* s_last = reinterpret_cast<int*>(tmem_slot + 1);
-    __syncthreads();
-    if (threadIdx.x == 0) *s_last = (atomicAdd(p.ws_count + w_first, 1u) == (unsigned)S - 1u) ? 1 : 0;
-    __syncthreads();
-    if (*s_last) {
-      __threadfence();
-      constexpr int CPG = TOKN / 8;
-      const int quad = threadIdx.x & 31, grp = threadIdx.x >> 5;
-      const int m_tile = w_first / p.n_tiles, n_tile = w_first % p.n_tiles;
-      const int n0 = m_tile * BLK_M + quad * 4, t0 = n_tile * TOKN, c0 = grp * CPG;
-      float acc[CPG][4];
-#pragma unroll
-      for (int ci = 0; ci < CPG; ++ci) { acc[ci][0] = acc[ci][1] = acc[ci][2] = acc[ci][3] = 0.f; }
-      const float* base = p.ws_part + ((int64_t)w_first * S * TOKN + c0) * BLK_M + quad * 4;
-      for (int s2 = 0; s2 < S; ++s2) {
-#pragma unroll
-        for (int ci = 0; ci < CPG; ++ci) {
-          const float4 v = __ldcg(reinterpret_cast<const float4*>(base + ((int64_t)s2 * TOKN + ci) * BLK_M));
-          acc[ci][0] += v.x; acc[ci][1] += v.y; acc[ci][2] += v.z; acc[ci][3] += v.w;
-        }
-      }
-      float bv4[4];
-#pragma unroll
-      for (int k = 0; k < 4; ++k) bv4[k] = (p.bias && n0 + k < p.N) ? bf2f(p.bias[n0 + k]) : 0.f;
-      const bool vec = (p.N & 3) == 0 && n0 + 3 < p.N;
-#pragma unroll
-      for (int ci = 0; ci < CPG; ++ci) {
-        const int t = t0 + c0 + ci;
-        if (t >= p.T) break;
-        float o[4];
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { o[k] = acc[ci][k] + bv4[k]; if (p.act == 1) o[k] = fmaxf(o[k], 0.f); }
-        bf16* dst = p.y + (int64_t)t * p.N + n0;
-        if (vec) {
-          uint2 w2;
-          w2.x = pack_bf2(o[0], o[1]); w2.y = pack_bf2(o[2], o[3]);
-          *reinterpret_cast<uint2*>(dst) = w2;
-        } else {
-#pragma unroll
-          for (int k = 0; k < 4; ++k) if (n0 + k < p.N) dst[k] = f2bf(o[k]);
-        }
-      }
-      if (threadIdx.x == 0) p.ws_count[w_first] = 0;      // ready for the next launch
-    }
-  }
   tc_fence_before();
   __syncthreads();
   if (PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
@@ -562,7 +620,6 @@ constexpr int kSlotsShallow = 2 * 148;
 
 template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool SHALLOW = false, bool WS = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
-  static_assert(!WS || SHALLOW, "the workspace split runs two CTAs per SM");
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
   constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
@@ -582,7 +639,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   attr[0].val.programmaticStreamSerializationAllowed = pdl_for_this_launch() ? 1 : 0;
   cfg.attrs = attr; cfg.numAttrs = 1;
   if (WS) {
-    cfg.gridDim = dim3(tiles * p.splits);        // CTA = (tile, split), no cluster: CTAs are placed wherever a half SM is free
+    cfg.gridDim = dim3(p.splits);                // stream-K: `splits` CTAs (one per SM), each a contiguous share of all k-blocks
   } else if (SPLIT) {
     cfg.gridDim = dim3(tiles * p.splits);
     attr[1].id = cudaLaunchAttributeClusterDimension;
@@ -660,13 +717,11 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M, bool ws_ok 
   const int tiles = g.m_tiles * g.n_tiles;
   int splits = 1;
   const int slots = gemm_shallow(g.tokn) ? kSlotsShallow : 148;      // CTAs that can be resident at once
-  if (ws_ok && rows_out == BLK_M && g.tokn <= 128 && tiles <= 148 && tunable(TUN_GEMM_WS)) {
-    // about two CTAs per SM in one wave, each with at least 4 k-blocks (256 of K)
-    int s = kSlotsShallow / tiles;
-    const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;
-    if (s > max_by_k) s = max_by_k;
-    if (s > 32) s = 32;
-    if (s >= 2) { g.ws = true; splits = s; }
+  if (ws_ok && g.tokn <= 128 && tiles <= (int)(kWsCounterBytes / 4) && tiles % 148 != 0 && tunable(TUN_GEMM_WS)) {
+    // stream-K: one CTA per SM, every CTA the same number of k-blocks (at least 4, i.e. 256 of K)
+    const int64_t units = (int64_t)tiles * g.kb_total;
+    int ctas = units / 4 < 148 ? (int)(units / 4) : 148;
+    if (ctas >= 2) { g.ws = true; splits = ctas; }
   }
   if (!g.ws && tiles <= slots / 2 && g.tokn <= 128) {
     int smax = slots / tiles;                   // never more CTAs than resident slots
@@ -676,6 +731,7 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M, bool ws_ok 
     for (int s = smax; s >= 2; --s)             // largest S whose clusters all fit in ONE wave
       if (tiles <= max_clusters(g.tokn, s)) { splits = s; break; }
   }
+  if (g.ws) { g.kb_per_split = g.kb_total; g.splits = splits; return g; }      // `splits` carries the grid size
   g.kb_per_split = (g.kb_total + splits - 1) / splits;
   g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;   // drop empty splits
   return g;
@@ -686,14 +742,12 @@ static bool gemm_uses_pair(const GemmPlan& g) { return g.tokn == 256 && g.splits
 
 template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
-  if constexpr (!GATED) {
-    if (g.ws) {
-      switch (g.tokn) {
-        case 16: return launch_gemm<16, false, false, false, true, true>(tw, tx, p, st);
-        case 32: return launch_gemm<32, false, false, false, true, true>(tw, tx, p, st);
-        case 64: return launch_gemm<64, false, false, false, true, true>(tw, tx, p, st);
-        default: return launch_gemm<128, false, false, false, true, true>(tw, tx, p, st);
-      }
+  if (g.ws) {
+    switch (g.tokn) {
+      case 16: return launch_gemm<16, false, GATED, false, false, true>(tw, tx, p, st);
+      case 32: return launch_gemm<32, false, GATED, false, false, true>(tw, tx, p, st);
+      case 64: return launch_gemm<64, false, GATED, false, false, true>(tw, tx, p, st);
+      default: return launch_gemm<128, false, GATED, false, false, true>(tw, tx, p, st);
     }
   }
   if (gemm_shallow(g.tokn)) {
@@ -734,14 +788,17 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
 
 using namespace kge;
 
-static int64_t ws_bytes_of(const GemmPlan& g) {
-  return g.ws ? kWsCounterBytes + (int64_t)g.m_tiles * g.n_tiles * g.splits * g.tokn * BLK_M * 4 : 0;
+static int64_t ws_bytes_of(const GemmPlan& g) {        // counters + two partial tiles per CTA
+  return g.ws ? kWsCounterBytes + (int64_t)g.splits * 2 * g.tokn * BLK_M * 4 : 0;
 }
 
 #ifndef KGE_HALF      // the same for both element types: exported once
 extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
   if (T <= 0 || N <= 0 || K <= 0) return 0;
-  return ws_bytes_of(plan_gemm(T, N, K, BLK_M, true));      // 0: this shape does not split K through a workspace
+  // enough for the plain projection and for the fused SiLU-gate one with f = N (64 output rows per tile); 0: this shape
+  // does not go through a workspace
+  const int64_t a = ws_bytes_of(plan_gemm(T, N, K, BLK_M, true)), b = ws_bytes_of(plan_gemm(T, N, K, 64, true));
+  return a > b ? a : b;
 }
 
 #endif
@@ -749,9 +806,11 @@ extern "C" int64_t kge_gemm_workspace_bytes(int T, int N, int K) {
 #ifdef KGE_HALF
 #define KGE_GEMM_NAME kge_gemm_f16
 #define KGE_GEMM_GATE_NAME kge_gemm_silu_gate_f16
+#define KGE_GEMM_GATE_WS_NAME kge_gemm_silu_gate_ws_f16
 #else
 #define KGE_GEMM_NAME kge_gemm_bf16
 #define KGE_GEMM_GATE_NAME kge_gemm_silu_gate_bf16
+#define KGE_GEMM_GATE_WS_NAME kge_gemm_silu_gate_ws_bf16
 #endif
 extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* bias, int T, int N, int K,
                              int act, void* workspace, int64_t workspace_bytes, void* stream) {
@@ -761,7 +820,7 @@ extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* 
   KGE_REQUIRE(act == 0 || act == 1, "kge_gemm_bf16: act=%d unsupported", act);
   if (T == 0) return 0;
   GemmPlan g = plan_gemm(T, N, K, BLK_M, workspace != nullptr);
-  if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0 || g.m_tiles * g.n_tiles > (int)(kWsCounterBytes / 4)))
+  if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0))
     g = plan_gemm(T, N, K);                        // scratch too small for this shape: split K inside a cluster instead
   GemmParams p;
   p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
@@ -776,21 +835,27 @@ extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* 
   return dispatch_gemm<false>(g, tw, tx, p, st);
 }
 
-extern "C" int KGE_GEMM_GATE_NAME(void* y, const void* x, const void* w_gate_up, int T, int f, int K,
-                                       void* stream) {
+extern "C" int KGE_GEMM_GATE_WS_NAME(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* workspace,
+                                    int64_t workspace_bytes, void* stream) {
   KGE_REQUIRE(y && x && w_gate_up, "kge_gemm_silu_gate_bf16: null pointer");
   KGE_REQUIRE(T >= 0 && f > 0 && K > 0 && K % 8 == 0, "kge_gemm_silu_gate_bf16: K=%d must be a positive multiple of 8", K);
   KGE_REQUIRE(f % 64 == 0, "kge_gemm_silu_gate_bf16: f=%d must be a multiple of 64", f);
   KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_gate_up & 15) == 0, "kge_gemm_silu_gate_bf16: x and w must be 16-byte aligned");
   if (T == 0) return 0;
-  const GemmPlan g = plan_gemm(T, f, K, 64);
+  GemmPlan g = plan_gemm(T, f, K, 64, workspace != nullptr);
+  if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0)) g = plan_gemm(T, f, K, 64);
   GemmParams p;
   p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
-  p.ws_count = nullptr; p.ws_part = nullptr;
+  p.ws_count = g.ws ? (unsigned int*)workspace : nullptr;
+  p.ws_part = g.ws ? (float*)((uint8_t*)workspace + kWsCounterBytes) : nullptr;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
   p.kb_total = g.kb_total; p.kb_per_split = g.kb_per_split;
   CUtensorMap tw, tx;
   if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, 64)) return rc;     // 64-row boxes: gate half, up half
   if (int rc = make_tmap(&tx, x, T, K, gemm_uses_pair(g) ? 128 : g.tokn)) return rc;
   return dispatch_gemm<true>(g, tw, tx, p, (cudaStream_t)stream);
+}
+
+extern "C" int KGE_GEMM_GATE_NAME(void* y, const void* x, const void* w_gate_up, int T, int f, int K, void* stream) {
+  return KGE_GEMM_GATE_WS_NAME(y, x, w_gate_up, T, f, K, nullptr, 0, stream);
 }

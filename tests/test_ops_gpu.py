@@ -294,29 +294,64 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
         assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 3e-3
 
 
-@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 128])
-def test_gemm_split_k_variants_agree(kge, L, T, N, K, bias, act):
-    """Decode-sized shapes split K two ways - through the caller's workspace (two CTAs per SM, last CTA reduces) or, with no
-    workspace, inside a thread-block cluster over distributed shared memory.  Both sum fp32 partials in a fixed order, so
-    each is deterministic; they differ from each other only by that order (<= 1 bf16 ulp on a few outputs).  A workspace
-    that is too small must fall back to the cluster split, not fail."""
+@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 128] + [(64, 6144, 4096, True, 1), (33, 14336, 4096, False, 0), (100, 4096, 14336, False, 0)])
+def test_gemm_stream_k_through_a_workspace(kge, L, T, N, K, bias, act):
+    """Knob gemm_ws: decode-sized shapes as stream-K - one CTA per SM, each a contiguous share of all (tile, k-block) units,
+    partial tiles reduced through the caller's workspace by the last CTA to arrive - against fp32 torch and against the
+    default (cluster split-K / persistent tiles).  Partials are summed in k order, so the result is the same bits on every
+    call; it differs from the default only by fp32 summation order.  A workspace that is too small must fall back, not fail."""
     g = torch.Generator().manual_seed(T + N + K)
-    x = dev(torch.randn(T, K, generator=g).to(BF))
-    w = dev((torch.randn(N, K, generator=g) * 0.05).to(BF))
-    b = dev(torch.randn(N, generator=g).to(BF)) if bias else None
-    nws = L.kge_gemm_workspace_bytes(T, N, K)
-    ws = torch.zeros(max(nws, 16), dtype=torch.uint8, device="cuda")
+    xh = torch.randn(T, K, generator=g).to(BF)
+    wh = (torch.randn(N, K, generator=g) * 0.05).to(BF)
+    bh = torch.randn(N, generator=g).to(BF) if bias else None
+    x, w, b = dev(xh), dev(wh), (dev(bh) if bias else None)
     outs = []
-    for (wsp, nb) in ((p(ws), nws), (p(ws), nws), (None, 0), (p(ws), 2048 if nws > 2048 else 0)):
-        y = torch.full((T, N), float("nan"), dtype=BF, device="cuda")
-        check_ok(kge, L.kge_gemm_bf16(p(y), p(x), p(w), p(b) if bias else None, T, N, K, act, wsp, nb, None), "gemm")
-        sync()
-        outs.append(y.cpu())
+    try:
+        check_ok(kge, L.kge_set_tunable(b"gemm_ws", 1), "tunable")
+        nws = L.kge_gemm_workspace_bytes(T, N, K)
+        ws = torch.zeros(max(nws, 16), dtype=torch.uint8, device="cuda")
+        for (wsp, nb) in ((p(ws), nws), (p(ws), nws), (None, 0), (p(ws), 2048 if nws > 2048 else 0)):
+            y = torch.full((T, N), float("nan"), dtype=BF, device="cuda")
+            check_ok(kge, L.kge_gemm_bf16(p(y), p(x), p(w), p(b) if bias else None, T, N, K, act, wsp, nb, None), "gemm")
+            sync()
+            outs.append(y.cpu())
+    finally:
+        L.kge_set_tunable(b"gemm_ws", 0)
     assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))          # workspace path: same bits every time
     assert torch.equal(outs[2].view(torch.int16), outs[3].view(torch.int16))          # too-small scratch == no scratch
     assert int(ws[:1024].max().item()) == 0                                            # the counters were left at zero
-    d = (outs[0].float() - outs[2].float()).abs()
-    assert (d <= 1.6e-2 * outs[2].float().abs() + 1e-3 * outs[2].float().abs().max()).all()
+    ref = gemm_ref(xh, wh, bh, act)
+    for o in (outs[0], outs[2]):
+        err = (o.float() - ref).abs()
+        assert (err <= 1e-3 * ref.abs().max().item() + 1.6e-2 * ref.abs()).all(), err.max().item()
+
+
+@pytest.mark.parametrize("T,f,K", [(64, 14336, 4096), (16, 3584, 8192), (64, 1024, 512), (128, 7168, 2048)])
+def test_gemm_silu_gate_stream_k(kge, L, T, f, K):
+    """The fused SiLU-gate projection through the stream-K path (knob gemm_ws): partial tiles carry gate AND up rows, the
+    reducing CTA applies silu(gate) * up after the sum - same cast points, so the same tolerance as the direct epilogue."""
+    g = torch.Generator().manual_seed(T + f + K)
+    x = dev(torch.randn(T, K, generator=g).to(BF))
+    w = dev((torch.randn(2 * f, K, generator=g) * 0.05).to(BF))
+    outs = []
+    try:
+        check_ok(kge, L.kge_set_tunable(b"gemm_ws", 1), "tunable")
+        nws = L.kge_gemm_workspace_bytes(T, f, K)
+        assert nws > 1024
+        ws = torch.zeros(nws, dtype=torch.uint8, device="cuda")
+        for (wsp, nb) in ((p(ws), nws), (p(ws), nws), (None, 0)):
+            y = torch.full((T, f), float("nan"), dtype=BF, device="cuda")
+            check_ok(kge, L.kge_gemm_silu_gate_ws_bf16(p(y), p(x), p(w), T, f, K, wsp, nb, None), "gemm_silu_gate_ws")
+            sync()
+            outs.append(y.cpu())
+    finally:
+        L.kge_set_tunable(b"gemm_ws", 0)
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
+    gu = (x.cpu().float() @ w.cpu().float().t()).to(BF)
+    ref = om.silu_and_mul(gu).float()
+    for o in outs:
+        err = (o.float() - ref).abs()
+        assert (err <= 4e-3 * ref.abs().max().item() + 3.2e-2 * ref.abs()).all(), err.max().item()
 
 
 EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
@@ -367,9 +402,13 @@ def test_gemm_rejects_bad_arguments(kge, L):
     assert L.kge_gemm_bf16(p(x), None, p(x), None, 4, 4, 64, 0, None, 0, None) == -1       # null x
     assert L.kge_gemm_bf16(p(x), p(x), p(x), None, 4, 4, 64, 7, None, 0, None) == -1       # unknown act
     assert b"act" in L.kge_last_error()
-    assert L.kge_gemm_workspace_bytes(64, 28672, 4096) == 0     # 224 tiles: persistent, no split-K, no scratch
-    assert L.kge_gemm_workspace_bytes(8192, 4096, 4096) == 0    # prefill-sized: CTA pairs
-    assert L.kge_gemm_workspace_bytes(1, 768, 4096) > 1024      # decode-sized: split-K through the workspace
+    assert L.kge_gemm_workspace_bytes(8192, 4096, 4096) == 0    # prefill-sized: CTA pairs, no scratch
+    try:
+        L.kge_set_tunable(b"gemm_ws", 1)
+        assert L.kge_gemm_workspace_bytes(1, 768, 4096) > 1024      # decode-sized: stream-K through the workspace
+        assert L.kge_gemm_workspace_bytes(64, 128256, 4096) == 0    # 1002 tiles: persistent tiles already balance
+    finally:
+        L.kge_set_tunable(b"gemm_ws", 0)
 
 
 # ------------------------------------------------------------------------------ attention

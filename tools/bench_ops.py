@@ -113,8 +113,12 @@ if __name__ == "__main__":
     ap.add_argument("what", choices=["gemm", "attn", "prefill"])
     ap.add_argument("--cublas", action="store_true")
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--knob", action="append", default=[], help="name=value launch-shape knob (kge_set_tunable), repeatable")
     a = ap.parse_args()
     kge.require_cuda()
+    for kv in a.knob:
+        k, v = kv.split("=")
+        kge.check(L.kge_set_tunable(k.encode(), int(v)), "kge_set_tunable")
     if a.what == "gemm":
         shapes = [(64, 6144, 4096), (64, 4096, 4096), (64, 28672, 4096), (64, 4096, 14336), (64, 128256, 4096),
                   (32, 3072, 2048), (32, 16384, 2048), (32, 2048, 8192),

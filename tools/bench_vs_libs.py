@@ -72,12 +72,25 @@ def gemm_rows():
             kge.check(L.kge_gemm_bf16(y.data_ptr(), x.data_ptr(), ws[i % ncopies].data_ptr(), None, T, N, K, 0, None, 0, st), "gemm")
         it = 20 if T > 256 else 60
         ms = time_ms(ours, it)
+        ms_sk = None
+        if T <= 128:          # the stream-K variant (knob gemm_ws) next to the default
+            L.kge_set_tunable(b"gemm_ws", 1)
+            nws = L.kge_gemm_workspace_bytes(T, N, K)
+            if nws:
+                wsb = torch.zeros(nws, dtype=torch.uint8, device="cuda")
+
+                def ours_sk(i, st):
+                    kge.check(L.kge_gemm_bf16(y.data_ptr(), x.data_ptr(), ws[i % ncopies].data_ptr(), None, T, N, K, 0, wsb.data_ptr(), nws, st), "gemm")
+                ms_sk = time_ms(ours_sk, it)
+            L.kge_set_tunable(b"gemm_ws", 0)
         ms2 = time_ms(lambda i, st: torch.matmul(x, ws[i % ncopies].t(), out=y), it)
         by, fl = 2.0 * (N * K + T * K + T * N), 2.0 * T * N * K
         rows.append({"T": T, "N": N, "K": K, "kge_ms": round(ms, 4), "cublas_ms": round(ms2, 4),
                      "kge_TFLOP/s": round(fl / ms / 1e9, 1), "cublas_TFLOP/s": round(fl / ms2 / 1e9, 1),
                      "kge_GB/s": round(by / ms / 1e6, 1), "cublas_GB/s": round(by / ms2 / 1e6, 1),
                      "winner": "kge" if ms <= ms2 else "cublas"})
+        if ms_sk is not None:
+            rows[-1]["kge_stream_k_ms"] = round(ms_sk, 4)
         print(json.dumps(rows[-1]), flush=True)
         del ws
     return rows

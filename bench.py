@@ -3,10 +3,11 @@
 
   python bench.py --gpus N --steps K --warmup W [--workload c3|c2|c1] [--impl ours|reference]
 
-A "step" is one whole job of the workload: every request prefilled (2k-token prompts, whole
-prompts, 8192 tokens per engine step) and decoded greedily to its output length.
-  value  device-resident replay: all step metadata is in HBM before the timed region, sampled ids
-         feed the next step on the device, CUDA events on the engine's stream (kge_engine_run_resident).
+A "step" is one whole job of the workload: every request prefilled (2k-token prompts, 8192 tokens
+per engine step as the continuous-batching scheduler cuts them) and decoded greedily to its output length.
+  value  device-resident replay of exactly the steps the scheduler made for that job: all step metadata is in HBM
+         before the timed region, sampled ids feed the next step on the device, CUDA events on the engine's stream
+         (kge_engine_record_steps / kge_engine_replay_recorded).  Same steps, so the same tokens as `e2e`.
   e2e    the same job through the public API (LLM.generate -> C++ continuous-batching scheduler):
          host token lists in, host token lists out; every engine step copies its metadata from pinned
          host memory and reads the sampled ids back, both inside the timed region.
@@ -367,10 +368,18 @@ def run_ours(args):
     def mx(x):
         return max_over_ranks(x, world)
 
-    # ---- value: device-resident replay
+    # ---- value: device-resident replay of the job's own steps.  One job goes through the public API with recording on;
+    # the replay then runs exactly the steps the scheduler made (same batches, block tables and kernels) with all metadata
+    # in HBM and sampled ids handed from step to step on the device, CUDA events on the engine's stream.
+    llm.record_steps(True)
+    outs_rec = llm.generate(prompts, sp)
+    llm.record_steps(False)
+    rec_ids = [o.request_id for o in outs_rec]
+    toks_rec = [o.outputs[0].token_ids for o in outs_rec]
+    cap = B * pout + 64
     for i in range(args.warmup):
-        toks_res, ms_w, _ = llm.run_resident(prompts, pout, pbatch)
-        log(f"resident warm-up {i}: {ms_w:.0f} ms")
+        _, n_steps, ms_w, _ = llm.replay_recorded(cap)
+        log(f"replay warm-up {i}: {ms_w:.0f} ms, {n_steps} steps")
     barrier()
     clocks = ClockSampler(local)
     clocks.start()
@@ -378,20 +387,25 @@ def run_ours(args):
     ms_total = dec_total = 0.0
     t_wall0 = time.perf_counter()
     for _ in range(args.steps):
-        toks_res, ms, dms = llm.run_resident(prompts, pout, pbatch)
+        rep, n_steps, ms, dms = llm.replay_recorded(cap)
         ms_total += ms
         dec_total += dms
     barrier()
     wall_resident = time.perf_counter() - t_wall0
     launches = llm.kernel_launches - l0
     clk = clocks.summary()
+    toks_res = [rep[r] for r in rec_ids]
     ms_step = mx(ms_total / args.steps)
-    dec_ms_step = mx(dec_total / args.steps)
     value = job_throughput(replicas, B, pout, ms_step * 1e-3)
+    # fixed-shape companion (whole prompts, pbatch per step, then full-batch decode): the decode step at full batch
+    llm.run_resident(prompts, pout, pbatch)
+    _, ms_fix, dms_fix = llm.run_resident(prompts, pout, pbatch)
+    dec_ms_step = mx(dms_fix)
+    fixed_shape = {"what": f"{B // pbatch} prefill steps of {pbatch} whole prompts, then {pout - 1} decode steps of all {B} requests (kge_engine_run_resident)",
+                   "ms_per_job": mx(ms_fix), "value": job_throughput(replicas, B, pout, mx(ms_fix) * 1e-3), "decode_ms_per_step": dec_ms_step / max(1, pout - 1),
+                   "prefill_ms_per_step": (mx(ms_fix) - dec_ms_step) / (B / pbatch)}
 
     # ---- e2e: public API with host buffers, scheduler-driven, per-step H2D/D2H inside the timing
-    for _ in range(min(args.warmup, 1)):
-        llm.generate(prompts, sp)
     io0 = llm.io_bytes()
     barrier()
     t0 = time.perf_counter()
@@ -404,8 +418,10 @@ def run_ours(args):
     log(f"value {value:.0f} tok/s, e2e {e2e:.0f} tok/s")
     toks_e2e = [o.outputs[0].token_ids for o in outs]
     same = sum(a == b for x, y in zip(toks_e2e, toks_res) for a, b in zip(x, y))
-    divergence = classify_divergences(kge, llm, prompts, pout, toks_e2e, toks_res)
-    log(f"legs: {divergence}")
+    # both legs run the same steps, so their tokens must be the same; if they ever differ, say where and how closely
+    divergence = classify_divergences(kge, llm, prompts, pout, toks_e2e, toks_res) if same != B * pout else \
+        {"requests": B, "first_divergences": 0, "not_near_tie": 0, "recorded_job_equal_to_timed_job": toks_rec == toks_e2e}
+    log(f"legs: {same}/{B * pout} tokens equal; {divergence}")
 
     # ---- latency (extra job through the public API; BASELINE.json's metric also names p50 TTFT and ITL)
     try:
@@ -454,7 +470,8 @@ def run_ours(args):
                                    else f"dp{world} (independent replicas, no collective)"),
                    "l2": "every step streams weights + KV >> 126 MB L2 (inputs larger than L2, no flush needed)",
                    "prefix_caching": "off: every job recomputes every prompt (the same prompts are replayed each step)"},
-        "decode_ms_per_step": dec_ms_step, "decode_ms_per_token_step": dec_ms_step / max(1, pout - 1),
+        "steps_per_job": n_steps, "trailing_decode_ms": mx(dec_total / args.steps), "fixed_shape": fixed_shape,
+        "decode_ms_per_token_step": fixed_shape["decode_ms_per_step"],
         "e2e": {"value": e2e, "unit": "output tokens/s", "h2d_bytes_per_step": (io1[0] - io0[0]) // args.steps,
                 "d2h_bytes_per_step": (io1[1] - io0[1]) // args.steps, "ms_per_step": e2e_s * 1e3,
                 "timer": "host wall clock between device synchronisations; includes the C++ scheduler",

@@ -44,6 +44,8 @@ int kge_device_sm_count(void);
  *   "gemm_ws" 0/1             1 = decode-sized projections split K over ordinary CTAs, two per SM, reduced through the caller's
  *                             workspace by the last CTA to arrive (faster alone, 19.5 vs 25.5 us on the 8B qkv shape, but not
  *                             inside the decode step, so off by default); 0 = the cluster / distributed-shared-memory split
+ *   "smem_carveout" 1/0       1 = every kernel prefers the all-shared-memory L1 split, so consecutive kernels never make an
+ *                             SM reconfigure (and drain) between them; 0 = small kernels keep the driver's default split
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 
@@ -329,6 +331,15 @@ int kge_engine_io_bytes(const kge_engine* e, int64_t* h2d, int64_t* d2h);
 int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_host, int32_t B, int32_t prompt_len,
                             int32_t out_len, int32_t prefill_batch, int32_t* out_tokens_host, float* ms,
                             float* decode_ms);
+
+/* The same measurement on the steps the SCHEDULER makes: record a job that is driven through kge_add_request /
+ * kge_engine_step (or kge_engine_run_to_completion), then replay exactly those steps - same batches, same block tables,
+ * same kernels - with all metadata resident in HBM and every sampled id handed to its next step on the device.  The
+ * replay's sampled tokens come back in sampling order with the request each belongs to; they equal the recorded job's.
+ * *decode_ms = device time of the trailing run of pure decode steps. */
+int kge_engine_record_steps(kge_engine* e, int enable);
+int kge_engine_replay_recorded(kge_engine* e, int32_t* out_tokens_host, int64_t* out_request_ids_host, int64_t cap,
+                               int64_t* n_samples, int32_t* n_steps, float* ms, float* decode_ms);
 
 /* Tensor parallelism (one engine = one rank = one GPU): all ranks share a 128-byte NCCL
  * unique id made by rank 0; after kge_engine_init_tp the forward pass sums the row-parallel

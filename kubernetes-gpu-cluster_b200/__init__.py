@@ -117,6 +117,8 @@ SIGNATURES = {
     "kge_engine_get_timing": (_I, [_P, _P]),
     "kge_engine_io_bytes": (_I, [_P, _P, _P]),
     "kge_engine_run_resident": (_I, [_P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, _P, _P, _P]),
+    "kge_engine_record_steps": (_I, [_P, _I]),
+    "kge_engine_replay_recorded": (_I, [_P, _P, _P, _L, C.POINTER(_L), C.POINTER(C.c_int32), _P, _P]),
     "kge_nccl_unique_id": (_I, [_P]),
     "kge_engine_init_tp": (_I, [_P, _P]),
     "kge_tp_comm_create": (_I, [C.POINTER(_P), _I, _I, _I, _L]),
@@ -369,6 +371,24 @@ class LLM:
         check(lib().kge_engine_run_resident(self._h, pr.ctypes.data, B, P, out_len, prefill_batch, out.ctypes.data,
                                             C.byref(ms), C.byref(dms)), "kge_engine_run_resident")
         return out.tolist(), ms.value, dms.value
+
+    def record_steps(self, enable: bool):
+        """While on, every scheduler-driven step of generate() is kept for replay_recorded()."""
+        check(lib().kge_engine_record_steps(self._h, int(enable)), "kge_engine_record_steps")
+
+    def replay_recorded(self, max_samples: int):
+        """Device-resident replay of the recorded job.  Returns ({request_id: [tokens]}, steps, total_ms, trailing_decode_ms)."""
+        import numpy as np
+        toks = np.zeros(max_samples, dtype=np.int32)
+        rids = np.zeros(max_samples, dtype=np.int64)
+        n, steps = C.c_int64(), C.c_int32()
+        ms, dms = C.c_float(), C.c_float()
+        check(lib().kge_engine_replay_recorded(self._h, toks.ctypes.data, rids.ctypes.data, max_samples, C.byref(n), C.byref(steps),
+                                               C.byref(ms), C.byref(dms)), "kge_engine_replay_recorded")
+        out = {}
+        for r, t in zip(rids[:n.value].tolist(), toks[:n.value].tolist()):
+            out.setdefault(r, []).append(t)
+        return out, steps.value, ms.value, dms.value
 
     def init_tp(self, unique_id: bytes):
         """NCCL exchange (what --disable-custom-all-reduce selects): every rank passes rank 0's kge_nccl_unique_id."""

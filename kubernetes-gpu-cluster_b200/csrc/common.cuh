@@ -19,7 +19,7 @@ void pdl_break_next();
 bool pdl_for_this_launch();
 // Launch-shape knobs behind kge_set_tunable() (api.cc): heuristics that only change HOW work is
 // partitioned, never results.  Defaults are the measured-best settings (profiles/).
-enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_GEMM_SHALLOW = 4, TUN_ATTN_TMA = 5, TUN_GEMM_WS = 6, TUN_COUNT = 7 };
+enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_GEMM_SHALLOW = 4, TUN_ATTN_TMA = 5, TUN_GEMM_WS = 6, TUN_SMEM_CARVEOUT = 7, TUN_COUNT = 8 };
 int tunable(Tunable t);
 
 #define KGE_CUDA_OK(expr)                                                              \
@@ -108,8 +108,18 @@ namespace kge {
 __device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
+// Every kernel of a step asks for the same L1 / shared-memory split (all shared memory): the GEMM and attention kernels
+// need ~200 KB per SM anyway, and an SM that has to change its split between two kernels must drain first, which
+// serialises exactly the kernel boundaries that programmatic dependent launch is there to overlap.  (Knob
+// "smem_carveout" 0 leaves the small kernels at the driver's default split.)
+template <typename K>
+inline void prefer_max_shared(K kern) {
+  if (tunable(TUN_SMEM_CARVEOUT)) (void)cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
+}
+
 template <typename... KArgs, typename... Args>
 inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args... args) {
+  prefer_max_shared(kern);
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid; cfg.blockDim = block; cfg.dynamicSmemBytes = smem; cfg.stream = st;
   cudaLaunchAttribute attr[1];

@@ -114,6 +114,23 @@ struct kge_engine {
   int step_num_decode = 0, step_dec_max_seq = 1;
   double step_dec_sum_seq = 0;
 
+  // Recording of the scheduler-driven steps of a job (kge_engine_record_steps) for a device-resident replay
+  // (kge_engine_replay_recorded): each step's packed metadata as it was shipped, plus, per token row, where its id comes
+  // from in a replay - a sampled token of an earlier step (index into the job's sample log) or the recorded prompt id (-1).
+  struct RecordedStep {
+    int T, B, R, stride, max_q, max_seq, num_decode, dec_max_seq;
+    double sum_seq, attn_flops, dec_sum_seq;
+    bool decode_only, any_random;
+    int64_t bytes;
+    int sample0;                               // index of this step's first sampled row in the job's sample log
+    std::vector<uint8_t> meta;
+    std::vector<int32_t> src;                  // [T]
+  };
+  bool recording = false;
+  std::vector<RecordedStep> recorded;
+  std::vector<int32_t> rec_pending_src;                               // handed from kge_engine_step to run_step
+  std::unordered_map<int64_t, std::vector<int32_t>> rec_samples;      // request id -> sample-log indices of its outputs
+  std::vector<int64_t> rec_sample_req;                                // sample-log index -> request id
   std::unique_ptr<kge::Scheduler> sched;
   int64_t launches = 0;
   int64_t h2d_bytes = 0, d2h_bytes = 0;      // metadata in / sampled ids out, summed over steps

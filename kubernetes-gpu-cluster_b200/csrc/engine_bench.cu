@@ -175,3 +175,91 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   cudaFree(d_arena); cudaFree(d_log); cudaFree(d_first);
   return rc;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Record the scheduler-driven steps of a job, then replay exactly those steps device-resident.
+namespace {
+__global__ void patch_ids_kernel(int32_t* ids, const int32_t* src, const int32_t* log, int T) {
+  const int t = blockIdx.x * blockDim.x + threadIdx.x;
+  if (t < T && src[t] >= 0) ids[t] = log[src[t]];
+}
+}  // namespace
+
+extern "C" int kge_engine_record_steps(kge_engine* e, int enable) {
+  KGE_REQUIRE(e, "kge_engine_record_steps: null engine");
+  if (enable) {
+    KGE_REQUIRE(!e->sched->has_unfinished(), "kge_engine_record_steps: start recording with an idle scheduler");
+    e->recorded.clear(); e->rec_samples.clear(); e->rec_sample_req.clear(); e->rec_pending_src.clear();
+  }
+  e->recording = enable != 0;
+  return 0;
+}
+
+extern "C" int kge_engine_replay_recorded(kge_engine* e, int32_t* out_tokens_host, int64_t* out_request_ids_host, int64_t cap,
+                                          int64_t* n_samples, int32_t* n_steps, float* ms, float* decode_ms) {
+  KGE_REQUIRE(e && out_tokens_host && out_request_ids_host && n_samples && ms, "kge_engine_replay_recorded: null argument");
+  KGE_REQUIRE(!e->recording && !e->recorded.empty(), "kge_engine_replay_recorded: record a job first (kge_engine_record_steps)");
+  KGE_REQUIRE(!e->sched->has_unfinished(), "kge_engine_replay_recorded: the scheduler must be idle");
+  const int64_t ns = (int64_t)e->rec_sample_req.size();
+  KGE_REQUIRE(cap >= ns, "kge_engine_replay_recorded: capacity %lld < %lld samples", (long long)cap, (long long)ns);
+  e->sched->invalidate_prefix_cache();          // the replay rewrites the KV blocks the recorded job used
+  KGE_CUDA_OK(cudaSetDevice(e->cfg.device));
+  const bool was_timing = e->timing;
+  e->timing = false;
+  // arena: per step [metadata block | src], 256-byte aligned
+  std::vector<int64_t> off_meta, off_src;
+  int64_t total = 0;
+  for (auto& st : e->recorded) {
+    off_meta.push_back(total); total += (st.bytes + 255) / 256 * 256;
+    off_src.push_back(total); total += ((int64_t)st.T * 4 + 255) / 256 * 256;
+  }
+  std::vector<uint8_t> arena((size_t)total, 0);
+  for (size_t i = 0; i < e->recorded.size(); ++i) {
+    memcpy(arena.data() + off_meta[i], e->recorded[i].meta.data(), (size_t)e->recorded[i].bytes);
+    memcpy(arena.data() + off_src[i], e->recorded[i].src.data(), (size_t)e->recorded[i].T * 4);
+  }
+  size_t first_all_decode = e->recorded.size();
+  while (first_all_decode > 0 && e->recorded[first_all_decode - 1].decode_only) --first_all_decode;
+  uint8_t* d_arena = nullptr;
+  int32_t* d_log = nullptr;
+  KGE_CUDA_OK(cudaMalloc((void**)&d_arena, arena.size()));
+  KGE_CUDA_OK(cudaMalloc((void**)&d_log, (size_t)std::max<int64_t>(1, ns) * 4));
+  KGE_CUDA_OK(cudaMemcpy(d_arena, arena.data(), arena.size(), cudaMemcpyHostToDevice));
+  cudaEvent_t ev0, ev1, ev2;
+  cudaEventCreate(&ev0); cudaEventCreate(&ev1); cudaEventCreate(&ev2);
+  KGE_CUDA_OK(cudaStreamSynchronize(e->stream));
+  // ---- timed region: device-to-device metadata moves, the id patch, and the step's kernels
+  int rc = 0;
+  cudaEventRecord(ev0, e->stream);
+  for (size_t i = 0; i < e->recorded.size() && rc == 0; ++i) {
+    const kge_engine::RecordedStep& st = e->recorded[i];
+    if (i == first_all_decode) cudaEventRecord(ev1, e->stream);
+    StepMeta dm = carve_meta(e->meta_dev, st.T, st.B, st.R, st.stride, nullptr);
+    cudaMemcpyAsync(e->meta_dev, d_arena + off_meta[i], (size_t)st.bytes, cudaMemcpyDeviceToDevice, e->stream);
+    patch_ids_kernel<<<(st.T + 255) / 256, 256, 0, e->stream>>>(dm.ids, (const int32_t*)(d_arena + off_src[i]), d_log, st.T);
+    e->step_num_decode = st.num_decode; e->step_dec_max_seq = st.dec_max_seq; e->step_dec_sum_seq = st.dec_sum_seq;
+    if (st.decode_only) rc = engine_decode_step(e, st.B, st.stride, st.max_seq, dm, st.any_random, st.sum_seq);
+    else rc = engine_forward(e, st.T, st.B, st.R, st.stride, st.max_q, st.max_seq, dm, st.any_random, st.sum_seq, st.attn_flops);
+    if (rc) break;
+    if (st.R > 0) cudaMemcpyAsync(d_log + st.sample0, e->d_out, (size_t)st.R * 4, cudaMemcpyDeviceToDevice, e->stream);
+  }
+  if (first_all_decode >= e->recorded.size()) cudaEventRecord(ev1, e->stream);
+  cudaEventRecord(ev2, e->stream);
+  cudaError_t serr = cudaStreamSynchronize(e->stream);
+  e->timing = was_timing;
+  if (rc == 0 && serr != cudaSuccess) { kge::set_error("kge_engine_replay_recorded: %s", cudaGetErrorString(serr)); rc = -2; }
+  if (rc == 0) {
+    float t_all = 0.f, t_dec = 0.f;
+    cudaEventElapsedTime(&t_all, ev0, ev2);
+    cudaEventElapsedTime(&t_dec, ev1, ev2);
+    *ms = t_all;
+    if (decode_ms) *decode_ms = t_dec;
+    cudaMemcpy(out_tokens_host, d_log, (size_t)ns * 4, cudaMemcpyDeviceToHost);
+    memcpy(out_request_ids_host, e->rec_sample_req.data(), (size_t)ns * 8);
+    *n_samples = ns;
+    if (n_steps) *n_steps = (int32_t)e->recorded.size();
+  }
+  cudaEventDestroy(ev0); cudaEventDestroy(ev1); cudaEventDestroy(ev2);
+  cudaFree(d_arena); cudaFree(d_log);
+  return rc;
+}

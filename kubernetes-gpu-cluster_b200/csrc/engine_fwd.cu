@@ -277,6 +277,18 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
     max_seq = std::max(max_seq, b->seq_lens[i]);
   }
   KGE_REQUIRE(b->query_start_loc[B] == T, "kge_step: query_start_loc[B]=%d != T=%d", b->query_start_loc[B], T);
+  if (e->recording) {
+    kge_engine::RecordedStep rs{};
+    rs.T = T; rs.B = B; rs.R = R; rs.stride = stride; rs.max_q = max_q; rs.max_seq = max_seq;
+    rs.num_decode = e->step_num_decode; rs.dec_max_seq = e->step_dec_max_seq; rs.dec_sum_seq = e->step_dec_sum_seq;
+    rs.sum_seq = sum_seq; rs.attn_flops = attn_flops; rs.decode_only = decode_only && max_q == 1; rs.any_random = any_random;
+    rs.bytes = bytes; rs.sample0 = (int)e->rec_sample_req.size();
+    rs.meta.assign(e->meta_host, e->meta_host + bytes);
+    rs.src = e->rec_pending_src;
+    rs.src.resize((size_t)T, -1);
+    e->rec_pending_src.clear();                 // a raw kge_step that follows has no sampled-token sources
+    e->recorded.push_back(std::move(rs));
+  }
   KGE_CUDA_OK(cudaMemcpyAsync(e->meta_dev, e->meta_host, (size_t)bytes, cudaMemcpyHostToDevice, e->stream));
   e->h2d_bytes += bytes;
   e->d2h_bytes += (int64_t)R * 4;
@@ -408,10 +420,16 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   int max_blocks = 1;
   for (auto& s : sc) max_blocks = std::max(max_blocks, (int)s.req->blocks.size());
   std::vector<int32_t> btab((size_t)B * max_blocks, 0);
+  e->rec_pending_src.clear();
   for (int i = 0; i < B; ++i) {
     Request* r = sc[i].req;
     const int n = sc[i].num_tokens, start = r->num_computed - n;
     for (int t = start; t < start + n; ++t) {
+      if (e->recording) {
+        const int k = t - (int)r->prompt.size();              // >= 0: the k-th output token of this request
+        const auto it = e->rec_samples.find(r->id);
+        e->rec_pending_src.push_back(k >= 0 && it != e->rec_samples.end() && k < (int)it->second.size() ? it->second[k] : -1);
+      }
       ids.push_back(r->token_at(t));
       pos.push_back(t);
       slots.push_back((int64_t)r->blocks[t / bs] * bs + t % bs);
@@ -444,6 +462,12 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   b.slot_mapping = slots.data(); b.logits_rows = rows.data(); b.R = (int)rows.size();
   std::vector<int32_t> sampled(rows.size());
   if (int rc = run_step(e, &b, temp.data(), top_k.data(), top_p.data(), seeds.data(), sampled.data(), nullptr, lp_n)) return rc;
+  if (e->recording)          // the sampled rows of this step, in row order, join the job's sample log
+    for (int i = 0; i < B; ++i)
+      if (Scheduler::needs_sample(sc[i])) {
+        e->rec_samples[sc[i].req->id].push_back((int32_t)e->rec_sample_req.size());
+        e->rec_sample_req.push_back(sc[i].req->id);
+      }
   std::vector<StepResult> res;
   e->sched->update(sampled, &res);
   for (size_t i = 0; i < res.size(); ++i) {

@@ -629,6 +629,7 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
   auto kern = gemm_tc_kernel<TOKN, STAGES, SPLIT, GATED, PAIR, WS>;
   KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+  prefer_max_shared(kern);
   const int tiles = p.m_tiles * p.n_tiles;
   cudaLaunchConfig_t cfg = {};
   cfg.blockDim = dim3(kGemmThreads);

@@ -255,6 +255,33 @@ def test_chunked_prefill_and_preemption_do_not_change_tokens(kge, model_dirs):
         assert diff <= 20, diff
 
 
+def test_replay_of_recorded_steps_reproduces_the_job(kge, model_dirs):
+    """bench.py's `value` leg: the steps the scheduler made for a job (chunked prompts mixed with decodes, a preemption,
+    requests of different lengths finishing at different steps) are recorded and replayed device-resident - same batches,
+    same kernels, sampled ids handed over on the device - and must give exactly the recorded job's tokens, every time."""
+    cfg, w, d = model_dirs("tiny-llama")
+    prompts = [om.make_prompts(cfg, 1, n, seed=300 + n)[0] for n in (70, 9, 45, 33, 81, 20)]
+    sps = [kge.SamplingParams(max_tokens=m, temperature=0.0, ignore_eos=True) for m in (20, 7, 15, 20, 3, 11)]
+    for kw in (dict(max_num_batched_tokens=512, num_gpu_blocks_override=128), dict(max_num_batched_tokens=32, num_gpu_blocks_override=128),
+               dict(max_num_batched_tokens=64, num_gpu_blocks_override=22)):
+        llm = kge.LLM(d, max_model_len=128, max_num_seqs=8, enable_prefix_caching=False, **kw)
+        llm.record_steps(True)
+        outs = llm.generate(prompts, sps)
+        llm.record_steps(False)
+        want = {o.request_id: o.outputs[0].token_ids for o in outs}
+        for _ in range(2):
+            got, steps, ms, dms = llm.replay_recorded(256)
+            assert got == want and steps > 0 and ms > 0 and 0 <= dms <= ms
+        # a random job replays too: the per-row noise seeds travel with the recorded metadata
+        rsp = kge.SamplingParams(max_tokens=9, temperature=1.2, top_p=0.9, seed=11, ignore_eos=True)
+        llm.record_steps(True)
+        outs = llm.generate(prompts[:3], rsp)
+        llm.record_steps(False)
+        got, _, _, _ = llm.replay_recorded(64)
+        assert got == {o.request_id: o.outputs[0].token_ids for o in outs}
+        llm.close()
+
+
 def test_prefix_caching_reuses_blocks_and_keeps_tokens(kge, model_dirs):
     """--enable-prefix-caching: requests that share a prompt prefix (and a second job with the same prompts) take the
     shared full blocks from the pool instead of recomputing them; the tokens are those of the oracle (near-ties

@@ -95,7 +95,7 @@ def engine_mode(kge, L, rank, world, name, prefix, how):
 def ops_mode(kge, L, rank, world, prefix):
     from cuda.bindings import runtime as cudart
     D2D = cudart.cudaMemcpyKind.cudaMemcpyDeviceToDevice
-    Tmax, dmax, V = 320, 1024, 1000
+    Tmax, dmax, V = 320, 1024, 504 * world       # V: the widest gathered row below
     off_x, off_y = 0, Tmax * dmax * 2
     off_g = 2 * Tmax * dmax * 2
     comm = C.c_void_p()

@@ -410,6 +410,7 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   e->lp_vals = (float*)aalloc((int64_t)Rm * 21, 4);
   e->lp_ids = (int32_t*)aalloc((int64_t)Rm * 21, 4);
   e->lp_rank = (int32_t*)aalloc(Rm, 4);
+  e->mask_pairs = (int32_t*)aalloc(2 * kge_engine::kMaxMaskPairs, 4);
   e->ws_gemm_bytes = 1024 + (int64_t)148 * 256 * 128 * 4;
   e->ws_gemm = aalloc(e->ws_gemm_bytes, 1);
   e->ws_attn_bytes = kge_attn_workspace_bytes(Rm, e->H_loc, s.hd, e->cfg.max_model_len);
@@ -418,13 +419,14 @@ extern "C" int kge_engine_create(kge_engine** out, const char* model_dir, const 
   carve_meta(nullptr, Tm, Rm, Rm, e->max_blocks_per_seq, &e->meta_bytes);
   e->meta_dev = (uint8_t*)aalloc(e->meta_bytes, 1);
   if (!e->h || !e->res || !e->xn || !e->qkv || !e->attn || !e->gu || !e->act || !e->xsel || !e->logits ||
-      !e->d_out || !e->lp_vals || !e->lp_ids || !e->lp_rank || !e->ws_gemm || !e->ws_attn || !e->meta_dev)
+      !e->d_out || !e->lp_vals || !e->lp_ids || !e->lp_rank || !e->mask_pairs || !e->ws_gemm || !e->ws_attn || !e->meta_dev)
     ENGINE_FAIL("kge_engine_create: activation arena allocation failed (%s)", cudaGetErrorString(cudaGetLastError()));
   if (cudaMallocHost((void**)&e->meta_host, e->meta_bytes) != cudaSuccess ||
       cudaMallocHost((void**)&e->out_host, (size_t)Rm * 4) != cudaSuccess ||
       cudaMallocHost((void**)&e->lp_vals_host, (size_t)Rm * 21 * 4) != cudaSuccess ||
       cudaMallocHost((void**)&e->lp_ids_host, (size_t)Rm * 21 * 4) != cudaSuccess ||
-      cudaMallocHost((void**)&e->lp_rank_host, (size_t)Rm * 4) != cudaSuccess)
+      cudaMallocHost((void**)&e->lp_rank_host, (size_t)Rm * 4) != cudaSuccess ||
+      cudaMallocHost((void**)&e->mask_pairs_host, (size_t)2 * kge_engine::kMaxMaskPairs * 4) != cudaSuccess)
     ENGINE_FAIL("kge_engine_create: pinned staging allocation failed");
   cudaMemsetAsync(e->ws_gemm, 0, 1024, e->stream);     // split-K tile counters start at zero
 
@@ -486,6 +488,7 @@ extern "C" void kge_engine_destroy(kge_engine* e) {
   if (e->lp_vals_host) cudaFreeHost(e->lp_vals_host);
   if (e->lp_ids_host) cudaFreeHost(e->lp_ids_host);
   if (e->lp_rank_host) cudaFreeHost(e->lp_rank_host);
+  if (e->mask_pairs_host) cudaFreeHost(e->mask_pairs_host);
   if (e->stream) cudaStreamDestroy(e->stream);
   delete e;
 }

@@ -109,6 +109,13 @@ struct kge_engine {
   std::vector<std::pair<int64_t, int>> graph_seen;   // key hash -> eager runs so far
   bool use_graphs = true;
 
+  // min_tokens (vllm:v1/sample/logits_processor/builtin.py MinTokensLogitsProcessor): (logits row, token id) pairs whose
+  // logit is set to -inf before sampling in this step - EOS and the stop ids of requests still short of min_tokens
+  int32_t* mask_pairs = nullptr;             // device [2 * kMaxMaskPairs]
+  int32_t* mask_pairs_host = nullptr;        // pinned
+  int step_num_masks = 0;
+  static constexpr int kMaxMaskPairs = 4096;
+
   // mixed steps: the scheduler lists running (decode) requests first; the forward pass sends that
   // prefix to the decode attention kernel and the rest to the prefill kernel
   int step_num_decode = 0, step_dec_max_seq = 1;

@@ -58,6 +58,7 @@ extern "C" int kge_engine_run_resident(kge_engine* e, const int32_t* prompts_hos
   const bool was_timing = e->timing;
   e->timing = false;
   e->step_num_decode = 0;                 // resident steps are pure prefill or pure decode
+  e->step_num_masks = 0;
 
   // ---- build every step's metadata on the host (untimed)
   std::vector<ResidentStep> steps;
@@ -206,6 +207,7 @@ extern "C" int kge_engine_replay_recorded(kge_engine* e, int32_t* out_tokens_hos
   KGE_CUDA_OK(cudaSetDevice(e->cfg.device));
   const bool was_timing = e->timing;
   e->timing = false;
+  e->step_num_masks = 0;                  // (a recorded job with min_tokens masks replays without them: bench jobs have none)
   // arena: per step [metadata block | src], 256-byte aligned
   std::vector<int64_t> off_meta, off_src;
   int64_t total = 0;

@@ -59,6 +59,7 @@ static int linear_rc(kge_engine* e, bf16* y, const bf16* x, const Linear& l, int
   FWD((T) <= 256 ? C_GEMM_S : C_GEMM_L, 2.0 * ((double)(l).N * (l).K + (double)(T) * ((l).K + (l).N)), \
       2.0 * (T) * (double)(l).N * (l).K, linear_rc(e, y, x, l, T, act))
 
+__global__ void mask_logits_kernel(bf16* logits, const int32_t* pairs, int n, int ld, int vocab, bool f16);
 int tp_all_reduce(kge_engine* e, bf16* buf, int64_t n);   // tp.cu
 int tp_all_gather_logits(kge_engine* e, int R);           // tp.cu (NCCL path)
 
@@ -170,6 +171,12 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
       else
         FWD(C_AR, 2.0 * R * s.vocab, 0, tp_all_gather_logits(e, R));
     }
+    if (e->step_num_masks > 0) {
+      mask_logits_kernel<<<(e->step_num_masks + 127) / 128, 128, 0, st>>>(e->logits, e->mask_pairs, e->step_num_masks, s.vocab, s.vocab, e->f16);
+      KGE_LAUNCH_OK();
+      ++e->launches;
+      pdl_break_next();
+    }
     if (any_random)
       FWD(C_SAMPLE, (double)R * s.vocab * 2, 0, e->op->sample(e->d_out, e->logits, R, s.vocab, s.vocab, m.temp, m.top_k, m.top_p, nullptr, m.seeds,
                      0 /* the step is folded into the per-row seeds */, nullptr, 0, st));
@@ -182,7 +189,7 @@ int engine_forward(kge_engine* e, int T, int B, int R, int max_blocks, int max_q
 int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const StepMeta& dm, bool any_random, double sum_seq) {
   const double attn_flops = 4.0 * sum_seq;
   const int ns = attn_decode_splits(B, e->KV_loc, max_seq_len);
-  if (!e->use_graphs || e->timing)
+  if (!e->use_graphs || e->timing || e->step_num_masks > 0)      // a masked step is rare and its mask list is not part of a graph
     return engine_forward(e, B, B, B, stride, 1, max_seq_len, dm, any_random, sum_seq, attn_flops);
   for (auto& g : e->graphs)
     if (g.B == B && g.ns == ns && g.stride == stride && g.rnd == any_random) {
@@ -210,6 +217,14 @@ int engine_decode_step(kge_engine* e, int B, int stride, int max_seq_len, const 
   e->graphs.push_back(g);
   KGE_CUDA_OK(cudaGraphLaunch(g.exec, e->stream));
   return 0;
+}
+
+// logits[row, token] = -inf for each (row, token) pair: tokens a request may not produce yet (min_tokens)
+__global__ void mask_logits_kernel(bf16* logits, const int32_t* pairs, int n, int ld, int vocab, bool f16) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const int row = pairs[2 * i], tok = pairs[2 * i + 1];
+  if (tok >= 0 && tok < vocab) reinterpret_cast<uint16_t*>(logits)[(int64_t)row * ld + tok] = f16 ? (uint16_t)0xFC00u : (uint16_t)0xFF80u;
 }
 
 __global__ void elt_to_f32_kernel(float* o, const bf16* x, int64_t n, bool f16) {
@@ -333,6 +348,7 @@ static int run_step(kge_engine* e, const kge_step_batch* b, const float* temp, c
 extern "C" int kge_step(kge_engine* e, const kge_step_batch* batch, int32_t* out_ids_host, float* out_logits_host) {
   KGE_REQUIRE(e && batch, "kge_step: null argument");
   e->sched->invalidate_prefix_cache();        // the caller's block tables may overwrite blocks the scheduler has cached
+  e->step_num_masks = 0;
   return run_step(e, batch, nullptr, nullptr, nullptr, nullptr, out_ids_host, out_logits_host);
 }
 
@@ -416,6 +432,7 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   std::vector<float> temp, top_p;
   std::vector<uint64_t> seeds;
   int lp_n = -1;
+  int n_masks = 0;
   e->lp_last.clear();
   int max_blocks = 1;
   for (auto& s : sc) max_blocks = std::max(max_blocks, (int)s.req->blocks.size());
@@ -449,6 +466,15 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
       z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
       z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
       seeds.push_back(z ^ (z >> 31));
+      if ((int)r->output.size() < r->sp.min_tokens) {
+        // this request may not stop yet: its EOS (unless ignored) and its stop ids cannot be sampled in this step
+        const int row = (int)rows.size() - 1;
+        auto ban = [&](int32_t tok) {
+          if (n_masks < kge_engine::kMaxMaskPairs) { e->mask_pairs_host[2 * n_masks] = row; e->mask_pairs_host[2 * n_masks + 1] = tok; ++n_masks; }
+        };
+        if (!r->sp.ignore_eos && e->spec.eos >= 0) ban(e->spec.eos);
+        for (int32_t t : r->sp.stop_token_ids) ban(t);
+      }
       if (r->sp.logprobs >= 0) {
         lp_n = std::max(lp_n, r->sp.logprobs);
         e->lp_last[r->id] = {(int)rows.size() - 1, r->sp.logprobs};
@@ -460,6 +486,9 @@ extern "C" int kge_engine_step(kge_engine* e, kge_step_output* outs, int32_t cap
   b.token_ids = ids.data(); b.positions = pos.data(); b.query_start_loc = qsl.data();
   b.seq_lens = seq_lens.data(); b.block_table = btab.data(); b.max_blocks = max_blocks;
   b.slot_mapping = slots.data(); b.logits_rows = rows.data(); b.R = (int)rows.size();
+  e->step_num_masks = n_masks;
+  if (n_masks > 0)
+    KGE_CUDA_OK(cudaMemcpyAsync(e->mask_pairs, e->mask_pairs_host, (size_t)n_masks * 8, cudaMemcpyHostToDevice, e->stream));
   std::vector<int32_t> sampled(rows.size());
   if (int rc = run_step(e, &b, temp.data(), top_k.data(), top_p.data(), seeds.data(), sampled.data(), nullptr, lp_n)) return rc;
   if (e->recording)          // the sampled rows of this step, in row order, join the job's sample log

@@ -334,6 +334,31 @@ def test_stop_rules_eos_and_stop_ids(kge, model_dirs):
     llm.close()
 
 
+def test_min_tokens_masks_stop_tokens_in_the_logits(kge, model_dirs):
+    """vLLM's MinTokensLogitsProcessor: until a request has min_tokens outputs, its EOS and stop ids are not merely ignored
+    as stop conditions - their logits are -inf, so they cannot be sampled at all.  Take the token greedy decoding emits at
+    step 3, make it a stop id with min_tokens = 8: it must be absent from the first 8 outputs (the runner-up is taken
+    instead), and the request stops at its first occurrence afterwards."""
+    cfg, w, d = model_dirs("tiny-llama")
+    prompts = om.make_prompts(cfg, 2, 12, seed=4)
+    llm = kge.LLM(d, max_model_len=96, max_num_seqs=4, max_num_batched_tokens=64, num_gpu_blocks_override=32, enable_prefix_caching=False)
+    free = [o.outputs[0].token_ids for o in llm.generate(prompts, kge.SamplingParams(max_tokens=40, temperature=0.0, ignore_eos=True))]
+    for b in range(2):
+        banned = free[b][3]
+        out = llm.generate([prompts[b]], kge.SamplingParams(max_tokens=40, min_tokens=8, temperature=0.0, ignore_eos=True,
+                                                            stop_token_ids=[banned]))[0].outputs[0]
+        assert out.token_ids[:3] == free[b][:3]                      # untouched until the banned token would have come
+        assert banned not in out.token_ids[:8], (banned, out.token_ids)
+        assert out.token_ids[3] != banned
+        if banned in out.token_ids:
+            assert out.finish_reason == "stop" and out.token_ids.index(banned) == len(out.token_ids) - 1 >= 8
+        # a random-sampling request obeys the mask too
+        out = llm.generate([prompts[b]], kge.SamplingParams(max_tokens=12, min_tokens=12, temperature=1.0, top_k=2, seed=3, ignore_eos=True,
+                                                            stop_token_ids=[banned, free[b][0]]))[0].outputs[0]
+        assert banned not in out.token_ids and free[b][0] not in out.token_ids and len(out.token_ids) == 12
+    llm.close()
+
+
 def test_random_sampling_respects_top_k(kge, model_dirs):
     cfg, w, d = model_dirs("tiny-llama")
     prompts = om.make_prompts(cfg, 4, 10, seed=6)

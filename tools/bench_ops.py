@@ -57,9 +57,8 @@ def bench_gemm(shapes, cublas):
     return rows
 
 
-def bench_attn(cases):
+def bench_attn(cases, bs=16):
     for (B, ctx, H, KV, hd) in cases:
-        bs = 16
         nb_seq = (ctx + bs - 1) // bs
         nblk = B * nb_seq + 1
         layers = max(2, int(400e6 // (nblk * KV * bs * hd * 4)) + 1)
@@ -84,9 +83,8 @@ def bench_attn(cases):
                           "GB/s": round(bytes_ / ms / 1e6, 1)}), flush=True)
 
 
-def bench_prefill(cases):
+def bench_prefill(cases, bs=16):
     for (B, qlen, H, KV, hd) in cases:
-        bs = 16
         nb_seq = (qlen + bs - 1) // bs
         nblk = B * nb_seq + 1
         kc = torch.randn(nblk, KV, bs, hd, device="cuda", dtype=BF)
@@ -113,6 +111,7 @@ if __name__ == "__main__":
     ap.add_argument("what", choices=["gemm", "attn", "prefill"])
     ap.add_argument("--cublas", action="store_true")
     ap.add_argument("--only", type=int, default=-1)
+    ap.add_argument("--bs", type=int, default=16, help="KV block size for the attention cases")
     ap.add_argument("--knob", action="append", default=[], help="name=value launch-shape knob (kge_set_tunable), repeatable")
     a = ap.parse_args()
     kge.require_cuda()
@@ -128,7 +127,7 @@ if __name__ == "__main__":
         bench_gemm(shapes, a.cublas)
     elif a.what == "prefill":
         cases = [(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128), (32, 128, 32, 8, 64), (4, 2048, 12, 12, 64)]
-        bench_prefill(cases if a.only < 0 else [cases[a.only]])
+        bench_prefill(cases if a.only < 0 else [cases[a.only]], a.bs)
     else:
         cases = [(64, 2176, 32, 8, 128), (64, 1024, 32, 8, 128), (32, 192, 32, 8, 64), (8, 8192, 32, 8, 128)]
-        bench_attn(cases if a.only < 0 else [cases[a.only]])
+        bench_attn(cases if a.only < 0 else [cases[a.only]], a.bs)

@@ -96,8 +96,7 @@ def gemm_rows():
     return rows
 
 
-def paged_setup(B, ctx, KV, hd, copies):
-    bs = 16
+def paged_setup(B, ctx, KV, hd, copies, bs=16):
     nb_seq = (ctx + bs - 1) // bs
     nblk = B * nb_seq + 1
     kv = [torch.randn(nblk, 2, KV, bs, hd, device="cuda", dtype=BF) for _ in range(copies)]   # FlashInfer HND: [page, 2, KV, page_size, hd]
@@ -107,8 +106,8 @@ def paged_setup(B, ctx, KV, hd, copies):
 
 def prefill_rows():
     rows = []
-    for (B, qlen, H, KV, hd) in [(4, 2048, 32, 8, 128), (1, 8192, 32, 8, 128)]:
-        bs, nb_seq, nblk, kvs, bt = paged_setup(B, qlen, KV, hd, 1)
+    for (B, qlen, H, KV, hd, bsz) in [(4, 2048, 32, 8, 128, 64), (1, 8192, 32, 8, 128, 64), (4, 2048, 32, 8, 128, 16)]:
+        bs, nb_seq, nblk, kvs, bt = paged_setup(B, qlen, KV, hd, 1, bsz)
         kv = kvs[0]
         kc, vc = kv[:, 0].contiguous(), kv[:, 1].contiguous()
         sl = torch.full((B,), qlen, dtype=torch.int32, device="cuda")
@@ -125,7 +124,7 @@ def prefill_rows():
         ms_old = time_ms(ours, 10)
         L.kge_set_tunable(b"attn_tma", 1)
         flops = 4.0 * H * hd * B * qlen * (qlen + 1) / 2
-        row = {"B": B, "q_len": qlen, "H": H, "KV": KV, "hd": hd, "kge_ms": round(ms, 4), "kge_TFLOP/s": round(flops / ms / 1e9, 1),
+        row = {"B": B, "q_len": qlen, "H": H, "KV": KV, "hd": hd, "kv_block": bs, "kge_ms": round(ms, 4), "kge_TFLOP/s": round(flops / ms / 1e9, 1),
                "kge_cp_async_variant_ms": round(ms_old, 4), "kge_cp_async_variant_TFLOP/s": round(flops / ms_old / 1e9, 1)}
         try:
             import flashinfer
@@ -150,8 +149,8 @@ def prefill_rows():
 
 def decode_rows():
     rows = []
-    for (B, ctx, H, KV, hd) in [(64, 2176, 32, 8, 128), (64, 2176, 8, 1, 128), (32, 192, 32, 8, 64)]:
-        bs, nb_seq, nblk, kvs, bt = paged_setup(B, ctx, KV, hd, 3)
+    for (B, ctx, H, KV, hd, bsz) in [(64, 2176, 32, 8, 128, 64), (64, 2176, 32, 8, 128, 16), (32, 192, 32, 8, 64, 64)]:
+        bs, nb_seq, nblk, kvs, bt = paged_setup(B, ctx, KV, hd, 3, bsz)
         kcs = [kv[:, 0].contiguous() for kv in kvs]
         vcs = [kv[:, 1].contiguous() for kv in kvs]
         sl = torch.full((B,), ctx, dtype=torch.int32, device="cuda")
@@ -170,7 +169,7 @@ def decode_rows():
         ms_old = time_ms(ours, 60)
         L.kge_set_tunable(b"attn_tma", 1)
         by = B * ctx * KV * hd * 4.0
-        row = {"B": B, "ctx": ctx, "H": H, "KV": KV, "hd": hd, "kge_ms": round(ms, 4), "kge_GB/s": round(by / ms / 1e6, 1),
+        row = {"B": B, "ctx": ctx, "H": H, "KV": KV, "hd": hd, "kv_block": bs, "kge_ms": round(ms, 4), "kge_GB/s": round(by / ms / 1e6, 1),
                "kge_cp_async_variant_ms": round(ms_old, 4), "kge_cp_async_variant_GB/s": round(by / ms_old / 1e6, 1)}
         try:
             import flashinfer

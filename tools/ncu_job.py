@@ -18,7 +18,7 @@ prompts = bench.rank_prompts(hf["vocab_size"], B, pin, 0, 1)
 with tempfile.TemporaryDirectory() as d:
     json.dump(hf, open(os.path.join(d, "config.json"), "w"))
     llm = kge.LLM(d, max_model_len=pin + 256 + 16, max_num_seqs=B, max_num_batched_tokens=pbatch * pin,
-                  num_gpu_blocks_override=B * ((pin + 256 + 15) // 16) + 2, load_format="dummy", seed=1234)
+                  num_gpu_blocks_override=B * ((pin + 256 + 63) // 64) + 2, load_format="dummy", seed=1234, block_size=64)
 _, ms, dms = llm.run_resident(prompts, pout, pbatch)
 print(json.dumps({"ncu_job_ms": ms, "decode_ms": dms, "launches": llm.kernel_launches}))
 llm.close()

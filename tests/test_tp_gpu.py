@@ -63,3 +63,61 @@ def test_tp_engine_matches_oracle(world, name, how, tmp_path):
     # most requests follow the oracle to the end; a request that meets a near-tie early stops counting there
     assert res["equal"] >= (2 * res["total"]) // 3, res
     assert res["second_job_identical"] and res["ranks_agree_on_random_tokens"], res
+
+
+@need(2)
+@pytest.mark.parametrize("extra", [[], ["--disable-custom-all-reduce"]], ids=["peer", "nccl"])
+def test_server_with_the_references_tp_flags(extra, tmp_path):
+    """`vllm serve <dir> --dtype float16 --enforce-eager --pipeline-parallel-size 1 --tensor-parallel-size 2` - the flags
+    of ref:values-01-minimal-example8.yaml:23-38 - on a Qwen2.5-shaped model (the family that file deploys), with and
+    without --disable-custom-all-reduce: the rank threads of one server process join over peer access (or NCCL), the
+    engine computes in float16, and the streamed greedy ids follow the float16 oracle up to its own near-ties."""
+    import socket
+    import time
+    import urllib.request
+    from oracle import model as om
+    cfg = om.CONFIGS["tiny-qwen2"]
+    w = om.make_weights(cfg, seed=0)
+    d = str(tmp_path / "m")
+    om.save_model_dir(d, cfg, w)                              # a bfloat16 checkpoint, served as float16
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    proc = subprocess.Popen([os.path.join(ROOT, "kubernetes-gpu-cluster_b200", "bin", "vllm"), "serve", d, "--host", "127.0.0.1", "--port", str(port),
+                             "--max-model-len", "256", "--max-num-seqs", "8", "--num-gpu-blocks-override", "64", "--served-model-name", "q",
+                             "--dtype", "float16", "--enforce-eager", "--trust-remote-code", "--pipeline-parallel-size", "1",
+                             "--tensor-parallel-size", "2", "--no-enable-prefix-caching"] + extra, stdout=subprocess.PIPE, stderr=subprocess.PIPE, text=True)
+    try:
+        t0 = time.time()
+        while True:
+            try:
+                if urllib.request.urlopen(f"http://127.0.0.1:{port}/health", timeout=2).status == 200:
+                    break
+            except Exception:
+                pass
+            assert proc.poll() is None, proc.stderr.read()[-3000:]
+            assert time.time() - t0 < 180, "server did not come up"
+            time.sleep(0.3)
+        prompts = [om.make_prompts(cfg, 1, n, seed=n)[0] for n in (9, 40, 70)]
+        N = 12
+        ref_ids, ref_lg = om.OracleModel(cfg, w, torch.float16).generate_greedy(prompts, N, return_logits=True)
+        equal = 0
+        for b, pr in enumerate(prompts):
+            req = urllib.request.Request(f"http://127.0.0.1:{port}/v1/completions", headers={"Content-Type": "application/json"},
+                                         data=json.dumps({"model": "q", "prompt": pr, "max_tokens": N, "temperature": 0, "ignore_eos": True,
+                                                          "stream": True}).encode())
+            raw = urllib.request.urlopen(req, timeout=120).read().decode()
+            got = [t for e in raw.split("\n\n") if e.startswith("data: {") for t in json.loads(e[6:])["choices"][0].get("token_ids", [])]
+            assert len(got) == N, raw[-500:]
+            for step, (a, e) in enumerate(zip(got, ref_ids[b])):
+                if a == e:
+                    equal += 1
+                    continue
+                t2 = ref_lg[step][b].topk(2).values
+                assert (t2[0] - t2[1]).item() <= 8e-3, (b, step, a, e, (t2[0] - t2[1]).item())     # float16 near-tie (TP rounds partials)
+                break
+        assert equal >= 2 * len(prompts) * N // 3, equal
+    finally:
+        proc.terminate()
+        try:
+            proc.wait(timeout=20)
+        except subprocess.TimeoutExpired:
+            proc.kill()

@@ -354,6 +354,27 @@ def test_gemm_silu_gate_stream_k(kge, L, T, f, K):
         assert (err <= 4e-3 * ref.abs().max().item() + 3.2e-2 * ref.abs()).all(), err.max().item()
 
 
+@pytest.mark.parametrize("T,N,K,bias,act", [(64, 4096, 4096, False, 0), (1000, 4096, 4096, True, 1), (8192, 2560, 8192, False, 0), (300, 2048, 2048, False, 0)])
+def test_gemm_with_l2_eviction_hints(kge, L, T, N, K, bias, act):
+    """Knob gemm_l2_hints only changes which L2 lines are kept (weights evict_first, activations evict_last): same bits."""
+    g = torch.Generator().manual_seed(T + N)
+    x = dev(torch.randn(T, K, generator=g).to(BF))
+    w = dev((torch.randn(N, K, generator=g) * 0.05).to(BF))
+    b = dev(torch.randn(N, generator=g).to(BF)) if bias else None
+    outs = []
+    try:
+        for knob in (0, 1):
+            check_ok(kge, L.kge_set_tunable(b"gemm_l2_hints", knob), "tunable")
+            y = torch.full((T, N), float("nan"), dtype=BF, device="cuda")
+            check_ok(kge, L.kge_gemm_bf16(p(y), p(x), p(w), p(b) if bias else None, T, N, K, act, None, 0, None), "gemm")
+            sync()
+            outs.append(y.cpu())
+    finally:
+        L.kge_set_tunable(b"gemm_l2_hints", 0)
+    assert torch.isfinite(outs[0].float()).all()
+    assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
+
+
 EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
                                   reason="default-off experiments prepared for the next round; set KGE_TEST_EXPERIMENTAL=1 to run them")
 

@@ -116,6 +116,7 @@ attn_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_co
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_k) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tm_v) : "memory");
   }
+  __syncthreads();                              // barriers initialised (before anything of the previous kernel is needed)
   pdl_launch_dependents();
   pdl_wait();                                   // q, the KV rows of this step and the metadata come from earlier kernels
   const int kv_len = seq_lens[b];
@@ -124,6 +125,7 @@ attn_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_co
   const int t_begin = split * tps, t_end = min(ntiles_all, t_begin + tps);
   const int qrow = qsl[b];
   if (warp < 4) {
+    // the Q tile arrives while the producer warp already has the first K/V tiles in flight
     for (int i = tid; i < 16 * CH; i += 128) {
       const int r = i / CH, c = i % CH;
       const bool ok = r < G;
@@ -132,8 +134,8 @@ attn_decode_tma_kernel(const __grid_constant__ CUtensorMap tm_k, const __grid_co
     }
     asm volatile("cp.async.commit_group;");
     asm volatile("cp.async.wait_group 0;" ::: "memory");
+    bar_compute();                              // Q tile visible to every compute warp
   }
-  __syncthreads();                              // barriers initialised, Q tile visible to every compute warp
 
   float o[HD / 8][4];
   float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;

@@ -342,7 +342,8 @@ def test_min_tokens_masks_stop_tokens_in_the_logits(kge, model_dirs):
     cfg, w, d = model_dirs("tiny-llama")
     prompts = om.make_prompts(cfg, 2, 12, seed=4)
     llm = kge.LLM(d, max_model_len=96, max_num_seqs=4, max_num_batched_tokens=64, num_gpu_blocks_override=32, enable_prefix_caching=False)
-    free = [o.outputs[0].token_ids for o in llm.generate(prompts, kge.SamplingParams(max_tokens=40, temperature=0.0, ignore_eos=True))]
+    # each request alone, as the masked runs below are: the same batches through the same kernels, so any difference is the mask's
+    free = [llm.generate([pr], kge.SamplingParams(max_tokens=40, temperature=0.0, ignore_eos=True))[0].outputs[0].token_ids for pr in prompts]
     for b in range(2):
         banned = free[b][3]
         out = llm.generate([prompts[b]], kge.SamplingParams(max_tokens=40, min_tokens=8, temperature=0.0, ignore_eos=True,

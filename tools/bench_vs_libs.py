@@ -19,6 +19,15 @@ from kge_loader import load  # noqa: E402
 kge = load()
 L = kge.lib()
 BF = torch.bfloat16
+_FI_WS = None
+
+
+def fi_workspace():
+    """One workspace for every FlashInfer call of the process (its trtllm-gen wrappers keep state keyed to the buffer)."""
+    global _FI_WS
+    if _FI_WS is None:
+        _FI_WS = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+    return _FI_WS
 
 
 def time_ms(fn, iters, warm=3):
@@ -129,7 +138,7 @@ def prefill_rows():
         try:
             import flashinfer
             q = qkv[:, :H * hd].reshape(B * qlen, H, hd).contiguous()
-            wsb = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+            wsb = fi_workspace()
             o2 = torch.empty(B * qlen, H, hd, device="cuda", dtype=BF)
 
             def fi(i, st):
@@ -174,7 +183,7 @@ def decode_rows():
         try:
             import flashinfer
             q = qkv[:, :H * hd].reshape(B, H, hd).contiguous()
-            wsb = torch.zeros(256 << 20, dtype=torch.uint8, device="cuda")
+            wsb = fi_workspace()
             o2 = torch.empty(B, H, hd, device="cuda", dtype=BF)
 
             def fi(i, st):

@@ -8,7 +8,7 @@ import sys
 
 
 def short(name):
-    m = re.match(r"(?:void )?(?:kge::)?(?:atc::)?(\w+)(<[^>]*>)?", name)
+    m = re.match(r"(?:void )?(?:\w+::)*(\w+)(<[^>]*>)?", name)      # any namespace prefix (kge::b16::atc::...)
     base = m.group(1)
     t = m.group(2) or ""
     t = t.replace("(bool)", "").replace("(int)", "").replace(" ", "")

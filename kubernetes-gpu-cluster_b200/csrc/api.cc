@@ -10,6 +10,7 @@
 #include <vector>
 
 #include "common.cuh"
+#include "half_bits.h"
 #include "kge.h"
 
 namespace kge {
@@ -71,34 +72,11 @@ static inline uint16_t f32_to_bf16_rne(float f) {
 
 // vllm:model_executor/layers/rotary_embedding/base.py:69-93 (fp32 inv_freq, fp32 outer product,
 // fp32 cos/sin, cast to the model dtype) and llama3_rope.py:33-54 (frequency rescale).
-// fp32 -> IEEE half bits, round to nearest even (the cast base.py:58-61 applies to the cos/sin cache of an fp16 model)
-static inline uint16_t f32_to_f16_rne(float f) {
-  uint32_t x;
-  memcpy(&x, &f, 4);
-  const uint32_t sign = (x >> 16) & 0x8000u;
-  x &= 0x7fffffffu;
-  if (x >= 0x7f800000u) return (uint16_t)(sign | 0x7c00u | (x > 0x7f800000u ? 0x200u : 0u));   // inf / NaN
-  if (x >= 0x477ff000u) return (uint16_t)(sign | 0x7c00u);                                        // rounds to inf
-  if (x < 0x33000001u) return (uint16_t)sign;                                                     // rounds to zero
-  if (x < 0x38800000u) {                                                                          // subnormal half
-    const int shift = 126 - (int)(x >> 23);                 // 14..24
-    const uint32_t man = (x & 0x7fffffu) | 0x800000u;
-    uint32_t r = man >> shift;
-    const uint32_t rem = man & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
-    if (rem > halfway || (rem == halfway && (r & 1u))) ++r;
-    return (uint16_t)(sign | r);
-  }
-  uint32_t r = ((x - 0x38000000u) >> 13);
-  const uint32_t rem = x & 0x1fffu;
-  if (rem > 0x1000u || (rem == 0x1000u && (r & 1u))) ++r;
-  return (uint16_t)(sign | r);
-}
-
 static int rope_cache_host(uint16_t* out_host, int max_pos, int hd, double theta, double factor,
                            double low_freq_factor, double high_freq_factor, int orig_max_pos, bool f16) {
   KGE_REQUIRE(out_host && max_pos > 0 && hd > 0 && hd % 2 == 0, "kge_rope_cache_host: bad arguments");
   const int half = hd / 2;
-  auto to16 = [f16](float v) { return f16 ? f32_to_f16_rne(v) : f32_to_bf16_rne(v); };
+  auto to16 = [f16](float v) { return f16 ? kge::f32_to_f16_bits(v) : f32_to_bf16_rne(v); };
   std::vector<float> inv(half);
   for (int i = 0; i < half; ++i) {
     const float e = (float)(2 * i) / (float)hd;               // arange(0,rd,2,float)/rd

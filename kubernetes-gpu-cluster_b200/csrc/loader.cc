@@ -1,5 +1,7 @@
 #include "loader.h"
 
+#include "half_bits.h"
+
 #include <dirent.h>
 #include <fcntl.h>
 #include <string.h>
@@ -175,28 +177,6 @@ static inline float f16_f32(uint16_t h) {
   return f;
 }
 
-// fp32 -> IEEE half bits, round to nearest even
-static inline uint16_t f32_f16(float f) {
-  uint32_t x;
-  memcpy(&x, &f, 4);
-  const uint32_t sign = (x >> 16) & 0x8000u;
-  x &= 0x7fffffffu;
-  if (x >= 0x7f800000u) return (uint16_t)(sign | 0x7c00u | (x > 0x7f800000u ? 0x200u : 0u));
-  if (x >= 0x477ff000u) return (uint16_t)(sign | 0x7c00u);
-  if (x < 0x33000001u) return (uint16_t)sign;
-  if (x < 0x38800000u) {
-    const int shift = 126 - (int)(x >> 23);
-    const uint32_t man = (x & 0x7fffffu) | 0x800000u;
-    uint32_t r = man >> shift;
-    const uint32_t rem = man & ((1u << shift) - 1u), halfway = 1u << (shift - 1);
-    if (rem > halfway || (rem == halfway && (r & 1u))) ++r;
-    return (uint16_t)(sign | r);
-  }
-  uint32_t r = ((x - 0x38000000u) >> 13);
-  const uint32_t rem = x & 0x1fffu;
-  if (rem > 0x1000u || (rem == 0x1000u && (r & 1u))) ++r;
-  return (uint16_t)(sign | r);
-}
 static inline float bf16_f32(uint16_t b) {
   const uint32_t u = (uint32_t)b << 16;
   float f;
@@ -230,10 +210,10 @@ bool ModelDir::read_16(const std::string& name, int64_t r0, int64_t r1, int64_t 
       for (int64_t c = 0; c < nc; ++c) dst[c] = f32_bf16(f16_f32(s[c]));
     } else if (t->dtype == "BF16") {
       const uint16_t* s = (const uint16_t*)t->data + src;
-      for (int64_t c = 0; c < nc; ++c) dst[c] = f32_f16(bf16_f32(s[c]));
+      for (int64_t c = 0; c < nc; ++c) dst[c] = f32_to_f16_bits(bf16_f32(s[c]));
     } else {
       const float* s = (const float*)t->data + src;
-      for (int64_t c = 0; c < nc; ++c) dst[c] = f16 ? f32_f16(s[c]) : f32_bf16(s[c]);
+      for (int64_t c = 0; c < nc; ++c) dst[c] = f16 ? f32_to_f16_bits(s[c]) : f32_bf16(s[c]);
     }
   }
   return true;

@@ -46,7 +46,8 @@ int kge_device_sm_count(void);
  *                             inside the decode step, so off by default); 0 = the cluster / distributed-shared-memory split
  *   "smem_carveout" 1/0       1 = every kernel prefers the all-shared-memory L1 split, so consecutive kernels never make an
  *                             SM reconfigure (and drain) between them; 0 = small kernels keep the driver's default split
- *   "gemm_l2_hints" 0/1       1 = the GEMM's TMA loads carry L2 eviction hints (weights evict_first, activations evict_last)
+ *   "gemm_l2_hints" 0/1       1 = the GEMM's TMA loads carry L2 eviction hints (weights evict_first, activations evict_last);
+ *                             measured slower on the prefill step (weight tiles are re-read by other CTA pairs), so off
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

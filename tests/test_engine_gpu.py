@@ -336,8 +336,8 @@ def test_stop_rules_eos_and_stop_ids(kge, model_dirs):
 
 def test_min_tokens_masks_stop_tokens_in_the_logits(kge, model_dirs):
     """vLLM's MinTokensLogitsProcessor: until a request has min_tokens outputs, its EOS and stop ids are not merely ignored
-    as stop conditions - their logits are -inf, so they cannot be sampled at all.  Take the token greedy decoding emits at
-    step 3, make it a stop id with min_tokens = 8: it must be absent from the first 8 outputs (the runner-up is taken
+    as stop conditions - their logits are -inf, so they cannot be sampled at all.  Take a token greedy decoding first emits
+    at some step k, make it a stop id with min_tokens = 8: it must be absent from the first 8 outputs (the runner-up is taken
     instead), and the request stops at its first occurrence afterwards."""
     cfg, w, d = model_dirs("tiny-llama")
     prompts = om.make_prompts(cfg, 2, 12, seed=4)
@@ -345,12 +345,14 @@ def test_min_tokens_masks_stop_tokens_in_the_logits(kge, model_dirs):
     # each request alone, as the masked runs below are: the same batches through the same kernels, so any difference is the mask's
     free = [llm.generate([pr], kge.SamplingParams(max_tokens=40, temperature=0.0, ignore_eos=True))[0].outputs[0].token_ids for pr in prompts]
     for b in range(2):
-        banned = free[b][3]
+        # the first token greedy decoding emits at a step >= 2 that it has not emitted before (a tiny random model repeats itself)
+        k = next(i for i in range(2, 8) if free[b][i] not in free[b][:i])
+        banned = free[b][k]
         out = llm.generate([prompts[b]], kge.SamplingParams(max_tokens=40, min_tokens=8, temperature=0.0, ignore_eos=True,
                                                             stop_token_ids=[banned]))[0].outputs[0]
-        assert out.token_ids[:3] == free[b][:3]                      # untouched until the banned token would have come
+        assert out.token_ids[:k] == free[b][:k]                      # untouched until the banned token would have come
         assert banned not in out.token_ids[:8], (banned, out.token_ids)
-        assert out.token_ids[3] != banned
+        assert out.token_ids[k] != banned
         if banned in out.token_ids:
             assert out.finish_reason == "stop" and out.token_ids.index(banned) == len(out.token_ids) - 1 >= 8
         # a random-sampling request obeys the mask too

@@ -51,6 +51,11 @@ int kge_device_sm_count(void);
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 
+/* Measurement hook (no counterpart in the reference): while `device_buffer` is non-null every following GEMM launch
+ * writes 16 uint64 per CTA there - %globaltimer at kernel entry, after set-up, at the first tile's arrival, after the last
+ * MMA, after the split exchange, at exit, and the SM id (slot list in tools/gemm_trace.py).  Null switches it off. */
+void kge_gemm_set_trace(void* device_buffer);
+
 /* ---------------------------------------------------------------- per-op entry points --- */
 
 /* Token (+ learned position) embedding gather.

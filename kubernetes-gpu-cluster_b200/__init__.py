@@ -142,6 +142,7 @@ SIGNATURES = {
     "kge_engine_stats": (_I, [_P, _P, _P, _P, _P]),
     "kge_sched_create": (_P, [C.c_int32] * 7),
     "kge_set_tunable": (C.c_int, [C.c_char_p, C.c_int]),
+    "kge_gemm_set_trace": (None, [C.c_void_p]),
     "kge_sched_destroy": (None, [_P]),
     "kge_sched_set_reserve_full_isl": (None, [_P, C.c_int32]),
     "kge_engine_set_reserve_full_isl": (None, [_P, C.c_int32]),

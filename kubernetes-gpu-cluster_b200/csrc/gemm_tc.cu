@@ -115,7 +115,17 @@ struct GemmParams {
   int T, N, K, act;
   int l2_hints;              // 1: weights evict_first, activations evict_last, output stored streaming
   int m_tiles, n_tiles, splits, kb_total, kb_per_split;
+  unsigned long long* trace; // phase timestamps, 16 per CTA (tools/gemm_trace.py); null outside that tool
 };
+
+// One %globaltimer stamp of this CTA's phase `slot` (see tools/gemm_trace.py for the slot list).
+__device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
+  if (p.trace) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t) :: "memory");
+    p.trace[(size_t)blockIdx.x * 16 + slot] = t;
+  }
+}
 
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ uint32_t cluster_nctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
@@ -128,6 +138,11 @@ __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
 }
 __device__ __forceinline__ void st_cluster_f32(uint32_t addr, float v) {
   asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ float4 lds_f4(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr) : "memory");
+  return v;
 }
 
 // exchange buffer of the split variant: [src rank][local column][128 rows] fp32
@@ -184,7 +199,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * STAGE_BYTES);
   // bars: full[STAGES], empty[STAGES], tmem_full[2], tmem_empty[2]
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
-  uint32_t* colmap = tmem_slot + 2;                      // [TOKN] remote address of each column's slot (SPLIT)
   float* xbuf = reinterpret_cast<float*>(smem + STAGES * STAGE_BYTES + 2048);   // SPLIT: exchange buffer;
                                                                                 // GATED && !SPLIT: up->gate hand-off [2][16][64]
   constexpr int ROWS_OUT = GATED ? 64 : BLK_M;           // output columns produced per tile
@@ -196,6 +210,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   auto tempty_bar = [&](int s) { return bar_base + 8u * (2 * STAGES + 2 + s); };
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    trace_stamp(p, 0);
+    if (p.trace) { uint32_t sm; asm volatile("mov.u32 %0, %%smid;" : "=r"(sm)); p.trace[(size_t)blockIdx.x * 16 + 15] = sm; }
+  }
   if (warp == 0 && lane == 0) {
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
     asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
@@ -218,6 +236,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) trace_stamp(p, 1);
   if (PAIR) { cluster_arrive(); cluster_wait(); }   // peer barriers are initialised before any remote signal
   // TMEM is held: the next kernel may start arriving now (see attn_tc.cu for why not earlier)
   pdl_launch_dependents();
@@ -313,6 +332,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         else tma_load_2d(b_dst, &tmap_x, full_bar(st), kb * BLK_K, n_tile * TOKN);
       };
       int w, kb0, kb1;
+      trace_stamp(p, 12);
       {
         SegIter peek = segments();
         if (peek.next(w, kb0, kb1)) {            // the first segment's first stages (a later segment's are loaded in the loop)
@@ -321,10 +341,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
           for (int i = 0; i < pre; ++i) {
             expect(i);
             load_a(i, kb0 + i, m_tile);
+            if (i == 0) trace_stamp(p, 13);
           }
         }
       }
+      trace_stamp(p, 2);
       pdl_wait();
+      trace_stamp(p, 3);
       SegIter it = segments();
       bool first_seg = true;
       while (it.next(w, kb0, kb1)) {
@@ -342,6 +365,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         }
         first_seg = false;
       }
+      trace_stamp(p, 4);
     }
   } else if (warp == 1) {
     if (lane == 0 && (!PAIR || mrank == 0)) {          // PAIR: the leader issues for both CTAs
@@ -349,6 +373,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       int acc = 0; uint32_t acc_phase = 0;
       SegIter it = segments();
       int w, kb0, kb1;
+      bool first_kb = true;
       while (it.next(w, kb0, kb1)) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
@@ -356,6 +381,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
+          if (first_kb) { trace_stamp(p, 5); first_kb = false; }
           const uint32_t a_addr = smem_base + stage * STAGE_BYTES, b_addr = a_addr + A_BYTES;
           const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(b_addr);
 #pragma unroll
@@ -372,19 +398,12 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         else tc_commit(tfull_bar(acc));         // accumulator complete
         if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
+      trace_stamp(p, 6);
     }
   } else if (warp >= 4) {
     const int q = warp - 4;                      // TMEM lane quarter == warp % 4
     const int et = threadIdx.x - 128;            // 0..127 == weight row within the tile
     int acc = 0; uint32_t acc_phase = 0;
-    if (SPLIT) {
-      // remote slot of column c: owner rank c / cols_per, my slice of its exchange buffer
-      for (int c = et; c < TOKN; c += 128) {
-        const int owner = c / cols_per, lc = c - owner * cols_per;
-        colmap[c] = mapa_u32(smem_addr(xbuf) + (uint32_t)((crank * cols_per + lc) * BLK_M * 4), (uint32_t)owner);
-      }
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-    }
     SegIter it = segments();
     int w, kb0, kb1;
     while (it.next(w, kb0, kb1)) {
@@ -393,6 +412,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       const int t0 = n_tile * TOKN;
       mbar_wait(tfull_bar(acc), acc_phase);
       tc_fence_after();
+      if (et == 0) trace_stamp(p, 7);              // (of the CTA's last segment: later segments overwrite the stamp)
       const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16) + acc * TOKN;
       const float bv = (p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f;
       if (WS && (kb0 != 0 || kb1 != KB)) {
@@ -419,6 +439,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         int* s_last = reinterpret_cast<int*>(tmem_slot + 1);
         if (et == 0) *s_last = (atomicAdd(p.ws_count + w, 1u) == (unsigned)(c_last - c_first)) ? 1 : 0;
         asm volatile("bar.sync 1, 128;" ::: "memory");
+        if (et == 0) trace_stamp(p, 8);
         if (*s_last) {
           // the LAST contributor to arrive reduces the tile: partials summed in k order (fixed), then the usual epilogue
           __threadfence();
@@ -533,38 +554,76 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         if (lane == 0) { if (PAIR) mbar_arrive_cluster(mapa_u32(tempty_bar(acc), 0u)); else mbar_arrive(tempty_bar(acc)); }
       } else {
         cluster_wait();                          // phase A done: peers' shared memory is live
+        // Phase 1: my 128 x TOKN fp32 partial goes to the owners' exchange buffers, [src rank][local column][128 rows]:
+        // one warp-wide store is 128 contiguous bytes of one remote column.
+        const uint32_t xb = smem_addr(xbuf);
+        {
+          int owner = 0, lc = 0;
 #pragma unroll 1
-        for (int c = 0; c < TOKN; c += 16) {
-          uint32_t r[16];
-          tmem_ld16(taddr + c, r);
+          for (int c = 0; c < TOKN; c += 16) {
+            uint32_t r[16];
+            tmem_ld16(taddr + c, r);
 #pragma unroll
-          for (int j = 0; j < 16; ++j) st_cluster_f32(colmap[c + j] + (uint32_t)(et * 4), __uint_as_float(r[j]));
+            for (int j = 0; j < 16; ++j) {
+              const uint32_t local = xb + (uint32_t)(((crank * cols_per + lc) * BLK_M + et) * 4);
+              st_cluster_f32(mapa_u32(local, (uint32_t)owner), __uint_as_float(r[j]));
+              if (++lc == cols_per) { lc = 0; ++owner; }
+            }
+          }
         }
         tc_fence_before();
+        if (et == 0) trace_stamp(p, 8);
         cluster_arrive();                        // phase B: my partials are in the owners' buffers
         cluster_wait();
+        if (et == 0) trace_stamp(p, 9);
+        // Phase 2: my columns, summed over the ranks in rank order.  One item = 8 consecutive weight rows of one column:
+        // 32 contiguous bytes per rank in shared memory, one 16-byte store of the output row.
         const int c_begin = crank * cols_per, c_end = min(TOKN, c_begin + cols_per);
-        if (n < p.N && (!GATED || et < 64)) {
-          for (int c = c_begin; c < c_end; ++c) {
-            const int t = t0 + c;
-            if (t >= p.T) break;
-            float v = 0.f, u = 0.f;
-            for (int s2 = 0; s2 < S; ++s2) {
-              v += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et];
-              if (GATED) u += xbuf[(s2 * cols_per + (c - c_begin)) * BLK_M + et + 64];
-            }
+        constexpr int RG = GATED ? 8 : 16;                       // 8-row groups per column
+        const int n_items = (c_end - c_begin) * RG;
+        const bool vec_ok = (p.N & 7) == 0;
+        for (int item = et; item < n_items; item += 128) {
+          const int lc = item / RG, rg = item % RG;
+          const int t = t0 + c_begin + lc;
+          if (t >= p.T) break;
+          float a[8], u[GATED ? 8 : 1];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) { a[k] = 0.f; if (GATED) u[k] = 0.f; }
+          for (int s2 = 0; s2 < S; ++s2) {
+            const uint32_t src = xb + (uint32_t)(((s2 * cols_per + lc) * BLK_M + rg * 8) * 4);
+            const float4 v0 = lds_f4(src), v1 = lds_f4(src + 16);
+            a[0] += v0.x; a[1] += v0.y; a[2] += v0.z; a[3] += v0.w;
+            a[4] += v1.x; a[5] += v1.y; a[6] += v1.z; a[7] += v1.w;
             if (GATED) {
-              v = silu_gate_bf16(v, u);
-            } else {
-              v += bv;
-              if (p.act == 1) v = fmaxf(v, 0.f);
+              const float4 w0 = lds_f4(src + 64 * 4), w1 = lds_f4(src + 64 * 4 + 16);
+              u[0] += w0.x; u[1] += w0.y; u[2] += w0.z; u[3] += w0.w;
+              u[4] += w1.x; u[5] += w1.y; u[6] += w1.z; u[7] += w1.w;
             }
-            p.y[(int64_t)t * p.N + n] = f2bf(v);
+          }
+          const int n0 = m_tile * ROWS_OUT + rg * 8;
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            if (GATED) {
+              a[k] = silu_gate_bf16(a[k], u[k]);
+            } else {
+              if (p.bias && n0 + k < p.N) a[k] += bf2f(p.bias[n0 + k]);
+              if (p.act == 1) a[k] = fmaxf(a[k], 0.f);
+            }
+          }
+          bf16* dst = p.y + (int64_t)t * p.N + n0;
+          if (vec_ok && n0 + 7 < p.N) {
+            uint4 o;
+            o.x = pack_bf2(a[0], a[1]); o.y = pack_bf2(a[2], a[3]); o.z = pack_bf2(a[4], a[5]); o.w = pack_bf2(a[6], a[7]);
+            *reinterpret_cast<uint4*>(dst) = o;
+          } else {
+#pragma unroll
+            for (int k = 0; k < 8; ++k) if (n0 + k < p.N) dst[k] = f2bf(a[k]);
           }
         }
       }
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (et == 0) trace_stamp(p, 10);
   }
   if (SPLIT && warp < 4) {                       // non-epilogue warps take part in both cluster phases
     cluster_wait();
@@ -573,6 +632,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) trace_stamp(p, 11);
   if (PAIR) { cluster_arrive(); cluster_wait(); }   // the peer may still signal my barriers until it is done too
   if (warp == 2) {
     tc_fence_after();
@@ -825,6 +885,15 @@ static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtenso
 
 using namespace kge;
 
+#ifndef KGE_HALF
+unsigned long long* g_gemm_trace = nullptr;
+// Measurement hook of tools/gemm_trace.py: device buffer of 16 timestamps per CTA of the following GEMM launches
+// (both element types), or null to stop.  No counterpart in the reference.
+extern "C" void kge_gemm_set_trace(void* device_buffer) { g_gemm_trace = (unsigned long long*)device_buffer; }
+#else
+extern unsigned long long* g_gemm_trace;
+#endif
+
 static int64_t ws_bytes_of(const GemmPlan& g) {        // counters + two partial tiles per CTA
   return g.ws ? kWsCounterBytes + (int64_t)g.splits * 2 * g.tokn * BLK_M * 4 : 0;
 }
@@ -862,6 +931,7 @@ extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* 
   GemmParams p;
   p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
   p.l2_hints = tunable(TUN_GEMM_L2_HINTS);
+  p.trace = g_gemm_trace;
   p.ws_count = g.ws ? (unsigned int*)workspace : nullptr;
   p.ws_part = g.ws ? (float*)((uint8_t*)workspace + kWsCounterBytes) : nullptr;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;
@@ -885,6 +955,7 @@ extern "C" int KGE_GEMM_GATE_WS_NAME(void* y, const void* x, const void* w_gate_
   GemmParams p;
   p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
   p.l2_hints = tunable(TUN_GEMM_L2_HINTS);
+  p.trace = g_gemm_trace;
   p.ws_count = g.ws ? (unsigned int*)workspace : nullptr;
   p.ws_part = g.ws ? (float*)((uint8_t*)workspace + kWsCounterBytes) : nullptr;
   p.m_tiles = g.m_tiles; p.n_tiles = g.n_tiles; p.splits = g.splits;

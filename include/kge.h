@@ -36,8 +36,6 @@ int kge_device_sm_count(void);
  *   "attn_cluster_merge" 0/1  decode attention: 1 = the split-KV CTAs of a (request, kv head) form a thread-block
  *                             cluster and merge over distributed shared memory instead of workspace + merge kernel
  *                             (same bits; measured slower, so off by default)
- *   "gemm_shallow" 0/1        experiment: decode-sized GEMMs (T <= 64) as twice as many CTAs with half the shared memory
- *                             each (two per SM), so the next kernel's CTAs move in as this one's retire; off by default
  *   "attn_tma" 1/0            attention K/V tiles fetched by the TMA unit (one producer thread, cp.async.bulk.tensor boxes
  *                             of one KV block) instead of per-thread 16-byte cp.async gathers; 0 = the round-1 kernels, kept
  *                             for same-box comparison and for block sizes below 8

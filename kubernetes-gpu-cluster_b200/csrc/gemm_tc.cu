@@ -373,7 +373,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
       int acc = 0; uint32_t acc_phase = 0;
       SegIter it = segments();
       int w, kb0, kb1;
-      bool first_kb = true;
+      if (p.trace) { mbar_wait(full_bar(0), 0); trace_stamp(p, 5); }      // (a wait does not consume the phase)
+      // This one thread paces a decode-sized GEMM (every instruction between two k-blocks is serial latency), so the
+      // loop carries the stage's descriptors along instead of rebuilding them.
+      const uint64_t adesc0 = umma_desc_sw128(smem_base), bdesc0 = umma_desc_sw128(smem_base + A_BYTES);
+      uint64_t adesc = adesc0, bdesc = bdesc0;
       while (it.next(w, kb0, kb1)) {
         mbar_wait(tempty_bar(acc), acc_phase ^ 1);
         tc_fence_after();
@@ -381,9 +385,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(full_bar(stage), phase);
           tc_fence_after();
-          if (first_kb) { trace_stamp(p, 5); first_kb = false; }
-          const uint32_t a_addr = smem_base + stage * STAGE_BYTES, b_addr = a_addr + A_BYTES;
-          const uint64_t adesc = umma_desc_sw128(a_addr), bdesc = umma_desc_sw128(b_addr);
 #pragma unroll
           for (int k = 0; k < BLK_K / UMMA_K; ++k) {
             // +32 B per 16-element k step inside the 128 B swizzle row (start address field is >>4)
@@ -392,7 +393,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
           }
           if (PAIR) tc_commit_cg2(empty_bar(stage), (uint16_t)3); // frees the stage in both CTAs
           else tc_commit(empty_bar(stage));     // frees the smem slot when these MMAs retire
-          if (++stage == STAGES) { stage = 0; phase ^= 1; }
+          adesc += STAGE_BYTES >> 4; bdesc += STAGE_BYTES >> 4;
+          if (++stage == STAGES) { stage = 0; phase ^= 1; adesc = adesc0; bdesc = bdesc0; }
         }
         if (PAIR) tc_commit_cg2(tfull_bar(acc), (uint16_t)3);   // both CTAs' epilogues
         else tc_commit(tfull_bar(acc));         // accumulator complete
@@ -705,21 +707,14 @@ int make_tmap(CUtensorMap* m, const void* ptr, int64_t rows, int64_t cols, int b
   return 0;
 }
 
-// SHALLOW (experiment, knob "gemm_shallow", off by default): at most half an SM's shared memory per CTA and twice as
-// many CTAs, so every SM holds TWO streaming CTAs - the same bytes in flight per SM as the deep pipeline, but when the
-// CTAs of one GEMM finish one by one, CTAs of the next kernel (launched early by PDL) move into the freed half and
-// start streaming their weights: HBM does not idle across the kernel boundary.  Round 1 measured only half of this
-// idea (shallow pipeline with ONE CTA per SM: slower); this is the full configuration, to be measured next round.
-constexpr int gemm_smem_budget(bool shallow) { return shallow ? 112 * 1024 : 224 * 1024; }
-static bool gemm_shallow(int tokn) { return tunable(TUN_GEMM_SHALLOW) != 0 && tokn <= 64; }
-constexpr int kSlotsShallow = 2 * 148;
+constexpr int kGemmSmemBudget = 224 * 1024;
 
-template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool SHALLOW = false, bool WS = false>
+template <int TOKN, bool SPLIT, bool GATED, bool PAIR = false, bool WS = false>
 static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + (PAIR ? 128 : TOKN) * BLK_K * 2;
   // barriers + column map, then the cluster exchange buffer (SPLIT) or the up->gate hand-off (GATED)
   constexpr int extra = 2048 + (SPLIT ? xbuf_bytes(TOKN) : (GATED ? 2 * 16 * 64 * 4 : 0));
-  constexpr int budget = gemm_smem_budget(SHALLOW) - 1024 - extra;
+  constexpr int budget = kGemmSmemBudget - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   static_assert(STAGES >= 3, "pipeline too shallow");
   constexpr int smem = STAGES * stage_bytes + 1024 /*align*/ + extra;
@@ -749,9 +744,9 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
     attr[1].val.clusterDim.x = 2; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
     cfg.numAttrs = 2;
   } else {
-    constexpr int slots = SHALLOW ? kSlotsShallow : 148;
+    constexpr int slots = 148;
     int grid = tiles < slots ? tiles : slots;
-    if (!SHALLOW && tunable(TUN_GEMM_EVEN_GRID) && tiles > 148) {
+    if (tunable(TUN_GEMM_EVEN_GRID) && tiles > 148) {
       // persistent round-robin: 224 tiles on 148 CTAs leaves 72 CTAs idle for the second half; 112 CTAs with two
       // tiles each keep every CTA streaming to the end (a weight-streaming GEMM needs bytes in flight, not SMs)
       const int rounds = (tiles + 147) / 148;
@@ -763,11 +758,11 @@ static int launch_gemm(const CUtensorMap& tw, const CUtensorMap& tx, const GemmP
   return 0;
 }
 
-template <int TOKN, bool SHALLOW>
+template <int TOKN>
 static int query_max_clusters(int S) {
   constexpr int stage_bytes = BLK_M * BLK_K * 2 + TOKN * BLK_K * 2;
   constexpr int extra = 2048 + xbuf_bytes(TOKN);
-  constexpr int budget = gemm_smem_budget(SHALLOW) - 1024 - extra;
+  constexpr int budget = kGemmSmemBudget - 1024 - extra;
   constexpr int STAGES = (budget / stage_bytes) > 8 ? 8 : (budget / stage_bytes);
   constexpr int smem = STAGES * stage_bytes + 1024 + extra;
   auto kern = gemm_tc_kernel<TOKN, STAGES, true, false>;   // the gated variant has the same footprint
@@ -786,17 +781,15 @@ static int query_max_clusters(int S) {
 // How many clusters of size S of the split kernel can be co-resident (GPC packing decides: 148 SMs
 // hold e.g. 34 clusters of 4 but fewer than 148/3 clusters of 3).  Cached per (token tile, S).
 static int max_clusters(int tokn, int S) {
-  static int cache[2][4][9];
-  static bool have[2][4][9];
+  static int cache[4][9];
+  static bool have[4][9];
   const int ti = tokn == 16 ? 0 : tokn == 32 ? 1 : tokn == 64 ? 2 : 3;
-  const int sh = gemm_shallow(tokn) ? 1 : 0;
-  if (!have[sh][ti][S]) {
-    if (sh) cache[sh][ti][S] = ti == 0 ? query_max_clusters<16, true>(S) : ti == 1 ? query_max_clusters<32, true>(S) : query_max_clusters<64, true>(S);
-    else cache[sh][ti][S] = ti == 0 ? query_max_clusters<16, false>(S) : ti == 1 ? query_max_clusters<32, false>(S)
-                          : ti == 2 ? query_max_clusters<64, false>(S) : query_max_clusters<128, false>(S);
-    have[sh][ti][S] = true;
+  if (!have[ti][S]) {
+    cache[ti][S] = ti == 0 ? query_max_clusters<16>(S) : ti == 1 ? query_max_clusters<32>(S)
+                 : ti == 2 ? query_max_clusters<64>(S) : query_max_clusters<128>(S);
+    have[ti][S] = true;
   }
-  return cache[sh][ti][S];
+  return cache[ti][S];
 }
 
 struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; bool ws; };
@@ -813,7 +806,7 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M, bool ws_ok 
   g.kb_total = (K + BLK_K - 1) / BLK_K;
   const int tiles = g.m_tiles * g.n_tiles;
   int splits = 1;
-  const int slots = gemm_shallow(g.tokn) ? kSlotsShallow : 148;      // CTAs that can be resident at once
+  const int slots = 148;                       // CTAs that can be resident at once
   if (ws_ok && g.tokn <= 128 && tiles <= (int)(kWsCounterBytes / 4) && tiles % 148 != 0 && tunable(TUN_GEMM_WS)) {
     // stream-K: one CTA per SM, every CTA the same number of k-blocks (at least 4, i.e. 256 of K)
     const int64_t units = (int64_t)tiles * g.kb_total;
@@ -841,24 +834,10 @@ template <bool GATED>
 static int dispatch_gemm(const GemmPlan& g, const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
   if (g.ws) {
     switch (g.tokn) {
-      case 16: return launch_gemm<16, false, GATED, false, false, true>(tw, tx, p, st);
-      case 32: return launch_gemm<32, false, GATED, false, false, true>(tw, tx, p, st);
-      case 64: return launch_gemm<64, false, GATED, false, false, true>(tw, tx, p, st);
-      default: return launch_gemm<128, false, GATED, false, false, true>(tw, tx, p, st);
-    }
-  }
-  if (gemm_shallow(g.tokn)) {
-    if (g.splits > 1) {
-      switch (g.tokn) {
-        case 16: return launch_gemm<16, true, GATED, false, true>(tw, tx, p, st);
-        case 32: return launch_gemm<32, true, GATED, false, true>(tw, tx, p, st);
-        default: return launch_gemm<64, true, GATED, false, true>(tw, tx, p, st);
-      }
-    }
-    switch (g.tokn) {
       case 16: return launch_gemm<16, false, GATED, false, true>(tw, tx, p, st);
       case 32: return launch_gemm<32, false, GATED, false, true>(tw, tx, p, st);
-      default: return launch_gemm<64, false, GATED, false, true>(tw, tx, p, st);
+      case 64: return launch_gemm<64, false, GATED, false, true>(tw, tx, p, st);
+      default: return launch_gemm<128, false, GATED, false, true>(tw, tx, p, st);
     }
   }
   if (g.splits > 1) {

@@ -266,6 +266,9 @@ GEMM_CASES = [
     (64, 8192, 2048, False, 0),               # 70B TP4 o_proj decode: 64 tiles, cluster of 2
     (8192, 8192, 2048, False, 0),             # 70B TP4 o_proj prefill: CTA pairs, short K
     (8192, 2560, 8192, False, 0),             # 70B TP4 qkv prefill: 20 row tiles -> 10 pairs
+    (64, 1000, 2048, True, 1),                # N % 8 != 0: scalar stores in the split reduce, ragged last tile
+    (48, 4104, 4096, False, 0),               # N a multiple of 8 but of no tile height
+    (100, 6144, 4096, True, 0),               # 128-token tile, split K
 ]
 
 
@@ -380,16 +383,6 @@ EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
 
 
 @EXPERIMENTAL
-@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 64])
-def test_gemm_shallow_variant(kge, L, T, N, K, bias, act):
-    """knob gemm_shallow: two half-footprint CTAs per SM (more, shorter split-K ranges): same tolerance as the default."""
-    try:
-        check_ok(kge, L.kge_set_tunable(b"gemm_shallow", 1), "tunable")
-        test_gemm_bf16(kge, L, T, N, K, bias, act)
-    finally:
-        L.kge_set_tunable(b"gemm_shallow", 0)
-
-
 @pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048),
                                    (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024),
                                    (64, 7168, 8192), (8192, 7168, 1024)])    # 70B TP4 gate_up: decode, prefill pairs

@@ -38,9 +38,9 @@ NAMES = ["entry", "setup", "w_issued", "dep", "loads_issued", "first_tile", "mma
 MAX_CTAS = 2048
 
 
-def trace_shape(T, N, K, gated, launches=8):
+def trace_shape(T, N, K, gated, launches=8, resident=False):
     rows_w = 2 * N if gated else N
-    ncopies = min(12, max(2, int(400e6 // (rows_w * K * 2)) + 1))
+    ncopies = 1 if resident else min(12, max(2, int(400e6 // (rows_w * K * 2)) + 1))
     ws = [torch.randn(rows_w, K, device="cuda", dtype=BF) * 0.02 for _ in range(ncopies)]
     x = torch.randn(T, K, device="cuda", dtype=BF)
     y = torch.empty(T, N, device="cuda", dtype=BF)
@@ -114,15 +114,20 @@ def main():
     ap.add_argument("--T", type=int, default=64)
     ap.add_argument("--knob", action="append", default=[])
     ap.add_argument("--out", default=None)
+    ap.add_argument("--resident", action="store_true", help="one weight copy: it stays in L2 between launches")
+    ap.add_argument("--shapes", default="all", help="all | decode (the four per-layer projections)")
     a = ap.parse_args()
     for kv in a.knob:
         k, v = kv.split("=")
         kge.check(L.kge_set_tunable(k.encode(), int(v)), "tunable")
     shapes = [(6144, 4096, False), (4096, 4096, False), (14336, 4096, True), (4096, 14336, False), (128256, 4096, False)]
     fh = open(a.out, "a") if a.out else None
+    if a.shapes == "decode":
+        shapes = shapes[:4]
     for (N, K, gated) in shapes:
-        row = trace_shape(a.T, N, K, gated)
+        row = trace_shape(a.T, N, K, gated, resident=a.resident)
         row["knobs"] = a.knob
+        row["resident"] = a.resident
         print(json.dumps(row), flush=True)
         if fh:
             fh.write(json.dumps(row) + "\n")

@@ -1,6 +1,6 @@
 """Real-mode (CUDA graphs + programmatic dependent launch) decode step time of C3 (llama-3.1-8b shapes, 64
 requests, ctx 2048..2048+N) under different launch-shape knobs.  One engine per setting (captured graphs keep
-their launch shapes).  python tools/probe_decode.py '{"gemm_shallow":1}' '{"gemm_even_grid":0}' ..."""
+their launch shapes).  python tools/probe_decode.py '{"gemm_ws":1}' '{"gemm_even_grid":0}' ..."""
 import json
 import os
 import sys
@@ -13,7 +13,7 @@ from kge_loader import load  # noqa: E402
 kge = load()
 L = kge.lib()
 BS = int(os.environ.get("PROBE_BLOCK", "64"))
-DEFAULTS = {"gemm_l2_hints": 0, "smem_carveout": 1, "gemm_ws": 0, "attn_tma": 1, "pdl": 1, "gemm_even_grid": 1, "attn_decode_splits": 0, "attn_split_balance": 0, "attn_cluster_merge": 0, "gemm_shallow": 0}
+DEFAULTS = {"gemm_l2_hints": 0, "smem_carveout": 1, "gemm_ws": 0, "attn_tma": 1, "pdl": 1, "gemm_even_grid": 1, "attn_decode_splits": 0, "attn_split_balance": 0, "attn_cluster_merge": 0}
 
 
 def main():

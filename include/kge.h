@@ -46,6 +46,11 @@ int kge_device_sm_count(void);
  *                             SM reconfigure (and drain) between them; 0 = small kernels keep the driver's default split
  *   "gemm_l2_hints" 0/1       1 = the GEMM's TMA loads carry L2 eviction hints (weights evict_first, activations evict_last);
  *                             measured slower on the prefill step (weight tiles are re-read by other CTA pairs), so off
+ *   "attn_persistent" 1/0     decode attention with 64-token KV blocks or larger: 1 = 2 x 148 resident CTAs each take an equal,
+ *                             contiguous share of all key tiles of the launch (a (request, kv head) group is cut where shares
+ *                             end; pieces merged by the last CTA of the group to arrive) - one round whatever the batch and
+ *                             the context lengths are; 0 = one CTA per (request, kv head, split) with equal splits.  Equal at
+ *                             64 x 2176 keys (96 us), 6-8 % faster at 64 x 1024 and 8 x 8192 (profiles/r02_summary.md)
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

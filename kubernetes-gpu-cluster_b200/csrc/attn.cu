@@ -323,7 +323,7 @@ int attn_decode_splits(int B, int KV, int max_seq_len);
 bool decode_tma_supported(int B, int KV, int bs);          // attn_decode_tma.cu
 int paged_attn_decode_tma(bf16* out, const bf16* q, int q_stride, const bf16* kc, const bf16* vc, const int32_t* bt, int max_blocks,
                           const int32_t* sl, const int32_t* qsl, int B, int H, int KV, int hd, int bs, int ns, float scale_log2,
-                          float* part_o, float* part_ml, cudaStream_t st);
+                          float* part_o, float* part_ml, void* ws, int64_t ws_bytes, int max_seq_len, cudaStream_t st);
 static int decode_splits(int B, int KV, int max_seq_len) { return attn_decode_splits(B, KV, max_seq_len); }
 // Split-KV factor of a decode launch; also part of the key of the engine's captured decode graphs.
 int attn_decode_splits(int B, int KV, int max_seq_len) {
@@ -391,7 +391,8 @@ static int launch_attn(bf16* out, const bf16* q, int q_stride, const bf16* kc, c
     // rate, not HBM, bounds the kernel - 107 us against 102 us for the cp.async gathers; from 32-token blocks on the
     // boxes are large enough and TMA wins, 96 us at 64)
     if (tunable(TUN_ATTN_TMA) && bs >= 32 && decode_tma_supported(B, KV, bs))
-      return paged_attn_decode_tma(out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, B, H, KV, HD, bs, ns, sl2, po, pml, st);
+      return paged_attn_decode_tma(out, q, q_stride, kc, vc, bt, max_blocks, sl, qsl, B, H, KV, HD, bs, ns, sl2, po, pml, ws, ws_bytes,
+                                   max_seq_len, st);
     auto kern = attn_decode_kernel<HD, kDecodeStages, false>;
     KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, decode_smem<HD>()));
     KGE_CUDA_OK(launch_pdl(kern, dim3(ns, KV, B), dim3(128), decode_smem<HD>(), st, out, po, pml, q, q_stride, kc, vc, bt,

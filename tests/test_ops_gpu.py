@@ -532,6 +532,8 @@ def test_paged_attention_bench_shapes(kge, L, H, KV, hd, q_lens, seq_lens, ramp)
     run_attn_case(kge, L, H, KV, hd, 16, q_lens, seq_lens, seed=H * 17 + sum(q_lens) + int(ramp), ramp=ramp)
 
 
+PERSISTENT_DEFAULT = 1          # the library's default for knob attn_persistent
+
 DECODE_SPLIT_CASES = [
     # H, KV, hd, q_lens, seq_lens, forced split-KV factor (0 = heuristic)
     (32, 8, 128, [1] * 3, [2176, 1500, 700], 0),
@@ -565,6 +567,39 @@ def test_decode_attention_variants_give_the_same_bits(kge, L, H, KV, hd, q_lens,
         L.kge_set_tunable(b"attn_tma", 1)
     for other in (a2, b, c):
         assert torch.equal(a.view(torch.int16), other.view(torch.int16))
+
+
+PERSISTENT_CASES = [
+    # H, KV, hd, block size, seq_lens, forced split factor
+    (32, 8, 128, 64, [2100 + 3 * i for i in range(48)], 0),        # 48 x 8 x 2 items > 296 resident CTAs: several items per CTA
+    (32, 8, 128, 64, [1 + 97 * i for i in range(40)], 3),          # ragged: empty splits, one-tile items
+    (32, 8, 128, 32, [700, 64, 65, 2176, 5], 2),
+    (64, 8, 128, 64, [900 + 11 * i for i in range(20)], 2),        # groups of 8 q heads: two merge passes
+    (32, 8, 64, 64, [40, 128, 129, 1000] * 12, 2),
+    (12, 12, 64, 128, [5, 130, 600] * 30, 1),                      # no split: results straight from the cross-warp merge
+    (16, 1, 128, 64, [3000, 17], 4),                               # groups of 16 q heads: four merge passes
+]
+
+
+@pytest.mark.parametrize("H,KV,hd,bs,seq_lens,splits", PERSISTENT_CASES)
+def test_decode_attention_persistent(kge, L, H, KV, hd, bs, seq_lens, splits):
+    """Knob attn_persistent: 2 x 148 CTAs each take an equal, contiguous share of all key tiles (a group is cut where the
+    shares end, not into equal splits).  Same tile arithmetic, other split points: against the oracle (run_attn_case),
+    within rounding of the one-CTA-per-split kernel, and the same bits on every run (partials merged in split order)."""
+    seed = H * 5 + sum(seq_lens) + splits
+    q_lens = [1] * len(seq_lens)
+    try:
+        check_ok(kge, L.kge_set_tunable(b"attn_decode_splits", splits), "tunable")
+        check_ok(kge, L.kge_set_tunable(b"attn_persistent", 0), "tunable")
+        a = run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed)
+        check_ok(kge, L.kge_set_tunable(b"attn_persistent", 1), "tunable")
+        b = run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed)
+        c = run_attn_case(kge, L, H, KV, hd, bs, q_lens, seq_lens, seed)
+    finally:
+        L.kge_set_tunable(b"attn_decode_splits", 0)
+        L.kge_set_tunable(b"attn_persistent", PERSISTENT_DEFAULT)
+    assert torch.equal(b.view(torch.int16), c.view(torch.int16))
+    assert (a.float() - b.float()).abs().max().item() <= 2e-2 * max(1.0, a.float().abs().max().item())
 
 
 @pytest.mark.parametrize("H,KV,hd,bs,q_lens,seq_lens", [c for c in ATTN_CASES if max(c[4]) > 1][:5] + [ATTN_LONG_CASES[2][:3] + (16,) + ATTN_LONG_CASES[2][3:5]])

@@ -616,20 +616,49 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
       }
       bar_compute();
       if (*s_last) {
-        for (int i = tid; i < G * HD; i += 128) {
-          const int r = i / HD, c = i % HD;
-          const int64_t p0 = ((int64_t)b * H + kvh * G + r) * slots;
-          float mm = -INFINITY;
-          for (int sidx = 0; sidx < nsplit; ++sidx) mm = fmaxf(mm, __ldcg(part_ml + (p0 + sidx) * 2));
-          const float basem = (mm == -INFINITY) ? 0.f : mm;
-          float acc = 0.f, ll = 0.f;
-          for (int sidx = 0; sidx < nsplit; ++sidx) {
-            const float sc = exp2f(__ldcg(part_ml + (p0 + sidx) * 2) - basem);
-            acc += __ldcg(part_o + (p0 + sidx) * HD + c) * sc;
-            ll += __ldcg(part_ml + (p0 + sidx) * 2 + 1) * sc;
-          }
-          out[(int64_t)qrow * H * HD + (kvh * G + r) * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+        // Every load here is an L2 round trip, and all CTAs reach this point together at the end of the kernel: first the
+        // (m, l) pairs of every (row, split) into shared memory in one trip, then the partial outputs eight loads at a time.
+        float* sMl = sRed;                          // [G][nsplit][2] (the merge passes are done with sRed)
+        const int64_t grp0 = ((int64_t)b * H + kvh * G) * slots;
+        for (int i = tid; i < G * nsplit * 2; i += 128) {
+          const int r = i / (nsplit * 2), rest = i % (nsplit * 2);
+          sMl[i] = __ldcg(part_ml + (grp0 + (int64_t)r * slots) * 2 + rest);
         }
+        bar_compute();
+        // item = (row r, column c); the (item, split) pairs of this thread form one flat sequence, consumed in order
+        const int n_my = (G * HD - tid + 127) / 128;          // items tid, tid + 128, ...
+        const int n_flat = n_my * nsplit;
+        float acc = 0.f, ll = 0.f, basem = 0.f;
+        for (int f0 = 0; f0 < n_flat; f0 += 8) {
+          float v[8];
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int f = f0 + k;
+            const int item = tid + 128 * (f / nsplit), sidx = f % nsplit;
+            const int r = item / HD, c = item % HD;
+            v[k] = f < n_flat ? __ldcg(part_o + (grp0 + (int64_t)r * slots + sidx) * HD + c) : 0.f;
+          }
+#pragma unroll
+          for (int k = 0; k < 8; ++k) {
+            const int f = f0 + k;
+            if (f < n_flat) {
+              const int item = tid + 128 * (f / nsplit), sidx = f % nsplit;
+              const int r = item / HD, c = item % HD;
+              const float* ml = sMl + (r * nsplit) * 2;
+              if (sidx == 0) {
+                float mm = -INFINITY;
+                for (int s2 = 0; s2 < nsplit; ++s2) mm = fmaxf(mm, ml[s2 * 2]);
+                basem = (mm == -INFINITY) ? 0.f : mm;
+                acc = 0.f; ll = 0.f;
+              }
+              const float sc = exp2f(ml[sidx * 2] - basem);
+              acc += v[k] * sc;
+              ll += ml[sidx * 2 + 1] * sc;
+              if (sidx == nsplit - 1) out[(int64_t)qrow * H * HD + (kvh * G + r) * HD + c] = f2bf(ll > 0.f ? acc / ll : 0.f);
+            }
+          }
+        }
+        bar_compute();                              // sMl is read: the next segment's merge passes may overwrite it
         if (tid == 0) g_split_arrivals[b * KV + kvh] = 0;
       }
     }

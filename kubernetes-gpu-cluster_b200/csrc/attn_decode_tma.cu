@@ -609,9 +609,8 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
     }
     if (nsplit > 1) {
       if (tid == 0) {                             // (the barrier above ordered every thread's partial stores before this)
-        __threadfence();
-        const unsigned prev = atomicAdd(&g_split_arrivals[b * KV + kvh], 1u);
-        __threadfence();
+        unsigned prev;                              // release my CTA's partials, acquire the others': one instruction
+        asm volatile("atom.add.acq_rel.gpu.global.u32 %0, [%1], 1;" : "=r"(prev) : "l"(&g_split_arrivals[b * KV + kvh]) : "memory");
         *s_last = (prev == (unsigned)nsplit - 1u) ? 1 : 0;
       }
       bar_compute();

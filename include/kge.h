@@ -46,6 +46,10 @@ int kge_device_sm_count(void);
  *                             SM reconfigure (and drain) between them; 0 = small kernels keep the driver's default split
  *   "gemm_l2_hints" 0/1       1 = the GEMM's TMA loads carry L2 eviction hints (weights evict_first, activations evict_last);
  *                             measured slower on the prefill step (weight tiles are re-read by other CTA pairs), so off
+ *   "gemm_wide" 1/0           GEMMs of up to 64 tokens: 1 = where it keeps as many CTAs streaming as the 128-row plan, tiles of
+ *                             256 weight rows with the tokens as the MMA's M side and the weights as its N side (a tcgen05.mma
+ *                             fed from shared memory costs ~165 cycles whatever its shape, so twice the weight bytes per MMA);
+ *                             0 = always 128-row tiles with the tokens as N.  C3 decode step 6.54-6.58 vs 6.64-6.71 ms
  *   "attn_persistent" 1/0     decode attention with 64-token KV blocks or larger: 1 = 2 x 148 resident CTAs each take an equal,
  *                             contiguous share of all key tiles of the launch (a (request, kv head) group is cut where shares
  *                             end; pieces merged by the last CTA of the group to arrive) - one round whatever the batch and

@@ -36,8 +36,8 @@ bool pdl_for_this_launch() {
   return pdl_enabled() && !brk;
 }
 
-static std::atomic<int> g_tun[TUN_COUNT] = {{1}, {0}, {0}, {0}, {1}, {0}, {1}, {0}, {1}};   // even grid measured +6.5 % on the C3 gate_up GEMM (profiles/r01_knob_sweep.md)
-static const char* const kTunNames[TUN_COUNT] = {"gemm_even_grid", "attn_decode_splits", "attn_split_balance", "attn_cluster_merge", "attn_tma", "gemm_ws", "smem_carveout", "gemm_l2_hints", "attn_persistent"};
+static std::atomic<int> g_tun[TUN_COUNT] = {{1}, {0}, {0}, {0}, {1}, {0}, {1}, {0}, {1}, {1}};   // even grid measured +6.5 % on the C3 gate_up GEMM (profiles/r01_knob_sweep.md)
+static const char* const kTunNames[TUN_COUNT] = {"gemm_even_grid", "attn_decode_splits", "attn_split_balance", "attn_cluster_merge", "attn_tma", "gemm_ws", "smem_carveout", "gemm_l2_hints", "attn_persistent", "gemm_wide"};
 int tunable(Tunable t) { return g_tun[t].load(std::memory_order_relaxed); }
 }  // namespace kge
 
@@ -46,7 +46,7 @@ extern "C" int kge_set_tunable(const char* name, int value) {
   if (!strcmp(name, "pdl")) { kge::pdl_set_enabled(value != 0); return 0; }
   for (int i = 0; i < kge::TUN_COUNT; ++i)
     if (!strcmp(name, kge::kTunNames[i])) { kge::g_tun[i].store(value, std::memory_order_relaxed); return 0; }
-  kge::set_error("kge_set_tunable: unknown knob '%s' (pdl, gemm_even_grid, attn_decode_splits, attn_split_balance, attn_cluster_merge, attn_tma, gemm_ws, smem_carveout, gemm_l2_hints, attn_persistent)", name);
+  kge::set_error("kge_set_tunable: unknown knob '%s' (pdl, gemm_even_grid, attn_decode_splits, attn_split_balance, attn_cluster_merge, attn_tma, gemm_ws, smem_carveout, gemm_l2_hints, attn_persistent, gemm_wide)", name);
   return -1;
 }
 

@@ -19,7 +19,7 @@ void pdl_break_next();
 bool pdl_for_this_launch();
 // Launch-shape knobs behind kge_set_tunable() (api.cc): heuristics that only change HOW work is
 // partitioned, never results.  Defaults are the measured-best settings (profiles/).
-enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_ATTN_TMA = 4, TUN_GEMM_WS = 5, TUN_SMEM_CARVEOUT = 6, TUN_GEMM_L2_HINTS = 7, TUN_ATTN_PERSISTENT = 8, TUN_COUNT = 9 };
+enum Tunable { TUN_GEMM_EVEN_GRID = 0, TUN_ATTN_DECODE_SPLITS = 1, TUN_ATTN_SPLIT_BALANCE = 2, TUN_ATTN_CLUSTER_MERGE = 3, TUN_ATTN_TMA = 4, TUN_GEMM_WS = 5, TUN_SMEM_CARVEOUT = 6, TUN_GEMM_L2_HINTS = 7, TUN_ATTN_PERSISTENT = 8, TUN_GEMM_WIDE = 9, TUN_COUNT = 10 };
 int tunable(Tunable t);
 
 #define KGE_CUDA_OK(expr)                                                              \

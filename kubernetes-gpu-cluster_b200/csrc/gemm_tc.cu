@@ -643,6 +643,260 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
   }
 }
 
+// ------------------------------------------------------------------------------ wide tiles for T <= 64
+// A tcgen05.mma whose operands both sit in shared memory costs ~165 cycles whatever its shape (profiles/r02_summary.md
+// section 3): with 128 weight rows as M and the tokens as N, a decode-sized GEMM pays four of them for every 16 KB of
+// weights and its main loop, not HBM, sets the pace (330-385 ns per k-block).  Here the roles are swapped and the tile
+// is wider: the tokens are the M side (64 rows loaded; the MMA is 128 tall and its upper half reads whatever follows
+// the token tile in shared memory - rows that are never read back), 256 weight rows are N of ONE MMA, so the same four
+// MMAs move 32 KB of weights.  D is [token][weight row] in TMEM: a thread owns a token and 256 consecutive outputs,
+// which it stores 16 bytes at a time; the fused SwiGLU epilogue finds gate (columns 0-127) and up (128-255) of an
+// output in the same thread.  One tile per CTA; K split over a cluster as above, the exchange buffer laid over the
+// pipeline stages once every CTA of the cluster is past its main loop.
+constexpr int WIDE_N = 256;                 // weight rows per tile (GATED: 128 gate rows + their 128 up rows)
+constexpr int WIDE_M = 64;                  // token rows per tile
+constexpr uint32_t WIDE_A_BYTES = WIDE_M * BLK_K * 2, WIDE_B_BYTES = WIDE_N * BLK_K * 2;
+constexpr uint32_t WIDE_STAGE = WIDE_A_BYTES + WIDE_B_BYTES;
+constexpr int kWideStages = 5;
+constexpr int kWideThreads = 384;           // warps 0-3 as in gemm_tc_kernel, two epilogue warpgroups
+
+__device__ __forceinline__ void st_cluster_f4(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared::cluster.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <bool SPLIT, bool GATED>
+__global__ void __launch_bounds__(kWideThreads, 1)
+gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, const GemmParams p) {
+  constexpr int STAGES = kWideStages;
+  constexpr uint32_t TMEM_COLS = WIDE_N;
+  constexpr uint32_t IDESC = (1u << 4) | KGE_IDESC_AB | ((uint32_t)(WIDE_N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
+  constexpr int OUT_PER_TILE = GATED ? WIDE_N / 2 : WIDE_N;   // outputs a tile produces per token
+  constexpr int UNIT = 16;                                     // outputs per exchange unit (GATED: 16 gate + 16 up columns)
+  constexpr int N_UNITS = OUT_PER_TILE / UNIT;
+  constexpr int UNIT_F = GATED ? 2 * UNIT : UNIT;              // fp32 values of a unit
+
+  extern __shared__ __align__(1024) uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * WIDE_STAGE);    // full[STAGES], empty[STAGES], tmem_full
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 2);
+  const uint32_t smem_base = smem_addr(smem);
+  const uint32_t bar_base = smem_addr(bars);
+  auto full_bar = [&](int s) { return bar_base + 8u * s; };
+  auto empty_bar = [&](int s) { return bar_base + 8u * (STAGES + s); };
+  const uint32_t tfull_bar = bar_base + 8u * (2 * STAGES);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) trace_stamp(p, 0);
+  if (warp == 0 && lane == 0) {
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_w) : "memory");
+    asm volatile("prefetch.tensormap [%0];" ::"l"(&tmap_x) : "memory");
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(full_bar(s), 1); mbar_init(empty_bar(s), 1); }
+    mbar_init(tfull_bar, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_addr(tmem_slot)), "n"(TMEM_COLS) : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  if (threadIdx.x == 0) trace_stamp(p, 1);
+  pdl_launch_dependents();
+  if (warp != 0) pdl_wait();          // warp 0 (TMA producer) prefetches weights first, then waits
+
+  const int S = SPLIT ? (int)cluster_nctarank() : 1;
+  const int crank = SPLIT ? (int)cluster_ctarank() : 0;
+  const int m_tile = SPLIT ? (int)blockIdx.x / S : (int)blockIdx.x;            // one tile per CTA (cluster)
+  const int kb0 = crank * p.kb_per_split, kb1 = min(p.kb_total, kb0 + p.kb_per_split);
+  const int n0 = m_tile * OUT_PER_TILE;                                         // first output column of the tile
+
+  if (warp == 0) {
+    if (lane == 0) {
+      auto load_w = [&](int st, int kb) {
+        const uint32_t dst = smem_base + st * WIDE_STAGE + WIDE_A_BYTES;
+        if (GATED) {
+          tma_load_2d(dst, &tmap_w, full_bar(st), kb * BLK_K, n0);                              // 128 gate rows
+          tma_load_2d(dst + (WIDE_N / 2) * BLK_K * 2, &tmap_w, full_bar(st), kb * BLK_K, p.N + n0);   // their up rows
+        } else {
+          tma_load_2d(dst, &tmap_w, full_bar(st), kb * BLK_K, n0);
+        }
+      };
+      trace_stamp(p, 12);
+      const int pre = min(STAGES, kb1 - kb0);
+      for (int i = 0; i < pre; ++i) {
+        mbar_expect_tx(full_bar(i), WIDE_STAGE);
+        load_w(i, kb0 + i);
+        if (i == 0) trace_stamp(p, 13);
+      }
+      trace_stamp(p, 2);
+      pdl_wait();
+      trace_stamp(p, 3);
+      int stage = 0; uint32_t phase = 0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        if (kb - kb0 >= pre) {
+          mbar_wait(empty_bar(stage), phase ^ 1);
+          mbar_expect_tx(full_bar(stage), WIDE_STAGE);
+          load_w(stage, kb);
+        }
+        tma_load_2d(smem_base + stage * WIDE_STAGE, &tmap_x, full_bar(stage), kb * BLK_K, 0);
+        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+      }
+      trace_stamp(p, 4);
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      if (p.trace) { mbar_wait(full_bar(0), 0); trace_stamp(p, 5); }
+      int stage = 0; uint32_t phase = 0;
+      const uint64_t adesc0 = umma_desc_sw128(smem_base), bdesc0 = umma_desc_sw128(smem_base + WIDE_A_BYTES);
+      uint64_t adesc = adesc0, bdesc = bdesc0;
+      for (int kb = kb0; kb < kb1; ++kb) {
+        mbar_wait(full_bar(stage), phase);
+        tc_fence_after();
+#pragma unroll
+        for (int k = 0; k < BLK_K / UMMA_K; ++k)
+          tc_mma_bf16(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(k * 2), IDESC, (kb > kb0 || k > 0) ? 1u : 0u);
+        tc_commit(empty_bar(stage));
+        adesc += WIDE_STAGE >> 4; bdesc += WIDE_STAGE >> 4;
+        if (++stage == STAGES) { stage = 0; phase ^= 1; adesc = adesc0; bdesc = bdesc0; }
+      }
+      tc_commit(tfull_bar);
+      trace_stamp(p, 6);
+    }
+  }
+  else if (warp >= 4) {
+    // Two epilogue warpgroups (warps 4-7, 8-11): a warp reads the TMEM lane quarter warp % 4, the tokens live in lanes
+    // 0-63, so warps 4, 5 take the first half of the tile's units for their tokens and warps 8, 9 the second half; all
+    // eight warps share the reduction of the split variant.
+    const int et = threadIdx.x - 128, q = warp & 3, eg = (warp - 4) >> 2;
+    const int tok = q * 32 + lane;                          // my token (TMEM lane) if q < 2
+    const int u_lo = eg * (N_UNITS / 2), u_hi = u_lo + N_UNITS / 2;
+    mbar_wait(tfull_bar, 0);
+    tc_fence_after();
+    if (et == 0) trace_stamp(p, 7);
+    const uint32_t taddr = tmem_base + ((uint32_t)(q * 32) << 16);
+    const bool vec_ok = (p.N & 7) == 0;
+    // the 16 outputs of unit u for my token from raw accumulators: bias / ReLU, or silu(gate) * up
+    auto finish = [&](int u, const float (&a)[16], const float (&up)[16], float (&o)[16]) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) {
+        if (GATED) {
+          o[j] = silu_gate_bf16(a[j], up[j]);
+        } else {
+          const int n = n0 + u * UNIT + j;
+          float v = a[j] + ((p.bias && n < p.N) ? bf2f(p.bias[n]) : 0.f);
+          if (p.act == 1) v = fmaxf(v, 0.f);
+          o[j] = v;
+        }
+      }
+    };
+    auto store16 = [&](int t, int u, const float (&o)[16]) {
+      if (t >= p.T) return;
+      const int n = n0 + u * UNIT;
+      bf16* dst = p.y + (int64_t)t * p.N + n;
+      if (vec_ok && n + 15 < p.N) {
+        uint4 w0, w1;
+        w0.x = pack_bf2(o[0], o[1]); w0.y = pack_bf2(o[2], o[3]); w0.z = pack_bf2(o[4], o[5]); w0.w = pack_bf2(o[6], o[7]);
+        w1.x = pack_bf2(o[8], o[9]); w1.y = pack_bf2(o[10], o[11]); w1.z = pack_bf2(o[12], o[13]); w1.w = pack_bf2(o[14], o[15]);
+        reinterpret_cast<uint4*>(dst)[0] = w0;
+        reinterpret_cast<uint4*>(dst)[1] = w1;
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) if (n + j < p.N) dst[j] = f2bf(o[j]);
+      }
+    };
+    if (!SPLIT) {
+      if (q < 2) {
+#pragma unroll 1
+        for (int u = u_lo; u < u_hi; ++u) {
+          uint32_t r[16], r2[16];
+          float a[16], up[16], o[16];
+          tmem_ld16(taddr + u * UNIT, r);
+          if (GATED) tmem_ld16(taddr + WIDE_N / 2 + u * UNIT, r2);
+#pragma unroll
+          for (int j = 0; j < 16; ++j) { a[j] = __uint_as_float(r[j]); up[j] = GATED ? __uint_as_float(r2[j]) : 0.f; }
+          finish(u, a, up, o);
+          store16(tok, u, o);
+        }
+      }
+    } else {
+      const int units_per = (N_UNITS + S - 1) / S;
+      constexpr int NJ = UNIT_F / 4;                        // 16-byte pieces of a unit
+      // exchange buffer of a CTA: [source rank][local unit][piece][token][4 fp32] - a warp stores (and later loads) 512
+      // contiguous bytes
+      const uint32_t xb = smem_base;                        // over the pipeline stages: dead once phase A completes
+      cluster_arrive();                                     // phase A: my MMAs have read their last stage
+      cluster_wait();
+      if (q < 2) {
+#pragma unroll 1
+        for (int u = u_lo; u < u_hi; ++u) {
+          uint32_t r[16], r2[16];
+          tmem_ld16(taddr + u * UNIT, r);
+          if (GATED) tmem_ld16(taddr + WIDE_N / 2 + u * UNIT, r2);
+          const int owner = u / units_per, lu = u - owner * units_per;
+          const uint32_t dst = mapa_u32(xb + (uint32_t)(((((crank * units_per + lu) * NJ) * WIDE_M) + tok) * 16), (uint32_t)owner);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            st_cluster_f4(dst + j * (WIDE_M * 16), __uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]), __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+          if (GATED) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+              st_cluster_f4(dst + (4 + j) * (WIDE_M * 16), __uint_as_float(r2[4 * j]), __uint_as_float(r2[4 * j + 1]), __uint_as_float(r2[4 * j + 2]), __uint_as_float(r2[4 * j + 3]));
+          }
+        }
+      }
+      tc_fence_before();
+      if (et == 0) trace_stamp(p, 8);
+      cluster_arrive();                                     // phase B: my partials are in the owners' buffers
+      cluster_wait();
+      if (et == 0) trace_stamp(p, 9);
+      // my units, summed over the ranks in rank order; one item = one token's 16 outputs of one unit
+      const int u_begin = crank * units_per;
+      const int my_units = min(N_UNITS, u_begin + units_per) - u_begin;
+      for (int item = et; item < my_units * WIDE_M; item += 256) {
+        const int t = item & (WIDE_M - 1), lu = item / WIDE_M;
+        float a[16], up[16], o[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { a[j] = 0.f; up[j] = 0.f; }
+        for (int s2 = 0; s2 < S; ++s2) {
+          const uint32_t src = xb + (uint32_t)(((((s2 * units_per + lu) * NJ) * WIDE_M) + t) * 16);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 v = lds_f4(src + j * (WIDE_M * 16));
+            a[4 * j] += v.x; a[4 * j + 1] += v.y; a[4 * j + 2] += v.z; a[4 * j + 3] += v.w;
+          }
+          if (GATED) {
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {
+              const float4 v = lds_f4(src + (4 + j) * (WIDE_M * 16));
+              up[4 * j] += v.x; up[4 * j + 1] += v.y; up[4 * j + 2] += v.z; up[4 * j + 3] += v.w;
+            }
+          }
+        }
+        finish(u_begin + lu, a, up, o);
+        store16(t, u_begin + lu, o);
+      }
+    }
+    if (et == 0) trace_stamp(p, 10);
+  }
+  if (SPLIT && warp < 4) {                       // non-epilogue warps take part in both cluster phases
+    cluster_arrive();
+    cluster_wait();
+    cluster_arrive();
+    cluster_wait();
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (threadIdx.x == 0) trace_stamp(p, 11);
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem_base), "n"(TMEM_COLS) : "memory");
+  }
+}
+
 // ------------------------------------------------------------------------------ host
 typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
                                   const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
@@ -827,6 +1081,84 @@ static GemmPlan plan_gemm(int T, int N, int K, int rows_out = BLK_M, bool ws_ok 
   return g;
 }
 
+// ---- wide tiles (T <= 64): one tile of 256 weight rows per CTA / cluster
+constexpr int kWideSmem = kWideStages * (int)WIDE_STAGE + 1024 /*align*/ + 2048 /*barriers*/;
+
+template <bool SPLIT, bool GATED>
+static int launch_wide(const CUtensorMap& tw, const CUtensorMap& tx, const GemmParams& p, cudaStream_t st) {
+  auto kern = gemm_wide_kernel<SPLIT, GATED>;
+  KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideSmem));
+  prefer_max_shared(kern);
+  cudaLaunchConfig_t cfg = {};
+  cfg.blockDim = dim3(kWideThreads);
+  cfg.dynamicSmemBytes = kWideSmem;
+  cfg.stream = st;
+  cfg.gridDim = dim3(p.m_tiles * p.splits);
+  cudaLaunchAttribute attr[2];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_for_this_launch() ? 1 : 0;
+  cfg.attrs = attr; cfg.numAttrs = 1;
+  if (SPLIT) {
+    attr[1].id = cudaLaunchAttributeClusterDimension;
+    attr[1].val.clusterDim.x = p.splits; attr[1].val.clusterDim.y = 1; attr[1].val.clusterDim.z = 1;
+    cfg.numAttrs = 2;
+  }
+  KGE_CUDA_OK(cudaLaunchKernelEx(&cfg, kern, tw, tx, p));
+  return 0;
+}
+
+static int max_clusters_wide(int S) {
+  static int cache[9];
+  static bool have[9];
+  if (!have[S]) {
+    auto kern = gemm_wide_kernel<true, false>;
+    int n = 0;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kWideSmem) == cudaSuccess) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = dim3(S * 64); cfg.blockDim = dim3(kWideThreads); cfg.dynamicSmemBytes = kWideSmem;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = S; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr; cfg.numAttrs = 1;
+      if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess) { (void)cudaGetLastError(); n = 0; }
+    }
+    cache[S] = n; have[S] = true;
+  }
+  return cache[S];
+}
+
+// outputs per tile: 256 (plain) or 128 (fused gate/up).  False: this problem keeps the 128-row kernels.
+static bool plan_wide(int T, int n_out, int K, bool gated, GemmPlan& g) {
+  if (!tunable(TUN_GEMM_WIDE) || T > WIDE_M) return false;
+  const int per = gated ? WIDE_N / 2 : WIDE_N;
+  const int tiles = (n_out + per - 1) / per;
+  if (tiles > 148) return false;
+  g.ws = false;
+  g.tokn = WIDE_M; g.m_tiles = tiles; g.n_tiles = 1;
+  g.kb_total = (K + BLK_K - 1) / BLK_K;
+  int splits = 1;
+  int smax = 148 / tiles;
+  const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
+  if (smax > max_by_k) smax = max_by_k;
+  if (smax > 8) smax = 8;
+  for (int s = smax; s >= 2; --s)
+    if (tiles <= max_clusters_wide(s)) { splits = s; break; }
+  g.kb_per_split = (g.kb_total + splits - 1) / splits;
+  g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;
+  // Both kernels stream at a per-CTA rate; the wide one turns a k-block of twice the bytes in the same time but packs
+  // into fewer, larger clusters.  Measured on the Llama-8B shapes (profiles/r02_summary.md section 7): it wins where it
+  // keeps at least as many CTAs streaming as the 128-row plan (qkv 120 vs 96, gate_up 112 vs 112) and loses where it
+  // does not (o and down: 96 vs 128).
+  const GemmPlan narrow = plan_gemm(T, n_out, K, gated ? 64 : BLK_M, false);
+  const int narrow_tiles = narrow.m_tiles * narrow.n_tiles;
+  int narrow_ctas = narrow_tiles * narrow.splits;
+  if (narrow_tiles > 148) {                                // persistent: the grid launch_gemm evens out
+    const int rounds = (narrow_tiles + 147) / 148;
+    narrow_ctas = tunable(TUN_GEMM_EVEN_GRID) ? (narrow_tiles + rounds - 1) / rounds : 148;
+  }
+  return g.m_tiles * g.splits >= narrow_ctas;
+}
+
 // prefill-sized problems run as CTA pairs (cta_group::2, 256 x 256 MMA tiles)
 static bool gemm_uses_pair(const GemmPlan& g) { return g.tokn == 256 && g.splits == 1 && g.m_tiles >= 2; }
 
@@ -904,6 +1236,24 @@ extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* 
   KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w & 15) == 0, "kge_gemm_bf16: x and w must be 16-byte aligned");
   KGE_REQUIRE(act == 0 || act == 1, "kge_gemm_bf16: act=%d unsupported", act);
   if (T == 0) return 0;
+  bool use_ws = workspace && tunable(TUN_GEMM_WS);          // stream-K through the caller's scratch, if it is large enough
+  if (use_ws) {
+    const GemmPlan gq = plan_gemm(T, N, K, BLK_M, true);
+    use_ws = gq.ws && workspace_bytes >= ws_bytes_of(gq) && ((uintptr_t)workspace & 15) == 0;
+  }
+  if (!use_ws) {
+    GemmPlan gw;
+    if (plan_wide(T, N, K, false, gw)) {
+      GemmParams p;
+      p.y = (bf16*)y; p.bias = (const bf16*)bias; p.T = T; p.N = N; p.K = K; p.act = act;
+      p.l2_hints = 0; p.trace = g_gemm_trace; p.ws_count = nullptr; p.ws_part = nullptr;
+      p.m_tiles = gw.m_tiles; p.n_tiles = 1; p.splits = gw.splits; p.kb_total = gw.kb_total; p.kb_per_split = gw.kb_per_split;
+      CUtensorMap tw, tx;
+      if (int rc = make_tmap(&tw, w, N, K, WIDE_N)) return rc;
+      if (int rc = make_tmap(&tx, x, T, K, WIDE_M)) return rc;
+      return gw.splits > 1 ? launch_wide<true, false>(tw, tx, p, (cudaStream_t)stream) : launch_wide<false, false>(tw, tx, p, (cudaStream_t)stream);
+    }
+  }
   GemmPlan g = plan_gemm(T, N, K, BLK_M, workspace != nullptr);
   if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0))
     g = plan_gemm(T, N, K);                        // scratch too small for this shape: split K inside a cluster instead
@@ -929,6 +1279,24 @@ extern "C" int KGE_GEMM_GATE_WS_NAME(void* y, const void* x, const void* w_gate_
   KGE_REQUIRE(f % 64 == 0, "kge_gemm_silu_gate_bf16: f=%d must be a multiple of 64", f);
   KGE_REQUIRE(((uintptr_t)x & 15) == 0 && ((uintptr_t)w_gate_up & 15) == 0, "kge_gemm_silu_gate_bf16: x and w must be 16-byte aligned");
   if (T == 0) return 0;
+  bool use_ws = workspace && tunable(TUN_GEMM_WS);
+  if (use_ws) {
+    const GemmPlan gq = plan_gemm(T, f, K, 64, true);
+    use_ws = gq.ws && workspace_bytes >= ws_bytes_of(gq) && ((uintptr_t)workspace & 15) == 0;
+  }
+  if (!use_ws) {
+    GemmPlan gw;
+    if (f % (WIDE_N / 2) == 0 && plan_wide(T, f, K, true, gw)) {
+      GemmParams p;
+      p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
+      p.l2_hints = 0; p.trace = g_gemm_trace; p.ws_count = nullptr; p.ws_part = nullptr;
+      p.m_tiles = gw.m_tiles; p.n_tiles = 1; p.splits = gw.splits; p.kb_total = gw.kb_total; p.kb_per_split = gw.kb_per_split;
+      CUtensorMap tw, tx;
+      if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, WIDE_N / 2)) return rc;
+      if (int rc = make_tmap(&tx, x, T, K, WIDE_M)) return rc;
+      return gw.splits > 1 ? launch_wide<true, true>(tw, tx, p, (cudaStream_t)stream) : launch_wide<false, true>(tw, tx, p, (cudaStream_t)stream);
+    }
+  }
   GemmPlan g = plan_gemm(T, f, K, 64, workspace != nullptr);
   if (g.ws && (workspace_bytes < ws_bytes_of(g) || ((uintptr_t)workspace & 15) != 0)) g = plan_gemm(T, f, K, 64);
   GemmParams p;

@@ -269,6 +269,9 @@ GEMM_CASES = [
     (64, 1000, 2048, True, 1),                # N % 8 != 0: scalar stores in the split reduce, ragged last tile
     (48, 4104, 4096, False, 0),               # N a multiple of 8 but of no tile height
     (100, 6144, 4096, True, 0),               # 128-token tile, split K
+    (64, 8192, 8192, True, 1),                # 32 wide tiles x 4 splits, bias + relu in the split reduce
+    (3, 37888, 1024, False, 0),               # 148 wide tiles exactly, no split
+    (50, 5120, 640, True, 0),                 # 20 wide tiles, K = 10 k-blocks: 2 splits of 5
 ]
 
 
@@ -295,6 +298,26 @@ def test_gemm_bf16(kge, L, T, N, K, bias, act):
         assert (err <= tol).all(), f"max err {err.max().item():.4g} (scale {scale:.3g}) at {torch.nonzero(err > tol)[:4].tolist()}"
         # and tight on average: one bf16 rounding of an fp32 accumulation
         assert (err / (ref.abs() + 1e-2 * scale)).mean().item() < 3e-3
+
+
+@pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 64])
+def test_gemm_128_row_tiles_for_small_batches(kge, L, T, N, K, bias, act):
+    """Knob gemm_wide=0: batches of up to 64 tokens through the 128-row weight tiles (tokens as MMA N) instead of the
+    256-row tiles with the tokens as MMA M - the same checks."""
+    try:
+        check_ok(kge, L.kge_set_tunable(b"gemm_wide", 0), "tunable")
+        test_gemm_bf16(kge, L, T, N, K, bias, act)
+    finally:
+        L.kge_set_tunable(b"gemm_wide", 1)
+
+
+@pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048), (64, 7168, 8192)])
+def test_gemm_silu_gate_128_row_tiles(kge, L, T, f, K):
+    try:
+        check_ok(kge, L.kge_set_tunable(b"gemm_wide", 0), "tunable")
+        test_gemm_silu_gate_fused(kge, L, T, f, K)
+    finally:
+        L.kge_set_tunable(b"gemm_wide", 1)
 
 
 @pytest.mark.parametrize("T,N,K,bias,act", [c for c in GEMM_CASES if c[0] <= 128] + [(64, 6144, 4096, True, 1), (33, 14336, 4096, False, 0), (100, 4096, 14336, False, 0)])

@@ -13,7 +13,7 @@ from kge_loader import load  # noqa: E402
 kge = load()
 L = kge.lib()
 BS = int(os.environ.get("PROBE_BLOCK", "64"))
-DEFAULTS = {"attn_persistent": 1, "gemm_l2_hints": 0, "smem_carveout": 1, "gemm_ws": 0, "attn_tma": 1, "pdl": 1, "gemm_even_grid": 1, "attn_decode_splits": 0, "attn_split_balance": 0, "attn_cluster_merge": 0}
+DEFAULTS = {"gemm_wide": 1, "attn_persistent": 1, "gemm_l2_hints": 0, "smem_carveout": 1, "gemm_ws": 0, "attn_tma": 1, "pdl": 1, "gemm_even_grid": 1, "attn_decode_splits": 0, "attn_split_balance": 0, "attn_cluster_merge": 0}
 
 
 def main():

@@ -115,6 +115,7 @@ struct GemmParams {
   int T, N, K, act;
   int l2_hints;              // 1: weights evict_first, activations evict_last, output stored streaming
   int m_tiles, n_tiles, splits, kb_total, kb_per_split;
+  int rows;                  // gemm_wide_kernel: outputs per tile
   unsigned long long* trace; // phase timestamps, 16 per CTA (tools/gemm_trace.py); null outside that tool
 };
 
@@ -669,11 +670,14 @@ __global__ void __launch_bounds__(kWideThreads, 1)
 gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_x, const GemmParams p) {
   constexpr int STAGES = kWideStages;
   constexpr uint32_t TMEM_COLS = WIDE_N;
-  constexpr uint32_t IDESC = (1u << 4) | KGE_IDESC_AB | ((uint32_t)(WIDE_N >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
-  constexpr int OUT_PER_TILE = GATED ? WIDE_N / 2 : WIDE_N;   // outputs a tile produces per token
+  // p.rows outputs per tile (a multiple of 16, up to 256; GATED: up to 128 gate rows + their up rows): the MMA's N
+  const int OUT_PER_TILE = p.rows;
+  const int N_MMA = GATED ? 2 * OUT_PER_TILE : OUT_PER_TILE;
+  const uint32_t IDESC = (1u << 4) | KGE_IDESC_AB | ((uint32_t)(N_MMA >> 3) << 17) | ((uint32_t)(128 >> 4) << 24);
   constexpr int UNIT = 16;                                     // outputs per exchange unit (GATED: 16 gate + 16 up columns)
-  constexpr int N_UNITS = OUT_PER_TILE / UNIT;
+  const int N_UNITS = OUT_PER_TILE / UNIT;
   constexpr int UNIT_F = GATED ? 2 * UNIT : UNIT;              // fp32 values of a unit
+  const uint32_t tx_bytes = WIDE_A_BYTES + (uint32_t)N_MMA * BLK_K * 2;
 
   extern __shared__ __align__(1024) uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -719,8 +723,8 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       auto load_w = [&](int st, int kb) {
         const uint32_t dst = smem_base + st * WIDE_STAGE + WIDE_A_BYTES;
         if (GATED) {
-          tma_load_2d(dst, &tmap_w, full_bar(st), kb * BLK_K, n0);                              // 128 gate rows
-          tma_load_2d(dst + (WIDE_N / 2) * BLK_K * 2, &tmap_w, full_bar(st), kb * BLK_K, p.N + n0);   // their up rows
+          tma_load_2d(dst, &tmap_w, full_bar(st), kb * BLK_K, n0);                              // the gate rows
+          tma_load_2d(dst + OUT_PER_TILE * BLK_K * 2, &tmap_w, full_bar(st), kb * BLK_K, p.N + n0);   // their up rows
         } else {
           tma_load_2d(dst, &tmap_w, full_bar(st), kb * BLK_K, n0);
         }
@@ -728,7 +732,7 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       trace_stamp(p, 12);
       const int pre = min(STAGES, kb1 - kb0);
       for (int i = 0; i < pre; ++i) {
-        mbar_expect_tx(full_bar(i), WIDE_STAGE);
+        mbar_expect_tx(full_bar(i), tx_bytes);
         load_w(i, kb0 + i);
         if (i == 0) trace_stamp(p, 13);
       }
@@ -739,7 +743,7 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
       for (int kb = kb0; kb < kb1; ++kb) {
         if (kb - kb0 >= pre) {
           mbar_wait(empty_bar(stage), phase ^ 1);
-          mbar_expect_tx(full_bar(stage), WIDE_STAGE);
+          mbar_expect_tx(full_bar(stage), tx_bytes);
           load_w(stage, kb);
         }
         tma_load_2d(smem_base + stage * WIDE_STAGE, &tmap_x, full_bar(stage), kb * BLK_K, 0);
@@ -773,7 +777,8 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
     // eight warps share the reduction of the split variant.
     const int et = threadIdx.x - 128, q = warp & 3, eg = (warp - 4) >> 2;
     const int tok = q * 32 + lane;                          // my token (TMEM lane) if q < 2
-    const int u_lo = eg * (N_UNITS / 2), u_hi = u_lo + N_UNITS / 2;
+    const int u_half = (N_UNITS + 1) / 2;
+    const int u_lo = eg * u_half, u_hi = eg ? N_UNITS : u_half;
     mbar_wait(tfull_bar, 0);
     tc_fence_after();
     if (et == 0) trace_stamp(p, 7);
@@ -815,7 +820,7 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
           uint32_t r[16], r2[16];
           float a[16], up[16], o[16];
           tmem_ld16(taddr + u * UNIT, r);
-          if (GATED) tmem_ld16(taddr + WIDE_N / 2 + u * UNIT, r2);
+          if (GATED) tmem_ld16(taddr + OUT_PER_TILE + u * UNIT, r2);
 #pragma unroll
           for (int j = 0; j < 16; ++j) { a[j] = __uint_as_float(r[j]); up[j] = GATED ? __uint_as_float(r2[j]) : 0.f; }
           finish(u, a, up, o);
@@ -835,7 +840,7 @@ gemm_wide_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_consta
         for (int u = u_lo; u < u_hi; ++u) {
           uint32_t r[16], r2[16];
           tmem_ld16(taddr + u * UNIT, r);
-          if (GATED) tmem_ld16(taddr + WIDE_N / 2 + u * UNIT, r2);
+          if (GATED) tmem_ld16(taddr + OUT_PER_TILE + u * UNIT, r2);
           const int owner = u / units_per, lu = u - owner * units_per;
           const uint32_t dst = mapa_u32(xb + (uint32_t)(((((crank * units_per + lu) * NJ) * WIDE_M) + tok) * 16), (uint32_t)owner);
 #pragma unroll
@@ -1046,7 +1051,7 @@ static int max_clusters(int tokn, int S) {
   return cache[ti][S];
 }
 
-struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; bool ws; };
+struct GemmPlan { int tokn, m_tiles, n_tiles, splits, kb_total, kb_per_split; bool ws; int rows; };
 
 constexpr int64_t kWsCounterBytes = 1024;        // per-tile arrival counters at the head of the workspace (<= 256 tiles)
 
@@ -1127,28 +1132,42 @@ static int max_clusters_wide(int S) {
   return cache[S];
 }
 
-// outputs per tile: 256 (plain) or 128 (fused gate/up).  False: this problem keeps the 128-row kernels.
+// Tile width (outputs per tile, a multiple of 16: up to 256, or 128 for the fused gate/up) and K split of the wide
+// kernel: full-width tiles with the largest cluster split that fits one round; where no split is possible (more than
+// 74 tiles) narrower tiles, down to 3/4 of the width, if that puts more CTAs to work (gate_up of Llama-8B: 128 tiles of
+// 112 outputs instead of 112 of 128).  A cost model over all widths and splits (k-block = max(MMA time, bytes at the
+// per-SM rate), price per split) picked plans that were faster alone and 0.35 ms per decode step SLOWER in the engine
+// (clusters of 3 and 5 next to the neighbouring kernels' CTAs); it was removed (profiles/r02_summary.md section 7).
+// False: this problem keeps the 128-row kernels.
 static bool plan_wide(int T, int n_out, int K, bool gated, GemmPlan& g) {
   if (!tunable(TUN_GEMM_WIDE) || T > WIDE_M) return false;
-  const int per = gated ? WIDE_N / 2 : WIDE_N;
-  const int tiles = (n_out + per - 1) / per;
-  if (tiles > 148) return false;
+  const int kb_total = (K + BLK_K - 1) / BLK_K;
+  const int max_rows = gated ? WIDE_N / 2 : WIDE_N;
+  const int max_by_k = kb_total / 4 > 0 ? kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
+  double best = 1e30;
+  int best_rows = 0, best_s = 0;
+  auto try_rows = [&](int rows) {               // largest split that fits one round; more CTAs win, then the wider tile
+    const int tiles = (n_out + rows - 1) / rows;
+    if (tiles > 148) return;
+    int sp = 148 / tiles;
+    if (sp > max_by_k) sp = max_by_k;
+    if (sp > 8) sp = 8;
+    while (sp > 1 && tiles > max_clusters_wide(sp)) --sp;
+    const double score = -(double)(tiles * sp) - rows * 1e-3;
+    if (score < best) { best = score; best_rows = rows; best_s = sp; }
+  };
+  try_rows(max_rows);
+  if (best_s == 1)                              // no split possible: spread the rows over more CTAs instead
+    for (int rows = max_rows - 16; rows >= (3 * max_rows) / 4; rows -= 16) try_rows(rows);
+  if (best_rows == 0) return false;
   g.ws = false;
-  g.tokn = WIDE_M; g.m_tiles = tiles; g.n_tiles = 1;
-  g.kb_total = (K + BLK_K - 1) / BLK_K;
-  int splits = 1;
-  int smax = 148 / tiles;
-  const int max_by_k = g.kb_total / 4 > 0 ? g.kb_total / 4 : 1;   // >= 4 k-blocks (256 of K) per split
-  if (smax > max_by_k) smax = max_by_k;
-  if (smax > 8) smax = 8;
-  for (int s = smax; s >= 2; --s)
-    if (tiles <= max_clusters_wide(s)) { splits = s; break; }
-  g.kb_per_split = (g.kb_total + splits - 1) / splits;
-  g.splits = (g.kb_total + g.kb_per_split - 1) / g.kb_per_split;
-  // Both kernels stream at a per-CTA rate; the wide one turns a k-block of twice the bytes in the same time but packs
-  // into fewer, larger clusters.  Measured on the Llama-8B shapes (profiles/r02_summary.md section 7): it wins where it
-  // keeps at least as many CTAs streaming as the 128-row plan (qkv 120 vs 96, gate_up 112 vs 112) and loses where it
-  // does not (o and down: 96 vs 128).
+  g.tokn = WIDE_M; g.n_tiles = 1;
+  g.rows = best_rows;
+  g.m_tiles = (n_out + best_rows - 1) / best_rows;
+  g.kb_total = kb_total;
+  g.kb_per_split = (kb_total + best_s - 1) / best_s;
+  g.splits = (kb_total + g.kb_per_split - 1) / g.kb_per_split;
+  // only where it keeps at least as many CTAs streaming as the 128-row plan (measured: otherwise it loses)
   const GemmPlan narrow = plan_gemm(T, n_out, K, gated ? 64 : BLK_M, false);
   const int narrow_tiles = narrow.m_tiles * narrow.n_tiles;
   int narrow_ctas = narrow_tiles * narrow.splits;
@@ -1249,7 +1268,8 @@ extern "C" int KGE_GEMM_NAME(void* y, const void* x, const void* w, const void* 
       p.l2_hints = 0; p.trace = g_gemm_trace; p.ws_count = nullptr; p.ws_part = nullptr;
       p.m_tiles = gw.m_tiles; p.n_tiles = 1; p.splits = gw.splits; p.kb_total = gw.kb_total; p.kb_per_split = gw.kb_per_split;
       CUtensorMap tw, tx;
-      if (int rc = make_tmap(&tw, w, N, K, WIDE_N)) return rc;
+      p.rows = gw.rows;
+      if (int rc = make_tmap(&tw, w, N, K, gw.rows)) return rc;
       if (int rc = make_tmap(&tx, x, T, K, WIDE_M)) return rc;
       return gw.splits > 1 ? launch_wide<true, false>(tw, tx, p, (cudaStream_t)stream) : launch_wide<false, false>(tw, tx, p, (cudaStream_t)stream);
     }
@@ -1286,13 +1306,14 @@ extern "C" int KGE_GEMM_GATE_WS_NAME(void* y, const void* x, const void* w_gate_
   }
   if (!use_ws) {
     GemmPlan gw;
-    if (f % (WIDE_N / 2) == 0 && plan_wide(T, f, K, true, gw)) {
+    if (plan_wide(T, f, K, true, gw)) {
       GemmParams p;
       p.y = (bf16*)y; p.bias = nullptr; p.T = T; p.N = f; p.K = K; p.act = 2;
       p.l2_hints = 0; p.trace = g_gemm_trace; p.ws_count = nullptr; p.ws_part = nullptr;
       p.m_tiles = gw.m_tiles; p.n_tiles = 1; p.splits = gw.splits; p.kb_total = gw.kb_total; p.kb_per_split = gw.kb_per_split;
       CUtensorMap tw, tx;
-      if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, WIDE_N / 2)) return rc;
+      p.rows = gw.rows;
+      if (int rc = make_tmap(&tw, w_gate_up, 2 * (int64_t)f, K, gw.rows)) return rc;
       if (int rc = make_tmap(&tx, x, T, K, WIDE_M)) return rc;
       return gw.splits > 1 ? launch_wide<true, true>(tw, tx, p, (cudaStream_t)stream) : launch_wide<false, true>(tw, tx, p, (cudaStream_t)stream);
     }

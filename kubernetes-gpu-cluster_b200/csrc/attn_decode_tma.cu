@@ -361,7 +361,6 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
   volatile int* s_last = reinterpret_cast<volatile int*>(bars + 2 * kStages);
   float* sRed = reinterpret_cast<float*>(smem + 2 * Q_BYTES + 2 * kStages * TILE + 2 * kStages * 8 + 64);   // [4 warps][4 rows][HD+2]
   int* s_pre = reinterpret_cast<int*>(sRed + 4 * 4 * RS);      // [B + 1] tiles of the requests before b (per kv head)
-  int* s_len = s_pre + B + 1;                                  // [B] keys of request b
 
   if (tid == 0) {
     if ((sQ & 1023u) != 0) __trap();
@@ -373,7 +372,7 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
   pdl_launch_dependents();
   pdl_wait();
   // tiles per request (a request without keys still gets one, fully masked, tile: its output rows are written as zeros)
-  for (int b = tid; b < B; b += 160) { const int len = seq_lens[b], n = (len + BN - 1) / BN; s_len[b] = len; s_pre[b + 1] = n > 0 ? n : 1; }
+  for (int b = tid; b < B; b += 160) { const int n = (seq_lens[b] + BN - 1) / BN; s_pre[b + 1] = n > 0 ? n : 1; }
   if (tid == 0) s_pre[0] = 0;
   __syncthreads();
   if (warp == 0) {                                 // inclusive scan, each lane a contiguous run of requests
@@ -399,7 +398,7 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
     int64_t u, u1;
     int b, chunk, KV;
     const int* pre;
-    const int* lens;
+    const int32_t* lens;          // (global: two or three loads per CTA; a shared copy would cost the second resident CTA from 98 requests on)
     __device__ __forceinline__ bool next(Segment& sg) {
       if (u >= u1) return false;
       while ((int64_t)pre[b + 1] * KV <= u) ++b;
@@ -419,7 +418,7 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
     }
   };
   auto walk = [&]() {
-    Walk w{u0, u1, 0, chunk, KV, s_pre, s_len};
+    Walk w{u0, u1, 0, chunk, KV, s_pre, seq_lens};
     if (u0 < u1) {                                 // first request of my share: binary search in the prefix
       int lo = 0, hi = B - 1;
       while (lo < hi) { const int mid = (lo + hi) >> 1; if ((int64_t)s_pre[mid + 1] * KV <= u0) lo = mid + 1; else hi = mid; }
@@ -666,7 +665,7 @@ attn_decode_tma_persistent_kernel(const __grid_constant__ CUtensorMap tm_k, cons
 }
 
 template <int HD> constexpr int smem_bytes_persistent(int B) {
-  return 2 * 16 * HD * 2 + 2 * kStages * BN * HD * 2 + 2 * kStages * 8 + 64 + 4 * 4 * (HD + 2) * 4 + (2 * B + 1) * 4;
+  return 2 * 16 * HD * 2 + 2 * kStages * BN * HD * 2 + 2 * kStages * 8 + 64 + 4 * 4 * (HD + 2) * 4 + (B + 1) * 4;
 }
 
 template <int HD> constexpr int smem_bytes() {
@@ -700,14 +699,22 @@ static int launch_decode_tma(bf16* out, const bf16* q, int q_stride, const bf16*
       const int smem = adt::smem_bytes_persistent<HD>(B);
       KGE_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
       prefer_max_shared(kern);
+      // the grid is 2 x 148 CTAs that must all be resident: the per-request prefix grows the footprint with B
+      static int occ_of[193];                      // 0: not asked yet
+      if (occ_of[B] == 0) {
+        int o = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&o, kern, 160, smem) != cudaSuccess) { (void)cudaGetLastError(); o = 1; }
+        occ_of[B] = o > 0 ? o : 1;
+      }
       const int64_t units = (int64_t)B * KV * max_tiles;
-      const int grid = units < 2 * 148 ? (int)units : 2 * 148;
-      if (units >= 2 * 2 * 148) {                  // (with less than two tiles per CTA the per-CTA prefix scan is not paid back)
-      float* po = (float*)ws;
-      float* pml = po + (int64_t)B * H * slots * HD;
-      KGE_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(160), smem, st, tk, tv, out, po, pml, q, q_stride, bt, max_blocks, sl, qsl, B, H, KV,
-                             bs_shift, scale_log2, (int)slots, min_chunk));
-      return 0;
+      // (with less than two tiles per CTA the per-CTA prefix scan is not paid back)
+      if (occ_of[B] >= 2 && units >= 2 * 2 * 148) {
+        const int grid = 2 * 148;
+        float* po = (float*)ws;
+        float* pml = po + (int64_t)B * H * slots * HD;
+        KGE_CUDA_OK(launch_pdl(kern, dim3(grid), dim3(160), smem, st, tk, tv, out, po, pml, q, q_stride, bt, max_blocks, sl, qsl, B, H, KV,
+                               bs_shift, scale_log2, (int)slots, min_chunk));
+        return 0;
       }
     }
   }

@@ -601,6 +601,8 @@ PERSISTENT_CASES = [
     (32, 8, 64, 64, [40, 128, 129, 1000] * 12, 2),
     (12, 12, 64, 128, [5, 130, 600] * 30, 1),                      # no split: results straight from the cross-warp merge
     (16, 1, 128, 64, [3000, 17], 4),                               # groups of 16 q heads: four merge passes
+    (32, 8, 128, 64, [130 + 7 * i for i in range(180)], 0),        # 180 requests: the per-request prefix is at its largest
+    (32, 8, 64, 64, [1 + i for i in range(192)], 0),
 ]
 
 

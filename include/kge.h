@@ -53,8 +53,10 @@ int kge_device_sm_count(void);
  *   "attn_persistent" 1/0     decode attention with 64-token KV blocks or larger: 1 = 2 x 148 resident CTAs each take an equal,
  *                             contiguous share of all key tiles of the launch (a (request, kv head) group is cut where shares
  *                             end; pieces merged by the last CTA of the group to arrive) - one round whatever the batch and
- *                             the context lengths are; 0 = one CTA per (request, kv head, split) with equal splits.  Equal at
- *                             64 x 2176 keys (96 us), 6-8 % faster at 64 x 1024 and 8 x 8192 (profiles/r02_summary.md)
+ *                             the context lengths are (launches of up to 192 requests with a workspace of at least three partial slots per
+ *                             head; others use the other kernel); 0 = one CTA per (request, kv head, split) with equal splits.  Equal at
+ *                             64 x 2176 keys: 91.6-93.3 us against 95.6; 64 x 1024: 49.7 against 56.5; 8 x 8192: 53.0 against 60.2
+ *                             (profiles/r02_summary.md section 6)
  * Returns 0, or -1 for an unknown name. */
 int kge_set_tunable(const char* name, int value);
 

@@ -54,7 +54,7 @@ int kge_device_sm_count(void);
  *                             contiguous share of all key tiles of the launch (a (request, kv head) group is cut where shares
  *                             end; pieces merged by the last CTA of the group to arrive) - one round whatever the batch and
  *                             the context lengths are (launches of up to 192 requests with a workspace of at least three partial slots per
- *                             head; others use the other kernel); 0 = one CTA per (request, kv head, split) with equal splits.  Equal at
+ *                             head; others use the other kernel); 0 = one CTA per (request, kv head, split) with equal splits.
  *                             64 x 2176 keys: 91.6-93.3 us against 95.6; 64 x 1024: 49.7 against 56.5; 8 x 8192: 53.0 against 60.2
  *                             (profiles/r02_summary.md section 6)
  * Returns 0, or -1 for an unknown name. */

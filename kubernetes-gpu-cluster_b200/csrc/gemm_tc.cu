@@ -131,6 +131,7 @@ __device__ __forceinline__ void trace_stamp(const GemmParams& p, int slot) {
 __device__ __forceinline__ uint32_t cluster_ctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ uint32_t cluster_nctarank() { uint32_t r; asm volatile("mov.u32 %0, %%cluster_nctarank;" : "=r"(r)); return r; }
 __device__ __forceinline__ void cluster_arrive() { asm volatile("barrier.cluster.arrive.release;" ::: "memory"); }
+__device__ __forceinline__ void cluster_arrive_relaxed() { asm volatile("barrier.cluster.arrive.relaxed;" ::: "memory"); }
 __device__ __forceinline__ void cluster_wait() { asm volatile("barrier.cluster.wait.acquire;" ::: "memory"); }
 __device__ __forceinline__ uint32_t mapa_u32(uint32_t local, uint32_t rank) {
   uint32_t r;
@@ -280,7 +281,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmap_w, const __grid_constant
     }
   };
   auto segments = [&]() { return WS ? SegIter{u_begin, u_end, 0, KB, 0, 0} : SegIter{(int64_t)w_first, (int64_t)total, w_step, KB, kb0f, kb1f}; };
-  if (SPLIT) cluster_arrive();                           // phase A: every CTA of the cluster has started
+  if (SPLIT) cluster_arrive_relaxed();                   // phase A: every CTA of the cluster has started (nothing to publish: no release)
 
   if (warp == 0) {
     if (lane == 0) {

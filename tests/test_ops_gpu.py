@@ -401,11 +401,6 @@ def test_gemm_with_l2_eviction_hints(kge, L, T, N, K, bias, act):
     assert torch.equal(outs[0].view(torch.int16), outs[1].view(torch.int16))
 
 
-EXPERIMENTAL = pytest.mark.skipif(not os.environ.get("KGE_TEST_EXPERIMENTAL"),
-                                  reason="default-off experiments prepared for the next round; set KGE_TEST_EXPERIMENTAL=1 to run them")
-
-
-@EXPERIMENTAL
 @pytest.mark.parametrize("T,f,K", [(1, 512, 256), (7, 1024, 512), (64, 14336, 4096), (64, 1792, 4096), (32, 8192, 2048),
                                    (130, 512, 1024), (300, 3584, 8192), (1000, 14336, 1024),
                                    (64, 7168, 8192), (8192, 7168, 1024)])    # 70B TP4 gate_up: decode, prefill pairs
